@@ -1,0 +1,391 @@
+"""autograd wrappers around the sm_100a kernels (C ABI in include/b200gpt.h).
+
+Conventions shared by all wrappers:
+
+* activations between kernels are bf16, the residual stream / LayerNorm input is fp32
+  (the reference's autocast contract);
+* weights are fp32 ``nn.Parameter`` masters; kernels read a cached bf16 copy
+  (``bf16_of``) that the fused AdamW keeps up to date, so no per-step cast exists;
+* weight/bias gradients are accumulated by the kernels *directly into* ``param.grad``
+  (a view of the flat gradient arena when one exists) and the autograd edge gets ``None``:
+  no AccumulateGrad copy, and a DDP bucket is ready the moment the kernel is queued.
+  ``grad_ready_hooks`` are called with the parameter right after that launch.
+"""
+from __future__ import annotations
+
+from typing import Callable, List, Optional
+
+import torch
+
+from . import _lib
+from ._lib import call, ptr, stream
+
+BF16 = torch.bfloat16
+grad_ready_hooks: List[Callable[[torch.nn.Parameter], None]] = []
+# per-parameter override of where the bf16 weights come from (FSDP installs gathered buffers)
+_LM_CHUNK_ROWS = 1024
+
+
+def _notify(*params):
+    if grad_ready_hooks:
+        for p in params:
+            if p is not None:
+                for h in grad_ready_hooks:
+                    h(p)
+
+
+def bf16_of(p: torch.Tensor) -> torch.Tensor:
+    """bf16 compute copy of an fp32 master weight (cached on the parameter)."""
+    if p.dtype == BF16:
+        return p
+    cached = getattr(p, "_b200_bf16", None)
+    if cached is not None and getattr(p, "_b200_bf16_version", -1) == p._version:
+        return cached
+    with torch.no_grad():
+        if cached is None or cached.shape != p.shape or cached.device != p.device:
+            cached = torch.empty(p.shape, dtype=BF16, device=p.device)
+            p._b200_bf16 = cached
+        call("b200_cast_bf16", p.data_ptr(), cached.data_ptr(), p.numel(), stream())
+        p._b200_bf16_version = p._version
+    return cached
+
+
+def grad_of(p: torch.nn.Parameter) -> torch.Tensor:
+    """fp32 gradient buffer the kernels accumulate into."""
+    if p.grad is None:
+        p.grad = torch.zeros_like(p, dtype=torch.float32)
+    return p.grad
+
+
+def _as_bf16_2d(x: torch.Tensor) -> torch.Tensor:
+    x2 = x.reshape(-1, x.shape[-1])
+    if x2.dtype != BF16:
+        x2 = x2.to(BF16)
+    return x2.contiguous()
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int, *,
+         a_mn_major: bool = False, b_mn_major: bool = False, lda=None, ldb=None,
+         bias=None, residual=None, act: int = 0, accumulate: bool = False,
+         aux_out=None, mask_src=None, cfg: int = 0):
+    """out[M,N] (+)= op(A)[M,K] . op(B)[N,K]^T with a fused epilogue (csrc/gemm_tcgen05.cu).
+
+    K-major operand: stored [rows, K] (row-major, ``ld`` = row stride).  MN-major operand:
+    stored [K, rows] (i.e. the transpose is what sits in memory) - used by dgrad/wgrad so
+    no tensor is ever transposed in memory.
+    """
+    lda = lda if lda is not None else a.stride(0)
+    ldb = ldb if ldb is not None else b.stride(0)
+    call("b200_gemm_bf16", a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, lda, ldb,
+         out.stride(0), int(a_mn_major), int(b_mn_major), ptr(bias), ptr(residual),
+         residual.stride(0) if residual is not None else 0, act, int(out.dtype == torch.float32),
+         int(accumulate), ptr(aux_out), ptr(mask_src), cfg, stream())
+    return out
+
+
+# ----------------------------------------------------------------------------------------
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, residual, act, out_fp32, params):
+        lead = x.shape[:-1]
+        x2 = _as_bf16_2d(x)
+        M, K = x2.shape
+        wb = bf16_of(weight)
+        N = wb.shape[0]
+        out = torch.empty((M, N), dtype=torch.float32 if out_fp32 else BF16, device=x.device)
+        res2 = residual.reshape(M, N) if residual is not None else None
+        need_aux = act != 0 and residual is not None and torch.is_grad_enabled()
+        aux = torch.empty((M, N), dtype=BF16, device=x.device) if need_aux else None
+        gemm(x2, wb, out, M, N, K, bias=bias, residual=res2, act=act, aux_out=aux)
+        ctx.act, ctx.params, ctx.has_res = act, params, residual is not None
+        ctx.in_dtype = x.dtype
+        y_act = None
+        if act != 0:
+            y_act = aux if need_aux else out
+        ctx.save_for_backward(x2, wb, y_act)
+        return out.view(*lead, N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, wb, y_act = ctx.saved_tensors
+        weight, bias = ctx.params
+        M, K = x2.shape
+        N = wb.shape[0]
+        dy2 = dy.reshape(M, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dres = dy if ctx.has_res else None
+        need_dz = ctx.act != 0 or dy2.dtype != BF16 or bias is not None
+        if need_dz:
+            dz = torch.empty((M, N), dtype=BF16, device=dy.device)
+            dbias = grad_of(bias) if (bias is not None and bias.requires_grad) else None
+            call("b200_relu_bwd", dy2.data_ptr(), ptr(y_act), dz.data_ptr(), ptr(dbias), M, N,
+                 int(dy2.dtype == torch.float32), stream())
+        else:
+            dz = dy2
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty((M, K), dtype=BF16, device=dy.device)
+            gemm(dz, wb, dx, M, K, N, b_mn_major=True)          # dX = dZ . W
+            dx = dx.view(*dy.shape[:-1], K)
+            if ctx.in_dtype != BF16:
+                dx = dx.to(ctx.in_dtype)
+        if weight.requires_grad:
+            gw = grad_of(weight)
+            gemm(dz, x2, gw, N, K, M, a_mn_major=True, b_mn_major=True, accumulate=True)  # dW += dZ^T . X
+        _notify(weight, bias)
+        return dx, None, None, dres, None, None, None
+
+
+def linear(x, weight, bias=None, activation: Optional[str] = None, residual=None, out_fp32=False):
+    act = {None: 0, "relu": 1}[activation]
+    return _Linear.apply(x, weight, bias, residual, act, out_fp32, (weight, bias))
+
+
+# ----------------------------------------------------------------------------------------
+def _packed(ts) -> Optional[torch.Tensor]:
+    """If the tensors are adjacent rows of one buffer return the packed [sum_rows, K] view."""
+    t0 = ts[0]
+    rows = 0
+    for t in ts:
+        if t.data_ptr() != t0.data_ptr() + rows * t0.shape[1] * t0.element_size() or not t.is_contiguous():
+            return None
+        rows += t.shape[0]
+    return torch.as_strided(t0, (rows, t0.shape[1]), (t0.shape[1], 1))
+
+
+class _LinearQKV(torch.autograd.Function):
+    """q,k,v projections as one GEMM over the three (adjacent) weight matrices.
+
+    The weights stay three parameters (state_dict contract); in the arena they are adjacent,
+    so the bf16 copies form one [3*inner, dim] operand and the three fp32 gradients one
+    [3*inner, dim] output.  Otherwise they are concatenated on the fly.
+    """
+
+    @staticmethod
+    def forward(ctx, x, wq, wk, wv, params):
+        lead = x.shape[:-1]
+        x2 = _as_bf16_2d(x)
+        M, K = x2.shape
+        ws = [bf16_of(w) for w in (wq, wk, wv)]
+        wp = _packed(ws)
+        if wp is None:
+            wp = torch.cat(ws, dim=0)
+        N = wp.shape[0]
+        out = torch.empty((M, N), dtype=BF16, device=x.device)
+        gemm(x2, wp, out, M, N, K)
+        ctx.params = params
+        ctx.in_dtype = x.dtype
+        ctx.save_for_backward(x2, wp)
+        return out.view(*lead, N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, wp = ctx.saved_tensors
+        M, K = x2.shape
+        N = wp.shape[0]
+        dz = dy.reshape(M, N)
+        if not dz.is_contiguous():
+            dz = dz.contiguous()
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty((M, K), dtype=BF16, device=dy.device)
+            gemm(dz, wp, dx, M, K, N, b_mn_major=True)
+            dx = dx.view(*dy.shape[:-1], K)
+            if ctx.in_dtype != BF16:
+                dx = dx.to(ctx.in_dtype)
+        params = ctx.params
+        grads = [grad_of(p) for p in params]
+        gp = _packed(grads)
+        if gp is not None:
+            gemm(dz, x2, gp, N, K, M, a_mn_major=True, b_mn_major=True, accumulate=True)
+        else:
+            r = 0
+            for g in grads:
+                n = g.shape[0]
+                gemm(dz[:, r:r + n], x2, g, n, K, M, a_mn_major=True, b_mn_major=True,
+                     accumulate=True, lda=dz.stride(0))
+                r += n
+        _notify(*params)
+        return dx, None, None, None, None
+
+
+def linear_qkv(x, wq, wk, wv):
+    return _LinearQKV.apply(x, wq, wk, wv, (wq, wk, wv))
+
+
+# ----------------------------------------------------------------------------------------
+class _LayerNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps, params):
+        D = x.shape[-1]
+        x2 = x.reshape(-1, D)
+        if x2.dtype != torch.float32:
+            x2 = x2.float()
+        x2 = x2.contiguous()
+        rows = x2.shape[0]
+        y = torch.empty((rows, D), dtype=BF16, device=x.device)
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        call("b200_layernorm_fwd", x2.data_ptr(), weight.data_ptr(), bias.data_ptr(), y.data_ptr(),
+             mean.data_ptr(), rstd.data_ptr(), rows, D, float(eps), stream())
+        ctx.params = params
+        ctx.in_dtype = x.dtype
+        ctx.save_for_backward(x2, mean, rstd)
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, mean, rstd = ctx.saved_tensors
+        weight, bias = ctx.params
+        rows, D = x2.shape
+        dy2 = dy.reshape(rows, D)
+        if dy2.dtype != BF16:
+            dy2 = dy2.to(BF16)
+        dy2 = dy2.contiguous()
+        dx = torch.empty((rows, D), dtype=torch.float32, device=dy.device)
+        call("b200_layernorm_bwd", dy2.data_ptr(), x2.data_ptr(), weight.data_ptr(), mean.data_ptr(),
+             rstd.data_ptr(), None, dx.data_ptr(), None, grad_of(weight).data_ptr(),
+             grad_of(bias).data_ptr(), rows, D, stream())
+        _notify(weight, bias)
+        dx = dx.view(dy.shape)
+        if ctx.in_dtype != torch.float32:
+            dx = dx.to(ctx.in_dtype)
+        return dx, None, None, None, None
+
+
+def layernorm(x, weight, bias, eps):
+    return _LayerNorm.apply(x, weight, bias, eps, (weight, bias))
+
+
+# ----------------------------------------------------------------------------------------
+class _Embedding(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, input_ids, position_ids, tok_w, pos_w, params):
+        ids = input_ids.reshape(-1).contiguous()
+        pos = position_ids.reshape(-1).contiguous()
+        n, D = ids.numel(), tok_w.shape[1]
+        out = torch.empty((n, D), dtype=torch.float32, device=ids.device)
+        call("b200_embedding_fwd", ids.data_ptr(), pos.data_ptr(), tok_w.data_ptr(), pos_w.data_ptr(),
+             out.data_ptr(), n, D, tok_w.shape[0], pos_w.shape[0], stream())
+        ctx.params = params
+        ctx.save_for_backward(ids, pos)
+        return out.view(*input_ids.shape, D)
+
+    @staticmethod
+    def backward(ctx, dout):
+        ids, pos = ctx.saved_tensors
+        tok_w, pos_w = ctx.params
+        D = tok_w.shape[1]
+        d2 = dout.reshape(-1, D)
+        if d2.dtype != torch.float32:
+            d2 = d2.float()
+        d2 = d2.contiguous()
+        call("b200_embedding_bwd", ids.data_ptr(), pos.data_ptr(), d2.data_ptr(),
+             grad_of(tok_w).data_ptr(), grad_of(pos_w).data_ptr(), ids.numel(), D,
+             tok_w.shape[0], pos_w.shape[0], stream())
+        _notify(tok_w, pos_w)
+        return None, None, None, None, None
+
+
+def embedding(input_ids, position_ids, tok_w, pos_w):
+    return _Embedding.apply(input_ids, position_ids, tok_w, pos_w, (tok_w, pos_w))
+
+
+# ----------------------------------------------------------------------------------------
+class _Attention(torch.autograd.Function):
+    """Causal flash attention over a packed [N, S, 3*h*d] qkv tensor (csrc/attention.cu)."""
+
+    @staticmethod
+    def forward(ctx, qkv, heads, head_dim, scale, key_mask):
+        N, S, _ = qkv.shape
+        qkv = qkv.contiguous()
+        out = torch.empty((N, S, heads * head_dim), dtype=BF16, device=qkv.device)
+        lse = torch.empty((N, heads, S), dtype=torch.float32, device=qkv.device)
+        km = None
+        if key_mask is not None:
+            km = key_mask.to(torch.uint8).contiguous()
+        call("b200_attn_fwd", qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), N, S, heads, head_dim,
+             float(scale), ptr(km), stream())
+        ctx.dims = (N, S, heads, head_dim, scale)
+        ctx.save_for_backward(qkv, out, lse, km)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, out, lse, km = ctx.saved_tensors
+        N, S, heads, head_dim, scale = ctx.dims
+        dout = dout.contiguous()
+        if dout.dtype != BF16:
+            dout = dout.to(BF16)
+        dqkv = torch.empty_like(qkv)
+        delta = torch.empty((N, heads, S), dtype=torch.float32, device=qkv.device)
+        call("b200_attn_bwd", qkv.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(),
+             dqkv.data_ptr(), delta.data_ptr(), N, S, heads, head_dim, float(scale), ptr(km), stream())
+        return dqkv, None, None, None, None
+
+
+def attention(qkv, heads, head_dim, scale, key_mask=None):
+    return _Attention.apply(qkv, heads, head_dim, scale, key_mask)
+
+
+# ----------------------------------------------------------------------------------------
+class _LMHeadCE(torch.autograd.Function):
+    """Fused LM head + cross-entropy (+ argmax accuracy) without [tokens, vocab] logits.
+
+    Rows are processed in chunks: a tcgen05 GEMM writes a bf16 logits chunk that stays in
+    the 126 MB L2, one pass of ``b200_ce_fwd_bwd`` turns it in place into dlogits (softmax -
+    onehot, already scaled by grad_scale / n_valid) while accumulating loss / correct counts,
+    and two more GEMMs consume it from L2 for dX and dW.  The gradient is therefore produced
+    in the forward pass; backward only hands dX over.  The incoming gradient of the loss must
+    be ``grad_scale`` (1.0 for plain training; pipeline engines pass 1/num_microbatches).
+    """
+
+    @staticmethod
+    def forward(ctx, x, weight, targets, ignore_index, grad_scale, params):
+        x2 = _as_bf16_2d(x)
+        M, D = x2.shape
+        wb = bf16_of(weight)
+        V = wb.shape[0]
+        ld = (V + 127) // 128 * 128
+        t = targets.reshape(-1).contiguous()
+        dev = x.device
+        stats = torch.zeros(4, dtype=torch.float32, device=dev)  # n_valid, loss_sum, n_correct
+        call("b200_count_valid", t.data_ptr(), stats.data_ptr(), ignore_index, M, stream())
+        want_grad = torch.is_grad_enabled() and (x.requires_grad or weight.requires_grad)
+        rows = min(_LM_CHUNK_ROWS, M)
+        logits = torch.empty((rows, ld), dtype=BF16, device=dev)
+        dx = torch.empty((M, D), dtype=BF16, device=dev) if want_grad else None
+        gw = grad_of(weight) if (want_grad and weight.requires_grad) else None
+        for r0 in range(0, M, rows):
+            r = min(rows, M - r0)
+            gemm(x2[r0:r0 + r], wb, logits, r, V, D)
+            call("b200_ce_fwd_bwd", logits.data_ptr(), t.data_ptr() + 8 * r0, stats.data_ptr(),
+                 r, V, ld, ignore_index, int(want_grad), float(grad_scale), stream())
+            if want_grad:
+                gemm(logits, wb, dx[r0:r0 + r], r, D, V, b_mn_major=True)       # dX = dL . W
+                if gw is not None:
+                    gemm(logits, x2[r0:r0 + r], gw, V, D, r, a_mn_major=True, b_mn_major=True,
+                         accumulate=True)                                       # dW += dL^T . X
+        if gw is not None:
+            _notify(weight)
+        loss = stats[1] / stats[0].clamp(min=1.0)
+        ctx.save_for_backward(dx)
+        ctx.x_shape, ctx.in_dtype = x.shape, x.dtype
+        ctx.mark_non_differentiable(stats)
+        return loss, stats
+
+    @staticmethod
+    def backward(ctx, dloss, _dstats):
+        (dx,) = ctx.saved_tensors
+        if dx is None:
+            return None, None, None, None, None, None
+        dx = dx.view(ctx.x_shape)
+        if ctx.in_dtype != BF16:
+            dx = dx.to(ctx.in_dtype)
+        return dx, None, None, None, None, None
+
+
+def lmhead_cross_entropy(x, weight, targets, ignore_index=-100, grad_scale: float = 1.0):
+    loss, stats = _LMHeadCE.apply(x, weight, targets, ignore_index, grad_scale, (weight,))
+    return loss, stats[0], stats[2]
