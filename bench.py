@@ -1,0 +1,355 @@
+#!/usr/bin/env python
+"""Headline benchmark: GPT training tokens/sec (BASELINE.json), device-timed, max over ranks.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Config = BASELINE.md row 2: the reference's default GPT (dim 256, head_dim 32, heads 8,
+layers 8, seq 256 -> 255 tokens/sample, vocab 50257), bf16, batch 64 per rank, AdamW step
+included; N = 1 is the single-GPU recipe, N > 1 the DDP recipe (weak scaling) launched by
+``python -m torch.distributed.run``.  Synthetic tokens, random-init weights.
+
+Two numbers per run:
+  value  - K steps replayed back to back from device-resident batches (kernel-only view);
+  e2e    - K steps through the public API (Strategy.train_step fed by utils.prepare_batch)
+           where every step copies its batch from pinned host memory and reads the loss back.
+Both are bracketed by barrier + cuda synchronize, timed with CUDA events, max over ranks.
+``--impl reference`` runs the reference's own model / loop from baseline/_ref instead.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+from pathlib import Path
+from types import SimpleNamespace
+
+import torch
+import torch.distributed as dist
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+CFG = dict(dim=256, head_dim=32, heads=8, num_layers=8, sequence_length=256, vocab_size=50257,
+           batch_size=64, learning_rate=1e-4)
+METRIC = "GPT training tokens/sec (device-timed, max over ranks)"
+
+
+# ------------------------------------------------------------------------------------------
+def world():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.proc, self.lines = gpu_index, None, []
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.idx)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+        return self
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            time.sleep(0.25)
+            self.proc.terminate()
+            try:
+                out, _ = self.proc.communicate(timeout=5)
+            except Exception:
+                self.proc.kill()
+                out = ""
+            self.lines = [l for l in out.splitlines() if l.strip()]
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except Exception:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def timed(fn, steps: int, device, sampler=None):
+    """barrier + sync, K x fn under CUDA events, sync + barrier; returns ms (max over ranks)."""
+    if dist.is_initialized():
+        dist.barrier()
+    torch.cuda.synchronize(device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ctx = sampler if sampler is not None else _Null()
+    with ctx:
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize(device)
+    if dist.is_initialized():
+        dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=device)
+    if dist.is_initialized():
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms)
+
+
+class _Null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+
+def host_batches(n: int, seed: int):
+    """n pinned host batches in the reference's dataset format ({input_ids, attention_mask} int64 [B,S])."""
+    g = torch.Generator().manual_seed(seed)
+    out = []
+    for _ in range(n):
+        ids = torch.randint(0, CFG["vocab_size"], (CFG["batch_size"], CFG["sequence_length"]), generator=g)
+        out.append({"input_ids": ids.pin_memory(), "attention_mask": torch.ones_like(ids).pin_memory()})
+    return out
+
+
+def result_line(impl, value, ms, e2e_value, n, steps, warmup, clocks, launches, extra_cfg, h2d, d2h):
+    baseline = None  # BASELINE.md publishes no number ("none published")
+    line = {
+        "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": n, "steps": steps, "warmup": warmup,
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": (value / baseline) if baseline else None, "dtype": "bf16", "data": "synthetic",
+        "impl": impl,
+        "config": {"model": "GPT dim256 head_dim32 heads8 layers8 vocab50257 (reference default, 32.1M params)",
+                   "global_batch": CFG["batch_size"] * n, "seq_len": CFG["sequence_length"],
+                   "tokens_per_sample": CFG["sequence_length"] - 1,
+                   "parallelism": "single" if n == 1 else f"dp{n}",
+                   "optimizer": "AdamW lr1e-4 (step inside timed region)",
+                   "l2": "no flush: per-step working set (0.5 GB params+optimizer state, >1 GB activations) "
+                         "exceeds the 126 MB L2",
+                   **extra_cfg},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": launches,
+    }
+    return line
+
+
+# ------------------------------------------------------------------------------------------
+def run_ours(args):
+    from distributed_pytorch_cookbook_b200.ops import _lib
+    from distributed_pytorch_cookbook_b200.trainer import SingleStrategy, build_model
+    from distributed_pytorch_cookbook_b200.utils import prepare_batch, seed_everything
+
+    rank, local_rank, n = world()
+    device = torch.device(f"cuda:{local_rank}")
+    torch.cuda.set_device(device)
+    if n > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=device)
+    assert _lib.available(), f"native sm_100a library not loaded: {_lib.load_error()}"
+    seed_everything(0)
+    ns = SimpleNamespace(**CFG, disable_amp=False, disable_cuda_graph=False, bucket_mb=args.bucket_mb,
+                         comm=args.comm, epochs=1)
+    model = build_model(ns, CFG["vocab_size"])
+    if n == 1:
+        strategy = SingleStrategy()
+    else:
+        from distributed_pytorch_cookbook_b200.parallel.ddp import DDPStrategy
+        strategy = DDPStrategy()
+    strategy.setup(model, ns, device)
+    strategy.train()
+
+    batches = host_batches(max(4, min(args.steps, 16)), seed=100 + rank)
+    pad = 2
+
+    def e2e_step(i):
+        b, t = prepare_batch(batches[i % len(batches)], pad, device)   # H2D from pinned memory
+        loss = strategy.train_step(b, t, amp=True)
+        return loss
+
+    # warm-up (also triggers CUDA-graph capture inside the strategy)
+    for i in range(max(args.warmup, 5)):
+        e2e_step(i)
+    torch.cuda.synchronize(device)
+
+    # kernel-only view: device-resident batches, no host traffic in the loop
+    dev_batches = [prepare_batch(b, pad, device) for b in batches]
+    torch.cuda.synchronize(device)
+    launches0 = _lib.launch_count()
+    per_step_launches = strategy.launches_per_step() if hasattr(strategy, "launches_per_step") else None
+
+    def dev_step(i):
+        b, t = dev_batches[i % len(dev_batches)]
+        strategy.train_step(b, t, amp=True)
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    ms_total = timed(dev_step, args.steps, device, sampler)
+    clocks = sampler.summary() if sampler is not None else None
+    launches = (_lib.launch_count() - launches0)
+    if per_step_launches:
+        launches = per_step_launches * args.steps
+
+    host_losses = []
+
+    def e2e_timed(i):
+        loss = e2e_step(i)
+        host_losses.append(loss.item())      # D2H read of the step's result, every step
+
+    ms_e2e = timed(e2e_timed, args.steps, device)
+    tokens_per_step = CFG["batch_size"] * (CFG["sequence_length"] - 1) * n
+    value = tokens_per_step * args.steps / ms_total * 1e3
+    e2e_value = tokens_per_step * args.steps / ms_e2e * 1e3
+    h2d = sum(v.numel() * v.element_size() for v in prepare_batch(batches[0], pad, "cpu")[0].values()) + \
+        CFG["batch_size"] * (CFG["sequence_length"] - 1) * 8
+    if rank == 0:
+        extra = {"cuda_graph": bool(getattr(strategy, "use_graph", False)),
+                 "final_loss": host_losses[-1] if host_losses else None,
+                 "comm": getattr(strategy, "comm_kind", None)}
+        print(json.dumps(result_line("ours", value, ms_total / args.steps, e2e_value, n, args.steps, args.warmup,
+                                     clocks, launches, extra, h2d, 4)), flush=True)
+    if dist.is_initialized():
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------
+def run_reference(args):
+    """The reference's own model + training step (torch autocast + GradScaler + AdamW, DDP for
+    N > 1, torch.compile as in its default), from the verbatim copy under baseline/_ref."""
+    from baseline.harness import load_reference, reference_unavailable_reason
+    why = reference_unavailable_reason()
+    rank, local_rank, n = world()
+    if why is not None:
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": why}), flush=True)
+        return
+    import torch.nn.functional as F
+    device = torch.device(f"cuda:{local_rank}")
+    torch.cuda.set_device(device)
+    if n > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=device)
+    ref = load_reference()
+    batches = host_batches(max(4, min(args.steps, 16)), seed=100 + rank)
+    pad = 2
+    results = {}
+    modes = {"both": [True, False], "on": [True], "off": [False]}[args.ref_compile]
+    clocks = None
+    for use_compile in modes:
+        torch.manual_seed(0)
+        sp_model = ref.gpt.TransformerDecoderLM(dim=CFG["dim"], head_dim=CFG["head_dim"], heads=CFG["heads"],
+                                                num_layers=CFG["num_layers"], vocab_size=CFG["vocab_size"],
+                                                max_position_embeddings=CFG["sequence_length"]).to(device)
+        model = sp_model
+        if n > 1:
+            from torch.nn.parallel import DistributedDataParallel as DDP
+            model = DDP(sp_model, device_ids=[device.index])
+        model.train()
+        compiled_ok = False
+        if use_compile:
+            try:
+                model = torch.compile(model)
+                compiled_ok = True
+            except Exception:
+                compiled_ok = False
+        optim = torch.optim.AdamW(model.parameters(), lr=CFG["learning_rate"])
+        scaler = torch.amp.GradScaler("cuda", enabled=True)
+
+        def step(batch, targets, read_loss):
+            optim.zero_grad()
+            with torch.autocast(device_type="cuda", dtype=torch.bfloat16, enabled=True):
+                logits = model(**batch)
+                logits, targets = logits.view(-1, sp_model.vocab_size), targets.view(-1)
+                loss = F.cross_entropy(logits, targets, ignore_index=-100)
+            scaler.scale(loss).backward()
+            scaler.step(optim)
+            scaler.update()
+            return loss.item() if read_loss else loss
+
+        try:
+            for i in range(max(args.warmup, 5)):
+                b, t = ref.utils.prepare_batch(batches[i % len(batches)], pad, device)
+                step(b, t, True)
+        except Exception as e:  # e.g. inductor unavailable on the box
+            if use_compile:
+                results[f"compile_error"] = repr(e)[:200]
+                continue
+            raise
+        torch.cuda.synchronize(device)
+        dev_batches = [ref.utils.prepare_batch(b, pad, device) for b in batches]
+        sampler = ClockSampler(local_rank) if rank == 0 else None
+        ms_dev = timed(lambda i: step(*dev_batches[i % len(dev_batches)], False), args.steps, device, sampler)
+        if sampler is not None:
+            clocks = sampler.summary()
+
+        def e2e(i):
+            b, t = ref.utils.prepare_batch(batches[i % len(batches)], pad, device)
+            step(b, t, True)
+        ms_e2e = timed(e2e, args.steps, device)
+        results["compile" if use_compile and compiled_ok else "eager"] = (ms_dev, ms_e2e)
+        del model, optim, sp_model
+        torch.cuda.empty_cache()
+
+    tokens_per_step = CFG["batch_size"] * (CFG["sequence_length"] - 1) * n
+    timed_modes = {k: v for k, v in results.items() if isinstance(v, tuple)}
+    best = min(timed_modes, key=lambda k: timed_modes[k][0])
+    ms_dev, ms_e2e = timed_modes[best]
+    if rank == 0:
+        extra = {"reference_mode": best,
+                 "all_modes_ms_per_step": {k: v[0] / args.steps for k, v in timed_modes.items()},
+                 "repairs_applied_in_memory": ref.repairs, "compile_error": results.get("compile_error")}
+        h2d = 3 * CFG["batch_size"] * (CFG["sequence_length"] - 1) * 8 + CFG["batch_size"] * (CFG["sequence_length"] - 1)
+        line = result_line("reference", tokens_per_step * args.steps / ms_dev * 1e3, ms_dev / args.steps,
+                           tokens_per_step * args.steps / ms_e2e * 1e3, n, args.steps, args.warmup, clocks,
+                           0, extra, h2d, 4)
+        print(json.dumps(line), flush=True)
+    if dist.is_initialized():
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--ref-compile", dest="ref_compile", choices=["both", "on", "off"], default="both")
+    ap.add_argument("--bucket_mb", type=float, default=4.0)
+    ap.add_argument("--comm", choices=["auto", "symm", "nccl"], default="auto")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    rank, _, n = world()
+    if args.gpus > 1 and n == 1:
+        # convenience: re-launch ourselves under torchrun when started as a plain process
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 400), __file__,
+               *sys.argv[1:]]
+        raise SystemExit(subprocess.call(cmd))
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device on this box"}))
+        return
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,575 @@
+// Causal flash attention (forward + backward) on tcgen05 for sm_100a.
+//
+// Reference semantics: models/gpt.py:75-100  softmax(q k^T / sqrt(d) + causal(-1e9) [+ key
+// padding]) v, with the S x S score matrix never written to memory and no host-built mask.
+// Input is the packed projection output qkv[B, T, 3, H, D] (q | k | v sections of width H*D).
+//
+// Tiling: 128 query rows x 128 keys per step, head_dim D in {32, 64, 128}, any T (tails are
+// zero-filled / masked).  All five backward GEMMs and both forward GEMMs run on tcgen05.mma
+// (M = 128, fp32 accumulators in TMEM); softmax runs on the 128 threads of the CTA, one TMEM
+// lane (= one score row) per thread.
+//
+// Shared-memory operand layout (one layout serves every use): a [128 x C] bf16 tile is
+// stored as 16-byte chunks  offset(row, col) = (col/8) * 2048 + row * 16 + (col%8) * 2,
+// i.e. the un-swizzled UMMA "core matrix" layout (8 rows x 16 B contiguous).  Read as a
+// K-major operand (rows = M/N, cols = K):  LBO = 2048 (next 8 columns), SBO = 128 (next 8
+// rows).  Read as an MN-major operand (cols = M/N, rows = K) - which is how P^T, dS^T, dO^T,
+// Q^T, K^T and V^T are consumed - LBO = 128 (next 8 rows = next K group), SBO = 2048 (next 8
+// columns = next MN group).  No tile is ever transposed.
+//
+// Forward, per CTA = (batch, head, 128-query tile): for each key tile up to the diagonal:
+//   S = Q K^T (TMEM) -> online softmax in registers -> P (bf16, smem) -> PV = P V (TMEM) ->
+//   O = O * alpha + PV in registers.  Writes O (bf16) and LSE (fp32).
+// Backward, per CTA = (batch, head, 128-key tile): loops over the query tiles at or below the
+// diagonal; S and dP = dO V^T into TMEM, P and dS = P * (dP - delta) * scale to smem, then
+// dV += P^T dO, dK += dS^T Q (TMEM accumulators across the loop) and dQ = dS K, which is
+// reduced across key tiles with fp32 vector atomics into a scratch buffer (converted to bf16
+// by a small second kernel).  delta = rowsum(dO * O) comes from a pre-pass.
+#include "../include/b200gpt.h"
+#include "common.cuh"
+
+namespace {
+
+constexpr int TQ = 128;   // query rows per tile (= UMMA M = TMEM lanes)
+constexpr int TK = 128;   // keys per tile
+constexpr int ATTN_THREADS = 128;
+constexpr uint32_t CHUNK_STRIDE = TQ * 16;  // 2048 B between 8-column groups
+constexpr float kLog2e = 1.4426950408889634f;
+
+enum : int { ERR_ATTN_FWD = 201, ERR_ATTN_BWD = 202 };
+
+// no-swizzle descriptors (layout type 0)
+__device__ __forceinline__ uint64_t desc_nosw(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
+// K-major view of a tile (rows = M/N): 16 K-columns per MMA = two 8-column chunks
+__device__ __forceinline__ uint64_t desc_kmajor(uint32_t tile, int kk) {
+  return desc_nosw(tile + kk * 2 * CHUNK_STRIDE, CHUNK_STRIDE, 128);
+}
+// MN-major view (cols = M/N, rows = K): 16 K-rows per MMA = two 8-row groups (256 B)
+__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile, int kk) {
+  return desc_nosw(tile + kk * 256, 128, CHUNK_STRIDE);
+}
+
+// global [rows x D] (row stride in elements) -> smem tile, rows >= nvalid zero-filled
+template <int D>
+__device__ __forceinline__ void load_tile(uint32_t smem_dst, const bf16* __restrict__ g, int nvalid,
+                                          size_t row_stride) {
+  constexpr int CPR = D / 8;  // 16-byte chunks per row
+#pragma unroll 4
+  for (int c = threadIdx.x; c < TQ * CPR; c += ATTN_THREADS) {
+    const int row = c / CPR, kc = c % CPR;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (row < nvalid) v = __ldg(reinterpret_cast<const uint4*>(g + static_cast<size_t>(row) * row_stride) + kc);
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(smem_dst + kc * CHUNK_STRIDE + row * 16),
+                 "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
+  }
+}
+
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d)
+               : "memory");
+}
+
+struct AttnParams {
+  const bf16* qkv;     // [B, T, 3*H*D]
+  bf16* out;           // [B, T, H*D]
+  float* lse;          // [B, H, T]
+  const bf16* dout;    // [B, T, H*D]
+  bf16* dqkv;          // [B, T, 3*H*D]
+  float* delta;        // [B, H, T]
+  float* dq_acc;       // [B, T, H*D] fp32 scratch
+  const uint8_t* key_mask;  // [B, T] 1 = padding, nullable
+  int B, T, H;
+  float scale;
+  int* err_word;
+};
+
+// ------------------------------------------------------------------------------------------
+// forward
+// ------------------------------------------------------------------------------------------
+template <int D>
+__global__ void __launch_bounds__(ATTN_THREADS)
+attn_fwd_kernel(const AttnParams p) {
+  constexpr int TILE_BYTES = TQ * D * 2;
+  constexpr uint32_t TMEM_COLS = 256;  // S: [0,128)  PV: [128,128+D)
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 127u) & ~127u;
+  const uint32_t sQ = base, sK = sQ + TILE_BYTES, sV = sK + TILE_BYTES, sP = sV + TILE_BYTES;
+  const uint32_t bar = sP + TQ * TK * 2;
+  uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + 3 * TILE_BYTES + TQ * TK * 2 + 8);
+  volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int HD = p.H * D;
+  const size_t row_stride = static_cast<size_t>(3) * HD;
+  const bf16* qkv_b = p.qkv + static_cast<size_t>(b) * p.T * row_stride;
+  const int q0 = qt * TQ;
+  const int q = q0 + tid;  // this thread's query row
+
+  if (tid == 0) {
+    *abort_flag = 0;
+    mbar_init(bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(smem_u32(tmem_ptr_smem), TMEM_COLS);
+    tmem_relinquish();
+  }
+  load_tile<D>(sQ, qkv_b + static_cast<size_t>(q0) * row_stride + h * D, min(TQ, p.T - q0), row_stride);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem = *tmem_ptr_smem;
+  const uint32_t t_lane = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+  const uint32_t idesc_s = umma_idesc_bf16(TQ, TK, 0, 0);
+  const uint32_t idesc_pv = umma_idesc_bf16(TQ, D, 0, 1);
+  const float sl2 = p.scale * kLog2e;
+
+  float o[D];
+#pragma unroll
+  for (int i = 0; i < D; ++i) o[i] = 0.f;
+  float m_run = -INFINITY, l_run = 0.f;
+  uint32_t phase = 0;
+  bool ok = true;
+
+  for (int kt = 0; kt <= qt && ok; ++kt) {
+    const int k0 = kt * TK;
+    __syncthreads();  // previous iteration's MMAs are complete (we waited); smem is reusable
+    load_tile<D>(sK, qkv_b + static_cast<size_t>(k0) * row_stride + HD + h * D, min(TK, p.T - k0), row_stride);
+    load_tile<D>(sV, qkv_b + static_cast<size_t>(k0) * row_stride + 2 * HD + h * D, min(TK, p.T - k0), row_stride);
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      tcgen05_fence_after();
+#pragma unroll
+      for (int kk = 0; kk < D / 16; ++kk)
+        umma_f16_ss(tmem, desc_kmajor(sQ, kk), desc_kmajor(sK, kk), idesc_s, kk > 0 ? 1u : 0u);
+      umma_commit(bar);
+    }
+    if (!mbar_wait(bar, phase, abort_flag, p.err_word, ERR_ATTN_FWD)) { ok = false; }
+    phase ^= 1;
+    if (!__syncthreads_and(ok)) { ok = false; break; }
+    tcgen05_fence_after();
+
+    // pass A: row max of the masked, scaled scores
+    const bool diag = (kt == qt);
+    float m_tile = -INFINITY;
+#pragma unroll 1
+    for (int c = 0; c < TK / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(t_lane + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int key = k0 + c * 32 + j;
+        bool keep = key < p.T && (!diag || key <= q);
+        if (keep && p.key_mask != nullptr) keep = p.key_mask[static_cast<size_t>(b) * p.T + key] == 0;
+        if (keep) m_tile = fmaxf(m_tile, __uint_as_float(r[j]));
+      }
+    }
+    const float m_new = fmaxf(m_run, m_tile * p.scale);  // scale > 0
+    const float m_safe = (m_new == -INFINITY) ? 0.f : m_new;
+    const float alpha = exp2f((m_run - m_safe) * kLog2e);  // m_run = -inf -> 0
+    const float m_l2 = m_safe * kLog2e;
+    // pass B: p = exp(s - m), row sum, P tile to smem (bf16)
+    float l_tile = 0.f;
+#pragma unroll 1
+    for (int c = 0; c < TK / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(t_lane + c * 32, r);
+      tmem_ld_wait();
+      uint32_t pk[16];
+#pragma unroll
+      for (int j = 0; j < 32; j += 2) {
+        float pv[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int key = k0 + c * 32 + j + u;
+          bool keep = key < p.T && (!diag || key <= q);
+          if (keep && p.key_mask != nullptr) keep = p.key_mask[static_cast<size_t>(b) * p.T + key] == 0;
+          pv[u] = keep ? exp2f(__uint_as_float(r[j + u]) * sl2 - m_l2) : 0.f;
+        }
+        // sum what the tensor core will actually see (bf16-rounded), like the reference bf16 path
+        const uint32_t packed = pack_bf16x2(pv[0], pv[1]);
+        const float2 back = unpack_bf16x2(packed);
+        l_tile += back.x + back.y;
+        pk[j >> 1] = packed;
+      }
+#pragma unroll
+      for (int g = 0; g < 4; ++g)  // 4 chunks of 8 keys
+        st_shared_v4(sP + (c * 4 + g) * CHUNK_STRIDE + tid * 16, pk[4 * g], pk[4 * g + 1], pk[4 * g + 2],
+                     pk[4 * g + 3]);
+    }
+    l_run = l_run * alpha + l_tile;
+    m_run = m_new;
+    tcgen05_fence_before();
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      tcgen05_fence_after();
+#pragma unroll
+      for (int kk = 0; kk < TK / 16; ++kk)
+        umma_f16_ss(tmem + TK, desc_kmajor(sP, kk), desc_mnmajor(sV, kk), idesc_pv, kk > 0 ? 1u : 0u);
+      umma_commit(bar);
+    }
+    if (!mbar_wait(bar, phase, abort_flag, p.err_word, ERR_ATTN_FWD)) { ok = false; }
+    phase ^= 1;
+    if (!__syncthreads_and(ok)) { ok = false; break; }
+    tcgen05_fence_after();
+#pragma unroll
+    for (int c = 0; c < D / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(t_lane + TK + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) o[c * 32 + j] = o[c * 32 + j] * alpha + __uint_as_float(r[j]);
+    }
+    tcgen05_fence_before();
+  }
+
+  if (ok && q < p.T) {
+    const float inv_l = l_run > 0.f ? 1.0f / l_run : 0.f;
+    bf16* orow = p.out + (static_cast<size_t>(b) * p.T + q) * HD + h * D;
+#pragma unroll
+    for (int j = 0; j < D; j += 8) {
+      *reinterpret_cast<uint4*>(orow + j) =
+          make_uint4(pack_bf16x2(o[j] * inv_l, o[j + 1] * inv_l), pack_bf16x2(o[j + 2] * inv_l, o[j + 3] * inv_l),
+                     pack_bf16x2(o[j + 4] * inv_l, o[j + 5] * inv_l), pack_bf16x2(o[j + 6] * inv_l, o[j + 7] * inv_l));
+    }
+    p.lse[(static_cast<size_t>(b) * p.H + h) * p.T + q] = l_run > 0.f ? m_run + logf(l_run) : -INFINITY;
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// backward
+// ------------------------------------------------------------------------------------------
+template <int D>
+__global__ void __launch_bounds__(256)
+attn_delta_kernel(const bf16* __restrict__ out, const bf16* __restrict__ dout, float* __restrict__ delta,
+                  int B, int T, int H) {
+  const int64_t total = static_cast<int64_t>(B) * T * H;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int h = static_cast<int>(i % H);
+    const int64_t bt = i / H;
+    const int t = static_cast<int>(bt % T);
+    const int b = static_cast<int>(bt / T);
+    const uint4* o4 = reinterpret_cast<const uint4*>(out + (bt * H + h) * D);
+    const uint4* d4 = reinterpret_cast<const uint4*>(dout + (bt * H + h) * D);
+    float s = 0.f;
+#pragma unroll
+    for (int c = 0; c < D / 8; ++c) {
+      const uint4 a = __ldg(o4 + c), g = __ldg(d4 + c);
+      const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, gw[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float2 x = unpack_bf16x2(aw[u]), y = unpack_bf16x2(gw[u]);
+        s += x.x * y.x + x.y * y.y;
+      }
+    }
+    delta[(static_cast<int64_t>(b) * H + h) * T + t] = s;
+  }
+}
+
+template <int D>
+__global__ void __launch_bounds__(ATTN_THREADS)
+attn_bwd_kernel(const AttnParams p) {
+  constexpr int TILE_BYTES = TQ * D * 2;
+  constexpr int SS_BYTES = TQ * TK * 2;
+  constexpr uint32_t TMEM_COLS = 512;  // S/dQ [0,128) dP [128,256) dV [256,256+D) dK [256+D,256+2D)
+  constexpr uint32_t C_S = 0, C_DP = 128, C_DV = 256, C_DK = 256 + D;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 127u) & ~127u;
+  const uint32_t sK = base, sV = sK + TILE_BYTES, sQ = sV + TILE_BYTES, sdO = sQ + TILE_BYTES;
+  const uint32_t sP = sdO + TILE_BYTES, sdS = sP + SS_BYTES;
+  const uint32_t bar = sdS + SS_BYTES;
+  uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + 4 * TILE_BYTES + 2 * SS_BYTES + 8);
+  volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int HD = p.H * D;
+  const size_t row_stride = static_cast<size_t>(3) * HD;
+  const bf16* qkv_b = p.qkv + static_cast<size_t>(b) * p.T * row_stride;
+  const bf16* dout_b = p.dout + static_cast<size_t>(b) * p.T * HD;
+  const int k0 = kt * TK;
+  const int nq_tiles = (p.T + TQ - 1) / TQ;
+
+  if (tid == 0) {
+    *abort_flag = 0;
+    mbar_init(bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(smem_u32(tmem_ptr_smem), TMEM_COLS);
+    tmem_relinquish();
+  }
+  load_tile<D>(sK, qkv_b + static_cast<size_t>(k0) * row_stride + HD + h * D, min(TK, p.T - k0), row_stride);
+  load_tile<D>(sV, qkv_b + static_cast<size_t>(k0) * row_stride + 2 * HD + h * D, min(TK, p.T - k0), row_stride);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem = *tmem_ptr_smem;
+  const uint32_t t_lane = tmem + (static_cast<uint32_t>(warp * 32) << 16);
+  const uint32_t idesc_ss = umma_idesc_bf16(TQ, TK, 0, 0);    // S, dP: K-major x K-major, N = 128
+  const uint32_t idesc_tt = umma_idesc_bf16(TK, D, 1, 1);     // dV, dK: MN-major x MN-major, N = D
+  const uint32_t idesc_dq = umma_idesc_bf16(TQ, D, 0, 1);     // dQ: K-major x MN-major, N = D
+  const float sl2 = p.scale * kLog2e;
+
+  uint32_t phase = 0;
+  bool ok = true;
+  for (int qt = kt; qt < nq_tiles && ok; ++qt) {
+    const int q0 = qt * TQ;
+    const int q = q0 + tid;
+    const bool q_ok = q < p.T;
+    __syncthreads();
+    load_tile<D>(sQ, qkv_b + static_cast<size_t>(q0) * row_stride + h * D, min(TQ, p.T - q0), row_stride);
+    load_tile<D>(sdO, dout_b + static_cast<size_t>(q0) * HD + h * D, min(TQ, p.T - q0), HD);
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      tcgen05_fence_after();
+#pragma unroll
+      for (int kk = 0; kk < D / 16; ++kk)
+        umma_f16_ss(tmem + C_S, desc_kmajor(sQ, kk), desc_kmajor(sK, kk), idesc_ss, kk > 0 ? 1u : 0u);
+#pragma unroll
+      for (int kk = 0; kk < D / 16; ++kk)
+        umma_f16_ss(tmem + C_DP, desc_kmajor(sdO, kk), desc_kmajor(sV, kk), idesc_ss, kk > 0 ? 1u : 0u);
+      umma_commit(bar);
+    }
+    const size_t stat_idx = (static_cast<size_t>(b) * p.H + h) * p.T + (q_ok ? q : 0);
+    const float lse_l2 = q_ok ? p.lse[stat_idx] * kLog2e : 0.f;
+    const float delta = q_ok ? p.delta[stat_idx] : 0.f;
+    if (!mbar_wait(bar, phase, abort_flag, p.err_word, ERR_ATTN_BWD)) { ok = false; }
+    phase ^= 1;
+    if (!__syncthreads_and(ok)) { ok = false; break; }
+    tcgen05_fence_after();
+
+    const bool diag = (qt == kt);
+#pragma unroll 1
+    for (int c = 0; c < TK / 32; ++c) {
+      uint32_t rs[32], rd[32];
+      tmem_ld_32x32b_x32(t_lane + C_S + c * 32, rs);
+      tmem_ld_32x32b_x32(t_lane + C_DP + c * 32, rd);
+      tmem_ld_wait();
+      uint32_t pk[16], dk[16];
+#pragma unroll
+      for (int j = 0; j < 32; j += 2) {
+        float pv[2], dsv[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int key = k0 + c * 32 + j + u;
+          bool keep = q_ok && key < p.T && (!diag || key <= q);
+          if (keep && p.key_mask != nullptr) keep = p.key_mask[static_cast<size_t>(b) * p.T + key] == 0;
+          const float pr = keep ? exp2f(__uint_as_float(rs[j + u]) * sl2 - lse_l2) : 0.f;
+          pv[u] = pr;
+          dsv[u] = pr * (__uint_as_float(rd[j + u]) - delta) * p.scale;
+        }
+        pk[j >> 1] = pack_bf16x2(pv[0], pv[1]);
+        dk[j >> 1] = pack_bf16x2(dsv[0], dsv[1]);
+      }
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const uint32_t off = (c * 4 + g) * CHUNK_STRIDE + tid * 16;
+        st_shared_v4(sP + off, pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+        st_shared_v4(sdS + off, dk[4 * g], dk[4 * g + 1], dk[4 * g + 2], dk[4 * g + 3]);
+      }
+    }
+    tcgen05_fence_before();
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      tcgen05_fence_after();
+      const uint32_t acc0 = (qt > kt) ? 1u : 0u;
+#pragma unroll
+      for (int kk = 0; kk < TQ / 16; ++kk)  // dV[key, d] += P^T dO   (reduction over the 128 queries)
+        umma_f16_ss(tmem + C_DV, desc_mnmajor(sP, kk), desc_mnmajor(sdO, kk), idesc_tt, (kk > 0) ? 1u : acc0);
+#pragma unroll
+      for (int kk = 0; kk < TQ / 16; ++kk)  // dK[key, d] += dS^T Q
+        umma_f16_ss(tmem + C_DK, desc_mnmajor(sdS, kk), desc_mnmajor(sQ, kk), idesc_tt, (kk > 0) ? 1u : acc0);
+#pragma unroll
+      for (int kk = 0; kk < TK / 16; ++kk)  // dQ[q, d] = dS K          (reduction over the 128 keys)
+        umma_f16_ss(tmem + C_S, desc_kmajor(sdS, kk), desc_mnmajor(sK, kk), idesc_dq, kk > 0 ? 1u : 0u);
+      umma_commit(bar);
+    }
+    if (!mbar_wait(bar, phase, abort_flag, p.err_word, ERR_ATTN_BWD)) { ok = false; }
+    phase ^= 1;
+    if (!__syncthreads_and(ok)) { ok = false; break; }
+    tcgen05_fence_after();
+    float* dq_row = p.dq_acc + (static_cast<size_t>(b) * p.T + (q_ok ? q : 0)) * HD + h * D;
+#pragma unroll
+    for (int c = 0; c < D / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(t_lane + C_S + c * 32, r);
+      tmem_ld_wait();
+      if (q_ok) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dq_row + c * 32 + j),
+                       "f"(__uint_as_float(r[j])), "f"(__uint_as_float(r[j + 1])),
+                       "f"(__uint_as_float(r[j + 2])), "f"(__uint_as_float(r[j + 3]))
+                       : "memory");
+      }
+    }
+    tcgen05_fence_before();
+  }
+
+  // dK / dV for this key tile: row = key
+  const int key = k0 + tid;
+  if (ok) {
+    bf16* dk_row = p.dqkv + (static_cast<size_t>(b) * p.T + (key < p.T ? key : 0)) * row_stride + HD + h * D;
+    bf16* dv_row = dk_row + HD;
+#pragma unroll
+    for (int c = 0; c < D / 32; ++c) {
+      uint32_t rk[32], rv[32];
+      tmem_ld_32x32b_x32(t_lane + C_DK + c * 32, rk);
+      tmem_ld_32x32b_x32(t_lane + C_DV + c * 32, rv);
+      tmem_ld_wait();
+      if (key < p.T) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+          *reinterpret_cast<uint4*>(dk_row + c * 32 + j) = make_uint4(
+              pack_bf16x2(__uint_as_float(rk[j]), __uint_as_float(rk[j + 1])),
+              pack_bf16x2(__uint_as_float(rk[j + 2]), __uint_as_float(rk[j + 3])),
+              pack_bf16x2(__uint_as_float(rk[j + 4]), __uint_as_float(rk[j + 5])),
+              pack_bf16x2(__uint_as_float(rk[j + 6]), __uint_as_float(rk[j + 7])));
+          *reinterpret_cast<uint4*>(dv_row + c * 32 + j) = make_uint4(
+              pack_bf16x2(__uint_as_float(rv[j]), __uint_as_float(rv[j + 1])),
+              pack_bf16x2(__uint_as_float(rv[j + 2]), __uint_as_float(rv[j + 3])),
+              pack_bf16x2(__uint_as_float(rv[j + 4]), __uint_as_float(rv[j + 5])),
+              pack_bf16x2(__uint_as_float(rv[j + 6]), __uint_as_float(rv[j + 7])));
+        }
+      }
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem, TMEM_COLS);
+  }
+}
+
+// dq fp32 scratch [B*T, H*D] -> bf16 q section of dqkv [B*T, 3*H*D]
+__global__ void __launch_bounds__(256)
+attn_dq_convert_kernel(const float* __restrict__ dq_acc, bf16* __restrict__ dqkv, int64_t rows, int HD) {
+  const int vec_per_row = HD >> 2;
+  const int64_t total = rows * vec_per_row;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int64_t r = i / vec_per_row;
+    const int c = static_cast<int>(i % vec_per_row);
+    const float4 f = __ldg(reinterpret_cast<const float4*>(dq_acc + r * HD) + c);
+    reinterpret_cast<uint2*>(dqkv + r * 3 * HD)[c] = make_uint2(pack_bf16x2(f.x, f.y), pack_bf16x2(f.z, f.w));
+  }
+}
+
+template <int D>
+int fwd_launch(const AttnParams& p, cudaStream_t st) {
+  constexpr int smem = 3 * TQ * D * 2 + TQ * TK * 2 + 8 + 16 + 128;
+  static bool configured[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!configured[dev & 63]) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured[dev & 63] = true;
+  }
+  dim3 grid(ceil_div(p.T, TQ), p.H, p.B);
+  attn_fwd_kernel<D><<<grid, ATTN_THREADS, smem, st>>>(p);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int D>
+int bwd_launch(const AttnParams& p, cudaStream_t st) {
+  constexpr int smem = 4 * TQ * D * 2 + 2 * TQ * TK * 2 + 8 + 16 + 128;
+  static bool configured[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!configured[dev & 63]) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured[dev & 63] = true;
+  }
+  const int64_t rows = static_cast<int64_t>(p.B) * p.T;
+  const int HD = p.H * D;
+  B200_CHECK_CUDA(cudaMemsetAsync(p.dq_acc, 0, rows * HD * sizeof(float), st));
+  {
+    const int64_t total = rows * p.H;
+    int grid = static_cast<int>((total + 255) / 256);
+    if (grid > b200_num_sms() * 16) grid = b200_num_sms() * 16;
+    attn_delta_kernel<D><<<grid, 256, 0, st>>>(p.out, p.dout, p.delta, p.B, p.T, p.H);
+    B200_LAUNCH_CHECK();
+  }
+  dim3 grid(ceil_div(p.T, TK), p.H, p.B);
+  attn_bwd_kernel<D><<<grid, ATTN_THREADS, smem, st>>>(p);
+  B200_LAUNCH_CHECK();
+  {
+    const int64_t total = rows * (HD / 4);
+    int grid2 = static_cast<int>((total + 255) / 256);
+    if (grid2 > b200_num_sms() * 16) grid2 = b200_num_sms() * 16;
+    attn_dq_convert_kernel<<<grid2, 256, 0, st>>>(p.dq_acc, p.dqkv, rows, HD);
+    B200_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int D, float scale,
+                  const void* key_mask, void* stream) {
+  B200_REQUIRE(D == 32 || D == 64 || D == 128, "attention: head_dim %d not supported (32, 64, 128)", D);
+  B200_REQUIRE(B > 0 && T > 0 && H > 0 && B <= 65535 && H <= 65535, "attention: bad shape");
+  AttnParams p{};
+  p.qkv = reinterpret_cast<const bf16*>(qkv);
+  p.out = reinterpret_cast<bf16*>(out);
+  p.lse = lse;
+  p.key_mask = reinterpret_cast<const uint8_t*>(key_mask);
+  p.B = B; p.T = T; p.H = H; p.scale = scale;
+  p.err_word = b200_error_word();
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (D == 32) return fwd_launch<32>(p, st);
+  if (D == 64) return fwd_launch<64>(p, st);
+  return fwd_launch<128>(p, st);
+}
+
+int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                  float* delta, float* dq_acc, int B, int T, int H, int D, float scale,
+                  const void* key_mask, void* stream) {
+  B200_REQUIRE(D == 32 || D == 64 || D == 128, "attention: head_dim %d not supported (32, 64, 128)", D);
+  B200_REQUIRE(B > 0 && T > 0 && H > 0 && B <= 65535 && H <= 65535, "attention: bad shape");
+  AttnParams p{};
+  p.qkv = reinterpret_cast<const bf16*>(qkv);
+  p.out = const_cast<bf16*>(reinterpret_cast<const bf16*>(out));
+  p.dout = reinterpret_cast<const bf16*>(dout);
+  p.lse = const_cast<float*>(lse);
+  p.dqkv = reinterpret_cast<bf16*>(dqkv);
+  p.delta = delta;
+  p.dq_acc = dq_acc;
+  p.key_mask = reinterpret_cast<const uint8_t*>(key_mask);
+  p.B = B; p.T = T; p.H = H; p.scale = scale;
+  p.err_word = b200_error_word();
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (D == 32) return bwd_launch<32>(p, st);
+  if (D == 64) return bwd_launch<64>(p, st);
+  return bwd_launch<128>(p, st);
+}
+
+}  // extern "C"

@@ -1,0 +1,644 @@
+// Memory-bound kernels of the GPT training step: fused token+position embedding (fwd/bwd),
+// LayerNorm fp32 -> bf16 (fwd/bwd with dgamma/dbeta), fused multi-tensor AdamW over the flat
+// arena (writes the bf16 compute copy in the same pass), ReLU-backward + bias-gradient, and the
+// in-place cross-entropy forward+backward over a bf16 logits chunk (loss, argmax accuracy and
+// dlogits in one pass).  All are vectorised (16-byte accesses) and sized against the measured
+// HBM roofline; none needs scratch memory.
+//
+// Reference call sites: models/gpt.py:185 (embeddings), :119,122,217 (LayerNorm), :35,38
+// (ReLU), main-single.py:42,99-101 (AdamW + GradScaler), :95-96,127-131 (CE + accuracy).
+#include <math.h>
+
+#include "../include/b200gpt.h"
+#include "common.cuh"
+
+namespace {
+
+// ------------------------------------------------------------------------------------------
+// embedding
+// ------------------------------------------------------------------------------------------
+__global__ void embedding_fwd_kernel(const int64_t* __restrict__ ids, const int64_t* __restrict__ pos,
+                                     const float* __restrict__ tok_w, const float* __restrict__ pos_w,
+                                     float* __restrict__ out, int n_tokens, int dim, int vocab,
+                                     int max_pos) {
+  const int vec_per_row = dim >> 2;
+  const int64_t total = static_cast<int64_t>(n_tokens) * vec_per_row;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int t = static_cast<int>(i / vec_per_row);
+    const int c = static_cast<int>(i % vec_per_row);
+    int64_t id = ids[t], ps = pos[t];
+    id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+    ps = ps < 0 ? 0 : (ps >= max_pos ? max_pos - 1 : ps);
+    const float4 a = __ldg(reinterpret_cast<const float4*>(tok_w + id * dim) + c);
+    const float4 b = __ldg(reinterpret_cast<const float4*>(pos_w + ps * dim) + c);
+    reinterpret_cast<float4*>(out + static_cast<int64_t>(t) * dim)[c] =
+        make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+  }
+}
+
+__device__ __forceinline__ void red_add_f32x4(float* addr, float4 v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+__global__ void embedding_bwd_kernel(const int64_t* __restrict__ ids, const int64_t* __restrict__ pos,
+                                     const float* __restrict__ dout, float* __restrict__ dtok,
+                                     float* __restrict__ dpos, int n_tokens, int dim, int vocab,
+                                     int max_pos) {
+  const int vec_per_row = dim >> 2;
+  const int64_t total = static_cast<int64_t>(n_tokens) * vec_per_row;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int t = static_cast<int>(i / vec_per_row);
+    const int c = static_cast<int>(i % vec_per_row);
+    int64_t id = ids[t], ps = pos[t];
+    id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+    ps = ps < 0 ? 0 : (ps >= max_pos ? max_pos - 1 : ps);
+    const float4 g = __ldg(reinterpret_cast<const float4*>(dout + static_cast<int64_t>(t) * dim) + c);
+    red_add_f32x4(dtok + id * dim + 4 * c, g);
+    red_add_f32x4(dpos + ps * dim + 4 * c, g);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// LayerNorm: one warp per row, NV float4 per lane held in registers (dim <= NV*128)
+// ------------------------------------------------------------------------------------------
+template <int NV>
+__global__ void __launch_bounds__(256)
+layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, bf16* __restrict__ y, float* __restrict__ mean_out,
+                     float* __restrict__ rstd_out, int rows, int dim, float eps) {
+  const int lane = threadIdx.x & 31;
+  const int warps_per_block = blockDim.x >> 5;
+  const int nvec = dim >> 2;
+  const float inv_dim = 1.0f / static_cast<float>(dim);
+  for (int row = blockIdx.x * warps_per_block + (threadIdx.x >> 5); row < rows;
+       row += gridDim.x * warps_per_block) {
+    const float4* xr = reinterpret_cast<const float4*>(x + static_cast<int64_t>(row) * dim);
+    float4 v[NV];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + 32 * i;
+      v[i] = c < nvec ? xr[c] : make_float4(0.f, 0.f, 0.f, 0.f);
+      s += v[i].x + v[i].y + v[i].z + v[i].w;
+    }
+    const float mean = warp_sum(s) * inv_dim;
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) {
+        const float a = v[i].x - mean, b = v[i].y - mean, cc = v[i].z - mean, d = v[i].w - mean;
+        sq += a * a + b * b + cc * cc + d * d;
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(sq) * inv_dim + eps);
+    uint2* yr = reinterpret_cast<uint2*>(y + static_cast<int64_t>(row) * dim);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) {
+        const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + c);
+        const float4 b = __ldg(reinterpret_cast<const float4*>(beta) + c);
+        const float o0 = (v[i].x - mean) * rstd * g.x + b.x;
+        const float o1 = (v[i].y - mean) * rstd * g.y + b.y;
+        const float o2 = (v[i].z - mean) * rstd * g.z + b.z;
+        const float o3 = (v[i].w - mean) * rstd * g.w + b.w;
+        yr[c] = make_uint2(pack_bf16x2(o0, o1), pack_bf16x2(o2, o3));
+      }
+    }
+    if (lane == 0) {
+      mean_out[row] = mean;
+      rstd_out[row] = rstd;
+    }
+  }
+}
+
+template <int NV>
+__global__ void __launch_bounds__(256)
+layernorm_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
+                     const float* __restrict__ gamma, const float* __restrict__ mean_in,
+                     const float* __restrict__ rstd_in, const float* __restrict__ dres,
+                     float* __restrict__ dx, bf16* __restrict__ dx_bf16, float* __restrict__ dgamma,
+                     float* __restrict__ dbeta, int rows, int dim) {
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int warps_per_block = blockDim.x >> 5;
+  const int nvec = dim >> 2;
+  const float inv_dim = 1.0f / static_cast<float>(dim);
+  const float4* g4p = reinterpret_cast<const float4*>(gamma);
+  float4 dg[NV], db[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    dg[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    db[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (int row = blockIdx.x * warps_per_block + warp; row < rows; row += gridDim.x * warps_per_block) {
+    const float4* xr = reinterpret_cast<const float4*>(x + static_cast<int64_t>(row) * dim);
+    const uint2* dyr = reinterpret_cast<const uint2*>(dy + static_cast<int64_t>(row) * dim);
+    const float mean = mean_in[row], rstd = rstd_in[row];
+    float c1 = 0.f, c2 = 0.f;
+    // pass 1: row statistics of dy*gamma and the dgamma/dbeta partials
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) {
+        const float4 xv = xr[c];
+        const uint2 u = dyr[c];
+        const float4 g = __ldg(g4p + c);
+        const float2 d01 = unpack_bf16x2(u.x), d23 = unpack_bf16x2(u.y);
+        const float h0 = (xv.x - mean) * rstd, h1 = (xv.y - mean) * rstd, h2 = (xv.z - mean) * rstd,
+                    h3 = (xv.w - mean) * rstd;
+        const float a0 = d01.x * g.x, a1 = d01.y * g.y, a2 = d23.x * g.z, a3 = d23.y * g.w;
+        c1 += a0 + a1 + a2 + a3;
+        c2 += a0 * h0 + a1 * h1 + a2 * h2 + a3 * h3;
+        dg[i].x += d01.x * h0; dg[i].y += d01.y * h1; dg[i].z += d23.x * h2; dg[i].w += d23.y * h3;
+        db[i].x += d01.x; db[i].y += d01.y; db[i].z += d23.x; db[i].w += d23.y;
+      }
+    }
+    c1 = warp_sum(c1) * inv_dim;
+    c2 = warp_sum(c2) * inv_dim;
+    // pass 2: dx (the row is re-read from L1; keeps the register footprint independent of dim)
+    float4* dxr = reinterpret_cast<float4*>(dx + static_cast<int64_t>(row) * dim);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nvec) {
+        const float4 xv = xr[c];
+        const uint2 u = dyr[c];
+        const float4 g = __ldg(g4p + c);
+        const float2 d01 = unpack_bf16x2(u.x), d23 = unpack_bf16x2(u.y);
+        float4 o;
+        o.x = (d01.x * g.x - c1 - (xv.x - mean) * rstd * c2) * rstd;
+        o.y = (d01.y * g.y - c1 - (xv.y - mean) * rstd * c2) * rstd;
+        o.z = (d23.x * g.z - c1 - (xv.z - mean) * rstd * c2) * rstd;
+        o.w = (d23.y * g.w - c1 - (xv.w - mean) * rstd * c2) * rstd;
+        if (dres != nullptr) {
+          const float4 r = reinterpret_cast<const float4*>(dres + static_cast<int64_t>(row) * dim)[c];
+          o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
+        }
+        dxr[c] = o;
+        if (dx_bf16 != nullptr)
+          reinterpret_cast<uint2*>(dx_bf16 + static_cast<int64_t>(row) * dim)[c] =
+              make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
+      }
+    }
+  }
+  // block reduction of the per-warp dgamma/dbeta partials, then one atomic per column per block
+  extern __shared__ float red[];  // [warps][2][dim]
+  float* my = red + static_cast<size_t>(warp) * 2 * dim;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = lane + 32 * i;
+    if (c < nvec) {
+      reinterpret_cast<float4*>(my)[c] = dg[i];
+      reinterpret_cast<float4*>(my + dim)[c] = db[i];
+    }
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < 2 * dim; j += blockDim.x) {
+    float s = 0.f;
+    for (int w = 0; w < warps_per_block; ++w) s += red[static_cast<size_t>(w) * 2 * dim + j];
+    if (j < dim) atomicAdd(dgamma + j, s);
+    else atomicAdd(dbeta + (j - dim), s);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// AdamW (decoupled weight decay), torch.optim.AdamW maths; hyper = {lr, step, ...} on device
+// ------------------------------------------------------------------------------------------
+__global__ void adamw_tick_kernel(float* hyper) { hyper[1] += 1.0f; }
+
+__global__ void __launch_bounds__(256)
+adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+             float* __restrict__ v, bf16* __restrict__ pb, int64_t n, const float* __restrict__ hyper,
+             float beta1, float beta2, float eps, float wd) {
+  const float lr = hyper[0];
+  const float step = hyper[1];
+  const float bc1 = 1.0f - powf(beta1, step);
+  const float bc2_rsqrt = rsqrtf(1.0f - powf(beta2, step));
+  const float step_size = lr / bc1;
+  const float decay = 1.0f - lr * wd;
+  const int64_t nvec = n >> 2;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < nvec; i += stride) {
+    float4 pv = reinterpret_cast<float4*>(p)[i];
+    const float4 gv = __ldg(reinterpret_cast<const float4*>(g) + i);
+    float4 mv = reinterpret_cast<float4*>(m)[i];
+    float4 vv = reinterpret_cast<float4*>(v)[i];
+    float* pp = &pv.x; const float* gp = &gv.x; float* mp = &mv.x; float* vp = &vv.x;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float gj = gp[j];
+      if (isfinite(gj)) {  // GradScaler-style skip of non-finite gradients, without a host sync
+        pp[j] *= decay;
+        mp[j] = beta1 * mp[j] + (1.0f - beta1) * gj;
+        vp[j] = beta2 * vp[j] + (1.0f - beta2) * gj * gj;
+        const float denom = sqrtf(vp[j]) * bc2_rsqrt + eps;
+        pp[j] -= step_size * mp[j] / denom;
+      }
+    }
+    reinterpret_cast<float4*>(p)[i] = pv;
+    reinterpret_cast<float4*>(m)[i] = mv;
+    reinterpret_cast<float4*>(v)[i] = vv;
+    if (pb != nullptr)
+      reinterpret_cast<uint2*>(pb)[i] = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
+  }
+  // tail (n not a multiple of 4)
+  for (int64_t i = (nvec << 2) + blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
+       i += stride) {
+    const float gj = g[i];
+    if (isfinite(gj)) {
+      float pj = p[i] * decay;
+      const float mj = beta1 * m[i] + (1.0f - beta1) * gj;
+      const float vj = beta2 * v[i] + (1.0f - beta2) * gj * gj;
+      pj -= step_size * mj / (sqrtf(vj) * bc2_rsqrt + eps);
+      p[i] = pj; m[i] = mj; v[i] = vj;
+    }
+    if (pb != nullptr) pb[i] = __float2bfloat16_rn(p[i]);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+cast_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, int64_t n) {
+  const int64_t nvec = n >> 2;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < nvec; i += stride) {
+    const float4 f = __ldg(reinterpret_cast<const float4*>(in) + i);
+    reinterpret_cast<uint2*>(out)[i] = make_uint2(pack_bf16x2(f.x, f.y), pack_bf16x2(f.z, f.w));
+  }
+  for (int64_t i = (nvec << 2) + blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
+       i += stride)
+    out[i] = __float2bfloat16_rn(in[i]);
+}
+
+// ------------------------------------------------------------------------------------------
+// dz = dy * (y_act > 0) -> bf16 ; dbias += column sums of dz.  block (32, 8): 32 column groups of
+// 8 columns x 8 row lanes, 64 rows per block.
+// ------------------------------------------------------------------------------------------
+template <bool DY_FP32>
+__global__ void __launch_bounds__(256)
+relu_bwd_kernel(const void* __restrict__ dy_, const bf16* __restrict__ y_act, bf16* __restrict__ dz,
+                float* __restrict__ dbias, int rows, int cols, int ld) {
+  const int cg = blockIdx.x * 32 + threadIdx.x;  // column group (8 columns)
+  const int col = cg * 8;
+  const bool col_ok = col < cols;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  const int r0 = blockIdx.y * 64;
+  if (col_ok) {
+    for (int r = r0 + threadIdx.y; r < min(r0 + 64, rows); r += 8) {
+      const size_t off = static_cast<size_t>(r) * ld + col;
+      float v[8];
+      if (DY_FP32) {
+        const float* dy = reinterpret_cast<const float*>(dy_) + off;
+        const float4 a = *reinterpret_cast<const float4*>(dy);
+        const float4 b = *reinterpret_cast<const float4*>(dy + 4);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+      } else {
+        const uint4 u = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(dy_) + off);
+        const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z),
+                     d = unpack_bf16x2(u.w);
+        v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+      }
+      if (y_act != nullptr) {
+        const uint4 u = *reinterpret_cast<const uint4*>(y_act + off);
+        const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const float2 f = unpack_bf16x2(w[t]);
+          if (!(f.x > 0.f)) v[2 * t] = 0.f;
+          if (!(f.y > 0.f)) v[2 * t + 1] = 0.f;
+        }
+      }
+      if (dz != nullptr)
+        *reinterpret_cast<uint4*>(dz + off) =
+            make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                       pack_bf16x2(v[6], v[7]));
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += v[j];
+    }
+  }
+  if (dbias == nullptr) return;
+  __shared__ float red[8][32][9];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[threadIdx.y][threadIdx.x][j] = acc[j];
+  __syncthreads();
+  if (threadIdx.y == 0 && col_ok) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float s = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) s += red[w][threadIdx.x][j];
+      atomicAdd(dbias + col + j, s);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// cross entropy
+// ------------------------------------------------------------------------------------------
+__global__ void count_valid_kernel(const int64_t* __restrict__ targets, float* __restrict__ stats,
+                                   int ignore_index, int64_t n) {
+  __shared__ int sm[32];
+  int c = 0;
+  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) c += (targets[i] != ignore_index) ? 1 : 0;
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) t += sm[w];
+    stats[0] = static_cast<float>(t);
+    stats[1] = 0.f;
+    stats[2] = 0.f;
+    stats[3] = 0.f;
+  }
+}
+
+constexpr int CE_THREADS = 512;
+constexpr int CE_CACHE = 16;  // uint4 (8 bf16) per thread held in registers: vocab <= 65536
+
+// One block per row.  logits row is read once into registers, reduced (max / argmax / sum-exp),
+// and - when write_grad - overwritten in place with dlogits = (softmax - onehot) * scale.
+__global__ void __launch_bounds__(CE_THREADS)
+ce_fwd_bwd_kernel(bf16* __restrict__ logits, const int64_t* __restrict__ targets,
+                  float* __restrict__ stats, int vocab, int ld, int ignore_index, int write_grad,
+                  float grad_scale) {
+  const int row = blockIdx.x;
+  bf16* lr = logits + static_cast<size_t>(row) * ld;
+  const int64_t tgt64 = targets[row];
+  const bool valid = tgt64 != ignore_index;
+  const int tgt = static_cast<int>(tgt64);
+  const int nvec = ld >> 3;
+  __shared__ float s_f[CE_THREADS / 32];
+  __shared__ int s_i[CE_THREADS / 32];
+  __shared__ float s_bcast[2];
+  __shared__ int s_arg;
+
+  if (!valid) {  // ignored row: no loss, zero gradient
+    if (write_grad)
+      for (int c = threadIdx.x; c < nvec; c += CE_THREADS)
+        reinterpret_cast<uint4*>(lr)[c] = make_uint4(0u, 0u, 0u, 0u);
+    return;
+  }
+  const float tgt_logit = __bfloat162float(lr[tgt]);  // read before anything is overwritten
+
+  uint4 cache[CE_CACHE];
+  float mx = -INFINITY;
+  int arg = 0;
+#pragma unroll
+  for (int i = 0; i < CE_CACHE; ++i) {
+    const int c = threadIdx.x + i * CE_THREADS;
+    if (c < nvec) {
+      cache[i] = reinterpret_cast<const uint4*>(lr)[c];
+      const uint32_t w[4] = {cache[i].x, cache[i].y, cache[i].z, cache[i].w};
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const float2 f = unpack_bf16x2(w[t]);
+        const int col = c * 8 + 2 * t;
+        if (col < vocab && f.x > mx) { mx = f.x; arg = col; }
+        if (col + 1 < vocab && f.y > mx) { mx = f.y; arg = col + 1; }
+      }
+    }
+  }
+  // block argmax (ties -> lowest index, like torch.argmax)
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+    const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (om > mx || (om == mx && oa < arg)) { mx = om; arg = oa; }
+  }
+  if (lane == 0) { s_f[warp] = mx; s_i[warp] = arg; }
+  __syncthreads();
+  if (warp == 0) {
+    float m2 = lane < CE_THREADS / 32 ? s_f[lane] : -INFINITY;
+    int a2 = lane < CE_THREADS / 32 ? s_i[lane] : 0x7fffffff;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, m2, o);
+      const int oa = __shfl_xor_sync(0xffffffffu, a2, o);
+      if (om > m2 || (om == m2 && oa < a2)) { m2 = om; a2 = oa; }
+    }
+    if (lane == 0) { s_bcast[0] = m2; s_arg = a2; }
+  }
+  __syncthreads();
+  const float row_max = s_bcast[0];
+  const float kLog2e = 1.4426950408889634f;
+  const float mscaled = row_max * kLog2e;
+
+  // p = exp(l - max), kept as bf16 in the same registers; sum in fp32
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < CE_CACHE; ++i) {
+    const int c = threadIdx.x + i * CE_THREADS;
+    if (c < nvec) {
+      uint32_t w[4] = {cache[i].x, cache[i].y, cache[i].z, cache[i].w};
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const float2 f = unpack_bf16x2(w[t]);
+        const int col = c * 8 + 2 * t;
+        const float p0 = col < vocab ? exp2f(f.x * kLog2e - mscaled) : 0.f;
+        const float p1 = col + 1 < vocab ? exp2f(f.y * kLog2e - mscaled) : 0.f;
+        sum += p0 + p1;
+        w[t] = pack_bf16x2(p0, p1);
+      }
+      cache[i] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+  sum = warp_sum(sum);
+  __syncthreads();  // s_f reuse
+  if (lane == 0) s_f[warp] = sum;
+  __syncthreads();
+  if (warp == 0) {
+    float s2 = lane < CE_THREADS / 32 ? s_f[lane] : 0.f;
+    s2 = warp_sum(s2);
+    if (lane == 0) s_bcast[1] = s2;
+  }
+  __syncthreads();
+  const float total = s_bcast[1];
+  if (threadIdx.x == 0) {
+    const float lse = row_max + logf(total);
+    atomicAdd(stats + 1, lse - tgt_logit);
+    if (s_arg == tgt) atomicAdd(stats + 2, 1.0f);
+  }
+  if (!write_grad) return;
+  const float n_valid = fmaxf(stats[0], 1.0f);
+  const float scale = grad_scale / n_valid;
+  const float pscale = scale / total;
+#pragma unroll
+  for (int i = 0; i < CE_CACHE; ++i) {
+    const int c = threadIdx.x + i * CE_THREADS;
+    if (c < nvec) {
+      uint32_t w[4] = {cache[i].x, cache[i].y, cache[i].z, cache[i].w};
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const float2 f = unpack_bf16x2(w[t]);
+        const int col = c * 8 + 2 * t;
+        float g0 = f.x * pscale, g1 = f.y * pscale;
+        if (col == tgt) g0 -= scale;
+        if (col + 1 == tgt) g1 -= scale;
+        w[t] = pack_bf16x2(g0, g1);
+      }
+      reinterpret_cast<uint4*>(lr)[c] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+}
+
+inline int grid_for(int64_t work_items, int threads, int max_blocks_per_sm = 8) {
+  int64_t blocks = ceil_div64(work_items, threads);
+  const int64_t cap = static_cast<int64_t>(b200_num_sms()) * max_blocks_per_sm;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return static_cast<int>(blocks);
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_embedding_fwd(const int64_t* ids, const int64_t* pos, const float* tok_w, const float* pos_w,
+                       float* out, int n_tokens, int dim, int vocab, int max_pos, void* stream) {
+  B200_REQUIRE(dim % 4 == 0, "embedding: dim %d must be a multiple of 4", dim);
+  if (n_tokens == 0) return 0;
+  const int grid = grid_for(static_cast<int64_t>(n_tokens) * (dim / 4), 256);
+  embedding_fwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(ids, pos, tok_w, pos_w, out,
+                                                                           n_tokens, dim, vocab, max_pos);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_embedding_bwd(const int64_t* ids, const int64_t* pos, const float* dout, float* dtok,
+                       float* dpos, int n_tokens, int dim, int vocab, int max_pos, void* stream) {
+  B200_REQUIRE(dim % 4 == 0, "embedding: dim %d must be a multiple of 4", dim);
+  if (n_tokens == 0) return 0;
+  const int grid = grid_for(static_cast<int64_t>(n_tokens) * (dim / 4), 256);
+  embedding_bwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(ids, pos, dout, dtok, dpos,
+                                                                           n_tokens, dim, vocab, max_pos);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_layernorm_fwd(const float* x, const float* gamma, const float* beta, void* y, float* mean,
+                       float* rstd, int rows, int dim, float eps, void* stream) {
+  B200_REQUIRE(dim % 4 == 0 && dim <= 4096, "layernorm: dim %d must be a multiple of 4 and <= 4096", dim);
+  if (rows == 0) return 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int grid = grid_for(static_cast<int64_t>(rows) * 32, 256);
+  bf16* yb = reinterpret_cast<bf16*>(y);
+  if (dim <= 256) layernorm_fwd_kernel<2><<<grid, 256, 0, st>>>(x, gamma, beta, yb, mean, rstd, rows, dim, eps);
+  else if (dim <= 1024) layernorm_fwd_kernel<8><<<grid, 256, 0, st>>>(x, gamma, beta, yb, mean, rstd, rows, dim, eps);
+  else if (dim <= 2048) layernorm_fwd_kernel<16><<<grid, 256, 0, st>>>(x, gamma, beta, yb, mean, rstd, rows, dim, eps);
+  else layernorm_fwd_kernel<32><<<grid, 256, 0, st>>>(x, gamma, beta, yb, mean, rstd, rows, dim, eps);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_layernorm_bwd(const void* dy, const float* x, const float* gamma, const float* mean,
+                       const float* rstd, const float* dres, float* dx, void* dx_bf16, float* dgamma,
+                       float* dbeta, int rows, int dim, void* stream) {
+  B200_REQUIRE(dim % 4 == 0 && dim <= 4096, "layernorm: dim %d must be a multiple of 4 and <= 4096", dim);
+  if (rows == 0) return 0;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int grid = b200_num_sms() * 4;
+  const int max_grid = ceil_div(rows, 8);
+  if (grid > max_grid) grid = max_grid;
+  const size_t smem = static_cast<size_t>(8) * 2 * dim * sizeof(float);
+  const bf16* dyb = reinterpret_cast<const bf16*>(dy);
+  bf16* dxb = reinterpret_cast<bf16*>(dx_bf16);
+#define LN_BWD(NV)                                                                                  \
+  do {                                                                                              \
+    if (smem > 48 * 1024)                                                                           \
+      B200_CHECK_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NV>,                                \
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    layernorm_bwd_kernel<NV><<<grid, 256, smem, st>>>(dyb, x, gamma, mean, rstd, dres, dx, dxb,     \
+                                                      dgamma, dbeta, rows, dim);                    \
+  } while (0)
+  if (dim <= 256) LN_BWD(2);
+  else if (dim <= 1024) LN_BWD(8);
+  else if (dim <= 2048) LN_BWD(16);
+  else LN_BWD(32);
+#undef LN_BWD
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_adamw_tick(float* hyper, void* stream) {
+  adamw_tick_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(hyper);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_adamw(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n,
+               const float* hyper, float beta1, float beta2, float eps, float wd, void* stream) {
+  if (n == 0) return 0;
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(p) & 15) == 0 && (reinterpret_cast<uintptr_t>(g) & 15) == 0 &&
+                   (reinterpret_cast<uintptr_t>(m) & 15) == 0 && (reinterpret_cast<uintptr_t>(v) & 15) == 0 &&
+                   (reinterpret_cast<uintptr_t>(p_bf16) & 7) == 0,
+               "adamw: buffers must be 16-byte aligned");
+  const int grid = grid_for(n / 4 + 1, 256, 16);
+  adamw_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      p, g, m, v, reinterpret_cast<bf16*>(p_bf16), n, hyper, beta1, beta2, eps, wd);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_cast_bf16(const float* in, void* out, int64_t n, void* stream) {
+  if (n == 0) return 0;
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 7) == 0,
+               "cast: buffers must be 16/8-byte aligned");
+  const int grid = grid_for(n / 4 + 1, 256, 16);
+  cast_bf16_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(in, reinterpret_cast<bf16*>(out), n);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_relu_bwd(const void* dy, const void* y_act, void* dz, float* dbias, int rows, int cols,
+                  int dy_fp32, void* stream) {
+  B200_REQUIRE(cols % 8 == 0, "relu_bwd: cols %d must be a multiple of 8", cols);
+  if (rows == 0) return 0;
+  dim3 grid(ceil_div(cols / 8, 32), ceil_div(rows, 64)), block(32, 8);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dy_fp32)
+    relu_bwd_kernel<true><<<grid, block, 0, st>>>(dy, reinterpret_cast<const bf16*>(y_act),
+                                                  reinterpret_cast<bf16*>(dz), dbias, rows, cols, cols);
+  else
+    relu_bwd_kernel<false><<<grid, block, 0, st>>>(dy, reinterpret_cast<const bf16*>(y_act),
+                                                   reinterpret_cast<bf16*>(dz), dbias, rows, cols, cols);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_colsum_bf16(const void* x, float* out_accum, int rows, int cols, int ld, void* stream) {
+  B200_REQUIRE(cols % 8 == 0 && ld % 8 == 0, "colsum: cols/ld must be multiples of 8");
+  if (rows == 0) return 0;
+  dim3 grid(ceil_div(cols / 8, 32), ceil_div(rows, 64)), block(32, 8);
+  relu_bwd_kernel<false><<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(
+      x, nullptr, nullptr, out_accum, rows, cols, ld);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_count_valid(const int64_t* targets, float* stats, int ignore_index, int64_t n, void* stream) {
+  count_valid_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(targets, stats, ignore_index, n);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_ce_fwd_bwd(void* logits, const int64_t* targets, float* stats, int rows, int vocab, int ld,
+                    int ignore_index, int write_grad, float grad_scale, void* stream) {
+  B200_REQUIRE(ld % 8 == 0 && ld >= vocab, "ce: ld %d must be a multiple of 8 and >= vocab %d", ld, vocab);
+  B200_REQUIRE(ld <= CE_THREADS * CE_CACHE * 8, "ce: vocab %d too large (max %d)", vocab,
+               CE_THREADS * CE_CACHE * 8);
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(logits) & 15) == 0, "ce: logits must be 16-byte aligned");
+  if (rows == 0) return 0;
+  ce_fwd_bwd_kernel<<<rows, CE_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<bf16*>(logits), targets, stats, vocab, ld, ignore_index, write_grad, grad_scale);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

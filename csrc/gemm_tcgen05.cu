@@ -1,0 +1,473 @@
+// Persistent, warp-specialised bf16 GEMM for sm_100a: TMA -> 128B-swizzled smem ring ->
+// tcgen05.mma (cta_group::1, 128 x BN x 16, fp32 accumulators double-buffered in TMEM) ->
+// tcgen05.ld epilogue with fused bias / ReLU / ReLU-mask / fp32 residual / cast / split-K
+// reduction.  One kernel serves forward (K-major x K-major), dgrad (K-major x MN-major) and
+// wgrad (MN-major x MN-major): operand major-ness only changes the TMA box shape and the
+// UMMA descriptors, so no tensor is ever transposed in memory.
+//
+//   C[M,N] (+)= A[M,K] . B[N,K]^T        K = reduction extent
+//   K-major  operand: memory is [rows][K]  (row stride ld)   -> one TMA box {64 k, rows}
+//   MN-major operand: memory is [K][rows]  (row stride ld)   -> rows/64 TMA boxes {64 rows, 64 k}
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
+// warps 2..5 = epilogue (TMEM lane quarter = warp_idx % 4).  All waits are bounded
+// (common.cuh: mbar_wait) so a protocol bug surfaces as an error code, never as a hung GPU.
+//
+// Serves reference call sites models/gpt.py:60-64,71-73,102 (projections), :29-38 (MLP),
+// :219,231 (LM head) and every backward GEMM autograd derives from them (SURVEY K3,K5-K9).
+#include <mutex>
+#include <unordered_map>
+
+#include "../include/b200gpt.h"
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int UMMA_K = 16;
+constexpr int GEMM_THREADS = 192;
+constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KB
+
+struct GemmParams {
+  int M, N, K;
+  int ldc, ldr;
+  int num_m_tiles, num_n_tiles;
+  int k_splits, kb_total, kb_per_split;
+  uint32_t idesc;
+  uint64_t a_desc_base, b_desc_base;
+  uint32_t a_kstep, b_kstep;  // smem byte advance per UMMA_K
+  int a_mn, b_mn;
+  const float* bias;
+  const float* residual;
+  void* C;
+  bf16* aux_out;
+  const bf16* mask_src;
+  int act, out_fp32, accumulate;
+  int* err_word;
+};
+
+enum : int { ERR_GEMM_PRODUCER = 101, ERR_GEMM_MMA = 102, ERR_GEMM_EPILOGUE = 103 };
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c),
+               "f"(d)
+               : "memory");
+}
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const GemmParams p) {
+  constexpr int B_STAGE_BYTES = BN * BK * 2;
+  constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  constexpr uint32_t TMEM_COLS = 2 * BN;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sA = smem_base;
+  const uint32_t sB = smem_base + STAGES * A_STAGE_BYTES;
+  const uint32_t bars = smem_base + STAGES * STAGE_BYTES;  // 8-byte mbarriers
+  const uint32_t full_bar = bars;
+  const uint32_t empty_bar = bars + 8 * STAGES;
+  const uint32_t tfull_bar = bars + 16 * STAGES;
+  const uint32_t tempty_bar = tfull_bar + 16;
+  uint8_t* gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + STAGES * STAGE_BYTES + 16 * STAGES + 32);
+  volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+
+  const int warp_idx = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    *abort_flag = 0;
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar + 8 * s, 1);
+      mbar_init(empty_bar + 8 * s, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(tfull_bar + 8 * i, 1);
+      mbar_init(tempty_bar + 8 * i, 4);
+    }
+    fence_barrier_init();
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp_idx == 1) {
+    tmem_alloc(smem_u32(tmem_ptr_smem), TMEM_COLS);
+    tmem_relinquish();
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  const int total_tiles = p.num_m_tiles * p.num_n_tiles * p.k_splits;
+
+  if (warp_idx == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      bool ok = true;
+      for (int tile = blockIdx.x; tile < total_tiles && ok; tile += gridDim.x) {
+        const int split = tile % p.k_splits;
+        const int t2 = tile / p.k_splits;
+        const int m0 = (t2 % p.num_m_tiles) * BM;
+        const int n0 = (t2 / p.num_m_tiles) * BN;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          if (!mbar_wait(empty_bar + 8 * stage, phase ^ 1, abort_flag, p.err_word, ERR_GEMM_PRODUCER)) {
+            ok = false;
+            break;
+          }
+          const uint32_t fb = full_bar + 8 * stage;
+          mbar_arrive_expect_tx(fb, STAGE_BYTES);
+          const int k0 = kb * BK;
+          const uint32_t a_dst = sA + stage * A_STAGE_BYTES;
+          const uint32_t b_dst = sB + stage * B_STAGE_BYTES;
+          if (!p.a_mn) {
+            tma_load_2d(a_dst, &tmA, fb, k0, m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j) tma_load_2d(a_dst + j * 8192, &tmA, fb, m0 + 64 * j, k0);
+          }
+          if (!p.b_mn) {
+            tma_load_2d(b_dst, &tmB, fb, k0, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) tma_load_2d(b_dst + j * 8192, &tmB, fb, n0 + 64 * j, k0);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp_idx == 1) {
+    // ===================== MMA issuer =====================
+    uint32_t stage = 0, phase = 0;
+    int lt = 0;
+    bool ok = true;
+    for (int tile = blockIdx.x; tile < total_tiles && ok; tile += gridDim.x, ++lt) {
+      const int split = tile % p.k_splits;
+      const int kb0 = split * p.kb_per_split;
+      const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+      const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
+      if (!mbar_wait(tempty_bar + 8 * as, aph ^ 1, abort_flag, p.err_word, ERR_GEMM_MMA)) break;
+      tcgen05_fence_after();
+      const uint32_t tmem_d = tmem_base + as * BN;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        if (!mbar_wait(full_bar + 8 * stage, phase, abort_flag, p.err_word, ERR_GEMM_MMA)) {
+          ok = false;
+          break;
+        }
+        tcgen05_fence_after();
+        if (lane == 0) {
+          const uint32_t a_src = sA + stage * A_STAGE_BYTES;
+          const uint32_t b_src = sB + stage * B_STAGE_BYTES;
+#pragma unroll
+          for (int kk = 0; kk < BK / UMMA_K; ++kk) {
+            const uint64_t ad = umma_desc_at(p.a_desc_base, a_src + kk * p.a_kstep);
+            const uint64_t bd = umma_desc_at(p.b_desc_base, b_src + kk * p.b_kstep);
+            umma_f16_ss(tmem_d, ad, bd, p.idesc, (kb > kb0 || kk > 0) ? 1u : 0u);
+          }
+          umma_commit(empty_bar + 8 * stage);  // frees the smem slot when these MMAs retire
+        }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      if (ok && lane == 0) umma_commit(tfull_bar + 8 * as);  // accumulator ready for the epilogue
+      __syncwarp();
+    }
+  } else {
+    // ===================== epilogue (4 warps) =====================
+    const int q = warp_idx & 3;  // TMEM lane quarter this warp may access
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      const int t2 = tile / p.k_splits;
+      const int m0 = (t2 % p.num_m_tiles) * BM;
+      const int n0 = (t2 / p.num_m_tiles) * BN;
+      const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
+      if (!mbar_wait(tfull_bar + 8 * as, aph, abort_flag, p.err_word, ERR_GEMM_EPILOGUE)) break;
+      tcgen05_fence_after();
+      const int row = m0 + q * 32 + lane;
+      const bool row_ok = row < p.M;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        __syncwarp();  // tcgen05.ld is .sync.aligned: reconverge after the predicated stores
+        tmem_ld_32x32b_x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        const int col0 = n0 + c * 32;
+        const int ncols = min(32, p.N - col0);
+        if (ncols <= 0 || !row_ok) continue;
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        if (p.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < ncols) v[j] += __ldg(p.bias + col0 + j);
+        }
+        if (p.act == 1) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
+        }
+        const size_t off_c = static_cast<size_t>(row) * p.ldc + col0;
+        const bool full = (ncols == 32);
+        if (p.aux_out != nullptr) {
+          bf16* dst = p.aux_out + off_c;
+          if (full && (p.ldc & 7) == 0) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 u = make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
+                                   pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
+              *reinterpret_cast<uint4*>(dst + j) = u;
+            }
+          } else {
+            for (int j = 0; j < ncols; ++j) dst[j] = __float2bfloat16_rn(v[j]);
+          }
+        }
+        if (p.mask_src != nullptr) {
+          const bf16* msk = p.mask_src + off_c;
+          if (full && (p.ldc & 7) == 0) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              const uint4 u = *reinterpret_cast<const uint4*>(msk + j);
+              const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+              for (int t = 0; t < 4; ++t) {
+                const float2 f = unpack_bf16x2(w[t]);
+                if (!(f.x > 0.0f)) v[j + 2 * t] = 0.0f;
+                if (!(f.y > 0.0f)) v[j + 2 * t + 1] = 0.0f;
+              }
+            }
+          } else {
+            for (int j = 0; j < ncols; ++j)
+              if (!(__bfloat162float(msk[j]) > 0.0f)) v[j] = 0.0f;
+          }
+        }
+        if (p.residual != nullptr) {
+          const float* res = p.residual + static_cast<size_t>(row) * p.ldr + col0;
+          if (full && (p.ldr & 3) == 0) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 f = *reinterpret_cast<const float4*>(res + j);
+              v[j] += f.x; v[j + 1] += f.y; v[j + 2] += f.z; v[j + 3] += f.w;
+            }
+          } else {
+            for (int j = 0; j < ncols; ++j) v[j] += res[j];
+          }
+        }
+        if (p.out_fp32) {
+          float* dst = reinterpret_cast<float*>(p.C) + off_c;
+          const bool vec = full && (p.ldc & 3) == 0;
+          if (p.accumulate) {
+            if (vec) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+              for (int j = 0; j < ncols; ++j) atomicAdd(dst + j, v[j]);
+            }
+          } else {
+            if (vec) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+              for (int j = 0; j < ncols; ++j) dst[j] = v[j];
+            }
+          }
+        } else {
+          bf16* dst = reinterpret_cast<bf16*>(p.C) + off_c;
+          if (full && (p.ldc & 7) == 0) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 u = make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
+                                   pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
+              *reinterpret_cast<uint4*>(dst + j) = u;
+            }
+          } else {
+            for (int j = 0; j < ncols; ++j) dst[j] = __float2bfloat16_rn(v[j]);
+          }
+        }
+      }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar + 8 * as);
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp_idx == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+struct TmapKey {
+  const void* base;
+  uint64_t inner, outer, ld;
+  uint32_t bi, bo;
+  int dev;
+  bool operator==(const TmapKey& o) const {
+    return base == o.base && inner == o.inner && outer == o.outer && ld == o.ld && bi == o.bi &&
+           bo == o.bo && dev == o.dev;
+  }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    size_t h = reinterpret_cast<size_t>(k.base);
+    auto mix = [&h](uint64_t v) { h ^= v + 0x9e3779b97f4a7c15ULL + (h << 6) + (h >> 2); };
+    mix(k.inner); mix(k.outer); mix(k.ld); mix(k.bi); mix(k.bo); mix((uint64_t)k.dev);
+    return h;
+  }
+};
+
+int get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
+             uint32_t bi, uint32_t bo) {
+  static std::mutex mu;
+  static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> cache;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  TmapKey key{base, inner, outer, ld, bi, bo, dev};
+  {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) {
+      *out = it->second;
+      return 0;
+    }
+  }
+  int rc = b200_make_tmap_2d(out, base, inner, outer, ld, bi, bo);
+  if (rc != 0) return rc;
+  std::lock_guard<std::mutex> g(mu);
+  if (cache.size() > 4096) cache.clear();
+  cache.emplace(key, *out);
+  return 0;
+}
+
+struct GemmOverrides {
+  int a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep;  // < 0 => default
+  int force_bn, force_splits;
+};
+
+template <int BN, int STAGES>
+int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid,
+           cudaStream_t stream) {
+  constexpr int smem = STAGES * (A_STAGE_BYTES + BN * BK * 2) + 16 * STAGES + 32 + 16 + 1024;
+  static bool configured[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!configured[dev & 63]) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured[dev & 63] = true;
+  }
+  gemm_tcgen05_kernel<BN, STAGES><<<grid, GEMM_THREADS, smem, stream>>>(tmA, tmB, p);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+              int a_mn, int b_mn, const float* bias, const float* residual, int ldr, int act,
+              int out_fp32, int accumulate, void* aux_out, const void* mask_src, int cfg,
+              const GemmOverrides* ov, void* stream) {
+  B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
+  B200_REQUIRE(!accumulate || out_fp32, "gemm: accumulate needs an fp32 output");
+  B200_REQUIRE(act == 0 || act == 1, "gemm: activation %d not supported (0 none, 1 relu)", act);
+
+  int bn = (cfg & 0x3ff);
+  if (ov && ov->force_bn > 0) bn = ov->force_bn;
+  if (bn == 0) bn = (N >= 4096 && M >= 512) ? 256 : 128;
+  B200_REQUIRE(bn == 128 || bn == 256, "gemm: tile N %d not supported", bn);
+
+  GemmParams p{};
+  p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.ldr = ldr;
+  p.num_m_tiles = ceil_div(M, BM);
+  p.num_n_tiles = ceil_div(N, bn);
+  p.kb_total = ceil_div(K, BK);
+  const int tiles = p.num_m_tiles * p.num_n_tiles;
+  const int sms = b200_num_sms();
+  int splits = 1;
+  const bool plain = (bias == nullptr && residual == nullptr && act == 0 && aux_out == nullptr &&
+                      mask_src == nullptr);
+  if (accumulate && out_fp32 && plain && tiles < sms) {
+    splits = sms / tiles;
+    const int max_splits = p.kb_total / 4 > 0 ? p.kb_total / 4 : 1;
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+  }
+  if (ov && ov->force_splits > 0) splits = ov->force_splits;
+  B200_REQUIRE(splits == 1 || (accumulate && plain), "gemm: split-K needs a plain accumulating epilogue");
+  p.kb_per_split = ceil_div(p.kb_total, splits);
+  p.k_splits = ceil_div(p.kb_total, p.kb_per_split);
+
+  p.idesc = umma_idesc_bf16(BM, bn, a_mn, b_mn);
+  // K-major SW128: 8-row groups 1024 B apart (SBO), LBO unused (1); K advance = 32 B in the row.
+  // MN-major SW128: 64-wide MN groups one TMA box (8192 B) apart (LBO), 8-k groups 1024 B apart (SBO);
+  //                 K advance of 16 = two k groups = 2048 B.
+  uint32_t a_lbo = a_mn ? 8192 : 16, a_sbo = 1024, a_kstep = a_mn ? 2048 : 32;
+  uint32_t b_lbo = b_mn ? 8192 : 16, b_sbo = 1024, b_kstep = b_mn ? 2048 : 32;
+  if (ov) {
+    if (ov->a_lbo >= 0) a_lbo = ov->a_lbo;
+    if (ov->a_sbo >= 0) a_sbo = ov->a_sbo;
+    if (ov->a_kstep >= 0) a_kstep = ov->a_kstep;
+    if (ov->b_lbo >= 0) b_lbo = ov->b_lbo;
+    if (ov->b_sbo >= 0) b_sbo = ov->b_sbo;
+    if (ov->b_kstep >= 0) b_kstep = ov->b_kstep;
+  }
+  p.a_desc_base = umma_smem_desc_base(a_lbo, a_sbo);
+  p.b_desc_base = umma_smem_desc_base(b_lbo, b_sbo);
+  p.a_kstep = a_kstep; p.b_kstep = b_kstep;
+  p.a_mn = a_mn; p.b_mn = b_mn;
+  p.bias = bias; p.residual = residual; p.C = C;
+  p.aux_out = reinterpret_cast<bf16*>(aux_out);
+  p.mask_src = reinterpret_cast<const bf16*>(mask_src);
+  p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate;
+  p.err_word = b200_error_word();
+  B200_REQUIRE(p.err_word != nullptr, "gemm: no CUDA device");
+
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!a_mn) rc = get_tmap(&tmA, A, K, M, lda, BK, BM);
+  else       rc = get_tmap(&tmA, A, M, K, lda, 64, BK);
+  if (rc != 0) return rc;
+  if (!b_mn) rc = get_tmap(&tmB, B, K, N, ldb, BK, bn);
+  else       rc = get_tmap(&tmB, B, N, K, ldb, 64, BK);
+  if (rc != 0) return rc;
+
+  const int total = tiles * p.k_splits;
+  const int grid = total < sms ? total : sms;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (bn == 128) return launch<128, 6>(tmA, tmB, p, grid, st);
+  return launch<256, 4>(tmA, tmB, p, grid, st);
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
+                   int ldc, int a_mn_major, int b_mn_major, const float* bias, const float* residual,
+                   int ldr, int act, int out_fp32, int accumulate, void* aux_out,
+                   const void* mask_src, int cfg, void* stream) {
+  return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, bias, residual, ldr, act,
+                   out_fp32, accumulate, aux_out, mask_src, cfg, nullptr, stream);
+}
+
+// Bring-up / regression entry: same GEMM with the UMMA descriptor fields overridable, so one GPU
+// session can check alternative encodings (values < 0 keep the defaults).  fp32 output, no epilogue.
+int b200_gemm_debug(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
+                    int ldc, int a_mn_major, int b_mn_major, int a_lbo, int a_sbo, int a_kstep,
+                    int b_lbo, int b_sbo, int b_kstep, int force_bn, int force_splits, void* stream) {
+  GemmOverrides ov{a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep, force_bn, force_splits};
+  return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, nullptr, nullptr, 0, 0, 1,
+                   force_splits > 1 ? 1 : 0, nullptr, nullptr, 0, &ov, stream);
+}
+
+}  // extern "C"

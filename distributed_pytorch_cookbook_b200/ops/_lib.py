@@ -32,14 +32,15 @@ _SIGS = {
     "b200_adamw": [P, P, P, P, P, L, P, Fl, Fl, Fl, Fl, P],
     "b200_adamw_tick": [P, P],
     "b200_cast_bf16": [P, P, L, P],
-    "b200_relu_bwd": [P, P, P, P, I, I, P],
+    "b200_relu_bwd": [P, P, P, P, I, I, I, P],
     "b200_colsum_bf16": [P, P, I, I, I, P],
     "b200_count_valid": [P, P, I, L, P],
-    "b200_ce_fwd_bwd": [P, P, P, P, P, I, I, I, L, I, P],
+    "b200_device_error": [P, I],
+    "b200_ce_fwd_bwd": [P, P, P, I, I, I, I, I, Fl, P],
     "b200_gemm_bf16": [P, P, P, I, I, I, I, I, I, I, I, P, P, I, I, I, I, P, P, I, P],
-    "b200_gemm_debug": [P, P, P, I, I, I, I, I, I, I, I, I, I, I, I, I, P],
+    "b200_gemm_debug": [P, P, P] + [I] * 16 + [P],
     "b200_attn_fwd": [P, P, P, I, I, I, I, Fl, P, P],
-    "b200_attn_bwd": [P, P, P, P, P, P, I, I, I, I, Fl, P, P],
+    "b200_attn_bwd": [P, P, P, P, P, P, P, I, I, I, I, Fl, P, P],
     "b200_allreduce": [P, P, P, I, I, L, Fl, I, I, P, P],
     "b200_rs_adamw": [P, P, I, I, L, Fl, P, P, P, P, P, Fl, Fl, Fl, Fl, I, P, P],
     "b200_ag_gemm_bf16": [P, P, P, P, I, I, I, I, I, P, I, I, P, P],

@@ -86,7 +86,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K:
 # ----------------------------------------------------------------------------------------
 class _Linear(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, residual, act, out_fp32, params):
+    def forward(ctx, x, weight, bias, residual, act, out_fp32, params, grad_on):
         lead = x.shape[:-1]
         x2 = _as_bf16_2d(x)
         M, K = x2.shape
@@ -94,7 +94,7 @@ class _Linear(torch.autograd.Function):
         N = wb.shape[0]
         out = torch.empty((M, N), dtype=torch.float32 if out_fp32 else BF16, device=x.device)
         res2 = residual.reshape(M, N) if residual is not None else None
-        need_aux = act != 0 and residual is not None and torch.is_grad_enabled()
+        need_aux = act != 0 and residual is not None and grad_on
         aux = torch.empty((M, N), dtype=BF16, device=x.device) if need_aux else None
         gemm(x2, wb, out, M, N, K, bias=bias, residual=res2, act=act, aux_out=aux)
         ctx.act, ctx.params, ctx.has_res = act, params, residual is not None
@@ -134,12 +134,12 @@ class _Linear(torch.autograd.Function):
             gw = grad_of(weight)
             gemm(dz, x2, gw, N, K, M, a_mn_major=True, b_mn_major=True, accumulate=True)  # dW += dZ^T . X
         _notify(weight, bias)
-        return dx, None, None, dres, None, None, None
+        return dx, None, None, dres, None, None, None, None
 
 
 def linear(x, weight, bias=None, activation: Optional[str] = None, residual=None, out_fp32=False):
     act = {None: 0, "relu": 1}[activation]
-    return _Linear.apply(x, weight, bias, residual, act, out_fp32, (weight, bias))
+    return _Linear.apply(x, weight, bias, residual, act, out_fp32, (weight, bias), torch.is_grad_enabled())
 
 
 # ----------------------------------------------------------------------------------------
@@ -319,13 +319,22 @@ class _Attention(torch.autograd.Function):
         if dout.dtype != BF16:
             dout = dout.to(BF16)
         dqkv = torch.empty_like(qkv)
+        # scratch: delta = rowsum(dO * O) and the fp32 dQ accumulator reduced across key tiles
         delta = torch.empty((N, heads, S), dtype=torch.float32, device=qkv.device)
+        dq_acc = torch.empty((N, S, heads * head_dim), dtype=torch.float32, device=qkv.device)
         call("b200_attn_bwd", qkv.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(),
-             dqkv.data_ptr(), delta.data_ptr(), N, S, heads, head_dim, float(scale), ptr(km), stream())
+             dqkv.data_ptr(), delta.data_ptr(), dq_acc.data_ptr(), N, S, heads, head_dim, float(scale),
+             ptr(km), stream())
         return dqkv, None, None, None, None
 
 
 def attention(qkv, heads, head_dim, scale, key_mask=None):
+    if not _lib.has("b200_attn_fwd"):
+        # bring-up only: the library was built without csrc/attention.cu
+        N, S, _ = qkv.shape
+        q, k, v = (t.reshape(N, S, heads, head_dim).transpose(1, 2) for t in qkv.chunk(3, dim=-1))
+        from . import attention_reference
+        return attention_reference(q, k, v, scale, key_mask).transpose(1, 2).reshape(N, S, heads * head_dim)
     return _Attention.apply(qkv, heads, head_dim, scale, key_mask)
 
 
@@ -342,7 +351,7 @@ class _LMHeadCE(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, x, weight, targets, ignore_index, grad_scale, params):
+    def forward(ctx, x, weight, targets, ignore_index, grad_scale, params, grad_on):
         x2 = _as_bf16_2d(x)
         M, D = x2.shape
         wb = bf16_of(weight)
@@ -352,7 +361,7 @@ class _LMHeadCE(torch.autograd.Function):
         dev = x.device
         stats = torch.zeros(4, dtype=torch.float32, device=dev)  # n_valid, loss_sum, n_correct
         call("b200_count_valid", t.data_ptr(), stats.data_ptr(), ignore_index, M, stream())
-        want_grad = torch.is_grad_enabled() and (x.requires_grad or weight.requires_grad)
+        want_grad = grad_on and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1])
         rows = min(_LM_CHUNK_ROWS, M)
         logits = torch.empty((rows, ld), dtype=BF16, device=dev)
         dx = torch.empty((M, D), dtype=BF16, device=dev) if want_grad else None
@@ -379,13 +388,14 @@ class _LMHeadCE(torch.autograd.Function):
     def backward(ctx, dloss, _dstats):
         (dx,) = ctx.saved_tensors
         if dx is None:
-            return None, None, None, None, None, None
+            return None, None, None, None, None, None, None
         dx = dx.view(ctx.x_shape)
         if ctx.in_dtype != BF16:
             dx = dx.to(ctx.in_dtype)
-        return dx, None, None, None, None, None
+        return dx, None, None, None, None, None, None
 
 
 def lmhead_cross_entropy(x, weight, targets, ignore_index=-100, grad_scale: float = 1.0):
-    loss, stats = _LMHeadCE.apply(x, weight, targets, ignore_index, grad_scale, (weight,))
+    loss, stats = _LMHeadCE.apply(x, weight, targets, ignore_index, grad_scale, (weight,),
+                                  torch.is_grad_enabled())
     return loss, stats[0], stats[2]

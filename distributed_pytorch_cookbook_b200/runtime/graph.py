@@ -21,6 +21,7 @@ class GraphedStep:
         self.static_in: List[torch.Tensor] = []
         self.static_out = None
         self.side = None
+        self.native_calls_per_replay = 0
 
     def __call__(self, *tensors: torch.Tensor):
         if self.graph is None:
@@ -35,9 +36,12 @@ class GraphedStep:
                 return out
             self.static_in = [t.clone() for t in tensors]
             torch.cuda.synchronize()
+            from ..ops import _lib
+            n0 = _lib.launch_count()
             self.graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self.graph, stream=self.side):
                 self.static_out = self.fn(*self.static_in)
+            self.native_calls_per_replay = _lib.launch_count() - n0
         for s, t in zip(self.static_in, tensors):
             s.copy_(t, non_blocking=True)
         self.graph.replay()

@@ -239,6 +239,10 @@ class SingleStrategy:
     def all_reduce_mean(self, t):
         return t
 
+    def launches_per_step(self):
+        """native entry-point calls captured in one CUDA-graph replay (None before capture)."""
+        return self._graphed.native_calls_per_replay if (self._graphed and self._graphed.graph) else None
+
     def generation_model(self):
         return self.model
 

@@ -1,0 +1,78 @@
+/* C ABI of libb200gpt.so - hand-written sm_100a kernels for GPT training on B200.
+ *
+ * Conventions: every function returns 0 on success, a negative code on failure
+ * (b200_last_error() has the message); pointers are device pointers unless stated; `stream`
+ * is a cudaStream_t; bf16 tensors are passed as void*.  No entry point allocates device
+ * memory, so all of them may be captured in a CUDA graph once warmed up.
+ *
+ * Each declaration cites the reference call site it serves (/root/reference).
+ */
+#ifndef B200GPT_H_
+#define B200GPT_H_
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* b200_last_error(void);
+/* sticky device-side error word (bounded waits that timed out); host-synchronous */
+int b200_device_error(int* out, int clear);
+int b200_smoke(void* stream);
+
+/* token + position embedding, fp32 out [n_tokens, dim]  (models/gpt.py:180-185) */
+int b200_embedding_fwd(const int64_t* ids, const int64_t* pos, const float* tok_w, const float* pos_w,
+                       float* out, int n_tokens, int dim, int vocab, int max_pos, void* stream);
+/* scatter-add of dout into both tables (accumulates)  (autograd of models/gpt.py:185) */
+int b200_embedding_bwd(const int64_t* ids, const int64_t* pos, const float* dout, float* dtok,
+                       float* dpos, int n_tokens, int dim, int vocab, int max_pos, void* stream);
+
+/* LayerNorm fp32 -> bf16, saves mean/rstd  (models/gpt.py:119,122,217) */
+int b200_layernorm_fwd(const float* x, const float* gamma, const float* beta, void* y_bf16, float* mean,
+                       float* rstd, int rows, int dim, float eps, void* stream);
+/* dx = LN'(dy) [+ dres]; optional bf16 copy of dx; dgamma/dbeta accumulate */
+int b200_layernorm_bwd(const void* dy_bf16, const float* x, const float* gamma, const float* mean,
+                       const float* rstd, const float* dres, float* dx, void* dx_bf16, float* dgamma,
+                       float* dbeta, int rows, int dim, void* stream);
+
+/* fused AdamW over a flat arena; hyper = {lr, step, ..} in device memory  (main-single.py:42,99-101) */
+int b200_adamw(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n,
+               const float* hyper, float beta1, float beta2, float eps, float wd, void* stream);
+int b200_adamw_tick(float* hyper, void* stream);
+int b200_cast_bf16(const float* in, void* out_bf16, int64_t n, void* stream);
+
+/* dz = dy * (y_act > 0) as bf16 (y_act NULL: plain cast); dbias += colsum(dz)  (models/gpt.py:35,38) */
+int b200_relu_bwd(const void* dy, const void* y_act_bf16, void* dz_bf16, float* dbias, int rows, int cols,
+                  int dy_is_fp32, void* stream);
+int b200_colsum_bf16(const void* x_bf16, float* out_accum, int rows, int cols, int ld, void* stream);
+
+/* cross entropy over a bf16 logits chunk, in place  (main-single.py:95-96,127-131)
+ * stats[0] = n_valid (input, from b200_count_valid), stats[1] += loss sum, stats[2] += #correct */
+int b200_count_valid(const int64_t* targets, float* stats, int ignore_index, int64_t n, void* stream);
+int b200_ce_fwd_bwd(void* logits_bf16, const int64_t* targets, float* stats, int rows, int vocab, int ld,
+                    int ignore_index, int write_grad, float grad_scale, void* stream);
+
+/* C[M,N] (+)= A[M,K] . B[N,K]^T on tcgen05 with a fused epilogue  (models/gpt.py:29-38,60-64,102,219)
+ * a/b_mn_major: 0 = operand stored [rows][K]; 1 = stored [K][rows] (dgrad / wgrad, no transposes).
+ * epilogue order: +bias -> act(1=ReLU) -> aux_out(bf16) -> *(mask_src>0) -> +residual(fp32) -> store. */
+int b200_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
+                   int ldc, int a_mn_major, int b_mn_major, const float* bias, const float* residual,
+                   int ldr, int act, int out_fp32, int accumulate, void* aux_out_bf16,
+                   const void* mask_src_bf16, int cfg, void* stream);
+int b200_gemm_debug(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
+                    int ldc, int a_mn_major, int b_mn_major, int a_lbo, int a_sbo, int a_kstep,
+                    int b_lbo, int b_sbo, int b_kstep, int force_bn, int force_splits, void* stream);
+
+/* causal flash attention over packed qkv[B,T,3,H,D] (D in 32/64/128)  (models/gpt.py:75-100)
+ * key_mask: optional uint8 [B,T], 1 = padding key.  lse = log-sum-exp of the scaled scores. */
+int b200_attn_fwd(const void* qkv_bf16, void* out_bf16, float* lse, int B, int T, int H, int D, float scale,
+                  const void* key_mask, void* stream);
+/* scratch (caller-provided, overwritten): delta fp32 [B,H,T], dq_acc fp32 [B,T,H*D] */
+int b200_attn_bwd(const void* qkv_bf16, const void* out_bf16, const void* dout_bf16, const float* lse,
+                  void* dqkv_bf16, float* delta, float* dq_acc, int B, int T, int H, int D, float scale,
+                  const void* key_mask, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200GPT_H_ */

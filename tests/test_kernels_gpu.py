@@ -1,0 +1,295 @@
+"""T3: every sm_100a kernel against a plain PyTorch fp32 reference of the same op."""
+import ctypes
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from distributed_pytorch_cookbook_b200.ops import _lib, native
+
+pytestmark = pytest.mark.gpu
+BF16 = torch.bfloat16
+
+
+def _dev_err():
+    v = ctypes.c_int(0)
+    _lib.call("b200_device_error", ctypes.addressof(v), 1)
+    return v.value
+
+
+@pytest.fixture(autouse=True)
+def _need_lib():
+    assert _lib.available(), f"native library not loaded: {_lib.load_error()}"
+    yield
+    torch.cuda.synchronize()
+    assert _dev_err() == 0
+
+
+def test_smoke_launch():
+    _lib.call("b200_smoke", _lib.stream())
+
+
+@pytest.mark.parametrize("n,dim,vocab", [(16320, 256, 50257), (77, 64, 1000)])
+def test_embedding_fwd_bwd(n, dim, vocab):
+    torch.manual_seed(0)
+    ids = torch.randint(0, vocab, (n,), device="cuda")
+    pos = torch.arange(n, device="cuda") % 255
+    tok = torch.randn(vocab, dim, device="cuda")
+    pw = torch.randn(256, dim, device="cuda")
+    out = torch.empty(n, dim, device="cuda")
+    _lib.call("b200_embedding_fwd", ids.data_ptr(), pos.data_ptr(), tok.data_ptr(), pw.data_ptr(),
+              out.data_ptr(), n, dim, vocab, 256, _lib.stream())
+    assert torch.equal(out, tok[ids] + pw[pos])
+    dout = torch.randn(n, dim, device="cuda")
+    dtok, dpos = torch.zeros_like(tok), torch.zeros_like(pw)
+    _lib.call("b200_embedding_bwd", ids.data_ptr(), pos.data_ptr(), dout.data_ptr(), dtok.data_ptr(),
+              dpos.data_ptr(), n, dim, vocab, 256, _lib.stream())
+    rt = torch.zeros_like(tok).index_add_(0, ids, dout)
+    rp = torch.zeros_like(pw).index_add_(0, pos, dout)
+    assert torch.allclose(dtok, rt, atol=1e-4, rtol=1e-4)
+    assert torch.allclose(dpos, rp, atol=1e-3, rtol=1e-4)
+
+
+@pytest.mark.parametrize("rows,dim", [(16320, 256), (513, 1024), (100, 2048), (33, 192)])
+def test_layernorm_fwd_bwd(rows, dim):
+    torch.manual_seed(0)
+    x = torch.randn(rows, dim, device="cuda") * 2 + 0.5
+    g = torch.randn(dim, device="cuda")
+    b = torch.randn(dim, device="cuda")
+    y = torch.empty(rows, dim, device="cuda", dtype=BF16)
+    mean = torch.empty(rows, device="cuda")
+    rstd = torch.empty(rows, device="cuda")
+    _lib.call("b200_layernorm_fwd", x.data_ptr(), g.data_ptr(), b.data_ptr(), y.data_ptr(),
+              mean.data_ptr(), rstd.data_ptr(), rows, dim, 1e-5, _lib.stream())
+    xr = x.clone().requires_grad_(True)
+    gr, br = g.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    ref = F.layer_norm(xr, (dim,), gr, br, 1e-5)
+    assert torch.allclose(y.float(), ref, atol=3e-2, rtol=2e-2)
+    dy = torch.randn(rows, dim, device="cuda").to(BF16)
+    dres = torch.randn(rows, dim, device="cuda")
+    ref.backward(dy.float())
+    dx = torch.empty(rows, dim, device="cuda")
+    dxb = torch.empty(rows, dim, device="cuda", dtype=BF16)
+    dg, db = torch.zeros(dim, device="cuda"), torch.zeros(dim, device="cuda")
+    _lib.call("b200_layernorm_bwd", dy.data_ptr(), x.data_ptr(), g.data_ptr(), mean.data_ptr(),
+              rstd.data_ptr(), dres.data_ptr(), dx.data_ptr(), dxb.data_ptr(), dg.data_ptr(),
+              db.data_ptr(), rows, dim, _lib.stream())
+    assert torch.allclose(dx, xr.grad + dres, atol=2e-3, rtol=1e-3)
+    assert torch.allclose(dxb.float(), dx, atol=5e-2, rtol=2e-2)
+    assert torch.allclose(dg, gr.grad, atol=2e-2 * rows ** 0.5, rtol=1e-3)
+    assert torch.allclose(db, br.grad, atol=2e-2 * rows ** 0.5, rtol=1e-3)
+
+
+def test_adamw_matches_torch():
+    torch.manual_seed(0)
+    n = 1_000_003
+    p = torch.randn(n, device="cuda")
+    ref_p = p.clone().requires_grad_(True)
+    opt = torch.optim.AdamW([ref_p], lr=1e-3)
+    m, v = torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    pb = torch.empty(n, device="cuda", dtype=BF16)
+    hyper = torch.tensor([1e-3, 0, 0, 0], device="cuda")
+    for _ in range(3):
+        g = torch.randn(n, device="cuda")
+        ref_p.grad = g.clone()
+        opt.step()
+        _lib.call("b200_adamw_tick", hyper.data_ptr(), _lib.stream())
+        _lib.call("b200_adamw", p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), pb.data_ptr(), n,
+                  hyper.data_ptr(), 0.9, 0.999, 1e-8, 0.01, _lib.stream())
+    assert torch.allclose(p, ref_p.detach(), atol=1e-6, rtol=1e-5)
+    assert torch.equal(pb, p.to(BF16))
+
+
+@pytest.mark.parametrize("fp32", [True, False])
+def test_relu_bwd_and_bias_grad(fp32):
+    torch.manual_seed(0)
+    rows, cols = 1000, 1024
+    dy = torch.randn(rows, cols, device="cuda")
+    if not fp32:
+        dy = dy.to(BF16)
+    y = torch.randn(rows, cols, device="cuda").relu().to(BF16)
+    dz = torch.empty(rows, cols, device="cuda", dtype=BF16)
+    dbias = torch.zeros(cols, device="cuda")
+    _lib.call("b200_relu_bwd", dy.data_ptr(), y.data_ptr(), dz.data_ptr(), dbias.data_ptr(), rows, cols,
+              int(fp32), _lib.stream())
+    ref = dy.float() * (y.float() > 0)
+    assert torch.allclose(dz.float(), ref, atol=2e-2, rtol=1e-2)
+    assert torch.allclose(dbias, ref.sum(0), atol=5e-2, rtol=1e-2)
+
+
+@pytest.mark.parametrize("rows,vocab", [(64, 50257), (33, 1000)])
+def test_cross_entropy_fwd_bwd(rows, vocab):
+    torch.manual_seed(0)
+    ld = (vocab + 127) // 128 * 128
+    logits = torch.zeros(rows, ld, device="cuda", dtype=BF16)
+    logits[:, :vocab] = (torch.randn(rows, vocab, device="cuda") * 3).to(BF16)
+    tgt = torch.randint(0, vocab, (rows,), device="cuda")
+    tgt[::7] = -100
+    tgt[1] = logits[1, :vocab].float().argmax()
+    ref_in = logits[:, :vocab].float().clone().requires_grad_(True)
+    ref = F.cross_entropy(ref_in, tgt, ignore_index=-100)
+    ref.backward()
+    stats = torch.zeros(4, device="cuda")
+    _lib.call("b200_count_valid", tgt.data_ptr(), stats.data_ptr(), -100, rows, _lib.stream())
+    _lib.call("b200_ce_fwd_bwd", logits.data_ptr(), tgt.data_ptr(), stats.data_ptr(), rows, vocab, ld,
+              -100, 1, 1.0, _lib.stream())
+    n_valid = int((tgt != -100).sum())
+    assert int(stats[0]) == n_valid
+    assert abs(float(stats[1]) / n_valid - float(ref)) < 2e-3
+    valid = tgt != -100
+    want_correct = int((ref_in.argmax(-1)[valid] == tgt[valid]).sum())
+    assert int(stats[2]) == want_correct
+    assert torch.allclose(logits[:, :vocab].float(), ref_in.grad, atol=2e-3 / n_valid + 1e-4, rtol=3e-2)
+    assert float(logits[:, vocab:].abs().max()) == 0.0 if ld > vocab else True
+
+
+GEMM_SHAPES = [(128, 128, 64), (16320, 768, 256), (1000, 1024, 1024), (300, 50257, 256), (16320, 256, 1024)]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_gemm_forward_epilogues(M, N, K):
+    torch.manual_seed(0)
+    A = torch.randn(M, K, device="cuda").to(BF16)
+    W = (torch.randn(N, K, device="cuda") / K ** 0.5).to(BF16)
+    bias = torch.randn(N, device="cuda")
+    res = torch.randn(M, N, device="cuda")
+    ld = (N + 7) // 8 * 8
+    ref = A.float() @ W.float().t()
+    out = torch.empty(M, ld, device="cuda", dtype=BF16)
+    native.gemm(A, W, out, M, N, K)
+    assert torch.allclose(out[:, :N].float(), ref, atol=3e-2, rtol=2e-2)
+    if N % 8 == 0:
+        out32 = torch.empty(M, N, device="cuda")
+        aux = torch.empty(M, N, device="cuda", dtype=BF16)
+        native.gemm(A, W, out32, M, N, K, bias=bias, residual=res, act=1, aux_out=aux)
+        r2 = (ref + bias).relu()
+        assert torch.allclose(aux.float(), r2, atol=3e-2, rtol=2e-2)
+        assert torch.allclose(out32, r2 + res, atol=3e-2, rtol=2e-2)
+
+
+@pytest.mark.parametrize("M,N,K", [(16320, 256, 768), (1024, 256, 50257), (500, 1024, 256)])
+def test_gemm_dgrad_mn_major_b(M, N, K):
+    """dX[M,N] = dZ[M,K] . W[K,N]  (W stored [K,N]: MN-major B)."""
+    torch.manual_seed(0)
+    ldk = (K + 7) // 8 * 8                       # TMA needs 16-byte row strides
+    dz = torch.zeros(M, ldk, device="cuda", dtype=BF16)
+    dz[:, :K] = torch.randn(M, K, device="cuda").to(BF16)
+    W = (torch.randn(K, N, device="cuda") / K ** 0.5).to(BF16)
+    mask = torch.randn(M, N, device="cuda").to(BF16)
+    ref = dz[:, :K].float() @ W.float()
+    out = torch.empty(M, N, device="cuda", dtype=BF16)
+    native.gemm(dz, W, out, M, N, K, b_mn_major=True)
+    assert torch.allclose(out.float(), ref, atol=3e-2, rtol=2e-2)
+    native.gemm(dz, W, out, M, N, K, b_mn_major=True, mask_src=mask)
+    assert torch.allclose(out.float(), ref * (mask.float() > 0), atol=3e-2, rtol=2e-2)
+
+
+@pytest.mark.parametrize("Mtok,N,K", [(16320, 1024, 256), (16320, 256, 256), (1024, 50257, 256), (777 * 8, 768, 256)])
+def test_gemm_wgrad_mn_major_both_accumulate(Mtok, N, K):
+    """dW[N,K] += dZ[Mtok,N]^T . X[Mtok,K] with split-K atomics."""
+    torch.manual_seed(0)
+    ldz = (N + 7) // 8 * 8
+    dzf = torch.zeros(Mtok, ldz, device="cuda")
+    dzf[:, :N] = torch.randn(Mtok, N, device="cuda") / Mtok ** 0.5
+    dz = dzf.to(BF16)
+    X = torch.randn(Mtok, K, device="cuda").to(BF16)
+    g0 = torch.randn(N, K, device="cuda")
+    g = g0.clone()
+    native.gemm(dz, X, g, N, K, Mtok, a_mn_major=True, b_mn_major=True, accumulate=True)
+    ref = g0 + dz[:, :N].float().t() @ X.float()
+    assert torch.allclose(g, ref, atol=3e-2, rtol=2e-2)
+
+
+def _tiny_model(dev, layers=2, dim=256, heads=8, head_dim=32, vocab=50257, seq=256):
+    from distributed_pytorch_cookbook_b200 import TransformerDecoderLM
+    torch.manual_seed(0)
+    return TransformerDecoderLM(dim=dim, head_dim=head_dim, heads=heads, num_layers=layers,
+                                vocab_size=vocab, max_position_embeddings=seq).to(dev)
+
+
+@pytest.mark.parametrize("B,T,vocab", [(4, 255, 50257), (3, 100, 1000)])
+def test_model_loss_and_grads_match_reference_math(B, T, vocab):
+    """Whole model through the native kernels vs the same model through PyTorch ops
+    (bf16 autocast) and vs fp32: loss and every parameter gradient."""
+    from distributed_pytorch_cookbook_b200 import ops
+    dev = torch.device("cuda")
+    model = _tiny_model(dev, vocab=vocab)
+    ids = torch.randint(0, vocab, (B, T), device=dev)
+    pos = torch.arange(T, device=dev).unsqueeze(0).repeat(B, 1)
+    tgt = torch.randint(0, vocab, (B, T), device=dev)
+    tgt[0, :5] = -100
+    with torch.autocast("cuda", dtype=BF16):
+        loss, n_valid, n_correct = model.loss(ids, pos, tgt)
+    loss.backward()
+    got = {n: p.grad.clone() for n, p in model.named_parameters()}
+    model.zero_grad(set_to_none=True)
+    with ops.force_reference():                      # fp32 PyTorch math
+        loss32, nv32, _ = model.loss(ids, pos, tgt)
+    loss32.backward()
+    ref32 = {n: p.grad.clone() for n, p in model.named_parameters()}
+    model.zero_grad(set_to_none=True)
+    with ops.force_reference(), torch.autocast("cuda", dtype=BF16):   # PyTorch bf16 autocast math
+        loss16, _, _ = model.loss(ids, pos, tgt)
+    loss16.backward()
+    ref16 = {n: p.grad.clone() for n, p in model.named_parameters()}
+    assert int(n_valid) == int(nv32) == B * T - 5
+    assert abs(float(loss) - float(loss32)) < 3e-2, (float(loss), float(loss32))
+
+    def rel(a, b):
+        return ((a - b).norm() / b.norm().clamp(min=1e-12)).item()
+
+    # our bf16 kernels must be as close to the fp32 oracle as PyTorch's own bf16 path is
+    worst = {}
+    for n in got:
+        ours, torch16 = rel(got[n], ref32[n]), rel(ref16[n], ref32[n])
+        if ours > max(2.0 * torch16, 0.02):
+            worst[n] = (ours, torch16)
+    assert not worst, worst
+
+
+def test_training_reduces_loss_with_fused_adamw_and_graph():
+    from distributed_pytorch_cookbook_b200.optim import build_optimizer
+    from distributed_pytorch_cookbook_b200.runtime import GraphedStep
+    dev = torch.device("cuda")
+    model = _tiny_model(dev, vocab=2048)
+    opt = build_optimizer(model, lr=1e-3, device=dev)
+    ids = torch.randint(0, 2048, (8, 128), device=dev)
+    pos = torch.arange(128, device=dev).unsqueeze(0).repeat(8, 1)
+
+    def step(i, p, t):
+        opt.zero_grad()
+        with torch.autocast("cuda", dtype=BF16):
+            loss, _, _ = model.loss(i, p, t)
+        loss.backward()
+        opt.step()
+        return loss.detach()
+
+    g = GraphedStep(step, warmup=3)
+    losses = [float(g(ids, pos, ids)) for _ in range(30)]
+    assert g.graph is not None
+    assert losses[-1] < losses[0] - 1.0, losses
+
+
+@pytest.mark.parametrize("B,T,H,D,masked", [(2, 255, 8, 32, False), (2, 100, 2, 64, True), (1, 300, 2, 128, False),
+                                            (64, 255, 8, 32, False), (1, 1023, 2, 128, True)])
+def test_flash_attention_fwd_bwd(B, T, H, D, masked):
+    from distributed_pytorch_cookbook_b200 import ops
+    torch.manual_seed(0)
+    qkv = (torch.randn(B, T, 3 * H * D, device="cuda") * 0.7).to(BF16).requires_grad_(True)
+    mask = None
+    if masked:
+        mask = torch.zeros(B, T, dtype=torch.bool, device="cuda")
+        mask[0, T - 17:] = True
+    scale = D ** -0.5
+    out = native.attention(qkv, H, D, scale, mask)
+    dout = torch.randn_like(out)
+    out.backward(dout)
+    got_dqkv = qkv.grad.clone()
+    q32 = qkv.detach().float().requires_grad_(True)
+    q, k, v = (t.reshape(B, T, H, D).transpose(1, 2) for t in q32.chunk(3, dim=-1))
+    ref = ops.attention_reference(q, k, v, scale, mask).transpose(1, 2).reshape(B, T, H * D)
+    ref.backward(dout.float())
+    valid = torch.ones(B, T, dtype=torch.bool, device="cuda") if mask is None else ~mask
+    assert torch.allclose(out.float()[valid], ref[valid], atol=3e-2, rtol=3e-2)
+    gd = (got_dqkv.float() - q32.grad)[valid]
+    assert gd.abs().max().item() <= 0.05 * q32.grad.abs().max().item() + 2e-2, gd.abs().max().item()
