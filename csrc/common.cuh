@@ -149,6 +149,22 @@ __device__ __forceinline__ void tma_load_3d(uint32_t smem_dst, const void* tmap,
       : "memory");
 }
 
+// 2D tiled store smem -> global (bulk async group); out-of-bounds parts of the box are clipped
+__device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t smem_src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_src), "r"(c0), "r"(c1)
+               : "memory");
+}
+// same, but global += smem (element-wise add done by the TMA unit; used for split-K / accumulate)
+__device__ __forceinline__ void tma_reduce_add_2d(const void* tmap, uint32_t smem_src, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_src), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // ----------------------------------------------------------------------------------------
 // tcgen05 / TMEM
 // ----------------------------------------------------------------------------------------
@@ -270,7 +286,7 @@ __host__ __device__ inline uint32_t umma_idesc_bf16(int M, int N, int a_mn_major
 // ----------------------------------------------------------------------------------------
 // 2D bf16 tensor [outer][inner] with row stride ld_elems; box = box_inner x box_outer; 128B swizzle.
 int b200_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
-                      uint64_t ld_elems, uint32_t box_inner, uint32_t box_outer);
+                      uint64_t ld_elems, uint32_t box_inner, uint32_t box_outer, int elem_bytes = 2);
 int b200_make_tmap_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t d1, uint64_t d2,
                       uint64_t stride1_elems, uint64_t stride2_elems, uint32_t b0, uint32_t b1,
                       uint32_t b2);

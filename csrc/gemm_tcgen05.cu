@@ -44,10 +44,11 @@ struct GemmParams {
   bf16* aux_out;
   const bf16* mask_src;
   int act, out_fp32, accumulate;
+  int tma_store;  // 1: epilogue stages tiles in smem and writes them with TMA (coalesced, clipped)
   int* err_word;
 };
 
-enum : int { ERR_GEMM_PRODUCER = 101, ERR_GEMM_MMA = 102, ERR_GEMM_EPILOGUE = 103 };
+enum : int { ERR_GEMM_PRODUCER = 101, ERR_GEMM_MMA = 102, ERR_GEMM_EPILOGUE = 103, ERR_GEMM_SMEM_ALIGN = 104 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c),
@@ -55,26 +56,35 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
                : "memory");
 }
 
-template <int BN, int STAGES>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+constexpr int STAGING_BYTES = 4 * 4096;  // one 32-row x 128-byte swizzled tile per epilogue warp
+
+template <int BN, int STAGES, int MIN_CTAS>
+__global__ void __launch_bounds__(GEMM_THREADS, MIN_CTAS)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const GemmParams p) {
+                    const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
   constexpr int B_STAGE_BYTES = BN * BK * 2;
   constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   constexpr uint32_t TMEM_COLS = 2 * BN;
 
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  // 128B-swizzled TMA/UMMA tiles need 1024-byte alignment; the dynamic smem window of a kernel
+  // without static smem starts 1024-aligned (checked below, reported through the error word).
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t smem_base = smem_u32(smem_raw);
   const uint32_t sA = smem_base;
   const uint32_t sB = smem_base + STAGES * A_STAGE_BYTES;
-  const uint32_t bars = smem_base + STAGES * STAGE_BYTES;  // 8-byte mbarriers
+  const uint32_t sStage = smem_base + STAGES * STAGE_BYTES;
+  const uint32_t bars = sStage + STAGING_BYTES;  // 8-byte mbarriers
   const uint32_t full_bar = bars;
   const uint32_t empty_bar = bars + 8 * STAGES;
   const uint32_t tfull_bar = bars + 16 * STAGES;
   const uint32_t tempty_bar = tfull_bar + 16;
-  uint8_t* gen = smem_raw + (smem_base - smem_u32(smem_raw));
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + STAGES * STAGE_BYTES + 16 * STAGES + 32);
+  uint32_t* tmem_ptr_smem =
+      reinterpret_cast<uint32_t*>(smem_raw + STAGES * STAGE_BYTES + STAGING_BYTES + 16 * STAGES + 32);
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+  if ((smem_base & 1023u) != 0u) {
+    if (threadIdx.x == 0) atomicCAS(p.err_word, 0, ERR_GEMM_SMEM_ALIGN);
+    return;
+  }
 
   const int warp_idx = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -92,6 +102,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     fence_barrier_init();
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if (p.tma_store) tma_prefetch_desc(&tmC);
   }
   if (warp_idx == 1) {
     tmem_alloc(smem_u32(tmem_ptr_smem), TMEM_COLS);
@@ -182,6 +193,165 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // ===================== epilogue (4 warps) =====================
     const int q = warp_idx & 3;  // TMEM lane quarter this warp may access
     int lt = 0;
+    if (p.tma_store) {
+      // TMEM -> registers -> (bias / ReLU / mask / residual) -> 128B-swizzled smem tile -> TMA store
+      // (or TMA reduce-add).  Global traffic is whole 128-byte rows, M/N tails are clipped by the
+      // tensor map, and the residual / mask operands of chunk c+1 are prefetched under chunk c.
+      const uint32_t stage_buf = sStage + q * 4096;
+      const uint32_t my_row = stage_buf + lane * 128;
+      const int swz = lane & 7;
+      const bool has_res = p.residual != nullptr, has_mask = p.mask_src != nullptr;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+        const int t2 = tile / p.k_splits;
+        const int m0 = (t2 % p.num_m_tiles) * BM;
+        const int n0 = (t2 / p.num_m_tiles) * BN;
+        const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
+        const int row = m0 + q * 32 + lane;
+        const bool row_ok = row < p.M;
+        const float* res_row = has_res ? p.residual + static_cast<size_t>(row_ok ? row : 0) * p.ldr : nullptr;
+        const bf16* msk_row = has_mask ? p.mask_src + static_cast<size_t>(row_ok ? row : 0) * p.ldc : nullptr;
+        float4 nres[8];
+        uint4 nmsk[4];
+        float nbias = 0.f;
+        // prefetch the epilogue operands of chunk 0 while the MMAs of this tile are still running
+        {
+          const int col0 = n0;
+          const bool full = (p.N - col0) >= 32;
+          if (p.bias != nullptr) nbias = (col0 + lane < p.N) ? __ldg(p.bias + col0 + lane) : 0.f;
+          if (has_res && row_ok && full && (p.ldr & 3) == 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) nres[j] = __ldg(reinterpret_cast<const float4*>(res_row + col0) + j);
+          }
+          if (has_mask && row_ok && full && (p.ldc & 7) == 0) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) nmsk[j] = __ldg(reinterpret_cast<const uint4*>(msk_row + col0) + j);
+          }
+        }
+        if (!mbar_wait(tfull_bar + 8 * as, aph, abort_flag, p.err_word, ERR_GEMM_EPILOGUE)) break;
+        tcgen05_fence_after();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t r[32];
+          __syncwarp();
+          tmem_ld_32x32b_x32(taddr + c * 32, r);
+          // current operands <- prefetched; issue the prefetch of the next chunk
+          float4 res[8];
+          uint4 msk[4];
+          const float biasv = nbias;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) res[j] = nres[j];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) msk[j] = nmsk[j];
+          const int col0 = n0 + c * 32;
+          const int ncols = min(32, p.N - col0);
+          if (c + 1 < BN / 32) {
+            const int ncol0 = col0 + 32;
+            const bool nfull = (p.N - ncol0) >= 32;
+            if (p.bias != nullptr) nbias = (ncol0 + lane < p.N) ? __ldg(p.bias + ncol0 + lane) : 0.f;
+            if (has_res && row_ok && nfull && (p.ldr & 3) == 0) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) nres[j] = __ldg(reinterpret_cast<const float4*>(res_row + ncol0) + j);
+            }
+            if (has_mask && row_ok && nfull && (p.ldc & 7) == 0) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) nmsk[j] = __ldg(reinterpret_cast<const uint4*>(msk_row + ncol0) + j);
+            }
+          }
+          tmem_ld_wait();
+          if (c == BN / 32 - 1) {  // accumulator fully in registers: hand the TMEM buffer back early
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar + 8 * as);
+          }
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          if (p.bias != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] += __shfl_sync(0xffffffffu, biasv, j);
+          }
+          if (p.act == 1) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
+          }
+          const bool full = (ncols == 32);
+          if (p.aux_out != nullptr && row_ok && ncols > 0) {
+            bf16* dst = p.aux_out + static_cast<size_t>(row) * p.ldc + col0;
+            if (full && (p.ldc & 7) == 0) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8)
+                *reinterpret_cast<uint4*>(dst + j) =
+                    make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
+                               pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
+            } else {
+              for (int j = 0; j < ncols; ++j) dst[j] = __float2bfloat16_rn(v[j]);
+            }
+          }
+          if (has_mask && row_ok && ncols > 0) {
+            if (full && (p.ldc & 7) == 0) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const uint32_t w[4] = {msk[j].x, msk[j].y, msk[j].z, msk[j].w};
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                  const float2 f = unpack_bf16x2(w[t]);
+                  if (!(f.x > 0.0f)) v[8 * j + 2 * t] = 0.0f;
+                  if (!(f.y > 0.0f)) v[8 * j + 2 * t + 1] = 0.0f;
+                }
+              }
+            } else {
+              for (int j = 0; j < ncols; ++j)
+                if (!(__bfloat162float(msk_row[col0 + j]) > 0.0f)) v[j] = 0.0f;
+            }
+          }
+          if (has_res && row_ok && ncols > 0) {
+            if (full && (p.ldr & 3) == 0) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                v[4 * j] += res[j].x; v[4 * j + 1] += res[j].y; v[4 * j + 2] += res[j].z; v[4 * j + 3] += res[j].w;
+              }
+            } else {
+              for (int j = 0; j < ncols; ++j) v[j] += res_row[col0 + j];
+            }
+          }
+          // stage: fp32 -> one 32x32 tile per chunk; bf16 -> two chunks fill one 32x64 tile
+          const bool first_half = p.out_fp32 || (c & 1) == 0;
+          if (first_half) {                 // the previous TMA store must be done reading the buffer
+            if (lane == 0) tma_store_wait_read0();
+            __syncwarp();
+          }
+          if (p.out_fp32) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((j ^ swz) << 4)),
+                           "f"(v[4 * j]), "f"(v[4 * j + 1]), "f"(v[4 * j + 2]), "f"(v[4 * j + 3]) : "memory");
+          } else {
+            const int half = (c & 1) * 4;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + (((half + j) ^ swz) << 4)),
+                           "r"(pack_bf16x2(v[8 * j], v[8 * j + 1])), "r"(pack_bf16x2(v[8 * j + 2], v[8 * j + 3])),
+                           "r"(pack_bf16x2(v[8 * j + 4], v[8 * j + 5])), "r"(pack_bf16x2(v[8 * j + 6], v[8 * j + 7]))
+                           : "memory");
+          }
+          if (p.out_fp32 || (c & 1) == 1) {
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              const int sc0 = p.out_fp32 ? col0 : col0 - 32;
+              if (sc0 < p.N && m0 + q * 32 < p.M) {
+                if (p.accumulate) tma_reduce_add_2d(&tmC, stage_buf, sc0, m0 + q * 32);
+                else tma_store_2d(&tmC, stage_buf, sc0, m0 + q * 32);
+              }
+              tma_store_commit();
+            }
+          }
+        }
+      }
+      if (lane == 0) tma_store_wait_all();
+      __syncwarp();
+    } else
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
       const int t2 = tile / p.k_splits;
       const int m0 = (t2 % p.num_m_tiles) * BM;
@@ -313,28 +483,28 @@ struct TmapKey {
   const void* base;
   uint64_t inner, outer, ld;
   uint32_t bi, bo;
-  int dev;
+  int dev, esz;
   bool operator==(const TmapKey& o) const {
     return base == o.base && inner == o.inner && outer == o.outer && ld == o.ld && bi == o.bi &&
-           bo == o.bo && dev == o.dev;
+           bo == o.bo && dev == o.dev && esz == o.esz;
   }
 };
 struct TmapKeyHash {
   size_t operator()(const TmapKey& k) const {
     size_t h = reinterpret_cast<size_t>(k.base);
     auto mix = [&h](uint64_t v) { h ^= v + 0x9e3779b97f4a7c15ULL + (h << 6) + (h >> 2); };
-    mix(k.inner); mix(k.outer); mix(k.ld); mix(k.bi); mix(k.bo); mix((uint64_t)k.dev);
+    mix(k.inner); mix(k.outer); mix(k.ld); mix(k.bi); mix(k.bo); mix((uint64_t)k.dev); mix((uint64_t)k.esz);
     return h;
   }
 };
 
 int get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
-             uint32_t bi, uint32_t bo) {
+             uint32_t bi, uint32_t bo, int esz = 2) {
   static std::mutex mu;
   static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> cache;
   int dev = 0;
   cudaGetDevice(&dev);
-  TmapKey key{base, inner, outer, ld, bi, bo, dev};
+  TmapKey key{base, inner, outer, ld, bi, bo, dev, esz};
   {
     std::lock_guard<std::mutex> g(mu);
     auto it = cache.find(key);
@@ -343,7 +513,7 @@ int get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
       return 0;
     }
   }
-  int rc = b200_make_tmap_2d(out, base, inner, outer, ld, bi, bo);
+  int rc = b200_make_tmap_2d(out, base, inner, outer, ld, bi, bo, esz);
   if (rc != 0) return rc;
   std::lock_guard<std::mutex> g(mu);
   if (cache.size() > 4096) cache.clear();
@@ -354,21 +524,24 @@ int get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
 struct GemmOverrides {
   int a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep;  // < 0 => default
   int force_bn, force_splits;
+  int no_tma_store;
 };
 
-template <int BN, int STAGES>
-int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int grid,
-           cudaStream_t stream) {
-  constexpr int smem = STAGES * (A_STAGE_BYTES + BN * BK * 2) + 16 * STAGES + 32 + 16 + 1024;
+template <int BN, int STAGES, int MIN_CTAS>
+int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p,
+           int grid, cudaStream_t stream) {
+  constexpr int smem = STAGES * (A_STAGE_BYTES + BN * BK * 2) + STAGING_BYTES + 16 * STAGES + 32 + 16;
   static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!configured[dev & 63]) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES>,
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS>,
+                                         cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     configured[dev & 63] = true;
   }
-  gemm_tcgen05_kernel<BN, STAGES><<<grid, GEMM_THREADS, smem, stream>>>(tmA, tmB, p);
+  gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS><<<grid, GEMM_THREADS, smem, stream>>>(tmA, tmB, tmC, p);
   B200_LAUNCH_CHECK();
   return 0;
 }
@@ -383,7 +556,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
 
   int bn = (cfg & 0x3ff);
   if (ov && ov->force_bn > 0) bn = ov->force_bn;
-  if (bn == 0) bn = (N >= 4096 && M >= 512) ? 256 : 128;
+  if (bn == 0) bn = 128;
   B200_REQUIRE(bn == 128 || bn == 256, "gemm: tile N %d not supported", bn);
 
   GemmParams p{};
@@ -396,8 +569,9 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   int splits = 1;
   const bool plain = (bias == nullptr && residual == nullptr && act == 0 && aux_out == nullptr &&
                       mask_src == nullptr);
-  if (accumulate && out_fp32 && plain && tiles < sms) {
-    splits = sms / tiles;
+  const int slots = sms * ((bn == 128) ? 2 : 1);
+  if (accumulate && out_fp32 && plain && tiles < slots) {
+    splits = slots / tiles;
     const int max_splits = p.kb_total / 4 > 0 ? p.kb_total / 4 : 1;
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
@@ -441,11 +615,22 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   else       rc = get_tmap(&tmB, B, N, K, ldb, 64, BK);
   if (rc != 0) return rc;
 
+  // output through TMA when the layout allows it (16-byte aligned base and row stride)
+  CUtensorMap tmC = tmA;
+  const int esz = out_fp32 ? 4 : 2;
+  p.tma_store = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (static_cast<int64_t>(ldc) * esz) % 16 == 0 &&
+                 !(ov && ov->no_tma_store)) ? 1 : 0;
+  if (p.tma_store) {
+    rc = get_tmap(&tmC, C, N, M, ldc, out_fp32 ? 32 : 64, 32, esz);
+    if (rc != 0) return rc;
+  }
   const int total = tiles * p.k_splits;
-  const int grid = total < sms ? total : sms;
+  const int ctas_per_sm = (bn == 128) ? 2 : 1;
+  const int cap = sms * ctas_per_sm;
+  const int grid = total < cap ? total : cap;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (bn == 128) return launch<128, 6>(tmA, tmB, p, grid, st);
-  return launch<256, 4>(tmA, tmB, p, grid, st);
+  if (bn == 128) return launch<128, 3, 2>(tmA, tmB, tmC, p, grid, st);
+  return launch<256, 4, 1>(tmA, tmB, tmC, p, grid, st);
 }
 
 }  // namespace
@@ -465,7 +650,7 @@ int b200_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, i
 int b200_gemm_debug(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
                     int ldc, int a_mn_major, int b_mn_major, int a_lbo, int a_sbo, int a_kstep,
                     int b_lbo, int b_sbo, int b_kstep, int force_bn, int force_splits, void* stream) {
-  GemmOverrides ov{a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep, force_bn, force_splits};
+  GemmOverrides ov{a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep, force_bn & 0xffff, force_splits, (force_bn >> 16) & 1};
   return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, nullptr, nullptr, 0, 0, 1,
                    force_splits > 1 ? 1 : 0, nullptr, nullptr, 0, &ov, stream);
 }

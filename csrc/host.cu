@@ -66,24 +66,26 @@ static PFN_encodeTiled get_encode() {
 }
 
 int b200_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
-                      uint64_t ld_elems, uint32_t box_inner, uint32_t box_outer) {
+                      uint64_t ld_elems, uint32_t box_inner, uint32_t box_outer, int elem_bytes) {
   PFN_encodeTiled enc = get_encode();
   B200_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point not found");
+  B200_REQUIRE(elem_bytes == 2 || elem_bytes == 4, "TMA element size %d not supported", elem_bytes);
   B200_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base %p not 16B aligned", base);
-  B200_REQUIRE((ld_elems * 2) % 16 == 0, "TMA row stride %llu elems not a multiple of 8",
-               (unsigned long long)ld_elems);
-  B200_REQUIRE(box_inner * 2 <= 128 && box_outer <= 256, "TMA box too large");
+  B200_REQUIRE((ld_elems * elem_bytes) % 16 == 0, "TMA row stride %llu elems (x%d B) not a multiple of 16 B",
+               (unsigned long long)ld_elems, elem_bytes);
+  B200_REQUIRE(box_inner * elem_bytes <= 128 && box_outer <= 256, "TMA box too large");
   cuuint64_t dims[2] = {inner, outer};
-  cuuint64_t strides[1] = {ld_elems * 2};
+  cuuint64_t strides[1] = {ld_elems * elem_bytes};
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
-                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = enc(out, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                   const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   B200_REQUIRE(r == CUDA_SUCCESS,
-               "cuTensorMapEncodeTiled(2d) failed: %d (inner=%llu outer=%llu ld=%llu box=%ux%u)",
+               "cuTensorMapEncodeTiled(2d) failed: %d (inner=%llu outer=%llu ld=%llu box=%ux%u esz=%d)",
                (int)r, (unsigned long long)inner, (unsigned long long)outer,
-               (unsigned long long)ld_elems, box_inner, box_outer);
+               (unsigned long long)ld_elems, box_inner, box_outer, elem_bytes);
   return 0;
 }
 

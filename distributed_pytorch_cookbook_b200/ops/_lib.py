@@ -41,10 +41,11 @@ _SIGS = {
     "b200_gemm_debug": [P, P, P] + [I] * 16 + [P],
     "b200_attn_fwd": [P, P, P, I, I, I, I, Fl, P, P],
     "b200_attn_bwd": [P, P, P, P, P, P, P, I, I, I, I, Fl, P, P],
-    "b200_allreduce": [P, P, P, I, I, L, Fl, I, I, P, P],
-    "b200_rs_adamw": [P, P, I, I, L, Fl, P, P, P, P, P, Fl, Fl, Fl, Fl, I, P, P],
+    "b200_allreduce": [P, P, P, I, I, L, L, Fl, I, I, P],
+    "b200_rs_adamw": [P, P, P, I, I, L, L, Fl, P, P, P, P, P, Fl, Fl, Fl, Fl, I, I, I, P],
+    "b200_allgather": [P, P, I, I, L, L, P, I, I, I, P],
     "b200_ag_gemm_bf16": [P, P, P, P, I, I, I, I, I, P, I, I, P, P],
-    "b200_barrier": [P, I, I, P, P],
+    "b200_barrier": [P, I, I, I, P],
     "b200_smoke": [P],
 }
 

@@ -147,8 +147,10 @@ def _packed(ts) -> Optional[torch.Tensor]:
     """If the tensors are adjacent rows of one buffer return the packed [sum_rows, K] view."""
     t0 = ts[0]
     rows = 0
+    base = t0.untyped_storage().data_ptr()
     for t in ts:
-        if t.data_ptr() != t0.data_ptr() + rows * t0.shape[1] * t0.element_size() or not t.is_contiguous():
+        if (t.untyped_storage().data_ptr() != base or not t.is_contiguous()
+                or t.data_ptr() != t0.data_ptr() + rows * t0.shape[1] * t0.element_size()):
             return None
         rows += t.shape[0]
     return torch.as_strided(t0, (rows, t0.shape[1]), (t0.shape[1], 1))
@@ -364,7 +366,9 @@ class _LMHeadCE(torch.autograd.Function):
         want_grad = grad_on and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1])
         rows = min(_LM_CHUNK_ROWS, M)
         logits = torch.empty((rows, ld), dtype=BF16, device=dev)
-        dx = torch.empty((M, D), dtype=BF16, device=dev) if want_grad else None
+        # dX is reduced over the vocabulary (K = 50257): few output tiles, long K -> split-K with
+        # fp32 atomics into a zeroed buffer, cast to bf16 once at the end
+        dx32 = torch.zeros((M, D), dtype=torch.float32, device=dev) if want_grad else None
         gw = grad_of(weight) if (want_grad and weight.requires_grad) else None
         for r0 in range(0, M, rows):
             r = min(rows, M - r0)
@@ -372,13 +376,14 @@ class _LMHeadCE(torch.autograd.Function):
             call("b200_ce_fwd_bwd", logits.data_ptr(), t.data_ptr() + 8 * r0, stats.data_ptr(),
                  r, V, ld, ignore_index, int(want_grad), float(grad_scale), stream())
             if want_grad:
-                gemm(logits, wb, dx[r0:r0 + r], r, D, V, b_mn_major=True)       # dX = dL . W
+                gemm(logits, wb, dx32[r0:r0 + r], r, D, V, b_mn_major=True, accumulate=True)  # dX = dL . W
                 if gw is not None:
                     gemm(logits, x2[r0:r0 + r], gw, V, D, r, a_mn_major=True, b_mn_major=True,
                          accumulate=True)                                       # dW += dL^T . X
         if gw is not None:
             _notify(weight)
         loss = stats[1] / stats[0].clamp(min=1.0)
+        dx = dx32.to(BF16) if want_grad else None
         ctx.save_for_backward(dx)
         ctx.x_shape, ctx.in_dtype = x.shape, x.dtype
         ctx.mark_non_differentiable(stats)

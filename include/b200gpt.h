@@ -72,6 +72,30 @@ int b200_attn_bwd(const void* qkv_bf16, const void* out_bf16, const void* dout_b
                   void* dqkv_bf16, float* delta, float* dq_acc, int B, int T, int H, int D, float scale,
                   const void* key_mask, void* stream);
 
+/* ---- NVLink / NVSwitch collectives over symmetric memory (no NCCL) --------------------------
+ * bufs_dev : device array [world] of every rank's base pointer of the symmetric data buffer
+ * mc_ptr   : NVLS multicast mapping of that buffer (NULL -> peer load/store fallback)
+ * flags_dev: device array [world] of every rank's flag buffer (256 channels x 16 uint32, zeroed)
+ * kernels that may run concurrently must use disjoint channel ranges [channel_base, +nblocks). */
+
+/* in-place bucket all-reduce (sum * scale) of elements [offset, offset+n) of the fp32 gradient
+ * arena  (the DDP reducer behind main-ddp.py:55,124) */
+int b200_allreduce(const void* bufs_dev, void* mc_ptr, const void* flags_dev, int rank, int world,
+                   int64_t offset_elems, int64_t n_elems, float scale, int nblocks, int channel_base,
+                   void* stream);
+/* reduce-scatter of this rank's shard fused with the sharded AdamW update and the bf16 shard
+ * write  (FSDP post-backward reduce-scatter + optimizer step, main-fsdp.py:138-140) */
+int b200_rs_adamw(const void* grad_bufs_dev, void* grad_mc_ptr, const void* flags_dev, int rank, int world,
+                  int64_t shard_off, int64_t shard_n, float scale, float* p, float* m, float* v,
+                  void* p_bf16, const float* hyper, float beta1, float beta2, float eps, float wd,
+                  int end_barrier, int nblocks, int channel_base, void* stream);
+/* pull all-gather: dst[peer * shard_bytes ...] = peer's bytes [src_off, src_off + shard_bytes)
+ * (FSDP pre-forward unshard, main-fsdp.py:131) */
+int b200_allgather(const void* src_bufs_dev, const void* flags_dev, int rank, int world,
+                   int64_t src_off_bytes, int64_t shard_bytes, void* dst, int start_barrier, int nblocks,
+                   int channel_base, void* stream);
+int b200_barrier(const void* flags_dev, int rank, int world, int channel, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
