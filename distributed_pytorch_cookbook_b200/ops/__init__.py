@@ -91,10 +91,13 @@ def lmhead_cross_entropy_reference(x, weight, targets, ignore_index: int = -100)
 # ----------------------------------------------------------------------------------------
 # dispatching entry points
 # ----------------------------------------------------------------------------------------
-def lmhead_cross_entropy(x, weight, targets, ignore_index: int = -100):
+def lmhead_cross_entropy(x, weight, targets, ignore_index: int = -100, grad_scale: float = 1.0):
+    """``grad_scale`` is the factor the caller will apply to the loss before ``backward()`` (1/M
+    for M pipeline micro-batches); the native op bakes it into the gradients it produces in the
+    forward pass, the PyTorch path gets it through autograd."""
     if use_native(x):
         from . import native
-        return native.lmhead_cross_entropy(x, weight, targets, ignore_index)
+        return native.lmhead_cross_entropy(x, weight, targets, ignore_index, grad_scale)
     return lmhead_cross_entropy_reference(x, weight, targets, ignore_index)
 
 

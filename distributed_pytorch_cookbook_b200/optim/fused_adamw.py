@@ -33,13 +33,13 @@ class FusedAdamW:
             self.hyper = torch.tensor([lr, 0.0, 0.0, 0.0], dtype=torch.float32, device=device)
             self.torch_opt = None
         else:
-            self.arena = None
+            self.arena = arena          # optional: flat fp32 params/grads (DDP buckets) on any device
             self.torch_opt = torch.optim.AdamW(self.params, lr=lr, betas=betas, eps=eps,
                                                weight_decay=weight_decay)
 
     # -- torch.optim-like surface ---------------------------------------------------------
     def zero_grad(self, set_to_none: bool = False):
-        if self.native:
+        if self.arena is not None:
             self.arena.zero_grad()
         else:
             self.torch_opt.zero_grad(set_to_none=set_to_none)

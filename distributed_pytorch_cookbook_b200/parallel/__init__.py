@@ -1,0 +1,2 @@
+from .ddp import DDPStrategy, GradReducer, plan_buckets  # noqa: F401
+from .pipe import PipelineStage, PipeStrategy, partition_layers, schedule_actions, stage_layer_range  # noqa: F401

@@ -1,0 +1,245 @@
+"""Data-parallel engine: bucketed gradient all-reduce over the flat gradient arena.
+
+Reference: ``DistributedDataParallel(model, device_ids=[dev])`` (main-ddp.py:55) - the c10d
+reducer copies grads into 25 MiB buckets, pre-divides, calls ncclAllReduce and copies back; at
+the default config that forms two buckets of which the second (73 MiB, closed by the input
+embedding) is fully exposed.
+
+Here the gradient arena itself lives in NVLink-mapped symmetric memory and the kernels write
+weight gradients straight into it, so a bucket is just ``arena.grad[lo:hi]``: no copy-in, no
+copy-out.  Buckets are small (one per decoder layer by default), become ready the moment the
+producing wgrad kernel is *queued* (``ops.native.grad_ready_hooks``; autograd post-accumulate
+hooks on the PyTorch fallback path) and are reduced in place by ``b200_allreduce`` on a side
+stream: NVLS ``multimem.ld_reduce`` + 1/world scale + ``multimem.st`` in one kernel, no NCCL.
+The LM-head gradient is complete right after the fused LM-head/CE *forward*, so its 49 MiB
+all-reduce overlaps the whole decoder backward.  Transport fallbacks: NCCL (``--comm nccl``)
+and gloo on CPU - same bucket plan, ``dist.all_reduce`` per bucket.
+"""
+from __future__ import annotations
+
+from contextlib import nullcontext
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib, native
+from ..optim import FusedAdamW
+from ..runtime.arena import ParamArena
+from ..runtime.symm import CH_ALLREDUCE, SymmContext, symmetric_memory_available
+
+
+def plan_buckets(params: List[torch.nn.Parameter], offsets: List[int], total: int, cap_elems: int):
+    """Contiguous arena slices, built in reverse registration order (~ backward order).
+
+    Returns a list of ``(lo, hi, [param indices])``; bucket 0 is the first to become ready.
+    A parameter larger than the cap gets a bucket of its own.
+    """
+    buckets = []
+    hi = total
+    cur: List[int] = []
+    cur_lo = total
+    for i in range(len(params) - 1, -1, -1):
+        lo = offsets[i]
+        if cur and (hi - lo) > cap_elems:
+            buckets.append((cur_lo, hi, cur))
+            hi, cur = cur_lo, []
+        cur.append(i)
+        cur_lo = lo
+    if cur:
+        buckets.append((cur_lo, hi, cur))
+    # make every slice 16-byte granular for the vector kernels
+    assert all(lo % 4 == 0 and hi % 4 == 0 for lo, hi, _ in buckets)
+    return buckets
+
+
+class GradReducer:
+    def __init__(self, arena: ParamArena, group=None, bucket_mb: float = 4.0, transport: str = "nccl",
+                 symm: Optional[SymmContext] = None, grad_buf=None, nblocks: int = 16):
+        self.arena, self.group, self.transport = arena, group, transport
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.symm, self.grad_buf, self.nblocks = symm, grad_buf, nblocks
+        cap = max(int(bucket_mb * (1 << 20) / 4), 1)
+        self.buckets = plan_buckets(arena.params, arena.offsets, arena.total, cap)
+        self.bucket_of = {}
+        for b, (_, _, idxs) in enumerate(self.buckets):
+            for i in idxs:
+                self.bucket_of[id(arena.params[i])] = b
+        self.remaining = [len(idxs) for _, _, idxs in self.buckets]
+        self.launched = [False] * len(self.buckets)
+        self.cuda = arena.device.type == "cuda"
+        self.comm_stream = torch.cuda.Stream(arena.device) if self.cuda else None
+        self.works = []
+        self.active = False
+        native.grad_ready_hooks.append(self.on_grad_ready)
+        for p in arena.params:
+            p.register_post_accumulate_grad_hook(self.on_grad_ready)
+
+    # ------------------------------------------------------------------------------
+    def begin(self):
+        self.remaining = [len(idxs) for _, _, idxs in self.buckets]
+        self.launched = [False] * len(self.buckets)
+        self.works = []
+        self.active = True
+
+    def on_grad_ready(self, p):
+        if not self.active:
+            return
+        b = self.bucket_of.get(id(p))
+        if b is None:
+            return
+        self.remaining[b] -= 1
+        if self.remaining[b] == 0 and not self.launched[b]:
+            self._launch(b)
+
+    def _launch(self, b: int):
+        self.launched[b] = True
+        lo, hi, _ = self.buckets[b]
+        if self.world == 1:
+            return
+        if self.transport == "symm":
+            ev = torch.cuda.Event()
+            ev.record()
+            self.comm_stream.wait_event(ev)
+            with torch.cuda.stream(self.comm_stream):
+                _lib.call("b200_allreduce", self.grad_buf.ptrs_dev, self.grad_buf.mc_ptr or None,
+                          self.symm.flags.ptrs_dev, self.rank, self.world, lo, hi - lo, 1.0 / self.world,
+                          self.nblocks, CH_ALLREDUCE, self.comm_stream.cuda_stream)
+        elif self.cuda:
+            ev = torch.cuda.Event()
+            ev.record()
+            self.comm_stream.wait_event(ev)
+            with torch.cuda.stream(self.comm_stream):
+                view = self.arena.grad[lo:hi]
+                view.mul_(1.0 / self.world)
+                dist.all_reduce(view, group=self.group)
+        else:
+            view = self.arena.grad[lo:hi]
+            view.mul_(1.0 / self.world)
+            self.works.append(dist.all_reduce(view, group=self.group, async_op=True))
+
+    def finish(self):
+        """Reduce whatever was not triggered by a hook and join the communication stream."""
+        for b in range(len(self.buckets)):
+            if not self.launched[b]:
+                self._launch(b)
+        for w in self.works:
+            w.wait()
+        self.works = []
+        if self.cuda and self.world > 1:
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        self.active = False
+
+
+class DDPStrategy:
+    """Trainer strategy for main-ddp.py (and the dp dimension of main-pipe-ddp.py)."""
+
+    def __init__(self, group=None):
+        self.group = group
+        self.comm_kind = None
+        self._graphed = None
+
+    def setup(self, model, args, device):
+        self.device = torch.device(device)
+        self.world = dist.get_world_size(self.group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(self.group) if dist.is_initialized() else 0
+        self.model = model.to(self.device)
+        cuda = self.device.type == "cuda"
+        want = getattr(args, "comm", "auto")
+        native_ok = cuda and _lib.available() and not args.disable_amp
+        transport = "gloo" if not cuda else "nccl"
+        self.symm = None
+        grad_buf = None
+        if self.world > 1 and native_ok and want in ("auto", "symm") and symmetric_memory_available(self.device):
+            try:
+                self.symm = SymmContext(self.device, self.group)
+                transport = "symm"
+            except Exception as e:  # fabric / driver without peer mapping
+                if want == "symm":
+                    raise
+                print(f"[ddp] symmetric memory unavailable ({e!r}); falling back to NCCL", flush=True)
+        params = [p for p in self.model.parameters() if p.requires_grad]
+        grad_alloc = None
+        if transport == "symm":
+            holder = {}
+
+            def grad_alloc(n):
+                holder["buf"] = self.symm.alloc(n, torch.float32)
+                return holder["buf"].tensor
+        self.arena = ParamArena(params, self.device, with_bf16=native_ok, with_moments=native_ok,
+                                grad_alloc=grad_alloc)
+        if transport == "symm":
+            grad_buf = holder["buf"]
+        self.optim = FusedAdamW(params, lr=args.learning_rate, device=self.device, arena=self.arena)
+        self.comm_kind = transport
+        self._verify_replicas()
+        self.reducer = GradReducer(self.arena, self.group, getattr(args, "bucket_mb", 4.0), transport,
+                                   self.symm, grad_buf)
+        self.use_graph = (transport == "symm" and not getattr(args, "disable_cuda_graph", False)) or \
+                         (self.world == 1 and native_ok and not getattr(args, "disable_cuda_graph", False))
+
+    def _verify_replicas(self):
+        """Replicas start identical because every rank seeds identically (no 122 MiB broadcast,
+        SURVEY C2); one checksum all-reduce proves it, else rank 0's weights are broadcast."""
+        if self.world == 1:
+            return
+        s = self.arena.fp32.double().sum().reshape(1)
+        lo, hi = s.clone(), s.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=self.group)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=self.group)
+        if float(lo) != float(hi):
+            src = dist.get_global_rank(self.group, 0) if self.group is not None else 0
+            dist.broadcast(self.arena.fp32, src=src, group=self.group)
+            self.arena.refresh_bf16()
+
+    def train(self):
+        self.model.train()
+
+    def eval(self):
+        self.model.eval()
+
+    def _autocast(self, amp):
+        if amp and self.device.type == "cuda":
+            return torch.autocast(device_type="cuda", dtype=torch.bfloat16)
+        return nullcontext()
+
+    def _raw_step(self, input_ids, position_ids, targets, mask, amp):
+        self.optim.zero_grad()
+        self.reducer.begin()
+        with self._autocast(amp):
+            loss, _, _ = self.model.loss(input_ids, position_ids, targets, mask=mask)
+        loss.backward()
+        self.reducer.finish()
+        self.optim.step()
+        return loss.detach()
+
+    def train_step(self, batch, targets, amp=True):
+        if self.use_graph and amp:
+            from ..runtime.graph import GraphedStep
+            if self._graphed is None:
+                self._graphed = GraphedStep(lambda i, p, t: self._raw_step(i, p, t, None, True))
+            return self._graphed(batch["input_ids"], batch["position_ids"], targets)
+        return self._raw_step(batch["input_ids"], batch["position_ids"], targets, batch.get("mask"), amp)
+
+    @torch.no_grad()
+    def eval_step(self, batch, targets, amp=True):
+        with self._autocast(amp):
+            return self.model.loss(batch["input_ids"], batch["position_ids"], targets, mask=batch.get("mask"))
+
+    def all_reduce_mean(self, t):
+        """One fused 2-float reduce per validation batch (reference: two, main-ddp.py:159-160)."""
+        if self.world > 1:
+            dist.all_reduce(t, group=self.group)
+            t /= self.world
+        return t
+
+    def launches_per_step(self):
+        return self._graphed.native_calls_per_replay if (self._graphed and self._graphed.graph) else None
+
+    def generation_model(self):
+        return self.model
+
+    def state_dict(self):
+        from ..utils import canonical_state_dict
+        return canonical_state_dict(self.model)

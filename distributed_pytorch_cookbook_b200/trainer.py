@@ -84,12 +84,16 @@ def build_data(args, rank: int = 0, world: int = 1, data_parallel: bool = False)
 
 class Trainer:
     def __init__(self, args, strategy, rank: int = 0, world: int = 1, device="cpu",
-                 data_parallel: bool = False):
+                 data_parallel: bool = False, is_main: Optional[bool] = None):
+        """``rank``/``world`` describe the *data-parallel* position (which shard of the data this
+        process reads); ``is_main`` who prints and saves (default: global rank 0)."""
         self.args, self.strategy = args, strategy
         self.rank, self.world = rank, world
         self.device = torch.device(device)
         self.data_parallel = data_parallel
-        self.main = rank == 0
+        if is_main is None:
+            is_main = (dist.get_rank() == 0) if dist.is_initialized() else rank == 0
+        self.main = is_main
         self.metrics = JsonlLogger(getattr(args, "metrics_jsonl", None), enabled=self.main)
 
     # ------------------------------------------------------------------------------
