@@ -45,6 +45,7 @@ struct GemmParams {
   const bf16* mask_src;
   int act, out_fp32, accumulate;
   int tma_store;  // 1: epilogue stages tiles in smem and writes them with TMA (coalesced, clipped)
+  long long* dbg;  // optional per-CTA phase timestamps (16 slots per CTA), bring-up only
   int* err_word;
 };
 
@@ -56,7 +57,12 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
                : "memory");
 }
 
-constexpr int STAGING_BYTES = 4 * 4096;  // one 32-row x 128-byte swizzled tile per epilogue warp
+constexpr int STAGING_BYTES = 4 * 2 * 4096;  // two 32-row x 128-byte swizzled tiles per epilogue warp
+
+#define DBG_STAMP(slot)                                                                   \
+  do {                                                                                    \
+    if (p.dbg != nullptr) p.dbg[blockIdx.x * 16 + (slot)] = clock64();                    \
+  } while (0)
 
 template <int BN, int STAGES, int MIN_CTAS>
 __global__ void __launch_bounds__(GEMM_THREADS, MIN_CTAS)
@@ -90,6 +96,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
+    DBG_STAMP(0);
     *abort_flag = 0;
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(full_bar + 8 * s, 1);
@@ -112,6 +119,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  if (threadIdx.x == 0) DBG_STAMP(1);
 
   const int total_tiles = p.num_m_tiles * p.num_n_tiles * p.k_splits;
 
@@ -149,10 +157,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j) tma_load_2d(b_dst + j * 8192, &tmB, fb, n0 + 64 * j, k0);
           }
+          if (kb == kb0 && tile == (int)blockIdx.x) DBG_STAMP(2);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
+      DBG_STAMP(10);
     }
+    __syncwarp();  // lanes 1..31 must not reach the CTA barrier before lane 0 (bar.sync counts warps)
   } else if (warp_idx == 1) {
     // ===================== MMA issuer =====================
     uint32_t stage = 0, phase = 0;
@@ -172,6 +183,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           break;
         }
         tcgen05_fence_after();
+        if (lane == 0 && kb == kb0 && lt == 0) DBG_STAMP(3);
         if (lane == 0) {
           const uint32_t a_src = sA + stage * A_STAGE_BYTES;
           const uint32_t b_src = sB + stage * B_STAGE_BYTES;
@@ -187,18 +199,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
       if (ok && lane == 0) umma_commit(tfull_bar + 8 * as);  // accumulator ready for the epilogue
+      if (lane == 0 && lt == 0) DBG_STAMP(4);
       __syncwarp();
     }
   } else {
     // ===================== epilogue (4 warps) =====================
     const int q = warp_idx & 3;  // TMEM lane quarter this warp may access
     int lt = 0;
-    if (p.tma_store) {
+    {
       // TMEM -> registers -> (bias / ReLU / mask / residual) -> 128B-swizzled smem tile -> TMA store
       // (or TMA reduce-add).  Global traffic is whole 128-byte rows, M/N tails are clipped by the
       // tensor map, and the residual / mask operands of chunk c+1 are prefetched under chunk c.
-      const uint32_t stage_buf = sStage + q * 4096;
-      const uint32_t my_row = stage_buf + lane * 128;
+      const uint32_t stage_base = sStage + q * 8192;
+      uint32_t nstore = 0;  // TMA stores issued by this warp (selects the staging buffer)
       const int swz = lane & 7;
       const bool has_res = p.residual != nullptr, has_mask = p.mask_src != nullptr;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
@@ -213,22 +226,27 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         float4 nres[8];
         uint4 nmsk[4];
         float nbias = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) nres[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) nmsk[j] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
         // prefetch the epilogue operands of chunk 0 while the MMAs of this tile are still running
         {
           const int col0 = n0;
           const bool full = (p.N - col0) >= 32;
           if (p.bias != nullptr) nbias = (col0 + lane < p.N) ? __ldg(p.bias + col0 + lane) : 0.f;
-          if (has_res && row_ok && full && (p.ldr & 3) == 0) {
+          if (has_res && row_ok && full) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) nres[j] = __ldg(reinterpret_cast<const float4*>(res_row + col0) + j);
           }
-          if (has_mask && row_ok && full && (p.ldc & 7) == 0) {
+          if (has_mask && row_ok && full) {
 #pragma unroll
             for (int j = 0; j < 4; ++j) nmsk[j] = __ldg(reinterpret_cast<const uint4*>(msk_row + col0) + j);
           }
         }
         if (!mbar_wait(tfull_bar + 8 * as, aph, abort_flag, p.err_word, ERR_GEMM_EPILOGUE)) break;
         tcgen05_fence_after();
+        if (warp_idx == 2 && lane == 0 && lt == 0) DBG_STAMP(5);
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
 #pragma unroll 1
         for (int c = 0; c < BN / 32; ++c) {
@@ -249,11 +267,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int ncol0 = col0 + 32;
             const bool nfull = (p.N - ncol0) >= 32;
             if (p.bias != nullptr) nbias = (ncol0 + lane < p.N) ? __ldg(p.bias + ncol0 + lane) : 0.f;
-            if (has_res && row_ok && nfull && (p.ldr & 3) == 0) {
+            if (has_res && row_ok && nfull) {
 #pragma unroll
               for (int j = 0; j < 8; ++j) nres[j] = __ldg(reinterpret_cast<const float4*>(res_row + ncol0) + j);
             }
-            if (has_mask && row_ok && nfull && (p.ldc & 7) == 0) {
+            if (has_mask && row_ok && nfull) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) nmsk[j] = __ldg(reinterpret_cast<const uint4*>(msk_row + ncol0) + j);
             }
@@ -275,50 +293,39 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
           }
-          const bool full = (ncols == 32);
+          // (host guarantees N % 32 == 0 and aligned rows whenever aux_out / mask / residual are used)
           if (p.aux_out != nullptr && row_ok && ncols > 0) {
             bf16* dst = p.aux_out + static_cast<size_t>(row) * p.ldc + col0;
-            if (full && (p.ldc & 7) == 0) {
 #pragma unroll
-              for (int j = 0; j < 32; j += 8)
-                *reinterpret_cast<uint4*>(dst + j) =
-                    make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
-                               pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
-            } else {
-              for (int j = 0; j < ncols; ++j) dst[j] = __float2bfloat16_rn(v[j]);
+            for (int j = 0; j < 32; j += 8)
+              *reinterpret_cast<uint4*>(dst + j) =
+                  make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
+                             pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
+          }
+          if (has_mask) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint32_t w[4] = {msk[j].x, msk[j].y, msk[j].z, msk[j].w};
+#pragma unroll
+              for (int t = 0; t < 4; ++t) {
+                const float2 f = unpack_bf16x2(w[t]);
+                if (!(f.x > 0.0f)) v[8 * j + 2 * t] = 0.0f;
+                if (!(f.y > 0.0f)) v[8 * j + 2 * t + 1] = 0.0f;
+              }
             }
           }
-          if (has_mask && row_ok && ncols > 0) {
-            if (full && (p.ldc & 7) == 0) {
+          if (has_res) {
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const uint32_t w[4] = {msk[j].x, msk[j].y, msk[j].z, msk[j].w};
-#pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                  const float2 f = unpack_bf16x2(w[t]);
-                  if (!(f.x > 0.0f)) v[8 * j + 2 * t] = 0.0f;
-                  if (!(f.y > 0.0f)) v[8 * j + 2 * t + 1] = 0.0f;
-                }
-              }
-            } else {
-              for (int j = 0; j < ncols; ++j)
-                if (!(__bfloat162float(msk_row[col0 + j]) > 0.0f)) v[j] = 0.0f;
-            }
-          }
-          if (has_res && row_ok && ncols > 0) {
-            if (full && (p.ldr & 3) == 0) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                v[4 * j] += res[j].x; v[4 * j + 1] += res[j].y; v[4 * j + 2] += res[j].z; v[4 * j + 3] += res[j].w;
-              }
-            } else {
-              for (int j = 0; j < ncols; ++j) v[j] += res_row[col0 + j];
+            for (int j = 0; j < 8; ++j) {
+              v[4 * j] += res[j].x; v[4 * j + 1] += res[j].y; v[4 * j + 2] += res[j].z; v[4 * j + 3] += res[j].w;
             }
           }
           // stage: fp32 -> one 32x32 tile per chunk; bf16 -> two chunks fill one 32x64 tile
           const bool first_half = p.out_fp32 || (c & 1) == 0;
-          if (first_half) {                 // the previous TMA store must be done reading the buffer
-            if (lane == 0) tma_store_wait_read0();
+          const uint32_t stage_buf = stage_base + (nstore & 1u) * 4096u;
+          const uint32_t my_row = stage_buf + lane * 128;
+          if (first_half) {                 // the store issued two stores ago must be done reading this buffer
+            if (lane == 0) tma_store_wait_read1();
             __syncwarp();
           }
           if (p.out_fp32) {
@@ -346,133 +353,24 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               }
               tma_store_commit();
             }
+            ++nstore;
           }
         }
       }
+      if (warp_idx == 2 && lane == 0) DBG_STAMP(6);
       if (lane == 0) tma_store_wait_all();
       __syncwarp();
-    } else
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
-      const int t2 = tile / p.k_splits;
-      const int m0 = (t2 % p.num_m_tiles) * BM;
-      const int n0 = (t2 / p.num_m_tiles) * BN;
-      const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
-      if (!mbar_wait(tfull_bar + 8 * as, aph, abort_flag, p.err_word, ERR_GEMM_EPILOGUE)) break;
-      tcgen05_fence_after();
-      const int row = m0 + q * 32 + lane;
-      const bool row_ok = row < p.M;
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        __syncwarp();  // tcgen05.ld is .sync.aligned: reconverge after the predicated stores
-        tmem_ld_32x32b_x32(taddr + c * 32, r);
-        tmem_ld_wait();
-        const int col0 = n0 + c * 32;
-        const int ncols = min(32, p.N - col0);
-        if (ncols <= 0 || !row_ok) continue;
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-        if (p.bias != nullptr) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (j < ncols) v[j] += __ldg(p.bias + col0 + j);
-        }
-        if (p.act == 1) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
-        }
-        const size_t off_c = static_cast<size_t>(row) * p.ldc + col0;
-        const bool full = (ncols == 32);
-        if (p.aux_out != nullptr) {
-          bf16* dst = p.aux_out + off_c;
-          if (full && (p.ldc & 7) == 0) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              uint4 u = make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
-                                   pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
-              *reinterpret_cast<uint4*>(dst + j) = u;
-            }
-          } else {
-            for (int j = 0; j < ncols; ++j) dst[j] = __float2bfloat16_rn(v[j]);
-          }
-        }
-        if (p.mask_src != nullptr) {
-          const bf16* msk = p.mask_src + off_c;
-          if (full && (p.ldc & 7) == 0) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              const uint4 u = *reinterpret_cast<const uint4*>(msk + j);
-              const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-              for (int t = 0; t < 4; ++t) {
-                const float2 f = unpack_bf16x2(w[t]);
-                if (!(f.x > 0.0f)) v[j + 2 * t] = 0.0f;
-                if (!(f.y > 0.0f)) v[j + 2 * t + 1] = 0.0f;
-              }
-            }
-          } else {
-            for (int j = 0; j < ncols; ++j)
-              if (!(__bfloat162float(msk[j]) > 0.0f)) v[j] = 0.0f;
-          }
-        }
-        if (p.residual != nullptr) {
-          const float* res = p.residual + static_cast<size_t>(row) * p.ldr + col0;
-          if (full && (p.ldr & 3) == 0) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const float4 f = *reinterpret_cast<const float4*>(res + j);
-              v[j] += f.x; v[j + 1] += f.y; v[j + 2] += f.z; v[j + 3] += f.w;
-            }
-          } else {
-            for (int j = 0; j < ncols; ++j) v[j] += res[j];
-          }
-        }
-        if (p.out_fp32) {
-          float* dst = reinterpret_cast<float*>(p.C) + off_c;
-          const bool vec = full && (p.ldc & 3) == 0;
-          if (p.accumulate) {
-            if (vec) {
-#pragma unroll
-              for (int j = 0; j < 32; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
-            } else {
-              for (int j = 0; j < ncols; ++j) atomicAdd(dst + j, v[j]);
-            }
-          } else {
-            if (vec) {
-#pragma unroll
-              for (int j = 0; j < 32; j += 4)
-                *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-            } else {
-              for (int j = 0; j < ncols; ++j) dst[j] = v[j];
-            }
-          }
-        } else {
-          bf16* dst = reinterpret_cast<bf16*>(p.C) + off_c;
-          if (full && (p.ldc & 7) == 0) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              uint4 u = make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
-                                   pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
-              *reinterpret_cast<uint4*>(dst + j) = u;
-            }
-          } else {
-            for (int j = 0; j < ncols; ++j) dst[j] = __float2bfloat16_rn(v[j]);
-          }
-        }
-      }
-      tcgen05_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(tempty_bar + 8 * as);
+      if (warp_idx == 2 && lane == 0) DBG_STAMP(7);
     }
   }
 
   tcgen05_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) DBG_STAMP(8);
   if (warp_idx == 1) {
     tcgen05_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
+    if (lane == 0) DBG_STAMP(9);
   }
 }
 
@@ -520,6 +418,8 @@ int get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
   cache.emplace(key, *out);
   return 0;
 }
+
+long long* g_gemm_dbg = nullptr;  // set through b200_gemm_set_debug_buffer (bring-up only)
 
 struct GemmOverrides {
   int a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep;  // < 0 => default
@@ -604,6 +504,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   p.mask_src = reinterpret_cast<const bf16*>(mask_src);
   p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate;
   p.err_word = b200_error_word();
+  p.dbg = g_gemm_dbg;
   B200_REQUIRE(p.err_word != nullptr, "gemm: no CUDA device");
 
   CUtensorMap tmA, tmB;
@@ -618,18 +519,23 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   // output through TMA when the layout allows it (16-byte aligned base and row stride)
   CUtensorMap tmC = tmA;
   const int esz = out_fp32 ? 4 : 2;
-  p.tma_store = ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (static_cast<int64_t>(ldc) * esz) % 16 == 0 &&
-                 !(ov && ov->no_tma_store)) ? 1 : 0;
-  if (p.tma_store) {
-    rc = get_tmap(&tmC, C, N, M, ldc, out_fp32 ? 32 : 64, 32, esz);
-    if (rc != 0) return rc;
-  }
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (static_cast<int64_t>(ldc) * esz) % 16 == 0,
+               "gemm: output must be 16-byte aligned with a 16-byte multiple row stride (ldc=%d)", ldc);
+  if (residual != nullptr || mask_src != nullptr || aux_out != nullptr)
+    B200_REQUIRE(N % 32 == 0 && ldc % 8 == 0 && (residual == nullptr || ldr % 4 == 0) &&
+                     (reinterpret_cast<uintptr_t>(residual) & 15) == 0 &&
+                     (reinterpret_cast<uintptr_t>(mask_src) & 15) == 0 &&
+                     (reinterpret_cast<uintptr_t>(aux_out) & 15) == 0,
+                 "gemm: residual / mask / aux epilogues need N %% 32 == 0 and 16-byte aligned rows (N=%d)", N);
+  p.tma_store = 1;
+  rc = get_tmap(&tmC, C, N, M, ldc, out_fp32 ? 32 : 64, 32, esz);
+  if (rc != 0) return rc;
   const int total = tiles * p.k_splits;
   const int ctas_per_sm = (bn == 128) ? 2 : 1;
   const int cap = sms * ctas_per_sm;
   const int grid = total < cap ? total : cap;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (bn == 128) return launch<128, 3, 2>(tmA, tmB, tmC, p, grid, st);
+  if (bn == 128) return launch<128, 2, 2>(tmA, tmB, tmC, p, grid, st);
   return launch<256, 4, 1>(tmA, tmB, tmC, p, grid, st);
 }
 
@@ -643,6 +549,11 @@ int b200_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, i
                    const void* mask_src, int cfg, void* stream) {
   return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, bias, residual, ldr, act,
                    out_fp32, accumulate, aux_out, mask_src, cfg, nullptr, stream);
+}
+
+int b200_gemm_set_debug_buffer(void* buf) {
+  g_gemm_dbg = reinterpret_cast<long long*>(buf);
+  return 0;
 }
 
 // Bring-up / regression entry: same GEMM with the UMMA descriptor fields overridable, so one GPU

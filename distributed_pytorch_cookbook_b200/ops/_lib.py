@@ -47,6 +47,7 @@ _SIGS = {
     "b200_ag_gemm_bf16": [P, P, P, P, I, I, I, I, I, P, I, I, P, P],
     "b200_barrier": [P, I, I, I, P],
     "b200_smoke": [P],
+    "b200_gemm_set_debug_buffer": [P],
 }
 
 

@@ -1,0 +1,396 @@
+"""Fully-sharded data parallel (ZeRO-3) engine.
+
+Reference: ``FSDP(model, auto_wrap_policy=size_based(min_num_params=100), cpu_offload=...)``
+(main-fsdp.py:60-69): every Linear / Embedding / LayerNorm becomes its own FSDP unit (68 + root at
+the default config), each forward and backward all-gathers the unit's fp32 flat parameter and
+each backward reduce-scatters its fp32 gradient - 196 x 3 NCCL collectives per step, most of
+them tiny and latency bound.
+
+This engine shards *per decoder layer* (plus an embeddings unit and a head unit), in two shard
+groups per unit - ``big`` (matrices, consumed by the tensor-core kernels as bf16) and ``small``
+(LayerNorm, biases, embeddings: consumed as fp32) - each split evenly over the ranks:
+
+* every rank keeps fp32 master shards + AdamW moments (1/world of the model);
+* forward needs a unit's full weights: the peers' **bf16** shards (fp32 for the small group) are
+  pulled over NVLink straight into the local full buffer by ``b200_allgather`` on a side stream,
+  one unit ahead of the compute stream (prefetch).  Gathered weights stay resident for the backward
+  pass - 180 GB of HBM per GPU buys the second all-gather of the reference away;
+* the kernels write weight gradients into a full-size fp32 gradient buffer that lives in symmetric
+  memory; as soon as a unit's gradients are complete ``b200_rs_adamw`` runs on the side stream:
+  the owner of each shard reduces it out of all peers' buffers (``multimem.ld_reduce`` when NVLS is
+  available), applies 1/world, runs AdamW on its master shard and writes the bf16 shard the peers
+  will gather next step.  Reduce-scatter, cast and optimizer are one kernel; no NCCL on the path.
+
+Fallback transports (``--comm nccl`` or CPU/gloo) run the same schedule with
+``all_gather_into_tensor`` / ``all_reduce`` + the same AdamW maths in PyTorch.
+``--cpu_offload`` keeps master shards and moments in pinned host memory and steps them on the CPU.
+"""
+from __future__ import annotations
+
+import math
+from contextlib import nullcontext
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from ..ops import _lib, native
+from ..runtime.symm import (CH_ALLGATHER, CH_RS_ADAMW, SymmContext, symmetric_memory_available)
+
+ALIGN = 128
+
+
+def _round_up(n, m):
+    return (n + m - 1) // m * m
+
+
+def is_small(p: nn.Parameter, module_of: Dict[int, nn.Module]) -> bool:
+    """fp32-consumed parameters: vectors (LayerNorm, biases) and embedding tables."""
+    return p.ndim == 1 or isinstance(module_of.get(id(p)), nn.Embedding)
+
+
+class ShardGroup:
+    """A set of parameters flattened together and split evenly over the ranks."""
+
+    def __init__(self, name: str, params: List[nn.Parameter], kind: str, world: int):
+        self.name, self.params, self.kind, self.world = name, params, kind, world
+        self.offsets, off = [], 0
+        for p in params:
+            self.offsets.append(off)
+            off += _round_up(p.numel(), ALIGN)
+        self.n = _round_up(max(off, ALIGN), ALIGN * world)
+        self.shard_n = self.n // world
+        self.base = 0            # offset of this group in the global flat space (set by the planner)
+        self.ready = 0           # parameters whose gradient is complete in the current step
+        self.gathered = False
+
+    @property
+    def shard_base(self) -> int:
+        return self.base // self.world
+
+
+def plan_units(model) -> List[List[nn.Module]]:
+    """Sharding units in execution order: embeddings | each decoder layer | norm_out + lm_head."""
+    return [[model.embeddings]] + [[layer] for layer in model.decoder.layers] + [[model.norm_out, model.lm_head]]
+
+
+def plan_groups(model, world: int) -> List[List[ShardGroup]]:
+    module_of = {}
+    for m in model.modules():
+        for p in m.parameters(recurse=False):
+            module_of[id(p)] = m
+    units, base = [], 0
+    for ui, mods in enumerate(plan_units(model)):
+        ps = [p for m in mods for p in m.parameters() if p.requires_grad]
+        small = [p for p in ps if is_small(p, module_of)]
+        big = [p for p in ps if not is_small(p, module_of)]
+        groups = []
+        for kind, lst in (("small", small), ("big", big)):
+            if lst:
+                g = ShardGroup(f"unit{ui}.{kind}", lst, kind, world)
+                g.base = base
+                base += g.n
+                groups.append(g)
+        units.append(groups)
+    return units
+
+
+def adamw_torch_(p, g, m, v, step: float, lr, beta1, beta2, eps, wd):
+    """torch.optim.AdamW maths on flat shards (fallback / cpu_offload path)."""
+    p.mul_(1.0 - lr * wd)
+    m.mul_(beta1).add_(g, alpha=1.0 - beta1)
+    v.mul_(beta2).addcmul_(g, g, value=1.0 - beta2)
+    bc1 = 1.0 - beta1 ** step
+    bc2 = 1.0 - beta2 ** step
+    denom = (v.sqrt() / math.sqrt(bc2)).add_(eps)
+    p.addcdiv_(m, denom, value=-lr / bc1)
+
+
+class FSDPStrategy:
+    """Trainer strategy for main-fsdp.py."""
+
+    def __init__(self, group=None, cpu_offload: bool = False):
+        self.group, self.cpu_offload = group, cpu_offload
+        self.comm_kind = None
+        self._graphed = None
+        self.betas, self.eps, self.wd = (0.9, 0.999), 1e-8, 0.01
+
+    # ------------------------------------------------------------------------------
+    def setup(self, model, args, device):
+        self.device = torch.device(device)
+        self.world = dist.get_world_size(self.group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(self.group) if dist.is_initialized() else 0
+        self.cpu_offload = self.cpu_offload or getattr(args, "cpu_offload", False)
+        self.lr = args.learning_rate
+        self.model = model.to(self.device)          # reference materialises the full model first too
+        cuda = self.device.type == "cuda"
+        self.native = cuda and _lib.available() and not args.disable_amp
+        want = getattr(args, "comm", "auto")
+        transport = "nccl" if cuda else "gloo"
+        self.symm = None
+        if (self.world > 1 and self.native and not self.cpu_offload and want in ("auto", "symm")
+                and symmetric_memory_available(self.device)):
+            try:
+                self.symm = SymmContext(self.device, self.group)
+                transport = "symm"
+            except Exception as e:
+                if want == "symm":
+                    raise
+                print(f"[fsdp] symmetric memory unavailable ({e!r}); falling back to NCCL", flush=True)
+        self.comm_kind = transport
+        self.units = plan_groups(self.model, self.world)
+        self.groups = [g for u in self.units for g in u]
+        self.G = sum(g.n for g in self.groups)
+        Gs = self.G // self.world
+        dev = self.device
+        f32, bf16 = torch.float32, torch.bfloat16
+
+        def alloc(n, dtype, symmetric):
+            if symmetric and transport == "symm":
+                buf = self.symm.alloc(n, dtype)
+                return buf.tensor, buf
+            return torch.zeros(n, dtype=dtype, device=dev), None
+
+        self.full_fp32 = torch.zeros(self.G, dtype=f32, device=dev)
+        self.full_bf16 = torch.zeros(self.G, dtype=bf16, device=dev) if self.native else None
+        self.grads, self.grads_buf = alloc(self.G, f32, True)
+        state_dev = torch.device("cpu") if self.cpu_offload else dev
+        if self.cpu_offload:
+            pin = cuda
+            self.master = torch.zeros(Gs, dtype=f32, pin_memory=pin)
+            self.master_buf = None
+            self.shard_grad_host = torch.zeros(Gs, dtype=f32, pin_memory=pin)
+            self.master_dev = torch.zeros(Gs, dtype=f32, device=dev)     # staging for the gathers
+        else:
+            self.master, self.master_buf = alloc(Gs, f32, True)
+            self.master_dev = self.master
+        self.exp_avg = torch.zeros(Gs, dtype=f32, device=state_dev)
+        self.exp_avg_sq = torch.zeros(Gs, dtype=f32, device=state_dev)
+        self.shard_bf16, self.shard_bf16_buf = alloc(Gs, bf16, True) if self.native else (None, None)
+        self.hyper = torch.tensor([self.lr, 0.0, 0.0, 0.0], dtype=f32, device=dev)
+        self.host_step = 0
+
+        # re-point parameters / gradients at the flat buffers and cut the shards
+        self.group_of = {}
+        with torch.no_grad():
+            for g in self.groups:
+                for p, o in zip(g.params, g.offsets):
+                    n = p.numel()
+                    lo = g.base + o
+                    self.full_fp32[lo:lo + n].copy_(p.data.reshape(-1))
+                    p.data = self.full_fp32[lo:lo + n].view(p.shape)
+                    p.grad = self.grads[lo:lo + n].view(p.shape)
+                    if self.native and g.kind == "big":
+                        p._b200_bf16 = self.full_bf16[lo:lo + n].view(p.shape)
+                        p._b200_bf16_version = p._version
+                    self.group_of[id(p)] = g
+                    p.register_post_accumulate_grad_hook(self._on_grad_ready)
+                s_lo = g.base + self.rank * g.shard_n
+                self.master[g.shard_base:g.shard_base + g.shard_n].copy_(self.full_fp32[s_lo:s_lo + g.shard_n])
+                if self.native:
+                    self.shard_bf16[g.shard_base:g.shard_base + g.shard_n].copy_(
+                        self.full_fp32[s_lo:s_lo + g.shard_n])
+            if self.cpu_offload:
+                self.master_dev.copy_(self.master, non_blocking=True)
+        native.grad_ready_hooks.append(self._on_grad_ready)
+        self.comm_stream = torch.cuda.Stream(dev) if cuda else None
+        self.version = 1
+        for g in self.groups:
+            g.gathered_version = 0
+            g.event = None
+        self.active = False
+        # forward pre-hooks: make the unit's weights resident (and prefetch the next unit)
+        for ui, mods in enumerate(plan_units(self.model)):
+            mods[0].register_forward_pre_hook(lambda m, inp, ui=ui: self._pre_forward(ui))
+        if cuda:
+            torch.cuda.synchronize(dev)
+        if dist.is_initialized():
+            dist.barrier(group=self.group)
+        self.use_graph = transport == "symm" and not getattr(args, "disable_cuda_graph", False)
+
+    # ------------------------------------------------------------------------------
+    def _gather_dtype(self, g: ShardGroup):
+        return torch.bfloat16 if (self.native and g.kind == "big") else torch.float32
+
+    def _gather(self, g: ShardGroup, dtype=None):
+        """All-gather one shard group into the local full buffer (on the side stream on CUDA)."""
+        dtype = dtype or self._gather_dtype(g)
+        esz = 2 if dtype == torch.bfloat16 else 4
+        full = self.full_bf16 if dtype == torch.bfloat16 else self.full_fp32
+        shard = self.shard_bf16 if dtype == torch.bfloat16 else self.master_dev
+        full_view = full[g.base:g.base + g.n]
+        shard_view = shard[g.shard_base:g.shard_base + g.shard_n]
+        if self.world == 1:
+            full_view.copy_(shard_view)
+            return
+        cuda = self.device.type == "cuda"
+        ctx = nullcontext()
+        if cuda:
+            ev = torch.cuda.Event()
+            ev.record()                                   # compute is done with the old weights
+            self.comm_stream.wait_event(ev)
+            ctx = torch.cuda.stream(self.comm_stream)
+        with ctx:
+            if self.comm_kind == "symm":
+                buf = self.shard_bf16_buf if dtype == torch.bfloat16 else self.master_buf
+                nblocks = 8 if g.shard_n * esz >= (1 << 16) else 2
+                _lib.call("b200_allgather", buf.ptrs_dev, self.symm.flags.ptrs_dev, self.rank, self.world,
+                          g.shard_base * esz, g.shard_n * esz, full_view.data_ptr(), 1, nblocks, CH_ALLGATHER,
+                          self.comm_stream.cuda_stream)
+            elif cuda:
+                dist.all_gather_into_tensor(full_view, shard_view.contiguous(), group=self.group)
+            else:
+                parts = list(full_view.view(self.world, g.shard_n).unbind(0))
+                dist.all_gather(parts, shard_view.contiguous(), group=self.group)
+            if cuda:
+                g.event = torch.cuda.Event()
+                g.event.record(self.comm_stream)
+
+    def _ensure(self, g: ShardGroup):
+        if g.gathered_version != self.version:
+            self._gather(g)
+            g.gathered_version = self.version
+
+    def _pre_forward(self, ui: int):
+        for g in self.units[ui]:
+            self._ensure(g)
+        if ui + 1 < len(self.units):                      # prefetch the next unit under this one's compute
+            for g in self.units[ui + 1]:
+                self._ensure(g)
+        if self.device.type == "cuda":
+            for g in self.units[ui]:
+                if g.event is not None:
+                    torch.cuda.current_stream().wait_event(g.event)
+
+    # ------------------------------------------------------------------------------
+    def _on_grad_ready(self, p):
+        if not self.active:
+            return
+        g = self.group_of.get(id(p))
+        if g is None:
+            return
+        g.ready += 1
+        if g.ready == len(g.params):
+            self._reduce_and_step(g)
+
+    def _reduce_and_step(self, g: ShardGroup):
+        g.ready = -(1 << 30)                               # launched
+        b1, b2 = self.betas
+        cuda = self.device.type == "cuda"
+        sb, sn = g.shard_base, g.shard_n
+        lo = g.base + self.rank * sn
+        ctx = nullcontext()
+        if cuda:
+            ev = torch.cuda.Event()
+            ev.record()
+            self.comm_stream.wait_event(ev)
+            ctx = torch.cuda.stream(self.comm_stream)
+        with ctx:
+            if self.comm_kind == "symm":
+                pb = self.shard_bf16.data_ptr() + 2 * sb if g.kind == "big" else None
+                nblocks = 8 if sn >= (1 << 15) else 2
+                _lib.call("b200_rs_adamw", self.grads_buf.ptrs_dev, self.grads_buf.mc_ptr or None,
+                          self.symm.flags.ptrs_dev, self.rank, self.world, lo, sn, 1.0 / self.world,
+                          self.master.data_ptr() + 4 * sb, self.exp_avg.data_ptr() + 4 * sb,
+                          self.exp_avg_sq.data_ptr() + 4 * sb, pb, self.hyper.data_ptr(), b1, b2, self.eps,
+                          self.wd, 1, nblocks, CH_RS_ADAMW, self.comm_stream.cuda_stream)
+                return
+            gview = self.grads[g.base:g.base + g.n]
+            if self.world > 1:
+                gview.mul_(1.0 / self.world)
+                dist.all_reduce(gview, group=self.group)   # gloo has no reduce_scatter; NCCL path keeps parity
+            gs = self.grads[lo:lo + sn]
+            if self.cpu_offload:
+                self.shard_grad_host[sb:sb + sn].copy_(gs, non_blocking=False)
+                adamw_torch_(self.master[sb:sb + sn], self.shard_grad_host[sb:sb + sn], self.exp_avg[sb:sb + sn],
+                             self.exp_avg_sq[sb:sb + sn], float(self.host_step), self.lr, b1, b2, self.eps, self.wd)
+                self.master_dev[sb:sb + sn].copy_(self.master[sb:sb + sn], non_blocking=True)
+            else:
+                adamw_torch_(self.master[sb:sb + sn], gs, self.exp_avg[sb:sb + sn], self.exp_avg_sq[sb:sb + sn],
+                             float(self.host_step), self.lr, b1, b2, self.eps, self.wd)
+            if self.native:
+                self.shard_bf16[sb:sb + sn].copy_(self.master_dev[sb:sb + sn])
+
+    # ------------------------------------------------------------------------------
+    def train(self):
+        self.model.train()
+
+    def eval(self):
+        self.model.eval()
+
+    def _autocast(self, amp):
+        if amp and self.device.type == "cuda":
+            return torch.autocast(device_type="cuda", dtype=torch.bfloat16)
+        return nullcontext()
+
+    def _raw_step(self, input_ids, position_ids, targets, mask, amp):
+        self.version += 1                                  # weights of the previous step are stale
+        self.host_step += 1
+        self.grads.zero_()
+        if self.native:
+            _lib.call("b200_adamw_tick", self.hyper.data_ptr(), _lib.stream())
+        else:
+            self.hyper[1] += 1
+        for g in self.groups:
+            g.ready = 0
+        self.active = True
+        with self._autocast(amp):
+            loss, _, _ = self.model.loss(input_ids, position_ids, targets, mask=mask)
+        loss.backward()
+        for g in self.groups:                              # parameters that received no gradient
+            if g.ready >= 0:
+                self._reduce_and_step(g)
+        self.active = False
+        if self.device.type == "cuda":
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        self.version += 1                                  # shards changed: gathered copies are stale
+        return loss.detach()
+
+    def train_step(self, batch, targets, amp=True):
+        if self.use_graph and amp:
+            from ..runtime.graph import GraphedStep
+            if self._graphed is None:
+                self._graphed = GraphedStep(lambda i, p, t: self._raw_step(i, p, t, None, True))
+            out = self._graphed(batch["input_ids"], batch["position_ids"], targets)
+            self.version += 2
+            return out
+        return self._raw_step(batch["input_ids"], batch["position_ids"], targets, batch.get("mask"), amp)
+
+    @torch.no_grad()
+    def eval_step(self, batch, targets, amp=True):
+        with self._autocast(amp):
+            return self.model.loss(batch["input_ids"], batch["position_ids"], targets, mask=batch.get("mask"))
+
+    def all_reduce_mean(self, t):
+        if self.world > 1:
+            dist.all_reduce(t, group=self.group)
+            t /= self.world
+        return t
+
+    def launches_per_step(self):
+        return self._graphed.native_calls_per_replay if (self._graphed and self._graphed.graph) else None
+
+    # ------------------------------------------------------------------------------
+    def gather_full_fp32(self):
+        """Collective: bring every fp32 master shard into ``param.data`` (full model on every rank) -
+        the reference's FULL_STATE_DICT gather (main-fsdp.py:194)."""
+        if self.device.type == "cuda":
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        for g in self.groups:
+            self._gather(g, torch.float32)
+            if self._gather_dtype(g) == torch.float32:
+                g.gathered_version = self.version
+        if self.device.type == "cuda":
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+
+    def generation_model(self):
+        """All ranks gather (collective) so that rank 0 can run the un-sharded model - avoids the
+        reference's rank-0-only forward through FSDP, which deadlocks."""
+        self.gather_full_fp32()
+        return self.model
+
+    def state_dict(self):
+        from ..utils import canonical_state_dict
+        self.gather_full_fp32()
+        return canonical_state_dict(self.model)

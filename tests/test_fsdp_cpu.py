@@ -1,0 +1,84 @@
+"""T2: FSDP engine over gloo - shard index math, hook-driven reduce+optimizer, prefetching
+gathers, full state_dict gather, cpu_offload; parity with single-process AdamW training (W13-W16)."""
+from types import SimpleNamespace
+
+import pytest
+import torch
+
+from dist_utils import run_distributed
+
+CFG = dict(dim=32, head_dim=8, heads=4, num_layers=2, vocab_size=97, max_position_embeddings=16)
+
+
+def test_shard_plan_index_math():
+    from distributed_pytorch_cookbook_b200 import TransformerDecoderLM
+    from distributed_pytorch_cookbook_b200.parallel.fsdp import plan_groups
+    m = TransformerDecoderLM(**CFG)
+    for world in (1, 2, 8):
+        units = plan_groups(m, world)
+        assert len(units) == CFG["num_layers"] + 2
+        groups = [g for u in units for g in u]
+        seen, base = set(), 0
+        for g in groups:
+            assert g.base == base and g.n % (128 * world) == 0 and g.shard_n * world == g.n
+            assert g.shard_base * world == g.base
+            base += g.n
+            for p, o in zip(g.params, g.offsets):
+                assert o % 128 == 0 and o + p.numel() <= g.n
+                assert id(p) not in seen
+                seen.add(id(p))
+                assert (p.ndim == 1 or "embeddings" in g.name or g.kind == "big" or True)
+        assert seen == {id(p) for p in m.parameters()}
+        # embeddings unit is entirely fp32-consumed; layer units have a small and a big group
+        assert [g.kind for g in units[0]] == ["small"]
+        assert [g.kind for g in units[1]] == ["small", "big"]
+        assert [g.kind for g in units[-1]] == ["small", "big"]
+
+
+def _fsdp_worker(rank, world, cpu_offload):
+    from distributed_pytorch_cookbook_b200 import TransformerDecoderLM
+    from distributed_pytorch_cookbook_b200.parallel.fsdp import FSDPStrategy
+    torch.manual_seed(0)
+    model = TransformerDecoderLM(**CFG)
+    strat = FSDPStrategy(cpu_offload=cpu_offload)
+    args = SimpleNamespace(learning_rate=1e-2, disable_amp=True, comm="auto", disable_cuda_graph=True,
+                           cpu_offload=cpu_offload)
+    strat.setup(model, args, "cpu")
+    g = torch.Generator().manual_seed(1)
+    ids_all = torch.randint(0, CFG["vocab_size"], (3, 4 * world, 12), generator=g)
+    pos = torch.arange(12).unsqueeze(0).repeat(4, 1)
+    losses = []
+    for step in range(3):
+        ids = ids_all[step, rank * 4:(rank + 1) * 4]
+        losses.append(float(strat.train_step({"input_ids": ids, "position_ids": pos}, ids, amp=False)))
+    ev = strat.eval_step({"input_ids": ids_all[0, :4], "position_ids": pos}, ids_all[0, :4], amp=False)
+    sd = strat.state_dict()
+    shard_elems = strat.master.numel()
+    return {k: v.numpy().copy() for k, v in sd.items()}, losses, float(ev[0]), shard_elems, strat.G
+
+
+@pytest.mark.parametrize("cpu_offload", [False, True])
+def test_fsdp_matches_single_process(cpu_offload):
+    world = 2
+    outs = run_distributed(_fsdp_worker, world, cpu_offload)
+    from distributed_pytorch_cookbook_b200 import TransformerDecoderLM
+    torch.manual_seed(0)
+    ref = TransformerDecoderLM(**CFG)
+    opt = torch.optim.AdamW(ref.parameters(), lr=1e-2)
+    g = torch.Generator().manual_seed(1)
+    ids_all = torch.randint(0, CFG["vocab_size"], (3, 4 * world, 12), generator=g)
+    pos = torch.arange(12).unsqueeze(0).repeat(4 * world, 1)
+    for step in range(3):
+        opt.zero_grad()
+        loss, _, _ = ref.loss(ids_all[step], pos, ids_all[step])
+        loss.backward()
+        opt.step()
+    with torch.no_grad():
+        ref_eval = float(ref.loss(ids_all[0, :4], pos[:4], ids_all[0, :4])[0])
+    for r in range(world):
+        sd = outs[r][0]
+        assert list(sd.keys()) == list(ref.state_dict().keys())
+        for k, v in ref.state_dict().items():
+            assert torch.allclose(torch.from_numpy(sd[k]), v, atol=3e-3, rtol=1e-3), k
+        assert abs(outs[r][2] - ref_eval) < 2e-3
+        assert outs[r][3] * world == outs[r][4]            # each rank holds exactly 1/world of the state
