@@ -77,6 +77,25 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
                : "memory");
 }
 
+
+// Bit j of the result is set when key (key0 + j) is visible to query row q: inside the sequence,
+// not above the causal diagonal (only checked on diagonal tiles) and not a padding key.  Built once
+// per 32-key chunk (one predicated byte load per lane + a ballot), so the per-element softmax
+// code is a bit test and a select - no branches.
+__device__ __forceinline__ uint32_t keep_bits(int key0, int q, bool diag, bool row_ok, int T,
+                                              const uint8_t* __restrict__ mask_row) {
+  int limit = T - key0;                       // keys < T
+  if (diag) limit = min(limit, q + 1 - key0);  // keys <= q
+  uint32_t bits = limit >= 32 ? 0xffffffffu : (limit <= 0 ? 0u : ((1u << limit) - 1u));
+  if (mask_row != nullptr) {
+    const int lane = threadIdx.x & 31;
+    const int key = key0 + lane;
+    const bool pad = key < T ? (mask_row[key] != 0) : true;
+    bits &= ~__ballot_sync(0xffffffffu, pad);
+  }
+  return row_ok ? bits : 0u;
+}
+
 struct AttnParams {
   const bf16* qkv;     // [B, T, 3*H*D]
   bf16* out;           // [B, T, H*D]
@@ -89,7 +108,26 @@ struct AttnParams {
   int B, T, H;
   float scale;
   int* err_word;
+  long long* dbg;  // optional per-CTA phase timestamps (32 slots), bring-up only
 };
+
+long long* g_attn_dbg = nullptr;
+
+__device__ __forceinline__ long long attn_global_ns() {
+  long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define ADBG(slot)                                                                                    \
+  do {                                                                                                \
+    if (p.dbg != nullptr && threadIdx.x == 0)                                                         \
+      p.dbg[((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 32 + (slot)] = clock64(); \
+  } while (0)
+#define ADBG_NS(slot)                                                                                 \
+  do {                                                                                                \
+    if (p.dbg != nullptr && threadIdx.x == 0)                                                         \
+      p.dbg[((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 32 + (slot)] = attn_global_ns(); \
+  } while (0)
 
 // ------------------------------------------------------------------------------------------
 // forward
@@ -114,6 +152,8 @@ attn_fwd_kernel(const AttnParams p) {
   const bf16* qkv_b = p.qkv + static_cast<size_t>(b) * p.T * row_stride;
   const int q0 = qt * TQ;
   const int q = q0 + tid;  // this thread's query row
+  ADBG(0);
+  ADBG_NS(24);
 
   if (tid == 0) {
     *abort_flag = 0;
@@ -133,6 +173,8 @@ attn_fwd_kernel(const AttnParams p) {
   const uint32_t idesc_s = umma_idesc_bf16(TQ, TK, 0, 0);
   const uint32_t idesc_pv = umma_idesc_bf16(TQ, D, 0, 1);
   const float sl2 = p.scale * kLog2e;
+  const uint8_t* mask_row = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
+  ADBG(1);
 
   float o[D];
 #pragma unroll
@@ -148,6 +190,7 @@ attn_fwd_kernel(const AttnParams p) {
     load_tile<D>(sV, qkv_b + static_cast<size_t>(k0) * row_stride + 2 * HD + h * D, min(TK, p.T - k0), row_stride);
     fence_proxy_async_smem();
     __syncthreads();
+    if (kt < 2) ADBG(2 + 6 * kt);
     if (tid == 0) {
       tcgen05_fence_after();
 #pragma unroll
@@ -159,6 +202,7 @@ attn_fwd_kernel(const AttnParams p) {
     phase ^= 1;
     if (!__syncthreads_and(ok)) { ok = false; break; }
     tcgen05_fence_after();
+    if (kt < 2) ADBG(3 + 6 * kt);
 
     // pass A: row max of the masked, scaled scores
     const bool diag = (kt == qt);
@@ -168,14 +212,12 @@ attn_fwd_kernel(const AttnParams p) {
       uint32_t r[32];
       tmem_ld_32x32b_x32(t_lane + c * 32, r);
       tmem_ld_wait();
+      const uint32_t kb = keep_bits(k0 + c * 32, q, diag, true, p.T, mask_row);
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int key = k0 + c * 32 + j;
-        bool keep = key < p.T && (!diag || key <= q);
-        if (keep && p.key_mask != nullptr) keep = p.key_mask[static_cast<size_t>(b) * p.T + key] == 0;
-        if (keep) m_tile = fmaxf(m_tile, __uint_as_float(r[j]));
-      }
+      for (int j = 0; j < 32; ++j)
+        m_tile = fmaxf(m_tile, ((kb >> j) & 1u) ? __uint_as_float(r[j]) : -INFINITY);
     }
+    if (kt < 2) ADBG(4 + 6 * kt);
     const float m_new = fmaxf(m_run, m_tile * p.scale);  // scale > 0
     const float m_safe = (m_new == -INFINITY) ? 0.f : m_new;
     const float alpha = exp2f((m_run - m_safe) * kLog2e);  // m_run = -inf -> 0
@@ -188,15 +230,14 @@ attn_fwd_kernel(const AttnParams p) {
       tmem_ld_32x32b_x32(t_lane + c * 32, r);
       tmem_ld_wait();
       uint32_t pk[16];
+      const uint32_t kb = keep_bits(k0 + c * 32, q, diag, true, p.T, mask_row);
 #pragma unroll
       for (int j = 0; j < 32; j += 2) {
         float pv[2];
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
-          const int key = k0 + c * 32 + j + u;
-          bool keep = key < p.T && (!diag || key <= q);
-          if (keep && p.key_mask != nullptr) keep = p.key_mask[static_cast<size_t>(b) * p.T + key] == 0;
-          pv[u] = keep ? exp2f(__uint_as_float(r[j + u]) * sl2 - m_l2) : 0.f;
+          const float e = exp2f(__uint_as_float(r[j + u]) * sl2 - m_l2);
+          pv[u] = ((kb >> (j + u)) & 1u) ? e : 0.f;
         }
         // sum what the tensor core will actually see (bf16-rounded), like the reference bf16 path
         const uint32_t packed = pack_bf16x2(pv[0], pv[1]);
@@ -214,6 +255,7 @@ attn_fwd_kernel(const AttnParams p) {
     tcgen05_fence_before();
     fence_proxy_async_smem();
     __syncthreads();
+    if (kt < 2) ADBG(5 + 6 * kt);
     if (tid == 0) {
       tcgen05_fence_after();
 #pragma unroll
@@ -225,6 +267,7 @@ attn_fwd_kernel(const AttnParams p) {
     phase ^= 1;
     if (!__syncthreads_and(ok)) { ok = false; break; }
     tcgen05_fence_after();
+    if (kt < 2) ADBG(6 + 6 * kt);
 #pragma unroll
     for (int c = 0; c < D / 32; ++c) {
       uint32_t r[32];
@@ -234,6 +277,7 @@ attn_fwd_kernel(const AttnParams p) {
       for (int j = 0; j < 32; ++j) o[c * 32 + j] = o[c * 32 + j] * alpha + __uint_as_float(r[j]);
     }
     tcgen05_fence_before();
+    if (kt < 2) ADBG(7 + 6 * kt);
   }
 
   if (ok && q < p.T) {
@@ -247,12 +291,14 @@ attn_fwd_kernel(const AttnParams p) {
     }
     p.lse[(static_cast<size_t>(b) * p.H + h) * p.T + q] = l_run > 0.f ? m_run + logf(l_run) : -INFINITY;
   }
+  ADBG(20);
   tcgen05_fence_before();
   __syncthreads();
   if (warp == 0) {
     tcgen05_fence_after();
     tmem_dealloc(tmem, TMEM_COLS);
   }
+  ADBG_NS(25);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -331,6 +377,7 @@ attn_bwd_kernel(const AttnParams p) {
   const uint32_t idesc_tt = umma_idesc_bf16(TK, D, 1, 1);     // dV, dK: MN-major x MN-major, N = D
   const uint32_t idesc_dq = umma_idesc_bf16(TQ, D, 0, 1);     // dQ: K-major x MN-major, N = D
   const float sl2 = p.scale * kLog2e;
+  const uint8_t* mask_row = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
 
   uint32_t phase = 0;
   bool ok = true;
@@ -369,15 +416,14 @@ attn_bwd_kernel(const AttnParams p) {
       tmem_ld_32x32b_x32(t_lane + C_DP + c * 32, rd);
       tmem_ld_wait();
       uint32_t pk[16], dk[16];
+      const uint32_t kb = keep_bits(k0 + c * 32, q, diag, q_ok, p.T, mask_row);
 #pragma unroll
       for (int j = 0; j < 32; j += 2) {
         float pv[2], dsv[2];
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
-          const int key = k0 + c * 32 + j + u;
-          bool keep = q_ok && key < p.T && (!diag || key <= q);
-          if (keep && p.key_mask != nullptr) keep = p.key_mask[static_cast<size_t>(b) * p.T + key] == 0;
-          const float pr = keep ? exp2f(__uint_as_float(rs[j + u]) * sl2 - lse_l2) : 0.f;
+          const float e = exp2f(__uint_as_float(rs[j + u]) * sl2 - lse_l2);
+          const float pr = ((kb >> (j + u)) & 1u) ? e : 0.f;
           pv[u] = pr;
           dsv[u] = pr * (__uint_as_float(rd[j + u]) - delta) * p.scale;
         }
@@ -533,6 +579,11 @@ int bwd_launch(const AttnParams& p, cudaStream_t st) {
 
 extern "C" {
 
+int b200_attn_set_debug_buffer(void* buf) {
+  g_attn_dbg = reinterpret_cast<long long*>(buf);
+  return 0;
+}
+
 int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int D, float scale,
                   const void* key_mask, void* stream) {
   B200_REQUIRE(D == 32 || D == 64 || D == 128, "attention: head_dim %d not supported (32, 64, 128)", D);
@@ -544,6 +595,7 @@ int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, i
   p.key_mask = reinterpret_cast<const uint8_t*>(key_mask);
   p.B = B; p.T = T; p.H = H; p.scale = scale;
   p.err_word = b200_error_word();
+  p.dbg = g_attn_dbg;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (D == 32) return fwd_launch<32>(p, st);
   if (D == 64) return fwd_launch<64>(p, st);

@@ -63,6 +63,42 @@ __global__ void embedding_bwd_kernel(const int64_t* __restrict__ ids, const int6
 }
 
 // ------------------------------------------------------------------------------------------
+// Column reductions (bias / gamma / beta gradients) without same-address atomic pile-ups: every
+// block adds its partial column sums into one of REPLICAS replica rows of a scratch buffer (so a
+// cache line sees 1/REPLICAS of the atomics), then takes a ticket; the block that draws the last
+// ticket folds the replicas into the real gradient and leaves scratch and ticket counter zeroed
+// for the next launch (so the kernels replay inside a CUDA graph).
+// scratch: [REPLICAS][ncols] floats, zero on entry;  counter: one int, zero on entry.
+// Launches that share one scratch buffer must not overlap on the GPU.
+// ------------------------------------------------------------------------------------------
+constexpr int REPLICAS = 16;
+
+__device__ __forceinline__ void finish_column_sums(float* __restrict__ scratch, int* __restrict__ counter,
+                                                   int ncols, int total_blocks, float* __restrict__ out_a,
+                                                   float* __restrict__ out_b, int split) {
+  __shared__ int s_last;
+  __threadfence();
+  __syncthreads();
+  const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+  const int nthreads = blockDim.x * blockDim.y;
+  if (tid == 0) s_last = (atomicAdd(counter, 1) == total_blocks - 1) ? 1 : 0;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  for (int c = tid; c < ncols; c += nthreads) {
+    float s = 0.f;
+#pragma unroll
+    for (int r = 0; r < REPLICAS; ++r) {
+      s += __ldcg(scratch + r * ncols + c);
+      scratch[r * ncols + c] = 0.f;
+    }
+    if (c < split) out_a[c] += s;
+    else out_b[c - split] += s;
+  }
+  if (tid == 0) *counter = 0;
+}
+
+// ------------------------------------------------------------------------------------------
 // LayerNorm: one warp per row, NV float4 per lane held in registers (dim <= NV*128)
 // ------------------------------------------------------------------------------------------
 template <int NV>
@@ -123,7 +159,8 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
                      const float* __restrict__ gamma, const float* __restrict__ mean_in,
                      const float* __restrict__ rstd_in, const float* __restrict__ dres,
                      float* __restrict__ dx, bf16* __restrict__ dx_bf16, float* __restrict__ dgamma,
-                     float* __restrict__ dbeta, int rows, int dim) {
+                     float* __restrict__ dbeta, int rows, int dim, float* __restrict__ scratch,
+                     int* __restrict__ counter) {
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int warps_per_block = blockDim.x >> 5;
@@ -199,12 +236,13 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
     }
   }
   __syncthreads();
+  float* rep = scratch + static_cast<size_t>(blockIdx.x % REPLICAS) * 2 * dim;
   for (int j = threadIdx.x; j < 2 * dim; j += blockDim.x) {
     float s = 0.f;
     for (int w = 0; w < warps_per_block; ++w) s += red[static_cast<size_t>(w) * 2 * dim + j];
-    if (j < dim) atomicAdd(dgamma + j, s);
-    else atomicAdd(dbeta + (j - dim), s);
+    atomicAdd(rep + j, s);
   }
+  finish_column_sums(scratch, counter, 2 * dim, gridDim.x, dgamma, dbeta, dim);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -279,17 +317,21 @@ cast_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, int64_t n
 // dz = dy * (y_act > 0) -> bf16 ; dbias += column sums of dz.  block (32, 8): 32 column groups of
 // 8 columns x 8 row lanes, 64 rows per block.
 // ------------------------------------------------------------------------------------------
+constexpr int RELU_ROWS = 64;  // rows per block (8 row lanes x 8)
+
 template <bool DY_FP32>
 __global__ void __launch_bounds__(256)
 relu_bwd_kernel(const void* __restrict__ dy_, const bf16* __restrict__ y_act, bf16* __restrict__ dz,
-                float* __restrict__ dbias, int rows, int cols, int ld) {
+                float* __restrict__ dbias, int rows, int cols, int ld, float* __restrict__ scratch,
+                int* __restrict__ counter) {
   const int cg = blockIdx.x * 32 + threadIdx.x;  // column group (8 columns)
   const int col = cg * 8;
   const bool col_ok = col < cols;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  const int r0 = blockIdx.y * 64;
+  const int r0 = blockIdx.y * RELU_ROWS;
   if (col_ok) {
-    for (int r = r0 + threadIdx.y; r < min(r0 + 64, rows); r += 8) {
+#pragma unroll 2
+    for (int r = r0 + threadIdx.y; r < min(r0 + RELU_ROWS, rows); r += 8) {
       const size_t off = static_cast<size_t>(r) * ld + col;
       float v[8];
       if (DY_FP32) {
@@ -332,9 +374,10 @@ relu_bwd_kernel(const void* __restrict__ dy_, const bf16* __restrict__ y_act, bf
       float s = 0.f;
 #pragma unroll
       for (int w = 0; w < 8; ++w) s += red[w][threadIdx.x][j];
-      atomicAdd(dbias + col + j, s);
+      atomicAdd(scratch + (blockIdx.y % REPLICAS) * cols + col + j, s);
     }
   }
+  finish_column_sums(scratch, counter, cols, gridDim.x * gridDim.y, dbias, dbias, cols);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -359,14 +402,21 @@ __global__ void count_valid_kernel(const int64_t* __restrict__ targets, float* _
 }
 
 constexpr int CE_THREADS = 512;
-constexpr int CE_CACHE = 16;  // uint4 (8 bf16) per thread held in registers: vocab <= 65536
 
-// One block per row.  logits row is read once into registers, reduced (max / argmax / sum-exp),
-// and - when write_grad - overwritten in place with dlogits = (softmax - onehot) * scale.
-__global__ void __launch_bounds__(CE_THREADS)
+__device__ __forceinline__ void cp_async_16(uint32_t smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
+
+// One block per row.  The logits row (bf16, <= 113 KB) is staged in shared memory with cp.async (no
+// register staging, so two rows per SM overlap each other's phases), reduced (max / argmax /
+// sum-exp) and - when write_grad - overwritten in place in global memory with
+// dlogits = (softmax - onehot) * scale.  exp() is evaluated once per element: p = exp(l - max) is
+// written back to the staged row as bf16 and reused by the gradient pass.
+__global__ void __launch_bounds__(CE_THREADS, 2)
 ce_fwd_bwd_kernel(bf16* __restrict__ logits, const int64_t* __restrict__ targets,
                   float* __restrict__ stats, int vocab, int ld, int ignore_index, int write_grad,
                   float grad_scale) {
+  extern __shared__ uint4 srow[];
   const int row = blockIdx.x;
   bf16* lr = logits + static_cast<size_t>(row) * ld;
   const int64_t tgt64 = targets[row];
@@ -384,24 +434,24 @@ ce_fwd_bwd_kernel(bf16* __restrict__ logits, const int64_t* __restrict__ targets
         reinterpret_cast<uint4*>(lr)[c] = make_uint4(0u, 0u, 0u, 0u);
     return;
   }
-  const float tgt_logit = __bfloat162float(lr[tgt]);  // read before anything is overwritten
+  const uint32_t sbase = smem_u32(srow);
+  for (int c = threadIdx.x; c < nvec; c += CE_THREADS) cp_async_16(sbase + c * 16, reinterpret_cast<const uint4*>(lr) + c);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  const float tgt_logit = __bfloat162float(lr[tgt]);
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
 
-  uint4 cache[CE_CACHE];
   float mx = -INFINITY;
   int arg = 0;
+  for (int c = threadIdx.x; c < nvec; c += CE_THREADS) {
+    const uint4 u = srow[c];
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
-  for (int i = 0; i < CE_CACHE; ++i) {
-    const int c = threadIdx.x + i * CE_THREADS;
-    if (c < nvec) {
-      cache[i] = reinterpret_cast<const uint4*>(lr)[c];
-      const uint32_t w[4] = {cache[i].x, cache[i].y, cache[i].z, cache[i].w};
-#pragma unroll
-      for (int t = 0; t < 4; ++t) {
-        const float2 f = unpack_bf16x2(w[t]);
-        const int col = c * 8 + 2 * t;
-        if (col < vocab && f.x > mx) { mx = f.x; arg = col; }
-        if (col + 1 < vocab && f.y > mx) { mx = f.y; arg = col + 1; }
-      }
+    for (int t = 0; t < 4; ++t) {
+      const float2 f = unpack_bf16x2(w[t]);
+      const int col = c * 8 + 2 * t;
+      if (col < vocab && f.x > mx) { mx = f.x; arg = col; }
+      if (col + 1 < vocab && f.y > mx) { mx = f.y; arg = col + 1; }
     }
   }
   // block argmax (ties -> lowest index, like torch.argmax)
@@ -430,27 +480,22 @@ ce_fwd_bwd_kernel(bf16* __restrict__ logits, const int64_t* __restrict__ targets
   const float kLog2e = 1.4426950408889634f;
   const float mscaled = row_max * kLog2e;
 
-  // p = exp(l - max), kept as bf16 in the same registers; sum in fp32
   float sum = 0.f;
+  for (int c = threadIdx.x; c < nvec; c += CE_THREADS) {
+    const uint4 u = srow[c];
+    uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
-  for (int i = 0; i < CE_CACHE; ++i) {
-    const int c = threadIdx.x + i * CE_THREADS;
-    if (c < nvec) {
-      uint32_t w[4] = {cache[i].x, cache[i].y, cache[i].z, cache[i].w};
-#pragma unroll
-      for (int t = 0; t < 4; ++t) {
-        const float2 f = unpack_bf16x2(w[t]);
-        const int col = c * 8 + 2 * t;
-        const float p0 = col < vocab ? exp2f(f.x * kLog2e - mscaled) : 0.f;
-        const float p1 = col + 1 < vocab ? exp2f(f.y * kLog2e - mscaled) : 0.f;
-        sum += p0 + p1;
-        w[t] = pack_bf16x2(p0, p1);
-      }
-      cache[i] = make_uint4(w[0], w[1], w[2], w[3]);
+    for (int t = 0; t < 4; ++t) {
+      const float2 f = unpack_bf16x2(w[t]);
+      const int col = c * 8 + 2 * t;
+      const float p0 = col < vocab ? exp2f(f.x * kLog2e - mscaled) : 0.f;
+      const float p1 = col + 1 < vocab ? exp2f(f.y * kLog2e - mscaled) : 0.f;
+      sum += p0 + p1;
+      w[t] = pack_bf16x2(p0, p1);
     }
+    srow[c] = make_uint4(w[0], w[1], w[2], w[3]);   // same thread re-reads it below: no sync needed
   }
   sum = warp_sum(sum);
-  __syncthreads();  // s_f reuse
   if (lane == 0) s_f[warp] = sum;
   __syncthreads();
   if (warp == 0) {
@@ -469,22 +514,19 @@ ce_fwd_bwd_kernel(bf16* __restrict__ logits, const int64_t* __restrict__ targets
   const float n_valid = fmaxf(stats[0], 1.0f);
   const float scale = grad_scale / n_valid;
   const float pscale = scale / total;
+  for (int c = threadIdx.x; c < nvec; c += CE_THREADS) {
+    const uint4 u = srow[c];
+    uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
-  for (int i = 0; i < CE_CACHE; ++i) {
-    const int c = threadIdx.x + i * CE_THREADS;
-    if (c < nvec) {
-      uint32_t w[4] = {cache[i].x, cache[i].y, cache[i].z, cache[i].w};
-#pragma unroll
-      for (int t = 0; t < 4; ++t) {
-        const float2 f = unpack_bf16x2(w[t]);
-        const int col = c * 8 + 2 * t;
-        float g0 = f.x * pscale, g1 = f.y * pscale;
-        if (col == tgt) g0 -= scale;
-        if (col + 1 == tgt) g1 -= scale;
-        w[t] = pack_bf16x2(g0, g1);
-      }
-      reinterpret_cast<uint4*>(lr)[c] = make_uint4(w[0], w[1], w[2], w[3]);
+    for (int t = 0; t < 4; ++t) {
+      const float2 f = unpack_bf16x2(w[t]);
+      const int col = c * 8 + 2 * t;
+      float g0 = f.x * pscale, g1 = f.y * pscale;
+      if (col == tgt) g0 -= scale;
+      if (col + 1 == tgt) g1 -= scale;
+      w[t] = pack_bf16x2(g0, g1);
     }
+    reinterpret_cast<uint4*>(lr)[c] = make_uint4(w[0], w[1], w[2], w[3]);
   }
 }
 
@@ -539,8 +581,9 @@ int b200_layernorm_fwd(const float* x, const float* gamma, const float* beta, vo
 
 int b200_layernorm_bwd(const void* dy, const float* x, const float* gamma, const float* mean,
                        const float* rstd, const float* dres, float* dx, void* dx_bf16, float* dgamma,
-                       float* dbeta, int rows, int dim, void* stream) {
+                       float* dbeta, int rows, int dim, float* scratch, int* counter, void* stream) {
   B200_REQUIRE(dim % 4 == 0 && dim <= 4096, "layernorm: dim %d must be a multiple of 4 and <= 4096", dim);
+  B200_REQUIRE(scratch != nullptr && counter != nullptr, "layernorm_bwd: scratch (16 x 2*dim floats) and counter required");
   if (rows == 0) return 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int grid = b200_num_sms() * 4;
@@ -555,7 +598,7 @@ int b200_layernorm_bwd(const void* dy, const float* x, const float* gamma, const
       B200_CHECK_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NV>,                                \
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
     layernorm_bwd_kernel<NV><<<grid, 256, smem, st>>>(dyb, x, gamma, mean, rstd, dres, dx, dxb,     \
-                                                      dgamma, dbeta, rows, dim);                    \
+                                                      dgamma, dbeta, rows, dim, scratch, counter);  \
   } while (0)
   if (dim <= 256) LN_BWD(2);
   else if (dim <= 1024) LN_BWD(8);
@@ -597,27 +640,32 @@ int b200_cast_bf16(const float* in, void* out, int64_t n, void* stream) {
 }
 
 int b200_relu_bwd(const void* dy, const void* y_act, void* dz, float* dbias, int rows, int cols,
-                  int dy_fp32, void* stream) {
+                  int dy_fp32, float* scratch, int* counter, void* stream) {
   B200_REQUIRE(cols % 8 == 0, "relu_bwd: cols %d must be a multiple of 8", cols);
+  B200_REQUIRE(dbias == nullptr || (scratch != nullptr && counter != nullptr),
+               "relu_bwd: bias gradient needs scratch (16 x cols floats) and a counter");
   if (rows == 0) return 0;
-  dim3 grid(ceil_div(cols / 8, 32), ceil_div(rows, 64)), block(32, 8);
+  dim3 grid(ceil_div(cols / 8, 32), ceil_div(rows, RELU_ROWS)), block(32, 8);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dy_fp32)
     relu_bwd_kernel<true><<<grid, block, 0, st>>>(dy, reinterpret_cast<const bf16*>(y_act),
-                                                  reinterpret_cast<bf16*>(dz), dbias, rows, cols, cols);
+                                                  reinterpret_cast<bf16*>(dz), dbias, rows, cols, cols, scratch, counter);
   else
     relu_bwd_kernel<false><<<grid, block, 0, st>>>(dy, reinterpret_cast<const bf16*>(y_act),
-                                                   reinterpret_cast<bf16*>(dz), dbias, rows, cols, cols);
+                                                   reinterpret_cast<bf16*>(dz), dbias, rows, cols, cols, scratch,
+                                                   counter);
   B200_LAUNCH_CHECK();
   return 0;
 }
 
-int b200_colsum_bf16(const void* x, float* out_accum, int rows, int cols, int ld, void* stream) {
+int b200_colsum_bf16(const void* x, float* out_accum, int rows, int cols, int ld, float* scratch,
+                     int* counter, void* stream) {
+  B200_REQUIRE(scratch != nullptr && counter != nullptr, "colsum: scratch and counter required");
   B200_REQUIRE(cols % 8 == 0 && ld % 8 == 0, "colsum: cols/ld must be multiples of 8");
   if (rows == 0) return 0;
-  dim3 grid(ceil_div(cols / 8, 32), ceil_div(rows, 64)), block(32, 8);
+  dim3 grid(ceil_div(cols / 8, 32), ceil_div(rows, RELU_ROWS)), block(32, 8);
   relu_bwd_kernel<false><<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(
-      x, nullptr, nullptr, out_accum, rows, cols, ld);
+      x, nullptr, nullptr, out_accum, rows, cols, ld, scratch, counter);
   B200_LAUNCH_CHECK();
   return 0;
 }
@@ -631,11 +679,19 @@ int b200_count_valid(const int64_t* targets, float* stats, int ignore_index, int
 int b200_ce_fwd_bwd(void* logits, const int64_t* targets, float* stats, int rows, int vocab, int ld,
                     int ignore_index, int write_grad, float grad_scale, void* stream) {
   B200_REQUIRE(ld % 8 == 0 && ld >= vocab, "ce: ld %d must be a multiple of 8 and >= vocab %d", ld, vocab);
-  B200_REQUIRE(ld <= CE_THREADS * CE_CACHE * 8, "ce: vocab %d too large (max %d)", vocab,
-               CE_THREADS * CE_CACHE * 8);
+  const size_t smem = static_cast<size_t>(ld) * 2;
+  B200_REQUIRE(smem <= 113 * 1024, "ce: vocab %d too large for the shared-memory row (max %d)", vocab, 113 * 512);
   B200_REQUIRE((reinterpret_cast<uintptr_t>(logits) & 15) == 0, "ce: logits must be 16-byte aligned");
   if (rows == 0) return 0;
-  ce_fwd_bwd_kernel<<<rows, CE_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+  static bool configured[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!configured[dev & 63]) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(ce_fwd_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 113 * 1024));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(ce_fwd_bwd_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    configured[dev & 63] = true;
+  }
+  ce_fwd_bwd_kernel<<<rows, CE_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<bf16*>(logits), targets, stats, vocab, ld, ignore_index, write_grad, grad_scale);
   B200_LAUNCH_CHECK();
   return 0;

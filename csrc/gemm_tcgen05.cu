@@ -51,20 +51,26 @@ struct GemmParams {
 
 enum : int { ERR_GEMM_PRODUCER = 101, ERR_GEMM_MMA = 102, ERR_GEMM_EPILOGUE = 103, ERR_GEMM_SMEM_ALIGN = 104 };
 
-__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c),
-               "f"(d)
-               : "memory");
-}
 
 constexpr int STAGING_BYTES = 4 * 2 * 4096;  // two 32-row x 128-byte swizzled tiles per epilogue warp
 
+__device__ __forceinline__ long long global_ns() {
+  long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define DBG_STAMP_NS(slot)                                                                \
+  do {                                                                                    \
+    if (p.dbg != nullptr) p.dbg[blockIdx.x * 32 + (slot)] = global_ns();                  \
+  } while (0)
 #define DBG_STAMP(slot)                                                                   \
   do {                                                                                    \
-    if (p.dbg != nullptr) p.dbg[blockIdx.x * 16 + (slot)] = clock64();                    \
+    if (p.dbg != nullptr) p.dbg[blockIdx.x * 32 + (slot)] = clock64();                    \
   } while (0)
 
-template <int BN, int STAGES, int MIN_CTAS>
+enum : int { EPI_BIAS = 1, EPI_RELU = 2, EPI_AUX = 4, EPI_MASK = 8, EPI_RES = 16, EPI_F32 = 32, EPI_ACC = 64 };
+
+template <int BN, int STAGES, int MIN_CTAS, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, MIN_CTAS)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
@@ -97,6 +103,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   if (threadIdx.x == 0) {
     DBG_STAMP(0);
+    DBG_STAMP_NS(12);
     *abort_flag = 0;
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(full_bar + 8 * s, 1);
@@ -109,7 +116,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     fence_barrier_init();
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    if (p.tma_store) tma_prefetch_desc(&tmC);
+    tma_prefetch_desc(&tmC);
   }
   if (warp_idx == 1) {
     tmem_alloc(smem_u32(tmem_ptr_smem), TMEM_COLS);
@@ -204,97 +211,98 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else {
     // ===================== epilogue (4 warps) =====================
+    // TMEM -> registers -> (bias / ReLU / aux / mask / residual, selected at compile time by EPI) ->
+    // 128B-swizzled smem tile -> TMA store (or TMA reduce-add).  Global traffic is whole 128-byte
+    // rows, M/N tails are clipped by the tensor map, and the residual / mask operands of chunk
+    // c+1 are prefetched under chunk c.
+    constexpr bool E_BIAS = (EPI & EPI_BIAS) != 0, E_RELU = (EPI & EPI_RELU) != 0, E_AUX = (EPI & EPI_AUX) != 0,
+                   E_MASK = (EPI & EPI_MASK) != 0, E_RES = (EPI & EPI_RES) != 0, E_F32 = (EPI & EPI_F32) != 0,
+                   E_ACC = (EPI & EPI_ACC) != 0;
     const int q = warp_idx & 3;  // TMEM lane quarter this warp may access
+    const uint32_t stage_base = sStage + q * 8192;
+    const int swz = lane & 7;
+    uint32_t nstore = 0;  // TMA stores issued by this warp (selects the staging buffer)
     int lt = 0;
-    {
-      // TMEM -> registers -> (bias / ReLU / mask / residual) -> 128B-swizzled smem tile -> TMA store
-      // (or TMA reduce-add).  Global traffic is whole 128-byte rows, M/N tails are clipped by the
-      // tensor map, and the residual / mask operands of chunk c+1 are prefetched under chunk c.
-      const uint32_t stage_base = sStage + q * 8192;
-      uint32_t nstore = 0;  // TMA stores issued by this warp (selects the staging buffer)
-      const int swz = lane & 7;
-      const bool has_res = p.residual != nullptr, has_mask = p.mask_src != nullptr;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
-        const int t2 = tile / p.k_splits;
-        const int m0 = (t2 % p.num_m_tiles) * BM;
-        const int n0 = (t2 / p.num_m_tiles) * BN;
-        const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
-        const int row = m0 + q * 32 + lane;
-        const bool row_ok = row < p.M;
-        const float* res_row = has_res ? p.residual + static_cast<size_t>(row_ok ? row : 0) * p.ldr : nullptr;
-        const bf16* msk_row = has_mask ? p.mask_src + static_cast<size_t>(row_ok ? row : 0) * p.ldc : nullptr;
-        float4 nres[8];
-        uint4 nmsk[4];
-        float nbias = 0.f;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      const int t2 = tile / p.k_splits;
+      const int m0 = (t2 % p.num_m_tiles) * BM;
+      const int n0 = (t2 / p.num_m_tiles) * BN;
+      const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
+      const int row = m0 + q * 32 + lane;
+      const bool row_ok = row < p.M;
+      const size_t row_c = static_cast<size_t>(row_ok ? row : 0);
+      [[maybe_unused]] const float* res_row = E_RES ? p.residual + row_c * p.ldr : nullptr;
+      [[maybe_unused]] const bf16* msk_row = E_MASK ? p.mask_src + row_c * p.ldc : nullptr;
+      [[maybe_unused]] float4 nres[8];
+      [[maybe_unused]] uint4 nmsk[4];
+      [[maybe_unused]] float nbias = 0.f;
+      // prefetch the epilogue operands of chunk 0 while the MMAs of this tile are still running
+      if constexpr (E_BIAS) nbias = (n0 + lane < p.N) ? __ldg(p.bias + n0 + lane) : 0.f;
+      if constexpr (E_RES) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) nres[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = 0; j < 8; ++j)
+          nres[j] = row_ok ? __ldg(reinterpret_cast<const float4*>(res_row + n0) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      if constexpr (E_MASK) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) nmsk[j] = make_uint4(0x3f803f80u, 0x3f803f80u, 0x3f803f80u, 0x3f803f80u);
-        // prefetch the epilogue operands of chunk 0 while the MMAs of this tile are still running
-        {
-          const int col0 = n0;
-          const bool full = (p.N - col0) >= 32;
-          if (p.bias != nullptr) nbias = (col0 + lane < p.N) ? __ldg(p.bias + col0 + lane) : 0.f;
-          if (has_res && row_ok && full) {
+        for (int j = 0; j < 4; ++j)
+          nmsk[j] = row_ok ? __ldg(reinterpret_cast<const uint4*>(msk_row + n0) + j) : make_uint4(0u, 0u, 0u, 0u);
+      }
+      if (!mbar_wait(tfull_bar + 8 * as, aph, abort_flag, p.err_word, ERR_GEMM_EPILOGUE)) break;
+      tcgen05_fence_after();
+      if (warp_idx == 2 && lane == 0 && lt == 0) DBG_STAMP(5);
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) nres[j] = __ldg(reinterpret_cast<const float4*>(res_row + col0) + j);
-          }
-          if (has_mask && row_ok && full) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) nmsk[j] = __ldg(reinterpret_cast<const uint4*>(msk_row + col0) + j);
-          }
-        }
-        if (!mbar_wait(tfull_bar + 8 * as, aph, abort_flag, p.err_word, ERR_GEMM_EPILOGUE)) break;
-        tcgen05_fence_after();
-        if (warp_idx == 2 && lane == 0 && lt == 0) DBG_STAMP(5);
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
-#pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
-          uint32_t r[32];
-          __syncwarp();
-          tmem_ld_32x32b_x32(taddr + c * 32, r);
-          // current operands <- prefetched; issue the prefetch of the next chunk
-          float4 res[8];
-          uint4 msk[4];
-          const float biasv = nbias;
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr + c * 32, r);
+        [[maybe_unused]] float4 res[8];
+        [[maybe_unused]] uint4 msk[4];
+        [[maybe_unused]] const float biasv = nbias;
+        const int col0 = n0 + c * 32;
+        if constexpr (E_RES) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) res[j] = nres[j];
+        }
+        if constexpr (E_MASK) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) msk[j] = nmsk[j];
-          const int col0 = n0 + c * 32;
-          const int ncols = min(32, p.N - col0);
-          if (c + 1 < BN / 32) {
-            const int ncol0 = col0 + 32;
-            const bool nfull = (p.N - ncol0) >= 32;
-            if (p.bias != nullptr) nbias = (ncol0 + lane < p.N) ? __ldg(p.bias + ncol0 + lane) : 0.f;
-            if (has_res && row_ok && nfull) {
+        }
+        if (c + 1 < BN / 32) {   // host guarantees N % 32 == 0 whenever res / mask / aux are used
+          const int ncol0 = col0 + 32;
+          if constexpr (E_BIAS) nbias = (ncol0 + lane < p.N) ? __ldg(p.bias + ncol0 + lane) : 0.f;
+          if constexpr (E_RES) {
+            if (row_ok && ncol0 < p.N) {
 #pragma unroll
               for (int j = 0; j < 8; ++j) nres[j] = __ldg(reinterpret_cast<const float4*>(res_row + ncol0) + j);
             }
-            if (has_mask && row_ok && nfull) {
+          }
+          if constexpr (E_MASK) {
+            if (row_ok && ncol0 < p.N) {
 #pragma unroll
               for (int j = 0; j < 4; ++j) nmsk[j] = __ldg(reinterpret_cast<const uint4*>(msk_row + ncol0) + j);
             }
           }
-          tmem_ld_wait();
-          if (c == BN / 32 - 1) {  // accumulator fully in registers: hand the TMEM buffer back early
-            tcgen05_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(tempty_bar + 8 * as);
-          }
-          float v[32];
+        }
+        tmem_ld_wait();
+        if (c == BN / 32 - 1) {  // accumulator fully in registers: hand the TMEM buffer back early
+          tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty_bar + 8 * as);
+        }
+        float v[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          if (p.bias != nullptr) {
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        if constexpr (E_BIAS) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] += __shfl_sync(0xffffffffu, biasv, j);
-          }
-          if (p.act == 1) {
+          for (int j = 0; j < 32; ++j) v[j] += __shfl_sync(0xffffffffu, biasv, j);
+        }
+        if constexpr (E_RELU) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
-          }
-          // (host guarantees N % 32 == 0 and aligned rows whenever aux_out / mask / residual are used)
-          if (p.aux_out != nullptr && row_ok && ncols > 0) {
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
+        }
+        if constexpr (E_AUX) {
+          if (row_ok && col0 < p.N) {
             bf16* dst = p.aux_out + static_cast<size_t>(row) * p.ldc + col0;
 #pragma unroll
             for (int j = 0; j < 32; j += 8)
@@ -302,66 +310,67 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                   make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
                              pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
           }
-          if (has_mask) {
+        }
+        if constexpr (E_MASK) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const uint32_t w[4] = {msk[j].x, msk[j].y, msk[j].z, msk[j].w};
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t w[4] = {msk[j].x, msk[j].y, msk[j].z, msk[j].w};
 #pragma unroll
-              for (int t = 0; t < 4; ++t) {
-                const float2 f = unpack_bf16x2(w[t]);
-                if (!(f.x > 0.0f)) v[8 * j + 2 * t] = 0.0f;
-                if (!(f.y > 0.0f)) v[8 * j + 2 * t + 1] = 0.0f;
-              }
+            for (int t = 0; t < 4; ++t) {
+              const float2 f = unpack_bf16x2(w[t]);
+              if (!(f.x > 0.0f)) v[8 * j + 2 * t] = 0.0f;
+              if (!(f.y > 0.0f)) v[8 * j + 2 * t + 1] = 0.0f;
             }
-          }
-          if (has_res) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              v[4 * j] += res[j].x; v[4 * j + 1] += res[j].y; v[4 * j + 2] += res[j].z; v[4 * j + 3] += res[j].w;
-            }
-          }
-          // stage: fp32 -> one 32x32 tile per chunk; bf16 -> two chunks fill one 32x64 tile
-          const bool first_half = p.out_fp32 || (c & 1) == 0;
-          const uint32_t stage_buf = stage_base + (nstore & 1u) * 4096u;
-          const uint32_t my_row = stage_buf + lane * 128;
-          if (first_half) {                 // the store issued two stores ago must be done reading this buffer
-            if (lane == 0) tma_store_wait_read1();
-            __syncwarp();
-          }
-          if (p.out_fp32) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((j ^ swz) << 4)),
-                           "f"(v[4 * j]), "f"(v[4 * j + 1]), "f"(v[4 * j + 2]), "f"(v[4 * j + 3]) : "memory");
-          } else {
-            const int half = (c & 1) * 4;
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + (((half + j) ^ swz) << 4)),
-                           "r"(pack_bf16x2(v[8 * j], v[8 * j + 1])), "r"(pack_bf16x2(v[8 * j + 2], v[8 * j + 3])),
-                           "r"(pack_bf16x2(v[8 * j + 4], v[8 * j + 5])), "r"(pack_bf16x2(v[8 * j + 6], v[8 * j + 7]))
-                           : "memory");
-          }
-          if (p.out_fp32 || (c & 1) == 1) {
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) {
-              const int sc0 = p.out_fp32 ? col0 : col0 - 32;
-              if (sc0 < p.N && m0 + q * 32 < p.M) {
-                if (p.accumulate) tma_reduce_add_2d(&tmC, stage_buf, sc0, m0 + q * 32);
-                else tma_store_2d(&tmC, stage_buf, sc0, m0 + q * 32);
-              }
-              tma_store_commit();
-            }
-            ++nstore;
           }
         }
+        if constexpr (E_RES) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            v[4 * j] += res[j].x; v[4 * j + 1] += res[j].y; v[4 * j + 2] += res[j].z; v[4 * j + 3] += res[j].w;
+          }
+        }
+        // stage: fp32 -> one 32x32 tile per chunk; bf16 -> two chunks fill one 32x64 tile
+        constexpr bool kStoreEvery = E_F32;
+        const bool first_half = kStoreEvery || (c & 1) == 0;
+        const uint32_t stage_buf = stage_base + (nstore & 1u) * 4096u;
+        const uint32_t my_row = stage_buf + lane * 128;
+        if (first_half) {  // the store issued two stores ago must be done reading this buffer
+          if (lane == 0) tma_store_wait_read1();
+          __syncwarp();
+        }
+        if constexpr (E_F32) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + ((j ^ swz) << 4)),
+                         "f"(v[4 * j]), "f"(v[4 * j + 1]), "f"(v[4 * j + 2]), "f"(v[4 * j + 3]) : "memory");
+        } else {
+          const int half = (c & 1) * 4;
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + (((half + j) ^ swz) << 4)),
+                         "r"(pack_bf16x2(v[8 * j], v[8 * j + 1])), "r"(pack_bf16x2(v[8 * j + 2], v[8 * j + 3])),
+                         "r"(pack_bf16x2(v[8 * j + 4], v[8 * j + 5])), "r"(pack_bf16x2(v[8 * j + 6], v[8 * j + 7]))
+                         : "memory");
+        }
+        if (kStoreEvery || (c & 1) == 1) {
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            const int sc0 = E_F32 ? col0 : col0 - 32;
+            if (sc0 < p.N && m0 + q * 32 < p.M) {
+              if constexpr (E_ACC) tma_reduce_add_2d(&tmC, stage_buf, sc0, m0 + q * 32);
+              else tma_store_2d(&tmC, stage_buf, sc0, m0 + q * 32);
+            }
+            tma_store_commit();
+          }
+          ++nstore;
+        }
       }
-      if (warp_idx == 2 && lane == 0) DBG_STAMP(6);
-      if (lane == 0) tma_store_wait_all();
-      __syncwarp();
-      if (warp_idx == 2 && lane == 0) DBG_STAMP(7);
     }
+    if (warp_idx == 2 && lane == 0) DBG_STAMP(6);
+    if (lane == 0) tma_store_wait_all();
+    __syncwarp();
+    if (warp_idx == 2 && lane == 0) DBG_STAMP(7);
   }
 
   tcgen05_fence_before();
@@ -371,6 +380,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tcgen05_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
     if (lane == 0) DBG_STAMP(9);
+    if (lane == 0) DBG_STAMP_NS(13);
   }
 }
 
@@ -427,7 +437,7 @@ struct GemmOverrides {
   int no_tma_store;
 };
 
-template <int BN, int STAGES, int MIN_CTAS>
+template <int BN, int STAGES, int MIN_CTAS, int EPI>
 int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p,
            int grid, cudaStream_t stream) {
   constexpr int smem = STAGES * (A_STAGE_BYTES + BN * BK * 2) + STAGING_BYTES + 16 * STAGES + 32 + 16;
@@ -435,15 +445,38 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tm
   int dev = 0;
   cudaGetDevice(&dev);
   if (!configured[dev & 63]) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS>,
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS>,
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI>,
                                          cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     configured[dev & 63] = true;
   }
-  gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS><<<grid, GEMM_THREADS, smem, stream>>>(tmA, tmB, tmC, p);
+  gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI><<<grid, GEMM_THREADS, smem, stream>>>(tmA, tmB, tmC, p);
   B200_LAUNCH_CHECK();
   return 0;
+}
+
+// the epilogue combinations the framework uses (one pruned kernel each)
+template <int BN, int STAGES, int MIN_CTAS>
+int launch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+               const GemmParams& p, int grid, cudaStream_t st) {
+  switch (epi) {
+#define B200_EPI_CASE(E) case (E): return launch<BN, STAGES, MIN_CTAS, (E)>(tmA, tmB, tmC, p, grid, st);
+    B200_EPI_CASE(0)                                                   // plain bf16 (QKV, dgrad, logits)
+    B200_EPI_CASE(EPI_BIAS)                                            // + bias
+    B200_EPI_CASE(EPI_BIAS | EPI_RELU)                                 // MLP up
+    B200_EPI_CASE(EPI_MASK)                                            // dgrad fused with the ReLU mask
+    B200_EPI_CASE(EPI_F32)                                             // plain fp32
+    B200_EPI_CASE(EPI_F32 | EPI_ACC)                                   // wgrad / split-K (TMA reduce-add)
+    B200_EPI_CASE(EPI_F32 | EPI_BIAS)
+    B200_EPI_CASE(EPI_F32 | EPI_BIAS | EPI_RES)                        // attention out-proj + residual
+    B200_EPI_CASE(EPI_F32 | EPI_RES)
+    B200_EPI_CASE(EPI_F32 | EPI_BIAS | EPI_RELU | EPI_RES)             // MLP down + residual (inference)
+    B200_EPI_CASE(EPI_F32 | EPI_BIAS | EPI_RELU | EPI_AUX | EPI_RES)   // MLP down + residual (training)
+#undef B200_EPI_CASE
+    default:
+      return b200_set_error(-1, "gemm: epilogue combination 0x%x is not instantiated", epi);
+  }
 }
 
 int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
@@ -535,8 +568,13 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   const int cap = sms * ctas_per_sm;
   const int grid = total < cap ? total : cap;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (bn == 128) return launch<128, 2, 2>(tmA, tmB, tmC, p, grid, st);
-  return launch<256, 4, 1>(tmA, tmB, tmC, p, grid, st);
+  const int epi = (bias ? EPI_BIAS : 0) | (act == 1 ? EPI_RELU : 0) | (aux_out ? EPI_AUX : 0) |
+                  (mask_src ? EPI_MASK : 0) | (residual ? EPI_RES : 0) | (out_fp32 ? EPI_F32 : 0) |
+                  (accumulate ? EPI_ACC : 0);
+  if (bn == 128) return launch_epi<128, 2, 2>(epi, tmA, tmB, tmC, p, grid, st);
+  B200_REQUIRE(epi == 0 || epi == (EPI_F32 | EPI_ACC), "gemm: BN=256 supports only plain epilogues");
+  if (epi == 0) return launch<256, 4, 1, 0>(tmA, tmB, tmC, p, grid, st);
+  return launch<256, 4, 1, EPI_F32 | EPI_ACC>(tmA, tmB, tmC, p, grid, st);
 }
 
 }  // namespace

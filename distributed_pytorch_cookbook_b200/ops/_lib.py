@@ -28,12 +28,12 @@ _SIGS = {
     "b200_embedding_fwd": [P, P, P, P, P, I, I, I, I, P],
     "b200_embedding_bwd": [P, P, P, P, P, I, I, I, I, P],
     "b200_layernorm_fwd": [P, P, P, P, P, P, I, I, Fl, P],
-    "b200_layernorm_bwd": [P, P, P, P, P, P, P, P, P, P, I, I, P],
+    "b200_layernorm_bwd": [P, P, P, P, P, P, P, P, P, P, I, I, P, P, P],
     "b200_adamw": [P, P, P, P, P, L, P, Fl, Fl, Fl, Fl, P],
     "b200_adamw_tick": [P, P],
     "b200_cast_bf16": [P, P, L, P],
-    "b200_relu_bwd": [P, P, P, P, I, I, I, P],
-    "b200_colsum_bf16": [P, P, I, I, I, P],
+    "b200_relu_bwd": [P, P, P, P, I, I, I, P, P, P],
+    "b200_colsum_bf16": [P, P, I, I, I, P, P, P],
     "b200_count_valid": [P, P, I, L, P],
     "b200_device_error": [P, I],
     "b200_ce_fwd_bwd": [P, P, P, I, I, I, I, I, Fl, P],
@@ -48,6 +48,7 @@ _SIGS = {
     "b200_barrier": [P, I, I, I, P],
     "b200_smoke": [P],
     "b200_gemm_set_debug_buffer": [P],
+    "b200_attn_set_debug_buffer": [P],
 }
 
 

@@ -26,6 +26,24 @@ grad_ready_hooks: List[Callable[[torch.nn.Parameter], None]] = []
 _LM_CHUNK_ROWS = 1024
 
 
+_SCRATCH = {}
+SCRATCH_COLS = 8192
+
+
+def colsum_scratch(device):
+    """Per-device scratch of the column-reduction kernels (bias / gamma / beta gradients):
+    16 replica rows x 8192 floats + a ticket counter, zero between launches (the kernels clean up
+    after themselves).  Shared by every launch on the device's compute stream - which is the only
+    stream these kernels run on - so launches never overlap."""
+    key = (device.type, device.index)
+    s = _SCRATCH.get(key)
+    if s is None:
+        s = (torch.zeros(16 * SCRATCH_COLS, dtype=torch.float32, device=device),
+             torch.zeros(1, dtype=torch.int32, device=device))
+        _SCRATCH[key] = s
+    return s
+
+
 def _notify(*params):
     if grad_ready_hooks:
         for p in params:
@@ -119,8 +137,9 @@ class _Linear(torch.autograd.Function):
         if need_dz:
             dz = torch.empty((M, N), dtype=BF16, device=dy.device)
             dbias = grad_of(bias) if (bias is not None and bias.requires_grad) else None
+            sc, cnt = colsum_scratch(dy.device)
             call("b200_relu_bwd", dy2.data_ptr(), ptr(y_act), dz.data_ptr(), ptr(dbias), M, N,
-                 int(dy2.dtype == torch.float32), stream())
+                 int(dy2.dtype == torch.float32), sc.data_ptr(), cnt.data_ptr(), stream())
         else:
             dz = dy2
         dx = None
@@ -248,7 +267,7 @@ class _LayerNorm(torch.autograd.Function):
         dx = torch.empty((rows, D), dtype=torch.float32, device=dy.device)
         call("b200_layernorm_bwd", dy2.data_ptr(), x2.data_ptr(), weight.data_ptr(), mean.data_ptr(),
              rstd.data_ptr(), None, dx.data_ptr(), None, grad_of(weight).data_ptr(),
-             grad_of(bias).data_ptr(), rows, D, stream())
+             grad_of(bias).data_ptr(), rows, D, *[t.data_ptr() for t in colsum_scratch(dy.device)], stream())
         _notify(weight, bias)
         dx = dx.view(dy.shape)
         if ctx.in_dtype != torch.float32:

@@ -31,9 +31,11 @@ int b200_embedding_bwd(const int64_t* ids, const int64_t* pos, const float* dout
 int b200_layernorm_fwd(const float* x, const float* gamma, const float* beta, void* y_bf16, float* mean,
                        float* rstd, int rows, int dim, float eps, void* stream);
 /* dx = LN'(dy) [+ dres]; optional bf16 copy of dx; dgamma/dbeta accumulate */
+/* scratch: [16][2*dim] floats + one int counter, both zero on entry and left zero on exit; launches
+ * sharing a scratch buffer must not overlap on the GPU */
 int b200_layernorm_bwd(const void* dy_bf16, const float* x, const float* gamma, const float* mean,
                        const float* rstd, const float* dres, float* dx, void* dx_bf16, float* dgamma,
-                       float* dbeta, int rows, int dim, void* stream);
+                       float* dbeta, int rows, int dim, float* scratch, int* counter, void* stream);
 
 /* fused AdamW over a flat arena; hyper = {lr, step, ..} in device memory  (main-single.py:42,99-101) */
 int b200_adamw(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n,
@@ -42,9 +44,11 @@ int b200_adamw_tick(float* hyper, void* stream);
 int b200_cast_bf16(const float* in, void* out_bf16, int64_t n, void* stream);
 
 /* dz = dy * (y_act > 0) as bf16 (y_act NULL: plain cast); dbias += colsum(dz)  (models/gpt.py:35,38) */
+/* scratch: [16][cols] floats + one int counter (same contract as b200_layernorm_bwd) */
 int b200_relu_bwd(const void* dy, const void* y_act_bf16, void* dz_bf16, float* dbias, int rows, int cols,
-                  int dy_is_fp32, void* stream);
-int b200_colsum_bf16(const void* x_bf16, float* out_accum, int rows, int cols, int ld, void* stream);
+                  int dy_is_fp32, float* scratch, int* counter, void* stream);
+int b200_colsum_bf16(const void* x_bf16, float* out_accum, int rows, int cols, int ld, float* scratch,
+                     int* counter, void* stream);
 
 /* cross entropy over a bf16 logits chunk, in place  (main-single.py:95-96,127-131)
  * stats[0] = n_valid (input, from b200_count_valid), stats[1] += loss sum, stats[2] += #correct */

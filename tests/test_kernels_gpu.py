@@ -73,7 +73,7 @@ def test_layernorm_fwd_bwd(rows, dim):
     dg, db = torch.zeros(dim, device="cuda"), torch.zeros(dim, device="cuda")
     _lib.call("b200_layernorm_bwd", dy.data_ptr(), x.data_ptr(), g.data_ptr(), mean.data_ptr(),
               rstd.data_ptr(), dres.data_ptr(), dx.data_ptr(), dxb.data_ptr(), dg.data_ptr(),
-              db.data_ptr(), rows, dim, _lib.stream())
+              db.data_ptr(), rows, dim, *[t.data_ptr() for t in native.colsum_scratch(x.device)], _lib.stream())
     assert torch.allclose(dx, xr.grad + dres, atol=2e-3, rtol=1e-3)
     assert torch.allclose(dxb.float(), dx, atol=5e-2, rtol=2e-2)
     assert torch.allclose(dg, gr.grad, atol=2e-2 * rows ** 0.5, rtol=1e-3)
@@ -110,8 +110,10 @@ def test_relu_bwd_and_bias_grad(fp32):
     y = torch.randn(rows, cols, device="cuda").relu().to(BF16)
     dz = torch.empty(rows, cols, device="cuda", dtype=BF16)
     dbias = torch.zeros(cols, device="cuda")
-    _lib.call("b200_relu_bwd", dy.data_ptr(), y.data_ptr(), dz.data_ptr(), dbias.data_ptr(), rows, cols,
-              int(fp32), _lib.stream())
+    for _ in range(2):   # twice: the scratch must come back clean
+        dbias.zero_()
+        _lib.call("b200_relu_bwd", dy.data_ptr(), y.data_ptr(), dz.data_ptr(), dbias.data_ptr(), rows, cols,
+                  int(fp32), *[t.data_ptr() for t in native.colsum_scratch(dy.device)], _lib.stream())
     ref = dy.float() * (y.float() > 0)
     assert torch.allclose(dz.float(), ref, atol=2e-2, rtol=1e-2)
     assert torch.allclose(dbias, ref.sum(0), atol=5e-2, rtol=1e-2)

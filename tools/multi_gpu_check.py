@@ -1,0 +1,201 @@
+"""Multi-GPU checks, launched under torchrun (one rank per GPU):
+  1. b200_allreduce (NVLS multimem or peer ld/st) vs NCCL all-reduce, bucket slices, repeated;
+  2. b200_allgather + b200_rs_adamw vs NCCL + torch.optim.AdamW;
+  3. DDP / FSDP / pipeline strategies: a few steps, loss parity across transports and vs 1 GPU.
+Prints one JSON line per check on rank 0; exit code != 0 on any failure."""
+import json
+import os
+import sys
+from pathlib import Path
+from types import SimpleNamespace
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from distributed_pytorch_cookbook_b200.ops import _lib  # noqa: E402
+from distributed_pytorch_cookbook_b200.runtime.symm import (CH_ALLGATHER, CH_ALLREDUCE, CH_RS_ADAMW,  # noqa: E402
+                                                            SymmContext)
+
+rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
+dev = torch.device(f"cuda:{local}")
+torch.cuda.set_device(dev)
+dist.init_process_group("nccl", device_id=dev)
+which = set(sys.argv[1].split(",")) if len(sys.argv) > 1 else {"kernels", "ddp", "fsdp", "pipe"}
+fails = []
+
+
+def report(name, ok, **kw):
+    if rank == 0:
+        print(json.dumps({"check": name, "ok": bool(ok), "world": world, **kw}), flush=True)
+    if not ok:
+        fails.append(name)
+
+
+def dev_err():
+    import ctypes
+    v = ctypes.c_int(0)
+    _lib.call("b200_device_error", ctypes.addressof(v), 1)
+    return v.value
+
+
+if "kernels" in which:
+    ctx = SymmContext(dev)
+    n = 8 * 1024 * 1024 + 4096
+    buf = ctx.alloc(n, torch.float32)
+    report("symm_setup", True, multicast=bool(buf.mc_ptr))
+    for use_mc in ([True, False] if buf.mc_ptr else [False]):
+        for (off, cnt) in [(0, n), (4096, 1 << 20), (128, 4096), (n - 1024, 1024)]:
+            torch.manual_seed(rank)
+            x = torch.randn(n, device=dev)
+            buf.tensor.copy_(x)
+            ref = x[off:off + cnt].clone()
+            dist.all_reduce(ref)
+            ref /= world
+            torch.cuda.synchronize(); dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            _lib.call("b200_allreduce", buf.ptrs_dev, buf.mc_ptr if use_mc else None, ctx.flags.ptrs_dev, rank, world,
+                      off, cnt, 1.0 / world, 16, CH_ALLREDUCE, _lib.stream())
+            e1.record()
+            torch.cuda.synchronize(); dist.barrier()
+            err = (buf.tensor[off:off + cnt] - ref).abs().max().item()
+            untouched = torch.equal(buf.tensor[:off], x[:off]) and torch.equal(buf.tensor[off + cnt:], x[off + cnt:])
+            report("allreduce", err < 1e-5 and untouched and dev_err() == 0, mc=use_mc, off=off, n=cnt, max_err=err,
+                   us=e0.elapsed_time(e1) * 1e3)
+    # bandwidth of the big bucket (graph of 10 launches)
+    torch.cuda.synchronize(); dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        _lib.call("b200_allreduce", buf.ptrs_dev, buf.mc_ptr or None, ctx.flags.ptrs_dev, rank, world, 0, n,
+                  1.0 / world, 16, CH_ALLREDUCE, _lib.stream())
+    e1.record(); torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 100
+    nc = torch.randn(n, device=dev)
+    dist.all_reduce(nc); torch.cuda.synchronize(); dist.barrier()
+    e0.record()
+    for _ in range(10):
+        dist.all_reduce(nc)
+    e1.record(); torch.cuda.synchronize()
+    report("allreduce_bw", True, bytes=4 * n, ours_us=us, nccl_us=e0.elapsed_time(e1) * 100,
+           ours_busbw_GBs=2 * (world - 1) / world * 4 * n / us / 1e3)
+
+    # all-gather + reduce-scatter/AdamW
+    S = 1 << 20
+    shard = ctx.alloc(S, torch.bfloat16)
+    torch.manual_seed(100 + rank)
+    shard.tensor.copy_(torch.randn(S, device=dev))
+    full = torch.empty(S * world, dtype=torch.bfloat16, device=dev)
+    ref_full = torch.empty_like(full)
+    dist.all_gather_into_tensor(ref_full, shard.tensor.clone())
+    torch.cuda.synchronize(); dist.barrier()
+    _lib.call("b200_allgather", shard.ptrs_dev, ctx.flags.ptrs_dev, rank, world, 0, S * 2, full.data_ptr(), 1, 8,
+              CH_ALLGATHER, _lib.stream())
+    torch.cuda.synchronize(); dist.barrier()
+    report("allgather", torch.equal(full, ref_full) and dev_err() == 0)
+
+    G = S * world
+    grads = ctx.alloc(G, torch.float32)
+    torch.manual_seed(200 + rank)
+    g_local = torch.randn(G, device=dev)
+    grads.tensor.copy_(g_local)
+    g_ref = g_local.clone(); dist.all_reduce(g_ref); g_ref /= world
+    p = torch.randn(S, device=dev, generator=torch.Generator(device=dev).manual_seed(5 + rank))
+    p_ref = p.clone().requires_grad_(True)
+    opt = torch.optim.AdamW([p_ref], lr=1e-3)
+    m, v = torch.zeros(S, device=dev), torch.zeros(S, device=dev)
+    pb = torch.empty(S, dtype=torch.bfloat16, device=dev)
+    hyper = torch.tensor([1e-3, 1.0, 0, 0], device=dev)
+    torch.cuda.synchronize(); dist.barrier()
+    for use_mc in ([True, False] if grads.mc_ptr else [False]):
+        if not use_mc and grads.mc_ptr:
+            p.copy_(p_ref.detach()); hyper[1] = 2.0
+        p_ref.grad = g_ref[rank * S:(rank + 1) * S].clone()
+        opt.step()
+        _lib.call("b200_rs_adamw", grads.ptrs_dev, grads.mc_ptr if use_mc else None, ctx.flags.ptrs_dev, rank, world,
+                  rank * S, S, 1.0 / world, p.data_ptr(), m.data_ptr(), v.data_ptr(), pb.data_ptr(), hyper.data_ptr(),
+                  0.9, 0.999, 1e-8, 0.01, 1, 8, CH_RS_ADAMW, _lib.stream())
+        torch.cuda.synchronize(); dist.barrier()
+        err = (p - p_ref.detach()).abs().max().item()
+        report("rs_adamw", err < 1e-5 and torch.equal(pb, p.to(torch.bfloat16)) and dev_err() == 0, mc=use_mc, max_err=err)
+
+CFG = dict(dim=256, head_dim=32, heads=8, num_layers=4, sequence_length=128, vocab_size=8192, batch_size=8,
+           learning_rate=1e-3)
+
+
+def run_strategy(make, comm, steps=6, graph=True, extra=None):
+    from distributed_pytorch_cookbook_b200.trainer import build_model
+    torch.manual_seed(0)
+    ns = SimpleNamespace(**CFG, disable_amp=False, disable_cuda_graph=not graph, bucket_mb=1.0, comm=comm,
+                         cpu_offload=False, **(extra or {}))
+    model = build_model(ns, CFG["vocab_size"])
+    st = make()
+    st.setup(model, ns, dev)
+    st.train()
+    g = torch.Generator().manual_seed(3)
+    ids_all = torch.randint(0, CFG["vocab_size"], (steps, CFG["batch_size"] * world, CFG["sequence_length"] - 1), generator=g)
+    pos = torch.arange(CFG["sequence_length"] - 1).unsqueeze(0).repeat(CFG["batch_size"], 1).to(dev)
+    losses = []
+    for s in range(steps):
+        ids = ids_all[s, rank * CFG["batch_size"]:(rank + 1) * CFG["batch_size"]].to(dev)
+        l = st.train_step({"input_ids": ids, "position_ids": pos}, ids, amp=True)
+        t = l.detach().float().reshape(1).clone()
+        dist.all_reduce(t)
+        losses.append(float(t) / world)
+    sd = st.state_dict()
+    torch.cuda.synchronize(); dist.barrier()
+    return losses, sd, st
+
+
+if "ddp" in which:
+    from distributed_pytorch_cookbook_b200.parallel.ddp import DDPStrategy
+    l_nccl, sd_nccl, _ = run_strategy(DDPStrategy, "nccl", graph=False)
+    l_symm, sd_symm, st = run_strategy(DDPStrategy, "symm", graph=True)
+    d = max(abs(a - b) for a, b in zip(l_nccl, l_symm))
+    report("ddp_symm_vs_nccl", st.comm_kind == "symm" and d < 2e-2 and l_symm[-1] < l_symm[0] and dev_err() == 0,
+           losses_symm=l_symm, losses_nccl=l_nccl, graph=bool(st._graphed and st._graphed.graph))
+
+if "fsdp" in which:
+    from distributed_pytorch_cookbook_b200.parallel.fsdp import FSDPStrategy
+    l_nccl, sd_nccl, _ = run_strategy(FSDPStrategy, "nccl", graph=False)
+    l_symm, sd_symm, st = run_strategy(FSDPStrategy, "symm", graph=False)
+    l_gr, sd_gr, st2 = run_strategy(FSDPStrategy, "symm", graph=True)
+    d = max(abs(a - b) for a, b in zip(l_nccl, l_symm))
+    d2 = max(abs(a - b) for a, b in zip(l_gr, l_symm))
+    worst = max((sd_nccl[k] - sd_symm[k]).abs().max().item() for k in sd_nccl) if rank == 0 else 0.0
+    report("fsdp_symm_vs_nccl", st.comm_kind == "symm" and d < 2e-2 and d2 < 2e-2 and l_symm[-1] < l_symm[0]
+           and dev_err() == 0, losses_symm=l_symm, losses_nccl=l_nccl, losses_graph=l_gr, max_param_diff=worst)
+
+if "pipe" in which and world >= 2:
+    from distributed_pytorch_cookbook_b200.parallel.pipe import PipeStrategy
+    # every rank feeds the same (rank-0) data slice in pipeline mode: emulate by forcing rank 0's slice
+    def run_pipe(schedule, dp):
+        from distributed_pytorch_cookbook_b200.trainer import build_model
+        torch.manual_seed(0)
+        ns = SimpleNamespace(**CFG, disable_amp=False, disable_cuda_graph=True, bucket_mb=1.0, comm="auto")
+        model = build_model(ns, CFG["vocab_size"])
+        st = PipeStrategy(num_stages=world // dp, num_microbatches=4, schedule=schedule, dp_size=dp)
+        st.setup(model, ns, dev)
+        g = torch.Generator().manual_seed(3)
+        ids_all = torch.randint(0, CFG["vocab_size"], (4, CFG["batch_size"] * dp, CFG["sequence_length"] - 1), generator=g)
+        pos = torch.arange(CFG["sequence_length"] - 1).unsqueeze(0).repeat(CFG["batch_size"], 1).to(dev)
+        out = []
+        r = rank % dp
+        for s in range(4):
+            ids = ids_all[s, r * CFG["batch_size"]:(r + 1) * CFG["batch_size"]].to(dev)
+            out.append(float(st.train_step({"input_ids": ids, "position_ids": pos}, ids, amp=True)))
+        sd = st.state_dict()
+        torch.cuda.synchronize(); dist.barrier()
+        return out, sd, st
+    for schedule in ("gpipe", "1f1b"):
+        out, sd, st = run_pipe(schedule, 1)
+        report(f"pipe_{schedule}", out[-1] < out[0] and all(x == x for x in out) and dev_err() == 0, losses=out,
+               comm=st.comm_kind, keys=len(sd) if sd else None)
+    if world >= 4 and world % 2 == 0:
+        out, sd, st = run_pipe("1f1b", world // 2)
+        report("pipe_ddp", out[-1] < out[0] and dev_err() == 0, losses=out, comm=st.comm_kind)
+
+dist.barrier()
+dist.destroy_process_group()
+sys.exit(1 if fails else 0)
