@@ -122,27 +122,53 @@ allreduce_kernel(const CommCtx c, int64_t off, int64_t n, float scale) {
   int64_t lo, hi;
   part_range(nvec, c.world, c.rank, lo, hi);
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  constexpr int U = 8;  // independent 16-byte transactions in flight per thread (NVLink latency ~2 us)
   if (USE_MC) {
     float* mc = reinterpret_cast<float*>(c.mc) + off;
-    for (int64_t i = lo + blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < hi; i += stride) {
-      float4 v = mc_ld_reduce_f32x4(mc + 4 * i);
-      v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
-      mc_st_f32x4(mc + 4 * i, v);
+    for (int64_t i0 = lo + blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i0 < hi; i0 += stride * U) {
+      float4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t i = i0 + u * stride;
+        if (i < hi) v[u] = mc_ld_reduce_f32x4(mc + 4 * i);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t i = i0 + u * stride;
+        if (i < hi) {
+          v[u].x *= scale; v[u].y *= scale; v[u].z *= scale; v[u].w *= scale;
+          mc_st_f32x4(mc + 4 * i, v[u]);
+        }
+      }
     }
   } else {
-    for (int64_t i = lo + blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < hi; i += stride) {
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t i0 = lo + blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i0 < hi; i0 += stride * 4) {
+      float4 acc[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 1
       for (int p = 0; p < c.world; ++p) {
         const int peer = (c.rank + p) % c.world;
-        const float4 v = ld_sys_f32x4(reinterpret_cast<const float*>(c.bufs[peer]) + off + 4 * i);
-        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        const float* src = reinterpret_cast<const float*>(c.bufs[peer]) + off;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int64_t i = i0 + u * stride;
+          if (i < hi) {
+            const float4 v = ld_sys_f32x4(src + 4 * i);
+            acc[u].x += v.x; acc[u].y += v.y; acc[u].z += v.z; acc[u].w += v.w;
+          }
+        }
       }
-      acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
 #pragma unroll 1
       for (int p = 0; p < c.world; ++p) {
         const int peer = (c.rank + p) % c.world;
-        st_sys_f32x4(reinterpret_cast<float*>(c.bufs[peer]) + off + 4 * i, acc);
+        float* dst = reinterpret_cast<float*>(c.bufs[peer]) + off;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int64_t i = i0 + u * stride;
+          if (i < hi)
+            st_sys_f32x4(dst + 4 * i, make_float4(acc[u].x * scale, acc[u].y * scale, acc[u].z * scale, acc[u].w * scale));
+        }
       }
     }
   }
@@ -172,38 +198,51 @@ rs_adamw_kernel(const CommCtx c, int64_t shard_off, int64_t shard_n, float scale
   const float step_size = lr / bc1, decay = 1.0f - lr * a.wd;
   const int64_t nvec = shard_n >> 2;
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < nvec; i += stride) {
-    float4 g;
-    if (USE_MC) {
-      g = mc_ld_reduce_f32x4(reinterpret_cast<const float*>(c.mc) + shard_off + 4 * i);
-    } else {
-      g = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 1
-      for (int p = 0; p < c.world; ++p) {
-        const int peer = (c.rank + p) % c.world;
-        const float4 v = ld_sys_f32x4(reinterpret_cast<const float*>(c.bufs[peer]) + shard_off + 4 * i);
-        g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
-      }
-    }
-    float4 pv = reinterpret_cast<float4*>(a.p)[i];
-    float4 mv = reinterpret_cast<float4*>(a.m)[i];
-    float4 vv = reinterpret_cast<float4*>(a.v)[i];
-    float* pp = &pv.x; float* gp = &g.x; float* mp = &mv.x; float* vp = &vv.x;
+  constexpr int U = 4;
+  for (int64_t i0 = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i0 < nvec; i0 += stride * U) {
+    float4 gq[U];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float gj = gp[j] * scale;
-      if (isfinite(gj)) {
-        pp[j] *= decay;
-        mp[j] = a.beta1 * mp[j] + (1.0f - a.beta1) * gj;
-        vp[j] = a.beta2 * vp[j] + (1.0f - a.beta2) * gj * gj;
-        pp[j] -= step_size * mp[j] / (sqrtf(vp[j]) * bc2_rsqrt + a.eps);
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = i0 + u * stride;
+      gq[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (i < nvec) {
+        if (USE_MC) {
+          gq[u] = mc_ld_reduce_f32x4(reinterpret_cast<const float*>(c.mc) + shard_off + 4 * i);
+        } else {
+#pragma unroll 1
+          for (int p = 0; p < c.world; ++p) {
+            const int peer = (c.rank + p) % c.world;
+            const float4 v = ld_sys_f32x4(reinterpret_cast<const float*>(c.bufs[peer]) + shard_off + 4 * i);
+            gq[u].x += v.x; gq[u].y += v.y; gq[u].z += v.z; gq[u].w += v.w;
+          }
+        }
       }
     }
-    reinterpret_cast<float4*>(a.p)[i] = pv;
-    reinterpret_cast<float4*>(a.m)[i] = mv;
-    reinterpret_cast<float4*>(a.v)[i] = vv;
-    if (a.p_bf16 != nullptr)
-      reinterpret_cast<uint2*>(a.p_bf16)[i] = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = i0 + u * stride;
+      if (i >= nvec) continue;
+      float4 g = gq[u];
+      float4 pv = reinterpret_cast<float4*>(a.p)[i];
+      float4 mv = reinterpret_cast<float4*>(a.m)[i];
+      float4 vv = reinterpret_cast<float4*>(a.v)[i];
+      float* pp = &pv.x; float* gp = &g.x; float* mp = &mv.x; float* vp = &vv.x;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float gj = gp[j] * scale;
+        if (isfinite(gj)) {
+          pp[j] *= decay;
+          mp[j] = a.beta1 * mp[j] + (1.0f - a.beta1) * gj;
+          vp[j] = a.beta2 * vp[j] + (1.0f - a.beta2) * gj * gj;
+          pp[j] -= step_size * mp[j] / (sqrtf(vp[j]) * bc2_rsqrt + a.eps);
+        }
+      }
+      reinterpret_cast<float4*>(a.p)[i] = pv;
+      reinterpret_cast<float4*>(a.m)[i] = mv;
+      reinterpret_cast<float4*>(a.v)[i] = vv;
+      if (a.p_bf16 != nullptr)
+        reinterpret_cast<uint2*>(a.p_bf16)[i] = make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
+    }
   }
   if (end_barrier) {
     __threadfence_system();
@@ -221,12 +260,24 @@ allgather_kernel(const CommCtx c, int64_t src_off_bytes, int64_t shard_bytes, ui
   const int64_t nvec = shard_bytes >> 4;
   const int64_t total = nvec * c.world;
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total; i += stride) {
-    const int p = static_cast<int>(i / nvec);
-    const int peer = (c.rank + p) % c.world;           // start with the local shard, then ring order
-    const int64_t j = i % nvec;
-    const uint4 v = ld_sys_b32x4(reinterpret_cast<const uint8_t*>(c.bufs[peer]) + src_off_bytes + 16 * j);
-    reinterpret_cast<uint4*>(dst + static_cast<int64_t>(peer) * shard_bytes)[j] = v;
+  for (int64_t i0 = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i0 < total; i0 += stride * 4) {
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t i = i0 + u * stride;
+      if (i < total) {
+        const int peer = (c.rank + static_cast<int>(i / nvec)) % c.world;   // local shard first, then ring order
+        v[u] = ld_sys_b32x4(reinterpret_cast<const uint8_t*>(c.bufs[peer]) + src_off_bytes + 16 * (i % nvec));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t i = i0 + u * stride;
+      if (i < total) {
+        const int peer = (c.rank + static_cast<int>(i / nvec)) % c.world;
+        reinterpret_cast<uint4*>(dst + static_cast<int64_t>(peer) * shard_bytes)[i % nvec] = v[u];
+      }
+    }
   }
 }
 

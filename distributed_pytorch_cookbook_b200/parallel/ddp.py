@@ -175,7 +175,7 @@ class DDPStrategy:
         self.comm_kind = transport
         self._verify_replicas()
         self.reducer = GradReducer(self.arena, self.group, getattr(args, "bucket_mb", 4.0), transport,
-                                   self.symm, grad_buf)
+                                   self.symm, grad_buf, nblocks=32)
         self.use_graph = (transport == "symm" and not getattr(args, "disable_cuda_graph", False)) or \
                          (self.world == 1 and native_ok and not getattr(args, "disable_cuda_graph", False))
 

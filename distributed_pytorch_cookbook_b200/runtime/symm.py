@@ -27,7 +27,8 @@ def symmetric_memory_available(device) -> bool:
     if torch.device(device).type != "cuda" or not dist.is_initialized():
         return False
     try:
-        import torch.distributed._symmetric_memory  # noqa: F401
+        import importlib
+        importlib.import_module("torch.distributed._symmetric_memory")
     except Exception:
         return False
     return True

@@ -56,7 +56,7 @@ if "kernels" in which:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             _lib.call("b200_allreduce", buf.ptrs_dev, buf.mc_ptr if use_mc else None, ctx.flags.ptrs_dev, rank, world,
-                      off, cnt, 1.0 / world, 16, CH_ALLREDUCE, _lib.stream())
+                      off, cnt, 1.0 / world, 32, CH_ALLREDUCE, _lib.stream())
             e1.record()
             torch.cuda.synchronize(); dist.barrier()
             err = (buf.tensor[off:off + cnt] - ref).abs().max().item()
@@ -69,7 +69,7 @@ if "kernels" in which:
     e0.record()
     for _ in range(10):
         _lib.call("b200_allreduce", buf.ptrs_dev, buf.mc_ptr or None, ctx.flags.ptrs_dev, rank, world, 0, n,
-                  1.0 / world, 16, CH_ALLREDUCE, _lib.stream())
+                  1.0 / world, 32, CH_ALLREDUCE, _lib.stream())
     e1.record(); torch.cuda.synchronize()
     us = e0.elapsed_time(e1) * 100
     nc = torch.randn(n, device=dev)
