@@ -9,6 +9,8 @@
 // (ReLU), main-single.py:42,99-101 (AdamW + GradScaler), :95-96,127-131 (CE + accuracy).
 #include <math.h>
 
+#include <mutex>
+
 #include "../include/b200gpt.h"
 #include "common.cuh"
 
@@ -698,3 +700,72 @@ int b200_ce_fwd_bwd(void* logits, const int64_t* targets, float* stats, int rows
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// b200_relu_bwd_static: the ReLU-backward + bias-gradient kernel for callers that have no device
+// memory of their own to lend.  b200_relu_bwd needs a scratch buffer (16 replica rows of column
+// sums plus a ticket counter) from the caller; here that scratch is a fixed array that is part of
+// the library image, so the call needs nothing but its inputs and outputs.
+// ------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int STATIC_MAX_COLS = 4096;  // widest matrix the built-in scratch can serve
+
+struct StaticColsumScratch {
+  float replicas[REPLICAS * STATIC_MAX_COLS];  // 256 KiB
+  int counter;
+  int pad[63];
+};
+// Lives in every GPU's memory from the moment the library is loaded on it until the process exits.
+static __device__ __align__(256) StaticColsumScratch g_static_colsum_scratch;
+
+// Device address of the array for each device, resolved on first use.  (In host code the symbol
+// name itself is only a handle - it must go through cudaGetSymbolAddress, with the target device
+// current, to become a pointer a kernel can use.)
+StaticColsumScratch* g_static_scratch_ptr[64] = {nullptr};
+std::mutex g_static_scratch_mu;
+
+int static_scratch_for_current_device(StaticColsumScratch** out) {
+  int dev = -1;
+  B200_CHECK_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < 64, "relu_bwd_static: device index %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+  if (g_static_scratch_ptr[dev] == nullptr) {
+    StaticColsumScratch* ptr = nullptr;
+    B200_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_static_colsum_scratch));
+    B200_REQUIRE(ptr != nullptr, "relu_bwd_static: could not resolve the scratch array on device %d", dev);
+    g_static_scratch_ptr[dev] = ptr;
+  }
+  *out = g_static_scratch_ptr[dev];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b200_relu_bwd_static(const void* dy, const void* y_act, void* dz, float* dbias, int rows,
+                                    int cols, int dy_fp32, void* stream) {
+  B200_REQUIRE(cols % 8 == 0, "relu_bwd_static: cols %d must be a multiple of 8", cols);
+  B200_REQUIRE(cols <= STATIC_MAX_COLS,
+               "relu_bwd_static: cols %d exceeds the built-in scratch (max %d columns); use b200_relu_bwd "
+               "with a caller-provided scratch buffer instead", cols, STATIC_MAX_COLS);
+  if (rows == 0) return 0;
+  StaticColsumScratch* sc = nullptr;
+  int rc = static_scratch_for_current_device(&sc);  // first call on a device resolves the address
+  if (rc != 0) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // The array keeps whatever the previous call (or an interrupted one) left behind: the replica
+  // rows this call will use and the ticket counter have to start from zero.
+  B200_CHECK_CUDA(cudaMemsetAsync(sc->replicas, 0, sizeof(float) * REPLICAS * static_cast<size_t>(cols), st));
+  B200_CHECK_CUDA(cudaMemsetAsync(&sc->counter, 0, sizeof(int), st));
+  dim3 grid(ceil_div(cols / 8, 32), ceil_div(rows, RELU_ROWS)), block(32, 8);
+  if (dy_fp32)
+    relu_bwd_kernel<true><<<grid, block, 0, st>>>(dy, reinterpret_cast<const bf16*>(y_act),
+                                                  reinterpret_cast<bf16*>(dz), dbias, rows, cols, cols,
+                                                  sc->replicas, &sc->counter);
+  else
+    relu_bwd_kernel<false><<<grid, block, 0, st>>>(dy, reinterpret_cast<const bf16*>(y_act),
+                                                   reinterpret_cast<bf16*>(dz), dbias, rows, cols, cols,
+                                                   sc->replicas, &sc->counter);
+  B200_LAUNCH_CHECK();
+  return 0;
+}

@@ -34,6 +34,7 @@ _SIGS = {
     "b200_cast_bf16": [P, P, L, P],
     "b200_relu_bwd": [P, P, P, P, I, I, I, P, P, P],
     "b200_colsum_bf16": [P, P, I, I, I, P, P, P],
+    "b200_relu_bwd_static": [P, P, P, P, I, I, I, P],
     "b200_count_valid": [P, P, I, L, P],
     "b200_device_error": [P, I],
     "b200_ce_fwd_bwd": [P, P, P, I, I, I, I, I, Fl, P],

@@ -49,6 +49,17 @@ int b200_relu_bwd(const void* dy, const void* y_act_bf16, void* dz_bf16, float* 
                   int dy_is_fp32, float* scratch, int* counter, void* stream);
 int b200_colsum_bf16(const void* x_bf16, float* out_accum, int rows, int cols, int ld, float* scratch,
                      int* counter, void* stream);
+/* No counterpart in the reference (an addition of this library).  Same result as b200_relu_bwd, for
+ * callers that cannot provide scratch memory: a host program whose device memory is entirely owned by
+ * its own pool or by another framework, or a call site (a callback, a latency-critical loop) where the
+ * CUDA allocator must not be entered.  The scratch is a 256 KiB array built into the library - every
+ * GPU that loads the library carries it until the process exits - so cols is limited to 4096; wider
+ * inputs are refused with an error.  Nothing is allocated or freed by this call.  The first call on a
+ * device also looks up the array's address on that device; make that first call outside any stream
+ * capture.  All calls on a device share the one array: two calls that overlap on the GPU (different
+ * streams, no ordering between them) corrupt each other's sums - order them. */
+int b200_relu_bwd_static(const void* dy, const void* y_act_bf16, void* dz_bf16, float* dbias, int rows, int cols,
+                         int dy_is_fp32, void* stream);
 
 /* cross entropy over a bf16 logits chunk, in place  (main-single.py:95-96,127-131)
  * stats[0] = n_valid (input, from b200_count_valid), stats[1] += loss sum, stats[2] += #correct */
