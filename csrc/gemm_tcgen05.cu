@@ -252,10 +252,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       tcgen05_fence_after();
       if (warp_idx == 2 && lane == 0 && lt == 0) DBG_STAMP(5);
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+      uint32_t rr[2][32];  // TMEM loads are software-pipelined: chunk c+1 is in flight under chunk c
+      tmem_ld_32x32b_x32(taddr, rr[0]);
 #pragma unroll
       for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(taddr + c * 32, r);
+        uint32_t* r = rr[c & 1];
         [[maybe_unused]] float4 res[8];
         [[maybe_unused]] uint4 msk[4];
         [[maybe_unused]] const float biasv = nbias;
@@ -284,7 +285,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
           }
         }
-        tmem_ld_wait();
+        tmem_ld_wait_dep(r);
+        if (c + 1 < BN / 32) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, rr[(c + 1) & 1]);
         if (c == BN / 32 - 1) {  // accumulator fully in registers: hand the TMEM buffer back early
           tcgen05_fence_before();
           __syncwarp();
@@ -489,7 +491,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
 
   int bn = (cfg & 0x3ff);
   if (ov && ov->force_bn > 0) bn = ov->force_bn;
-  if (bn == 0) bn = 128;
+  if (bn == 0) bn = (N >= 256) ? 256 : 128;  // 128x256 tiles read 25% less operand data from L2 per FLOP
   B200_REQUIRE(bn == 128 || bn == 256, "gemm: tile N %d not supported", bn);
 
   GemmParams p{};
@@ -572,9 +574,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
                   (mask_src ? EPI_MASK : 0) | (residual ? EPI_RES : 0) | (out_fp32 ? EPI_F32 : 0) |
                   (accumulate ? EPI_ACC : 0);
   if (bn == 128) return launch_epi<128, 2, 2>(epi, tmA, tmB, tmC, p, grid, st);
-  B200_REQUIRE(epi == 0 || epi == (EPI_F32 | EPI_ACC), "gemm: BN=256 supports only plain epilogues");
-  if (epi == 0) return launch<256, 4, 1, 0>(tmA, tmB, tmC, p, grid, st);
-  return launch<256, 4, 1, EPI_F32 | EPI_ACC>(tmA, tmB, tmC, p, grid, st);
+  return launch_epi<256, 4, 1>(epi, tmA, tmB, tmC, p, grid, st);
 }
 
 }  // namespace

@@ -12,7 +12,10 @@ CASES = [("fwd qkv", 16320, 768, 256, False, 0, 0, False), ("fwd out+res", 16320
          ("lm fwd", 1024, 50257, 256, False, 0, 0, False),
          ("wgrad up", 1024, 256, 16320, False, 1, 1, True), ("wgrad qkv", 768, 256, 16320, False, 1, 1, True),
          ("wgrad out", 256, 256, 16320, False, 1, 1, True), ("wgrad lm", 50257, 256, 1024, False, 1, 1, True),
-         ("dgrad lm", 1024, 256, 50257, False, 0, 1, True), ("dgrad up", 16320, 256, 1024, False, 0, 1, False)]
+         ("dgrad lm", 1024, 256, 50257, False, 0, 1, True), ("dgrad up", 16320, 256, 1024, False, 0, 1, False),
+         ("fwd qkv bn256", 16320, 768, 256, False, 0, 0, False), ("lm fwd bn256", 1024, 50257, 256, False, 0, 0, False),
+         ("wgrad lm bn256", 50257, 256, 1024, False, 1, 1, True), ("dgrad lm bn256", 1024, 256, 50257, False, 0, 1, True),
+         ("lm fwd 2048 rows", 2048, 50257, 256, False, 0, 0, False), ("lm fwd 2048 bn256", 2048, 50257, 256, False, 0, 0, False)]
 for (name, M, N, K, res, a_mn, b_mn, acc) in CASES:
     Kp = (K + 7) // 8 * 8
     A = torch.randn(K, (M + 7) // 8 * 8, device="cuda").to(BF16) if a_mn else torch.randn(M, Kp, device="cuda").to(BF16)
@@ -21,7 +24,7 @@ for (name, M, N, K, res, a_mn, b_mn, acc) in CASES:
     out = torch.zeros(M, ld, device="cuda", dtype=torch.float32 if (res or acc) else BF16)
     r = torch.randn(M, ld, device="cuda") if res else None
     dbg = torch.zeros(4096 * 32, dtype=torch.int64, device="cuda")
-    kw = dict(residual=r, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), accumulate=acc)
+    kw = dict(residual=r, a_mn_major=bool(a_mn), b_mn_major=bool(b_mn), accumulate=acc, cfg=256 if "bn256" in name else 0)
     for it in range(3):
         native.gemm(A, W, out, M, N, K, **kw)
     torch.cuda.synchronize()
