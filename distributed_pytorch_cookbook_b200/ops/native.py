@@ -24,7 +24,7 @@ BF16 = torch.bfloat16
 grad_ready_hooks: List[Callable[[torch.nn.Parameter], None]] = []
 # per-parameter override of where the bf16 weights come from (FSDP installs gathered buffers)
 import os as _os
-_LM_CHUNK_ROWS = int(_os.environ.get("B200GPT_LM_CHUNK", "1024"))  # rows of logits kept in flight (L2 resident)
+_LM_CHUNK_ROWS = int(_os.environ.get("B200GPT_LM_CHUNK", "4096"))  # rows of logits kept in flight (L2 resident)
 
 
 _SCRATCH = {}

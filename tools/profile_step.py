@@ -11,10 +11,12 @@ from torch.profiler import ProfilerActivity, profile  # noqa: E402
 
 from distributed_pytorch_cookbook_b200.trainer import SingleStrategy, build_model  # noqa: E402
 
-B, S, V = 64, 256, 50257
+BIG = os.environ.get("MODEL") == "1.3b"
+B, S, V = (8, 1024, 50257) if BIG else (64, 256, 50257)
 dev = torch.device("cuda")
 torch.manual_seed(0)
-ns = SimpleNamespace(dim=256, head_dim=32, heads=8, num_layers=8, sequence_length=S, learning_rate=1e-4,
+ns = SimpleNamespace(dim=2048 if BIG else 256, head_dim=128 if BIG else 32, heads=16 if BIG else 8,
+                     num_layers=24 if BIG else 8, sequence_length=S, learning_rate=1e-4,
                      disable_amp=False, disable_cuda_graph=os.environ.get("NOGRAPH") == "1")
 model = build_model(ns, V)
 st = SingleStrategy()
