@@ -56,20 +56,27 @@ __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile, int kk) {
   return desc_nosw(tile + kk * 256, 128, CHUNK_STRIDE);
 }
 
-// global [rows x D] (row stride in elements) -> smem tile, rows >= nvalid zero-filled
+// global [rows x D] (row stride in elements) -> smem tile, rows >= nvalid zero-filled.
+// Asynchronous copies (cp.async, 16 B each, zero-fill through src-size 0): a thread fires all its
+// copies back to back and the caller waits once with load_tiles_wait(), so a tile costs one
+// global-memory latency instead of one per 16-byte chunk.
 template <int D>
 __device__ __forceinline__ void load_tile(uint32_t smem_dst, const bf16* __restrict__ g, int nvalid,
                                           size_t row_stride) {
   constexpr int CPR = D / 8;  // 16-byte chunks per row
-#pragma unroll 4
+#pragma unroll
   for (int c = threadIdx.x; c < TQ * CPR; c += ATTN_THREADS) {
     const int row = c / CPR, kc = c % CPR;
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (row < nvalid) v = __ldg(reinterpret_cast<const uint4*>(g + static_cast<size_t>(row) * row_stride) + kc);
-    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(smem_dst + kc * CHUNK_STRIDE + row * 16),
-                 "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+    const bool ok = row < nvalid;
+    const bf16* src = g + static_cast<size_t>(ok ? row : 0) * row_stride + kc * 8;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_dst + kc * CHUNK_STRIDE + row * 16),
+                 "l"(src), "r"(ok ? 16 : 0)
                  : "memory");
   }
+}
+__device__ __forceinline__ void load_tiles_wait() {
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
@@ -164,6 +171,7 @@ attn_fwd_kernel(const AttnParams p) {
     tmem_alloc(smem_u32(tmem_ptr_smem), TMEM_COLS);
     tmem_relinquish();
   }
+  // Q is waited for together with the first K/V tile (one global-memory latency for all three)
   load_tile<D>(sQ, qkv_b + static_cast<size_t>(q0) * row_stride + h * D, min(TQ, p.T - q0), row_stride);
   tcgen05_fence_before();
   __syncthreads();
@@ -188,6 +196,7 @@ attn_fwd_kernel(const AttnParams p) {
     __syncthreads();  // previous iteration's MMAs are complete (we waited); smem is reusable
     load_tile<D>(sK, qkv_b + static_cast<size_t>(k0) * row_stride + HD + h * D, min(TK, p.T - k0), row_stride);
     load_tile<D>(sV, qkv_b + static_cast<size_t>(k0) * row_stride + 2 * HD + h * D, min(TK, p.T - k0), row_stride);
+    load_tiles_wait();
     fence_proxy_async_smem();
     __syncthreads();
     if (kt < 2) ADBG(2 + 6 * kt);
@@ -368,6 +377,7 @@ attn_bwd_kernel(const AttnParams p) {
   }
   load_tile<D>(sK, qkv_b + static_cast<size_t>(k0) * row_stride + HD + h * D, min(TK, p.T - k0), row_stride);
   load_tile<D>(sV, qkv_b + static_cast<size_t>(k0) * row_stride + 2 * HD + h * D, min(TK, p.T - k0), row_stride);
+  load_tiles_wait();
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
@@ -388,6 +398,7 @@ attn_bwd_kernel(const AttnParams p) {
     __syncthreads();
     load_tile<D>(sQ, qkv_b + static_cast<size_t>(q0) * row_stride + h * D, min(TQ, p.T - q0), row_stride);
     load_tile<D>(sdO, dout_b + static_cast<size_t>(q0) * HD + h * D, min(TQ, p.T - q0), HD);
+    load_tiles_wait();
     fence_proxy_async_smem();
     __syncthreads();
     if (tid == 0) {

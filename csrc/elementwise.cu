@@ -155,7 +155,7 @@ layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
   }
 }
 
-template <int NV>
+template <int NV, bool DX_ONLY = false>
 __global__ void __launch_bounds__(256)
 layernorm_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
                      const float* __restrict__ gamma, const float* __restrict__ mean_in,
@@ -169,9 +169,9 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
   const int nvec = dim >> 2;
   const float inv_dim = 1.0f / static_cast<float>(dim);
   const float4* g4p = reinterpret_cast<const float4*>(gamma);
-  float4 dg[NV], db[NV];
+  float4 dg[DX_ONLY ? 1 : NV], db[DX_ONLY ? 1 : NV];
 #pragma unroll
-  for (int i = 0; i < NV; ++i) {
+  for (int i = 0; i < (DX_ONLY ? 1 : NV); ++i) {
     dg[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     db[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
@@ -194,8 +194,10 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
         const float a0 = d01.x * g.x, a1 = d01.y * g.y, a2 = d23.x * g.z, a3 = d23.y * g.w;
         c1 += a0 + a1 + a2 + a3;
         c2 += a0 * h0 + a1 * h1 + a2 * h2 + a3 * h3;
-        dg[i].x += d01.x * h0; dg[i].y += d01.y * h1; dg[i].z += d23.x * h2; dg[i].w += d23.y * h3;
-        db[i].x += d01.x; db[i].y += d01.y; db[i].z += d23.x; db[i].w += d23.y;
+        if constexpr (!DX_ONLY) {
+          dg[i].x += d01.x * h0; dg[i].y += d01.y * h1; dg[i].z += d23.x * h2; dg[i].w += d23.y * h3;
+          db[i].x += d01.x; db[i].y += d01.y; db[i].z += d23.x; db[i].w += d23.y;
+        }
       }
     }
     c1 = warp_sum(c1) * inv_dim;
@@ -226,6 +228,7 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
       }
     }
   }
+  if constexpr (DX_ONLY) return;
   // block reduction of the per-warp dgamma/dbeta partials, then one atomic per column per block
   extern __shared__ float red[];  // [warps][2][dim]
   float* my = red + static_cast<size_t>(warp) * 2 * dim;
@@ -245,6 +248,50 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
     atomicAdd(rep + j, s);
   }
   finish_column_sums(scratch, counter, 2 * dim, gridDim.x, dgamma, dbeta, dim);
+}
+
+// dgamma / dbeta for wide rows: block (32 column groups of 4, 8 row lanes) walks a slab of rows,
+// recomputing xhat from the saved statistics; partial sums go through the replica scratch.
+constexpr int LN_DG_ROWS = 128;
+__global__ void __launch_bounds__(256)
+layernorm_bwd_dgdb_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
+                          const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
+                          float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int dim,
+                          float* __restrict__ scratch, int* __restrict__ counter) {
+  const int cg = blockIdx.x * 32 + threadIdx.x;
+  const int col = cg * 4;
+  const bool col_ok = col < dim;
+  float4 g = make_float4(0.f, 0.f, 0.f, 0.f), b = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int r0 = blockIdx.y * LN_DG_ROWS;
+  if (col_ok) {
+#pragma unroll 4
+    for (int r = r0 + threadIdx.y; r < min(r0 + LN_DG_ROWS, rows); r += 8) {
+      const float4 xv = *reinterpret_cast<const float4*>(x + static_cast<size_t>(r) * dim + col);
+      const uint2 u = *reinterpret_cast<const uint2*>(dy + static_cast<size_t>(r) * dim + col);
+      const float mean = mean_in[r], rstd = rstd_in[r];
+      const float2 d01 = unpack_bf16x2(u.x), d23 = unpack_bf16x2(u.y);
+      g.x += d01.x * (xv.x - mean) * rstd; g.y += d01.y * (xv.y - mean) * rstd;
+      g.z += d23.x * (xv.z - mean) * rstd; g.w += d23.y * (xv.w - mean) * rstd;
+      b.x += d01.x; b.y += d01.y; b.z += d23.x; b.w += d23.y;
+    }
+  }
+  __shared__ float red[8][32][9];
+  red[threadIdx.y][threadIdx.x][0] = g.x; red[threadIdx.y][threadIdx.x][1] = g.y;
+  red[threadIdx.y][threadIdx.x][2] = g.z; red[threadIdx.y][threadIdx.x][3] = g.w;
+  red[threadIdx.y][threadIdx.x][4] = b.x; red[threadIdx.y][threadIdx.x][5] = b.y;
+  red[threadIdx.y][threadIdx.x][6] = b.z; red[threadIdx.y][threadIdx.x][7] = b.w;
+  __syncthreads();
+  if (threadIdx.y == 0 && col_ok) {
+    float* rep = scratch + static_cast<size_t>(blockIdx.y % REPLICAS) * 2 * dim;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float s = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) s += red[w][threadIdx.x][j];
+      atomicAdd(rep + (j < 4 ? col + j : dim + col + (j - 4)), s);
+    }
+  }
+  finish_column_sums(scratch, counter, 2 * dim, gridDim.x * gridDim.y, dgamma, dbeta, dim);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -604,8 +651,20 @@ int b200_layernorm_bwd(const void* dy, const float* x, const float* gamma, const
   } while (0)
   if (dim <= 256) LN_BWD(2);
   else if (dim <= 1024) LN_BWD(8);
-  else if (dim <= 2048) LN_BWD(16);
-  else LN_BWD(32);
+  else {
+    // wide rows: dx by the warp-per-row kernel without the column accumulators (they would need
+    // 128+ registers per lane), dgamma/dbeta by a column-parallel pass
+    const int gdx = (rows + 7) / 8 < b200_num_sms() * 8 ? (rows + 7) / 8 : b200_num_sms() * 8;
+    if (dim <= 2048)
+      layernorm_bwd_kernel<16, true><<<gdx, 256, 0, st>>>(dyb, x, gamma, mean, rstd, dres, dx, dxb, dgamma, dbeta,
+                                                          rows, dim, scratch, counter);
+    else
+      layernorm_bwd_kernel<32, true><<<gdx, 256, 0, st>>>(dyb, x, gamma, mean, rstd, dres, dx, dxb, dgamma, dbeta,
+                                                          rows, dim, scratch, counter);
+    B200_LAUNCH_CHECK();
+    dim3 g2(ceil_div(dim / 4, 32), ceil_div(rows, LN_DG_ROWS)), b2(32, 8);
+    layernorm_bwd_dgdb_kernel<<<g2, b2, 0, st>>>(dyb, x, mean, rstd, dgamma, dbeta, rows, dim, scratch, counter);
+  }
 #undef LN_BWD
   B200_LAUNCH_CHECK();
   return 0;

@@ -103,9 +103,10 @@ class GradReducer:
             ev.record()
             self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
+                nblocks = max(4, min(self.nblocks, ((hi - lo) * 4) >> 18))      # ~256 KiB of bucket per block
                 _lib.call("b200_allreduce", self.grad_buf.ptrs_dev, self.grad_buf.mc_ptr or None,
                           self.symm.flags.ptrs_dev, self.rank, self.world, lo, hi - lo, 1.0 / self.world,
-                          self.nblocks, CH_ALLREDUCE, self.comm_stream.cuda_stream)
+                          nblocks, CH_ALLREDUCE, self.comm_stream.cuda_stream)
         elif self.cuda:
             ev = torch.cuda.Event()
             ev.record()
@@ -175,7 +176,7 @@ class DDPStrategy:
         self.comm_kind = transport
         self._verify_replicas()
         self.reducer = GradReducer(self.arena, self.group, getattr(args, "bucket_mb", 4.0), transport,
-                                   self.symm, grad_buf, nblocks=32)
+                                   self.symm, grad_buf, nblocks=64)
         self.use_graph = (transport == "symm" and not getattr(args, "disable_cuda_graph", False)) or \
                          (self.world == 1 and native_ok and not getattr(args, "disable_cuda_graph", False))
 

@@ -234,7 +234,7 @@ class FSDPStrategy:
         with ctx:
             if self.comm_kind == "symm":
                 buf = self.shard_bf16_buf if dtype == torch.bfloat16 else self.master_buf
-                nblocks = 8 if g.shard_n * esz >= (1 << 16) else 2
+                nblocks = max(2, min(64, (g.shard_n * esz * self.world) >> 18))   # ~256 KiB in flight per block
                 _lib.call("b200_allgather", buf.ptrs_dev, self.symm.flags.ptrs_dev, self.rank, self.world,
                           g.shard_base * esz, g.shard_n * esz, full_view.data_ptr(), 1, nblocks, CH_ALLGATHER,
                           self.comm_stream.cuda_stream)
@@ -289,7 +289,7 @@ class FSDPStrategy:
         with ctx:
             if self.comm_kind == "symm":
                 pb = self.shard_bf16.data_ptr() + 2 * sb if g.kind == "big" else None
-                nblocks = 8 if sn >= (1 << 15) else 2
+                nblocks = max(2, min(64, (sn * 4) >> 17))                        # ~128 KiB of shard per block
                 _lib.call("b200_rs_adamw", self.grads_buf.ptrs_dev, self.grads_buf.mc_ptr or None,
                           self.symm.flags.ptrs_dev, self.rank, self.world, lo, sn, 1.0 / self.world,
                           self.master.data_ptr() + 4 * sb, self.exp_avg.data_ptr() + 4 * sb,
