@@ -47,9 +47,18 @@ struct GemmParams {
   int tma_store;  // 1: epilogue stages tiles in smem and writes them with TMA (coalesced, clipped)
   long long* dbg;  // optional per-CTA phase timestamps (16 slots per CTA), bring-up only
   int* err_word;
+  // Fused all-gather of the B operand (FSDP, b200_ag_gemm_bf16): before its B tiles are read, the
+  // kernel itself pulls bytes [ag_off, ag_off + ag_bytes) of a flat parameter group, sharded evenly
+  // over the ranks, out of the owning peers' shard buffers (NVLink peer loads) into the local
+  // full buffer that the B tensor map points at.  ag_bytes == 0 disables it.
+  const uint8_t* const* ag_peers;  // device array [world]: base of each rank's shard of the group
+  uint8_t* ag_full;                // local full (un-sharded) buffer of the group
+  long long ag_off, ag_bytes, ag_shard_bytes;
+  int* ag_sync;                    // [0] copied-CTA counter, [1] exited-CTA counter (both zero between launches)
 };
 
-enum : int { ERR_GEMM_PRODUCER = 101, ERR_GEMM_MMA = 102, ERR_GEMM_EPILOGUE = 103, ERR_GEMM_SMEM_ALIGN = 104 };
+enum : int { ERR_GEMM_PRODUCER = 101, ERR_GEMM_MMA = 102, ERR_GEMM_EPILOGUE = 103, ERR_GEMM_SMEM_ALIGN = 104,
+             ERR_GEMM_AG_WAIT = 105 };
 
 
 constexpr int STAGING_BYTES = 4 * 2 * 4096;  // two 32-row x 128-byte swizzled tiles per epilogue warp
@@ -135,6 +144,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
       bool ok = true;
+      bool ag_ready = false;
       for (int tile = blockIdx.x; tile < total_tiles && ok; tile += gridDim.x) {
         const int split = tile % p.k_splits;
         const int t2 = tile / p.k_splits;
@@ -157,6 +167,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           } else {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j) tma_load_2d(a_dst + j * 8192, &tmA, fb, m0 + 64 * j, k0);
+          }
+          if (p.ag_bytes > 0 && !ag_ready) {
+            // every CTA has pulled its slice of the weight from the peers: wait for all of them
+            const long long t0 = clock64();
+            int seen = 0;
+            for (;;) {
+              asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(p.ag_sync) : "memory");
+              if (seen >= static_cast<int>(gridDim.x)) break;
+              if (clock64() - t0 > B200_WAIT_TIMEOUT_CYCLES) {
+                *abort_flag = 1;
+                atomicCAS(p.err_word, 0, ERR_GEMM_AG_WAIT);
+                break;
+              }
+            }
+            asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy writes -> TMA (async proxy) reads
+            ag_ready = true;
           }
           if (!p.b_mn) {
             tma_load_2d(b_dst, &tmB, fb, k0, n0);
@@ -223,6 +249,36 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int swz = lane & 7;
     uint32_t nstore = 0;  // TMA stores issued by this warp (selects the staging buffer)
     int lt = 0;
+    if (p.ag_bytes > 0) {
+      // fused all-gather: the 128 epilogue threads of every CTA pull this CTA's slice of the weight
+      // bytes from the owning ranks (the local rank's shard included) into the full buffer
+      const int te = threadIdx.x - 64;
+      const long long nvec = p.ag_bytes >> 4;
+      const long long per = (nvec + gridDim.x - 1) / gridDim.x;
+      const long long v0 = per * blockIdx.x, v1 = (v0 + per < nvec) ? v0 + per : nvec;
+      for (long long vb = v0 + te; vb < v1; vb += 128 * 4) {
+        uint4 val[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const long long v = vb + u * 128;
+          if (v < v1) {
+            const long long byte = p.ag_off + (v << 4);
+            const int peer = static_cast<int>(byte / p.ag_shard_bytes);
+            const uint8_t* src = p.ag_peers[peer] + (byte - peer * p.ag_shard_bytes);
+            asm volatile("ld.relaxed.sys.global.v4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(val[u].x), "=r"(val[u].y), "=r"(val[u].z), "=r"(val[u].w) : "l"(src) : "memory");
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const long long v = vb + u * 128;
+          if (v < v1) *reinterpret_cast<uint4*>(p.ag_full + p.ag_off + (v << 4)) = val[u];
+        }
+      }
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (te == 0) asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.ag_sync) : "memory");
+    }
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
       const int t2 = tile / p.k_splits;
       const int m0 = (t2 % p.num_m_tiles) * BM;
@@ -377,6 +433,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   tcgen05_fence_before();
   __syncthreads();
+  if (p.ag_bytes > 0 && threadIdx.x == 0) {
+    // the last CTA to leave knows every producer has passed its wait: leave the counters at zero
+    if (atomicAdd(p.ag_sync + 1, 1) == static_cast<int>(gridDim.x) - 1) {
+      p.ag_sync[0] = 0;
+      __threadfence();
+      p.ag_sync[1] = 0;
+    }
+  }
   if (threadIdx.x == 0) DBG_STAMP(8);
   if (warp_idx == 1) {
     tcgen05_fence_after();
@@ -431,6 +495,13 @@ int get_tmap(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
   return 0;
 }
 
+struct AgArgs {
+  const void* peers_dev;
+  void* full_base;
+  long long off, bytes, shard_bytes;
+  int* sync;
+};
+
 long long* g_gemm_dbg = nullptr;  // set through b200_gemm_set_debug_buffer (bring-up only)
 
 struct GemmOverrides {
@@ -484,7 +555,7 @@ int launch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
 int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
               int a_mn, int b_mn, const float* bias, const float* residual, int ldr, int act,
               int out_fp32, int accumulate, void* aux_out, const void* mask_src, int cfg,
-              const GemmOverrides* ov, void* stream) {
+              const GemmOverrides* ov, void* stream, const AgArgs* ag = nullptr) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
   B200_REQUIRE(!accumulate || out_fp32, "gemm: accumulate needs an fp32 output");
   B200_REQUIRE(act == 0 || act == 1, "gemm: activation %d not supported (0 none, 1 relu)", act);
@@ -540,6 +611,17 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate;
   p.err_word = b200_error_word();
   p.dbg = g_gemm_dbg;
+  if (ag != nullptr && ag->bytes > 0) {
+    B200_REQUIRE(!b_mn && splits == 1, "ag_gemm: B must be a K-major weight and the GEMM un-split");
+    B200_REQUIRE(ag->off % 16 == 0 && ag->bytes % 16 == 0 && ag->shard_bytes % 16 == 0 && ag->shard_bytes > 0,
+                 "ag_gemm: byte ranges must be multiples of 16");
+    B200_REQUIRE(reinterpret_cast<const uint8_t*>(B) == reinterpret_cast<const uint8_t*>(ag->full_base) + ag->off,
+                 "ag_gemm: B must point at offset ag_off of the full buffer");
+    p.ag_peers = reinterpret_cast<const uint8_t* const*>(ag->peers_dev);
+    p.ag_full = reinterpret_cast<uint8_t*>(ag->full_base);
+    p.ag_off = ag->off; p.ag_bytes = ag->bytes; p.ag_shard_bytes = ag->shard_bytes;
+    p.ag_sync = ag->sync;
+  }
   B200_REQUIRE(p.err_word != nullptr, "gemm: no CUDA device");
 
   CUtensorMap tmA, tmB;
@@ -587,6 +669,23 @@ int b200_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, i
                    const void* mask_src, int cfg, void* stream) {
   return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, bias, residual, ldr, act,
                    out_fp32, accumulate, aux_out, mask_src, cfg, nullptr, stream);
+}
+
+// GEMM with the all-gather of its weight operand fused in (FSDP forward): W = B[N,K] (K-major) sits at
+// byte offset ag_off of a flat parameter group whose full copy lives at full_base; the group is
+// sharded evenly over `world` ranks (shard_bytes each) and peers_dev is a device array of every
+// rank's shard base pointer (symmetric memory).  The kernel pulls the weight's bytes over NVLink
+// while its prologue and A loads run, then computes C = A . W^T with the usual epilogue.
+// ag_sync: two ints in device memory, zero on entry and on exit.  All peers' shards must be final
+// (b200_rs_adamw ends with a cross-GPU barrier for exactly that).
+int b200_ag_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                      const float* bias, const float* residual, int ldr, int act, int out_fp32, void* aux_out,
+                      const void* peers_dev, void* full_base, int64_t ag_off, int64_t ag_bytes,
+                      int64_t shard_bytes, int* ag_sync, void* stream) {
+  AgArgs ag{peers_dev, full_base, static_cast<long long>(ag_off), static_cast<long long>(ag_bytes),
+            static_cast<long long>(shard_bytes), ag_sync};
+  return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, 0, 0, bias, residual, ldr, act, out_fp32, 0, aux_out, nullptr,
+                   0, nullptr, stream, &ag);
 }
 
 int b200_gemm_set_debug_buffer(void* buf) {

@@ -86,7 +86,7 @@ def _as_bf16_2d(x: torch.Tensor) -> torch.Tensor:
 def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int, *,
          a_mn_major: bool = False, b_mn_major: bool = False, lda=None, ldb=None,
          bias=None, residual=None, act: int = 0, accumulate: bool = False,
-         aux_out=None, mask_src=None, cfg: int = 0):
+         aux_out=None, mask_src=None, cfg: int = 0, ag=None):
     """out[M,N] (+)= op(A)[M,K] . op(B)[N,K]^T with a fused epilogue (csrc/gemm_tcgen05.cu).
 
     K-major operand: stored [rows, K] (row-major, ``ld`` = row stride).  MN-major operand:
@@ -95,11 +95,37 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K:
     """
     lda = lda if lda is not None else a.stride(0)
     ldb = ldb if ldb is not None else b.stride(0)
+    if ag is not None:   # FSDP: the all-gather of this weight is fused into the GEMM (csrc/gemm_tcgen05.cu)
+        peers_dev, full_base, off, nbytes, shard_bytes, sync = ag
+        assert not a_mn_major and not b_mn_major and not accumulate and mask_src is None
+        call("b200_ag_gemm_bf16", a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, lda, ldb, out.stride(0),
+             ptr(bias), ptr(residual), residual.stride(0) if residual is not None else 0, act,
+             int(out.dtype == torch.float32), ptr(aux_out), peers_dev, full_base, off, nbytes, shard_bytes, sync,
+             stream())
+        return out
     call("b200_gemm_bf16", a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, lda, ldb,
          out.stride(0), int(a_mn_major), int(b_mn_major), ptr(bias), ptr(residual),
          residual.stride(0) if residual is not None else 0, act, int(out.dtype == torch.float32),
          int(accumulate), ptr(aux_out), ptr(mask_src), cfg, stream())
     return out
+
+
+def fused_gather_args(weights):
+    """FSDP hook: if these (adjacent) weights are sharded and their gathered bf16 copy is stale,
+    return the arguments that make the consuming GEMM pull them from the peers itself, and mark
+    them gathered.  ``None`` when there is nothing to do (not sharded / already resident)."""
+    info = getattr(weights[0], "_b200_ag", None)
+    if info is None:
+        return None
+    eng, grp, off0, _ = info
+    if not eng.fused_ag or all(getattr(w, "_b200_ag_version", -1) == eng.version for w in weights):
+        return None
+    last = weights[-1]._b200_ag
+    end = last[2] + last[3]
+    for w in weights:
+        w._b200_ag_version = eng.version
+    return (grp.peers_dev.data_ptr(), eng.full_bf16.data_ptr() + 2 * grp.base, off0, end - off0,
+            2 * grp.shard_n, grp.ag_sync.data_ptr())
 
 
 # ----------------------------------------------------------------------------------------
@@ -115,7 +141,7 @@ class _Linear(torch.autograd.Function):
         res2 = residual.reshape(M, N) if residual is not None else None
         need_aux = act != 0 and residual is not None and grad_on
         aux = torch.empty((M, N), dtype=BF16, device=x.device) if need_aux else None
-        gemm(x2, wb, out, M, N, K, bias=bias, residual=res2, act=act, aux_out=aux)
+        gemm(x2, wb, out, M, N, K, bias=bias, residual=res2, act=act, aux_out=aux, ag=fused_gather_args([weight]))
         ctx.act, ctx.params, ctx.has_res = act, params, residual is not None
         ctx.in_dtype = x.dtype
         y_act = None
@@ -191,11 +217,16 @@ class _LinearQKV(torch.autograd.Function):
         M, K = x2.shape
         ws = [bf16_of(w) for w in (wq, wk, wv)]
         wp = _packed(ws)
+        ag = fused_gather_args([wq, wk, wv]) if wp is not None else None
         if wp is None:
+            for w in (wq, wk, wv):      # not adjacent: gather each on its own before concatenating
+                a1 = fused_gather_args([w])
+                if a1 is not None:
+                    raise RuntimeError("sharded q/k/v weights must be adjacent in their shard group")
             wp = torch.cat(ws, dim=0)
         N = wp.shape[0]
         out = torch.empty((M, N), dtype=BF16, device=x.device)
-        gemm(x2, wp, out, M, N, K)
+        gemm(x2, wp, out, M, N, K, ag=ag)
         ctx.params = params
         ctx.in_dtype = x.dtype
         ctx.save_for_backward(x2, wp)
@@ -392,7 +423,7 @@ class _LMHeadCE(torch.autograd.Function):
         gw = grad_of(weight) if (want_grad and weight.requires_grad) else None
         for r0 in range(0, M, rows):
             r = min(rows, M - r0)
-            gemm(x2[r0:r0 + r], wb, logits, r, V, D)
+            gemm(x2[r0:r0 + r], wb, logits, r, V, D, ag=fused_gather_args([weight]) if r0 == 0 else None)
             call("b200_ce_fwd_bwd", logits.data_ptr(), t.data_ptr() + 8 * r0, stats.data_ptr(),
                  r, V, ld, ignore_index, int(want_grad), float(grad_scale), stream())
             if want_grad:

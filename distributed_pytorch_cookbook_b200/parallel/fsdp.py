@@ -193,6 +193,20 @@ class FSDPStrategy:
                         self.full_fp32[s_lo:s_lo + g.shard_n])
             if self.cpu_offload:
                 self.master_dev.copy_(self.master, non_blocking=True)
+        # fused all-gather: big (bf16) groups are not gathered by a separate kernel - the first GEMM that
+        # consumes each weight pulls it from the peers' shards itself (b200_ag_gemm_bf16)
+        import os
+        self.fused_ag = transport == "symm" and os.environ.get("B200GPT_FUSED_AG", "1") != "0"
+        if self.fused_ag:
+            for g in self.groups:
+                if g.kind != "big":
+                    continue
+                g.peers_dev = torch.tensor([pp + 2 * g.shard_base for pp in self.shard_bf16_buf.peer_ptrs],
+                                           dtype=torch.int64, device=dev)
+                g.ag_sync = torch.zeros(2, dtype=torch.int32, device=dev)
+                for p, o in zip(g.params, g.offsets):
+                    p._b200_ag = (self, g, 2 * o, 2 * p.numel())
+                    p._b200_ag_version = 0
         native.grad_ready_hooks.append(self._on_grad_ready)
         self.comm_stream = torch.cuda.Stream(dev) if cuda else None
         self.version = 1
@@ -248,6 +262,8 @@ class FSDPStrategy:
                 g.event.record(self.comm_stream)
 
     def _ensure(self, g: ShardGroup):
+        if self.fused_ag and g.kind == "big":
+            return                                        # gathered inside the consuming GEMMs
         if g.gathered_version != self.version:
             self._gather(g)
             g.gathered_version = self.version

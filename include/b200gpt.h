@@ -74,6 +74,15 @@ int b200_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, i
                    int ldc, int a_mn_major, int b_mn_major, const float* bias, const float* residual,
                    int ldr, int act, int out_fp32, int accumulate, void* aux_out_bf16,
                    const void* mask_src_bf16, int cfg, void* stream);
+/* GEMM with the FSDP all-gather of its weight fused in (pre-forward unshard of main-fsdp.py:131, folded
+ * into the first consuming GEMM): the kernel pulls bytes [ag_off, ag_off+ag_bytes) of a flat, evenly
+ * sharded parameter group from the owning peers' shard buffers over NVLink into full_base, then
+ * computes C = A . W^T (W = B = full_base + ag_off, K-major).  peers_dev: device array [world] of shard
+ * base pointers; ag_sync: 2 ints of device memory, zero on entry and exit. */
+int b200_ag_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                      const float* bias, const float* residual, int ldr, int act, int out_fp32, void* aux_out_bf16,
+                      const void* peers_dev, void* full_base, int64_t ag_off, int64_t ag_bytes,
+                      int64_t shard_bytes, int* ag_sync, void* stream);
 int b200_gemm_debug(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
                     int ldc, int a_mn_major, int b_mn_major, int a_lbo, int a_sbo, int a_kstep,
                     int b_lbo, int b_sbo, int b_kstep, int force_bn, int force_splits, void* stream);

@@ -50,6 +50,7 @@ def main():
     ap.add_argument("--microbatches", type=int, default=0)
     ap.add_argument("--comm", default="auto")
     ap.add_argument("--no_graph", action="store_true")
+    ap.add_argument("--profile", action="store_true")
     a = ap.parse_args()
     rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
     dev = torch.device(f"cuda:{local}")
@@ -152,6 +153,20 @@ def main():
                 optim.step()
     for i in range(a.warmup):
         step(i)
+    if a.profile:
+        from torch.profiler import ProfilerActivity, profile
+        torch.cuda.synchronize(dev); dist.barrier()
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for i in range(3):
+                step(i)
+            torch.cuda.synchronize(dev)
+        if rank == 0:
+            rows = sorted(prof.key_averages(), key=lambda e: -e.device_time_total)
+            tot = sum(e.device_time_total for e in rows)
+            print(f"total device time {tot/3:.1f} us/step (sum over streams)")
+            for e in rows[:16]:
+                print(f"{e.device_time_total/3:10.1f} us/step n/step={e.count/3:6.1f} avg={e.device_time_total/e.count:9.1f}  {e.key[:100]}")
+        dist.barrier()
     ms = timed(step, a.steps, dev)
     tokens = B * (S - 1) * dp
     if rank == 0:

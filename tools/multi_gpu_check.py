@@ -120,6 +120,35 @@ if "kernels" in which:
         err = (p - p_ref.detach()).abs().max().item()
         report("rs_adamw", err < 1e-5 and torch.equal(pb, p.to(torch.bfloat16)) and dev_err() == 0, mc=use_mc, max_err=err)
 
+if "kernels" in which:
+    # all-gather fused into the GEMM: W [N, K] bf16 sharded evenly (as a flat byte range) over the ranks
+    from distributed_pytorch_cookbook_b200.ops import native
+    ctx2 = SymmContext(dev)
+    for (M, N, K) in [(4096, 768, 256), (1000, 2048, 1024)]:
+        n_el = N * K
+        shard_el = n_el // world
+        shard = ctx2.alloc(shard_el, torch.bfloat16)
+        torch.manual_seed(7)
+        W = (torch.randn(N, K, device=dev) / K ** 0.5).to(torch.bfloat16)       # same on every rank
+        shard.tensor.copy_(W.reshape(-1)[rank * shard_el:(rank + 1) * shard_el])
+        torch.manual_seed(8 + rank)
+        A = torch.randn(M, K, device=dev).to(torch.bfloat16)
+        full = torch.zeros(n_el, dtype=torch.bfloat16, device=dev)
+        peers = torch.tensor(shard.peer_ptrs, dtype=torch.int64, device=dev)
+        sync = torch.zeros(2, dtype=torch.int32, device=dev)
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+        torch.cuda.synchronize(); dist.barrier()
+        for rep in range(2):
+            full.zero_()
+            native.gemm(A, full.view(N, K), out, M, N, K,
+                        ag=(peers.data_ptr(), full.data_ptr(), 0, n_el * 2, shard_el * 2, sync.data_ptr()))
+            torch.cuda.synchronize()
+        ref = A.float() @ W.float().t()
+        err = (out.float() - ref).abs().max().item()
+        dist.barrier()
+        report("ag_gemm", err < 5e-2 and torch.equal(full.view(N, K), W) and int(sync.abs().sum()) == 0 and dev_err() == 0,
+               M=M, N=N, K=K, max_err=err)
+
 CFG = dict(dim=256, head_dim=32, heads=8, num_layers=4, sequence_length=128, vocab_size=8192, batch_size=8,
            learning_rate=1e-3)
 
