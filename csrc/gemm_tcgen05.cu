@@ -26,7 +26,7 @@ namespace {
 constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int UMMA_K = 16;
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_THREADS = 224;  // TMA producer, MMA issuer, 4 epilogue warps, gather warp (fused all-gather)
 constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KB
 
 struct GemmParams {
@@ -54,14 +54,16 @@ struct GemmParams {
   const uint8_t* const* ag_peers;  // device array [world]: base of each rank's shard of the group
   uint8_t* ag_full;                // local full (un-sharded) buffer of the group
   long long ag_off, ag_bytes, ag_shard_bytes;
-  int* ag_sync;                    // [0] copied-CTA counter, [1] exited-CTA counter (both zero between launches)
+  int* ag_sync;                    // [1] exited-CTA tickets, [2 + j] slices landed for n-tile j (all zero between launches)
+  int ag_tile_bytes;               // bytes of W per n-tile (BN * K * 2), a multiple of AG_SLICE
 };
 
 enum : int { ERR_GEMM_PRODUCER = 101, ERR_GEMM_MMA = 102, ERR_GEMM_EPILOGUE = 103, ERR_GEMM_SMEM_ALIGN = 104,
              ERR_GEMM_AG_WAIT = 105 };
 
 
-constexpr int STAGING_BYTES = 4 * 2 * 4096;  // two 32-row x 128-byte swizzled tiles per epilogue warp
+constexpr int STAGING_BYTES = 4 * 4096;  // one 32-row x 128-byte swizzled tile per epilogue warp
+constexpr int AG_SLICE = 16384;           // bounce buffer of the gather warp (fused all-gather)
 
 __device__ __forceinline__ long long global_ns() {
   long long t;
@@ -94,13 +96,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t sA = smem_base;
   const uint32_t sB = smem_base + STAGES * A_STAGE_BYTES;
   const uint32_t sStage = smem_base + STAGES * STAGE_BYTES;
-  const uint32_t bars = sStage + STAGING_BYTES;  // 8-byte mbarriers
+  const uint32_t sBounce = sStage + STAGING_BYTES;
+  const uint32_t bars = sBounce + AG_SLICE;  // 8-byte mbarriers
   const uint32_t full_bar = bars;
   const uint32_t empty_bar = bars + 8 * STAGES;
   const uint32_t tfull_bar = bars + 16 * STAGES;
   const uint32_t tempty_bar = tfull_bar + 16;
+  const uint32_t gather_bar = tempty_bar + 16;
   uint32_t* tmem_ptr_smem =
-      reinterpret_cast<uint32_t*>(smem_raw + STAGES * STAGE_BYTES + STAGING_BYTES + 16 * STAGES + 32);
+      reinterpret_cast<uint32_t*>(smem_raw + STAGES * STAGE_BYTES + STAGING_BYTES + AG_SLICE + 16 * STAGES + 40);
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
   if ((smem_base & 1023u) != 0u) {
     if (threadIdx.x == 0) atomicCAS(p.err_word, 0, ERR_GEMM_SMEM_ALIGN);
@@ -122,6 +126,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_init(tfull_bar + 8 * i, 1);
       mbar_init(tempty_bar + 8 * i, 4);
     }
+    mbar_init(gather_bar, 1);
     fence_barrier_init();
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
@@ -144,7 +149,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
       bool ok = true;
-      bool ag_ready = false;
+      int ag_tile_seen = -1;
       for (int tile = blockIdx.x; tile < total_tiles && ok; tile += gridDim.x) {
         const int split = tile % p.k_splits;
         const int t2 = tile / p.k_splits;
@@ -168,21 +173,24 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j) tma_load_2d(a_dst + j * 8192, &tmA, fb, m0 + 64 * j, k0);
           }
-          if (p.ag_bytes > 0 && !ag_ready) {
-            // every CTA has pulled its slice of the weight from the peers: wait for all of them
+          if (p.ag_bytes > 0 && ag_tile_seen != n0) {
+            // the gather warps of all CTAs pull W from the peers tile by tile: wait for this n-tile
+            const int j = n0 / BN;
+            const long long left = p.ag_bytes - static_cast<long long>(j) * p.ag_tile_bytes;
+            const int expect = static_cast<int>(((left < p.ag_tile_bytes ? left : p.ag_tile_bytes) + AG_SLICE - 1) / AG_SLICE);
             const long long t0 = clock64();
             int seen = 0;
             for (;;) {
-              asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(p.ag_sync) : "memory");
-              if (seen >= static_cast<int>(gridDim.x)) break;
+              asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(p.ag_sync + 2 + j) : "memory");
+              if (seen >= expect) break;
               if (clock64() - t0 > B200_WAIT_TIMEOUT_CYCLES) {
                 *abort_flag = 1;
                 atomicCAS(p.err_word, 0, ERR_GEMM_AG_WAIT);
                 break;
               }
             }
-            asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy writes -> TMA (async proxy) reads
-            ag_ready = true;
+            asm volatile("fence.proxy.async;" ::: "memory");  // peers' bytes were written through the async proxy of other SMs
+            ag_tile_seen = n0;
           }
           if (!p.b_mn) {
             tma_load_2d(b_dst, &tmB, fb, k0, n0);
@@ -235,6 +243,38 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if (lane == 0 && lt == 0) DBG_STAMP(4);
       __syncwarp();
     }
+  } else if (warp_idx == 6) {
+    // ===================== gather warp (fused all-gather of the B operand) =====================
+    // One lane moves this CTA's share of W with the TMA engine: 16 KB slices, peer shard -> smem bounce
+    // buffer -> local full buffer, round-robin over the CTAs in n-tile order so the first tiles land first.
+    if (lane == 0 && p.ag_bytes > 0) {
+      const long long nslices = (p.ag_bytes + AG_SLICE - 1) / AG_SLICE;
+      uint32_t gphase = 0;
+      bool ok = true;
+      for (long long sidx = blockIdx.x; sidx < nslices && ok; sidx += gridDim.x) {
+        long long byte = sidx * AG_SLICE;
+        long long left = p.ag_bytes - byte < AG_SLICE ? p.ag_bytes - byte : AG_SLICE;
+        const int tile_j = static_cast<int>(byte / p.ag_tile_bytes);
+        while (left > 0 && ok) {   // a slice may straddle a shard boundary: one bulk copy per owner
+          const long long gbyte = p.ag_off + byte;
+          const int peer = static_cast<int>(gbyte / p.ag_shard_bytes);
+          const long long in_shard = gbyte - peer * p.ag_shard_bytes;
+          long long seg = p.ag_shard_bytes - in_shard;
+          if (seg > left) seg = left;
+          mbar_arrive_expect_tx(gather_bar, static_cast<uint32_t>(seg));
+          bulk_load_g2s(sBounce, p.ag_peers[peer] + in_shard, static_cast<uint32_t>(seg), gather_bar);
+          if (!mbar_wait(gather_bar, gphase, abort_flag, p.err_word, ERR_GEMM_AG_WAIT)) { ok = false; break; }
+          gphase ^= 1;
+          bulk_store_s2g(p.ag_full + gbyte, sBounce, static_cast<uint32_t>(seg));
+          tma_store_commit();
+          tma_store_wait_all();     // bytes are in global memory before the tile is announced / the buffer reused
+          byte += seg;
+          left -= seg;
+        }
+        if (ok) asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.ag_sync + 2 + tile_j) : "memory");
+      }
+    }
+    __syncwarp();
   } else {
     // ===================== epilogue (4 warps) =====================
     // TMEM -> registers -> (bias / ReLU / aux / mask / residual, selected at compile time by EPI) ->
@@ -245,40 +285,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                    E_MASK = (EPI & EPI_MASK) != 0, E_RES = (EPI & EPI_RES) != 0, E_F32 = (EPI & EPI_F32) != 0,
                    E_ACC = (EPI & EPI_ACC) != 0;
     const int q = warp_idx & 3;  // TMEM lane quarter this warp may access
-    const uint32_t stage_base = sStage + q * 8192;
+    const uint32_t stage_base = sStage + q * 4096;
     const int swz = lane & 7;
     uint32_t nstore = 0;  // TMA stores issued by this warp (selects the staging buffer)
     int lt = 0;
-    if (p.ag_bytes > 0) {
-      // fused all-gather: the 128 epilogue threads of every CTA pull this CTA's slice of the weight
-      // bytes from the owning ranks (the local rank's shard included) into the full buffer
-      const int te = threadIdx.x - 64;
-      const long long nvec = p.ag_bytes >> 4;
-      const long long per = (nvec + gridDim.x - 1) / gridDim.x;
-      const long long v0 = per * blockIdx.x, v1 = (v0 + per < nvec) ? v0 + per : nvec;
-      for (long long vb = v0 + te; vb < v1; vb += 128 * 4) {
-        uint4 val[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const long long v = vb + u * 128;
-          if (v < v1) {
-            const long long byte = p.ag_off + (v << 4);
-            const int peer = static_cast<int>(byte / p.ag_shard_bytes);
-            const uint8_t* src = p.ag_peers[peer] + (byte - peer * p.ag_shard_bytes);
-            asm volatile("ld.relaxed.sys.global.v4.b32 {%0, %1, %2, %3}, [%4];"
-                         : "=r"(val[u].x), "=r"(val[u].y), "=r"(val[u].z), "=r"(val[u].w) : "l"(src) : "memory");
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const long long v = vb + u * 128;
-          if (v < v1) *reinterpret_cast<uint4*>(p.ag_full + p.ag_off + (v << 4)) = val[u];
-        }
-      }
-      __threadfence();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (te == 0) asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.ag_sync) : "memory");
-    }
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
       const int t2 = tile / p.k_splits;
       const int m0 = (t2 % p.num_m_tiles) * BM;
@@ -390,10 +400,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         // stage: fp32 -> one 32x32 tile per chunk; bf16 -> two chunks fill one 32x64 tile
         constexpr bool kStoreEvery = E_F32;
         const bool first_half = kStoreEvery || (c & 1) == 0;
-        const uint32_t stage_buf = stage_base + (nstore & 1u) * 4096u;
+        const uint32_t stage_buf = stage_base;
         const uint32_t my_row = stage_buf + lane * 128;
         if (first_half) {  // the store issued two stores ago must be done reading this buffer
-          if (lane == 0) tma_store_wait_read1();
+          if (lane == 0) tma_store_wait_read0();
           __syncwarp();
         }
         if constexpr (E_F32) {
@@ -436,7 +446,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (p.ag_bytes > 0 && threadIdx.x == 0) {
     // the last CTA to leave knows every producer has passed its wait: leave the counters at zero
     if (atomicAdd(p.ag_sync + 1, 1) == static_cast<int>(gridDim.x) - 1) {
-      p.ag_sync[0] = 0;
+      for (int j = 0; j < p.num_n_tiles; ++j) p.ag_sync[2 + j] = 0;
       __threadfence();
       p.ag_sync[1] = 0;
     }
@@ -500,6 +510,7 @@ struct AgArgs {
   void* full_base;
   long long off, bytes, shard_bytes;
   int* sync;
+  int max_tiles;
 };
 
 long long* g_gemm_dbg = nullptr;  // set through b200_gemm_set_debug_buffer (bring-up only)
@@ -513,7 +524,7 @@ struct GemmOverrides {
 template <int BN, int STAGES, int MIN_CTAS, int EPI>
 int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p,
            int grid, cudaStream_t stream) {
-  constexpr int smem = STAGES * (A_STAGE_BYTES + BN * BK * 2) + STAGING_BYTES + 16 * STAGES + 32 + 16;
+  constexpr int smem = STAGES * (A_STAGE_BYTES + BN * BK * 2) + STAGING_BYTES + AG_SLICE + 16 * STAGES + 40 + 16;
   static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -621,6 +632,10 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
     p.ag_full = reinterpret_cast<uint8_t*>(ag->full_base);
     p.ag_off = ag->off; p.ag_bytes = ag->bytes; p.ag_shard_bytes = ag->shard_bytes;
     p.ag_sync = ag->sync;
+    p.ag_tile_bytes = bn * K * 2;
+    B200_REQUIRE(p.ag_tile_bytes % AG_SLICE == 0 && ldb == K && p.num_n_tiles <= ag->max_tiles,
+                 "ag_gemm: needs a contiguous weight with (tile N x K x 2) %% 16 KiB == 0 and <= %d n-tiles (N=%d K=%d)",
+                 ag->max_tiles, N, K);
   }
   B200_REQUIRE(p.err_word != nullptr, "gemm: no CUDA device");
 
@@ -676,14 +691,14 @@ int b200_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, i
 // sharded evenly over `world` ranks (shard_bytes each) and peers_dev is a device array of every
 // rank's shard base pointer (symmetric memory).  The kernel pulls the weight's bytes over NVLink
 // while its prologue and A loads run, then computes C = A . W^T with the usual epilogue.
-// ag_sync: two ints in device memory, zero on entry and on exit.  All peers' shards must be final
+// ag_sync: 2 + ag_sync_tiles ints in device memory (ag_sync_tiles >= number of n-tiles), zero on entry and on exit.  All peers' shards must be final
 // (b200_rs_adamw ends with a cross-GPU barrier for exactly that).
 int b200_ag_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
                       const float* bias, const float* residual, int ldr, int act, int out_fp32, void* aux_out,
                       const void* peers_dev, void* full_base, int64_t ag_off, int64_t ag_bytes,
-                      int64_t shard_bytes, int* ag_sync, void* stream) {
+                      int64_t shard_bytes, int* ag_sync, int ag_sync_tiles, void* stream) {
   AgArgs ag{peers_dev, full_base, static_cast<long long>(ag_off), static_cast<long long>(ag_bytes),
-            static_cast<long long>(shard_bytes), ag_sync};
+            static_cast<long long>(shard_bytes), ag_sync, ag_sync_tiles};
   return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, 0, 0, bias, residual, ldr, act, out_fp32, 0, aux_out, nullptr,
                    0, nullptr, stream, &ag);
 }

@@ -96,12 +96,12 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K:
     lda = lda if lda is not None else a.stride(0)
     ldb = ldb if ldb is not None else b.stride(0)
     if ag is not None:   # FSDP: the all-gather of this weight is fused into the GEMM (csrc/gemm_tcgen05.cu)
-        peers_dev, full_base, off, nbytes, shard_bytes, sync = ag
+        peers_dev, full_base, off, nbytes, shard_bytes, sync, sync_tiles = ag
         assert not a_mn_major and not b_mn_major and not accumulate and mask_src is None
         call("b200_ag_gemm_bf16", a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, lda, ldb, out.stride(0),
              ptr(bias), ptr(residual), residual.stride(0) if residual is not None else 0, act,
              int(out.dtype == torch.float32), ptr(aux_out), peers_dev, full_base, off, nbytes, shard_bytes, sync,
-             stream())
+             sync_tiles, stream())
         return out
     call("b200_gemm_bf16", a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, lda, ldb,
          out.stride(0), int(a_mn_major), int(b_mn_major), ptr(bias), ptr(residual),
@@ -125,7 +125,7 @@ def fused_gather_args(weights):
     for w in weights:
         w._b200_ag_version = eng.version
     return (grp.peers_dev.data_ptr(), eng.full_bf16.data_ptr() + 2 * grp.base, off0, end - off0,
-            2 * grp.shard_n, grp.ag_sync.data_ptr())
+            2 * grp.shard_n, grp.ag_sync.data_ptr(), grp.ag_sync.numel() - 2)
 
 
 # ----------------------------------------------------------------------------------------

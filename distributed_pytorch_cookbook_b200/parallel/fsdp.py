@@ -203,7 +203,7 @@ class FSDPStrategy:
                     continue
                 g.peers_dev = torch.tensor([pp + 2 * g.shard_base for pp in self.shard_bf16_buf.peer_ptrs],
                                            dtype=torch.int64, device=dev)
-                g.ag_sync = torch.zeros(2, dtype=torch.int32, device=dev)
+                g.ag_sync = torch.zeros(2 + 1024, dtype=torch.int32, device=dev)
                 for p, o in zip(g.params, g.offsets):
                     p._b200_ag = (self, g, 2 * o, 2 * p.numel())
                     p._b200_ag_version = 0

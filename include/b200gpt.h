@@ -78,11 +78,11 @@ int b200_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, i
  * into the first consuming GEMM): the kernel pulls bytes [ag_off, ag_off+ag_bytes) of a flat, evenly
  * sharded parameter group from the owning peers' shard buffers over NVLink into full_base, then
  * computes C = A . W^T (W = B = full_base + ag_off, K-major).  peers_dev: device array [world] of shard
- * base pointers; ag_sync: 2 ints of device memory, zero on entry and exit. */
+ * base pointers; ag_sync: 2 + ag_sync_tiles ints of device memory (>= N/256 tiles), zero on entry and exit. */
 int b200_ag_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
                       const float* bias, const float* residual, int ldr, int act, int out_fp32, void* aux_out_bf16,
                       const void* peers_dev, void* full_base, int64_t ag_off, int64_t ag_bytes,
-                      int64_t shard_bytes, int* ag_sync, void* stream);
+                      int64_t shard_bytes, int* ag_sync, int ag_sync_tiles, void* stream);
 int b200_gemm_debug(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
                     int ldc, int a_mn_major, int b_mn_major, int a_lbo, int a_sbo, int a_kstep,
                     int b_lbo, int b_sbo, int b_kstep, int force_bn, int force_splits, void* stream);

@@ -135,13 +135,13 @@ if "kernels" in which:
         A = torch.randn(M, K, device=dev).to(torch.bfloat16)
         full = torch.zeros(n_el, dtype=torch.bfloat16, device=dev)
         peers = torch.tensor(shard.peer_ptrs, dtype=torch.int64, device=dev)
-        sync = torch.zeros(2, dtype=torch.int32, device=dev)
+        sync = torch.zeros(2 + 64, dtype=torch.int32, device=dev)
         out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
         torch.cuda.synchronize(); dist.barrier()
         for rep in range(2):
             full.zero_()
             native.gemm(A, full.view(N, K), out, M, N, K,
-                        ag=(peers.data_ptr(), full.data_ptr(), 0, n_el * 2, shard_el * 2, sync.data_ptr()))
+                        ag=(peers.data_ptr(), full.data_ptr(), 0, n_el * 2, shard_el * 2, sync.data_ptr(), 64))
             torch.cuda.synchronize()
         ref = A.float() @ W.float().t()
         err = (out.float() - ref).abs().max().item()
