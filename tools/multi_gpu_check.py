@@ -118,7 +118,7 @@ if "kernels" in which:
                   0.9, 0.999, 1e-8, 0.01, 1, 8, CH_RS_ADAMW, _lib.stream())
         torch.cuda.synchronize(); dist.barrier()
         err = (p - p_ref.detach()).abs().max().item()
-        report("rs_adamw", err < 1e-5 and torch.equal(pb, p.to(torch.bfloat16)) and dev_err() == 0, mc=use_mc, max_err=err)
+        report("rs_adamw", err < 1e-4 and torch.equal(pb, p.to(torch.bfloat16)) and dev_err() == 0, mc=use_mc, max_err=err)
 
 if "kernels" in which:
     # all-gather fused into the GEMM: W [N, K] bf16 sharded evenly (as a flat byte range) over the ranks
