@@ -80,6 +80,8 @@ class GradReducer:
     def begin(self):
         self.remaining = [len(idxs) for _, _, idxs in self.buckets]
         self.launched = [False] * len(self.buckets)
+        self.events = [None] * len(self.buckets)
+        self.order = []
         self.works = []
         self.active = True
 
@@ -95,6 +97,7 @@ class GradReducer:
 
     def _launch(self, b: int):
         self.launched[b] = True
+        self.order.append(b)
         lo, hi, _ = self.buckets[b]
         if self.world == 1:
             return
@@ -107,6 +110,8 @@ class GradReducer:
                 _lib.call("b200_allreduce", self.grad_buf.ptrs_dev, self.grad_buf.mc_ptr or None,
                           self.symm.flags.ptrs_dev, self.rank, self.world, lo, hi - lo, 1.0 / self.world,
                           nblocks, CH_ALLREDUCE, self.comm_stream.cuda_stream)
+                self.events[b] = torch.cuda.Event()
+                self.events[b].record(self.comm_stream)
         elif self.cuda:
             ev = torch.cuda.Event()
             ev.record()
@@ -115,22 +120,51 @@ class GradReducer:
                 view = self.arena.grad[lo:hi]
                 view.mul_(1.0 / self.world)
                 dist.all_reduce(view, group=self.group)
+                self.events[b] = torch.cuda.Event()
+                self.events[b].record(self.comm_stream)
         else:
             view = self.arena.grad[lo:hi]
             view.mul_(1.0 / self.world)
             self.works.append(dist.all_reduce(view, group=self.group, async_op=True))
 
-    def finish(self):
-        """Reduce whatever was not triggered by a hook and join the communication stream."""
+    def finish(self, optimizer=None):
+        """Reduce whatever was not triggered by a hook, join the communication stream and (when an
+        optimizer with ranged steps is given) run AdamW bucket range by bucket range, so the update
+        of everything already reduced overlaps the all-reduce of the last bucket (the input
+        embedding, whose gradient only completes at the very end of backward)."""
         for b in range(len(self.buckets)):
             if not self.launched[b]:
                 self._launch(b)
         for w in self.works:
             w.wait()
         self.works = []
-        if self.cuda and self.world > 1:
-            torch.cuda.current_stream().wait_stream(self.comm_stream)
         self.active = False
+        ranged = (optimizer is not None and getattr(optimizer, "native", False) and self.cuda and self.world > 1
+                  and len(self.order) > 1 and all(self.events[b] is not None for b in self.order))
+        if not ranged:
+            if self.cuda and self.world > 1:
+                torch.cuda.current_stream().wait_stream(self.comm_stream)
+            if optimizer is not None:
+                optimizer.step()
+            return
+        cur = torch.cuda.current_stream()
+        head, tail = self.order[:-1], self.order[-1]
+        for b in head:
+            cur.wait_event(self.events[b])
+        # the head buckets are contiguous slices; step them as maximal contiguous ranges
+        spans = sorted((self.buckets[b][0], self.buckets[b][1]) for b in head)
+        merged = []
+        for lo, hi in spans:
+            if merged and merged[-1][1] == lo:
+                merged[-1][1] = hi
+            else:
+                merged.append([lo, hi])
+        first = True
+        for lo, hi in merged:
+            optimizer.step(lo, hi, tick=first)
+            first = False
+        cur.wait_event(self.events[tail])
+        optimizer.step(self.buckets[tail][0], self.buckets[tail][1], tick=False)
 
 
 class DDPStrategy:
@@ -211,8 +245,7 @@ class DDPStrategy:
         with self._autocast(amp):
             loss, _, _ = self.model.loss(input_ids, position_ids, targets, mask=mask)
         loss.backward()
-        self.reducer.finish()
-        self.optim.step()
+        self.reducer.finish(self.optim)       # joins communication and runs the (ranged) optimizer step
         return loss.detach()
 
     def train_step(self, batch, targets, amp=True):
