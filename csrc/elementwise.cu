@@ -155,6 +155,120 @@ layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
   }
 }
 
+// Narrow rows (dim <= 256): one warp handles R rows per iteration with every load of the R rows
+// issued before the first use (the kernel is latency bound: a row is only 1.5 KB), values stay in
+// registers for the single pass, and the dres (residual-branch gradient) add is folded in.
+template <int NV, int R>
+__global__ void __launch_bounds__(256)
+layernorm_bwd_small_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
+                           const float* __restrict__ gamma, const float* __restrict__ mean_in,
+                           const float* __restrict__ rstd_in, const float* __restrict__ dres,
+                           float* __restrict__ dx, bf16* __restrict__ dx_bf16, float* __restrict__ dgamma,
+                           float* __restrict__ dbeta, int rows, int dim, float* __restrict__ scratch,
+                           int* __restrict__ counter) {
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int warps_per_block = blockDim.x >> 5;
+  const int nvec = dim >> 2;
+  const float inv_dim = 1.0f / static_cast<float>(dim);
+  float4 g4[NV], dg[NV], db[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = lane + 32 * i;
+    g4[i] = c < nvec ? __ldg(reinterpret_cast<const float4*>(gamma) + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+    dg[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    db[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  const int row_stride = gridDim.x * warps_per_block * R;
+  for (int row0 = (blockIdx.x * warps_per_block + warp) * R; row0 < rows; row0 += row_stride) {
+    float4 xv[R][NV], rv[R][NV];
+    uint2 dv[R][NV];
+    float mean[R], rstd[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int row = row0 + r;
+      const bool ok = row < rows;
+      mean[r] = ok ? mean_in[row] : 0.f;
+      rstd[r] = ok ? rstd_in[row] : 0.f;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int c = lane + 32 * i;
+        const bool okc = ok && c < nvec;
+        const size_t off = static_cast<size_t>(ok ? row : 0) * dim;
+        xv[r][i] = okc ? reinterpret_cast<const float4*>(x + off)[c] : make_float4(0.f, 0.f, 0.f, 0.f);
+        dv[r][i] = okc ? reinterpret_cast<const uint2*>(dy + off)[c] : make_uint2(0u, 0u);
+        rv[r][i] = (okc && dres != nullptr) ? reinterpret_cast<const float4*>(dres + off)[c]
+                                            : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+    float c1[R], c2[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      c1[r] = 0.f; c2[r] = 0.f;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const float2 d01 = unpack_bf16x2(dv[r][i].x), d23 = unpack_bf16x2(dv[r][i].y);
+        const float h0 = (xv[r][i].x - mean[r]) * rstd[r], h1 = (xv[r][i].y - mean[r]) * rstd[r],
+                    h2 = (xv[r][i].z - mean[r]) * rstd[r], h3 = (xv[r][i].w - mean[r]) * rstd[r];
+        const float a0 = d01.x * g4[i].x, a1 = d01.y * g4[i].y, a2 = d23.x * g4[i].z, a3 = d23.y * g4[i].w;
+        c1[r] += a0 + a1 + a2 + a3;
+        c2[r] += a0 * h0 + a1 * h1 + a2 * h2 + a3 * h3;
+        dg[i].x += d01.x * h0; dg[i].y += d01.y * h1; dg[i].z += d23.x * h2; dg[i].w += d23.y * h3;
+        db[i].x += d01.x; db[i].y += d01.y; db[i].z += d23.x; db[i].w += d23.y;
+        xv[r][i] = make_float4(h0, h1, h2, h3);   // keep xhat
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        c1[r] += __shfl_xor_sync(0xffffffffu, c1[r], o);
+        c2[r] += __shfl_xor_sync(0xffffffffu, c2[r], o);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int row = row0 + r;
+      if (row >= rows) continue;
+      const float m1 = c1[r] * inv_dim, m2 = c2[r] * inv_dim;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int c = lane + 32 * i;
+        if (c < nvec) {
+          const float2 d01 = unpack_bf16x2(dv[r][i].x), d23 = unpack_bf16x2(dv[r][i].y);
+          float4 o;
+          o.x = (d01.x * g4[i].x - m1 - xv[r][i].x * m2) * rstd[r] + rv[r][i].x;
+          o.y = (d01.y * g4[i].y - m1 - xv[r][i].y * m2) * rstd[r] + rv[r][i].y;
+          o.z = (d23.x * g4[i].z - m1 - xv[r][i].z * m2) * rstd[r] + rv[r][i].z;
+          o.w = (d23.y * g4[i].w - m1 - xv[r][i].w * m2) * rstd[r] + rv[r][i].w;
+          reinterpret_cast<float4*>(dx + static_cast<size_t>(row) * dim)[c] = o;
+          if (dx_bf16 != nullptr)
+            reinterpret_cast<uint2*>(dx_bf16 + static_cast<size_t>(row) * dim)[c] =
+                make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
+        }
+      }
+    }
+  }
+  extern __shared__ float red[];  // [warps][2][dim]
+  float* my = red + static_cast<size_t>(warp) * 2 * dim;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = lane + 32 * i;
+    if (c < nvec) {
+      reinterpret_cast<float4*>(my)[c] = dg[i];
+      reinterpret_cast<float4*>(my + dim)[c] = db[i];
+    }
+  }
+  __syncthreads();
+  float* rep = scratch + static_cast<size_t>(blockIdx.x % REPLICAS) * 2 * dim;
+  for (int j = threadIdx.x; j < 2 * dim; j += blockDim.x) {
+    float sacc = 0.f;
+    for (int w = 0; w < warps_per_block; ++w) sacc += red[static_cast<size_t>(w) * 2 * dim + j];
+    atomicAdd(rep + j, sacc);
+  }
+  finish_column_sums(scratch, counter, 2 * dim, gridDim.x, dgamma, dbeta, dim);
+}
+
 template <int NV, bool DX_ONLY = false>
 __global__ void __launch_bounds__(256)
 layernorm_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
@@ -649,8 +763,18 @@ int b200_layernorm_bwd(const void* dy, const float* x, const float* gamma, const
     layernorm_bwd_kernel<NV><<<grid, 256, smem, st>>>(dyb, x, gamma, mean, rstd, dres, dx, dxb,     \
                                                       dgamma, dbeta, rows, dim, scratch, counter);  \
   } while (0)
-  if (dim <= 256) LN_BWD(2);
-  else if (dim <= 1024) LN_BWD(8);
+  if (dim <= 256) {
+    int g = b200_num_sms() * 2;
+    const int mg = ceil_div(rows, 8 * 4);
+    if (g > mg) g = mg;
+    if (g < 1) g = 1;
+    if (dim <= 128)
+      layernorm_bwd_small_kernel<1, 4><<<g, 256, smem, st>>>(dyb, x, gamma, mean, rstd, dres, dx, dxb, dgamma, dbeta,
+                                                             rows, dim, scratch, counter);
+    else
+      layernorm_bwd_small_kernel<2, 4><<<g, 256, smem, st>>>(dyb, x, gamma, mean, rstd, dres, dx, dxb, dgamma, dbeta,
+                                                             rows, dim, scratch, counter);
+  } else if (dim <= 1024) LN_BWD(8);
   else {
     // wide rows: dx by the warp-per-row kernel without the column accumulators (they would need
     // 128+ registers per lane), dgamma/dbeta by a column-parallel pass

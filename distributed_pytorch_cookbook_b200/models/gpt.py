@@ -62,7 +62,10 @@ class FeedForward(nn.Module):
 
     def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
         act = _act_name(self.activation)
-        if ops.use_native(x) and act is not None and self.dropout.p == 0.0:
+        if ops.use_native(x) and act == "relu" and self.bias and self.dropout.p == 0.0:
+            return ops.mlp(x, self.up_proj.weight, self.up_proj.bias, self.down_proj.weight, self.down_proj.bias,
+                           residual=residual)
+        if ops.use_native(x) and act == "relu" and self.dropout.p == 0.0:
             h = ops.linear(x, self.up_proj.weight, self.up_proj.bias, activation=act)
             return ops.linear(h, self.down_proj.weight, self.down_proj.bias, activation=act,
                               residual=residual, out_fp32=residual is not None)
@@ -129,9 +132,9 @@ class DecoderLayer(nn.Module):
 
     def forward(self, x: torch.Tensor, mask: Optional[torch.Tensor] = None) -> torch.Tensor:
         if ops.use_native(x):
-            h = ops.layernorm(x, self.norm1.weight, self.norm1.bias, self.norm1.eps)
+            x, h = ops.layernorm_residual(x, self.norm1.weight, self.norm1.bias, self.norm1.eps)
             x = self.attn(h, mask, residual=x)
-            h = ops.layernorm(x, self.norm2.weight, self.norm2.bias, self.norm2.eps)
+            x, h = ops.layernorm_residual(x, self.norm2.weight, self.norm2.bias, self.norm2.eps)
             return self.fc(h, residual=x)
         x = self.attn(self.norm1(x), mask) + x
         x = self.fc(self.norm2(x)) + x

@@ -107,6 +107,11 @@ def linear(x, weight, bias=None, activation: Optional[str] = None, residual=None
     return native.linear(x, weight, bias, activation, residual, out_fp32)
 
 
+def mlp(x, w1, b1, w2, b2, residual=None):
+    from . import native
+    return native.mlp(x, w1, b1, w2, b2, residual)
+
+
 def linear_qkv(x, wq, wk, wv):
     from . import native
     return native.linear_qkv(x, wq, wk, wv)
@@ -120,6 +125,11 @@ def attention(qkv, heads: int, head_dim: int, scale: float, key_mask=None):
 def layernorm(x, weight, bias, eps: float):
     from . import native
     return native.layernorm(x, weight, bias, eps)
+
+
+def layernorm_residual(x, weight, bias, eps: float):
+    from . import native
+    return native.layernorm_residual(x, weight, bias, eps)
 
 
 def embedding(input_ids, position_ids, tok_w, pos_w):

@@ -189,6 +189,66 @@ def linear(x, weight, bias=None, activation: Optional[str] = None, residual=None
 
 
 # ----------------------------------------------------------------------------------------
+class _MLP(torch.autograd.Function):
+    """relu(relu(x W1^T + b1) W2^T + b2) [+ residual] as one autograd node (reference gpt.py:33-41).
+
+    Forward is two epilogue-fused GEMMs.  Backward fuses the first ReLU's mask into the dgrad GEMM
+    that produces its input gradient (``mask_src`` epilogue: dZ1 = (dZ2 W2) * (u > 0)), so the
+    [tokens, 4*dim] activation gradient is written once, already masked, and only a column-sum
+    pass is left for the bias gradient.
+    """
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, residual, params, grad_on):
+        lead = x.shape[:-1]
+        x2 = _as_bf16_2d(x)
+        M, K = x2.shape
+        w1b, w2b = bf16_of(w1), bf16_of(w2)
+        F1, N = w1b.shape[0], w2b.shape[0]
+        u = torch.empty((M, F1), dtype=BF16, device=x.device)
+        gemm(x2, w1b, u, M, F1, K, bias=b1, act=1, ag=fused_gather_args([w1]))
+        res2 = residual.reshape(M, N) if residual is not None else None
+        out = torch.empty((M, N), dtype=torch.float32 if residual is not None else BF16, device=x.device)
+        aux = torch.empty((M, N), dtype=BF16, device=x.device) if (residual is not None and grad_on) else None
+        gemm(u, w2b, out, M, N, F1, bias=b2, residual=res2, act=1, aux_out=aux, ag=fused_gather_args([w2]))
+        ctx.params, ctx.has_res, ctx.in_dtype = params, residual is not None, x.dtype
+        ctx.save_for_backward(x2, w1b, w2b, u, aux if aux is not None else out)
+        return out.view(*lead, N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w1b, w2b, u, y_act = ctx.saved_tensors
+        w1, b1, w2, b2 = ctx.params
+        M, K = x2.shape
+        F1, N = w1b.shape[0], w2b.shape[0]
+        dy2 = dy.reshape(M, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        sc, cnt = colsum_scratch(dy.device)
+        dz2 = torch.empty((M, N), dtype=BF16, device=dy.device)
+        call("b200_relu_bwd", dy2.data_ptr(), y_act.data_ptr(), dz2.data_ptr(), grad_of(b2).data_ptr(), M, N,
+             int(dy2.dtype == torch.float32), sc.data_ptr(), cnt.data_ptr(), stream())
+        gemm(dz2, u, grad_of(w2), N, F1, M, a_mn_major=True, b_mn_major=True, accumulate=True)     # dW2 += dZ2^T u
+        dz1 = torch.empty((M, F1), dtype=BF16, device=dy.device)
+        gemm(dz2, w2b, dz1, M, F1, N, b_mn_major=True, mask_src=u)                                # dZ1 = (dZ2 W2) * (u > 0)
+        call("b200_colsum_bf16", dz1.data_ptr(), grad_of(b1).data_ptr(), M, F1, F1, sc.data_ptr(), cnt.data_ptr(), stream())
+        gemm(dz1, x2, grad_of(w1), F1, K, M, a_mn_major=True, b_mn_major=True, accumulate=True)    # dW1 += dZ1^T x
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty((M, K), dtype=BF16, device=dy.device)
+            gemm(dz1, w1b, dx, M, K, F1, b_mn_major=True)                                         # dX = dZ1 W1
+            dx = dx.view(*dy.shape[:-1], K)
+            if ctx.in_dtype != BF16:
+                dx = dx.to(ctx.in_dtype)
+        _notify(w2, b2, w1, b1)
+        return dx, None, None, None, None, (dy if ctx.has_res else None), None, None
+
+
+def mlp(x, w1, b1, w2, b2, residual=None):
+    return _MLP.apply(x, w1, b1, w2, b2, residual, (w1, b1, w2, b2), torch.is_grad_enabled())
+
+
+# ----------------------------------------------------------------------------------------
 def _packed(ts) -> Optional[torch.Tensor]:
     """If the tensors are adjacent rows of one buffer return the packed [sum_rows, K] view."""
     t0 = ts[0]
@@ -309,6 +369,62 @@ class _LayerNorm(torch.autograd.Function):
 
 def layernorm(x, weight, bias, eps):
     return _LayerNorm.apply(x, weight, bias, eps, (weight, bias))
+
+
+class _LayerNormResidual(torch.autograd.Function):
+    """``(x, LayerNorm(x))``: the pre-LN block needs both - the normalised activations for the
+    sub-layer and x itself for the residual add that the sub-layer's last GEMM performs in its
+    epilogue.  Routing both through one autograd node lets the backward kernel add the residual
+    branch's gradient while it writes dx (``dres`` of b200_layernorm_bwd) instead of autograd
+    launching a separate fp32 add over the whole residual stream."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps, params):
+        D = x.shape[-1]
+        x2 = x.reshape(-1, D)
+        if x2.dtype != torch.float32 or not x2.is_contiguous():
+            x2 = x2.float().contiguous()
+        rows = x2.shape[0]
+        y = torch.empty((rows, D), dtype=BF16, device=x.device)
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        call("b200_layernorm_fwd", x2.data_ptr(), weight.data_ptr(), bias.data_ptr(), y.data_ptr(),
+             mean.data_ptr(), rstd.data_ptr(), rows, D, float(eps), stream())
+        ctx.params = params
+        ctx.in_dtype = x.dtype
+        ctx.save_for_backward(x2, mean, rstd)
+        return x.view_as(x), y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dres, dy):
+        x2, mean, rstd = ctx.saved_tensors
+        weight, bias = ctx.params
+        rows, D = x2.shape
+        if dy is None:
+            return dres, None, None, None, None
+        dy2 = dy.reshape(rows, D)
+        if dy2.dtype != BF16:
+            dy2 = dy2.to(BF16)
+        dy2 = dy2.contiguous()
+        dr = None
+        if dres is not None:
+            dr = dres.reshape(rows, D)
+            if dr.dtype != torch.float32 or not dr.is_contiguous():
+                dr = dr.float().contiguous()
+        dx = torch.empty((rows, D), dtype=torch.float32, device=dy.device)
+        call("b200_layernorm_bwd", dy2.data_ptr(), x2.data_ptr(), weight.data_ptr(), mean.data_ptr(),
+             rstd.data_ptr(), ptr(dr), dx.data_ptr(), None, grad_of(weight).data_ptr(),
+             grad_of(bias).data_ptr(), rows, D, *[t.data_ptr() for t in colsum_scratch(dy.device)], stream())
+        _notify(weight, bias)
+        dx = dx.view(dy.shape)
+        if ctx.in_dtype != torch.float32:
+            dx = dx.to(ctx.in_dtype)
+        return dx, None, None, None, None
+
+
+def layernorm_residual(x, weight, bias, eps):
+    """-> (x for the residual branch, LayerNorm(x) as bf16)"""
+    return _LayerNormResidual.apply(x, weight, bias, eps, (weight, bias))
 
 
 # ----------------------------------------------------------------------------------------
