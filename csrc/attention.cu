@@ -346,8 +346,12 @@ __global__ void __launch_bounds__(ATTN_THREADS)
 attn_bwd_kernel(const AttnParams p) {
   constexpr int TILE_BYTES = TQ * D * 2;
   constexpr int SS_BYTES = TQ * TK * 2;
-  constexpr uint32_t TMEM_COLS = 512;  // S/dQ [0,128) dP [128,256) dV [256,256+D) dK [256+D,256+2D)
-  constexpr uint32_t C_S = 0, C_DP = 128, C_DV = 256, C_DK = 256 + D;
+  // TMEM columns.  D <= 64 ("compact"): S, then dP, then dQ reuse [0,128) one after the other and
+  // dV / dK follow at 128 / 128+D - 256 columns, so two CTAs share an SM and hide each other's
+  // MMA / softmax latencies.  D = 128: S/dQ [0,128) dP [128,256) dV [256,384) dK [384,512).
+  constexpr bool COMPACT = (128 + 2 * D) <= 256;
+  constexpr uint32_t TMEM_COLS = COMPACT ? 256 : 512;
+  constexpr uint32_t C_S = 0, C_DP = COMPACT ? 0 : 128, C_DV = COMPACT ? 128 : 256, C_DK = C_DV + D;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 127u) & ~127u;
   const uint32_t sK = base, sV = sK + TILE_BYTES, sQ = sV + TILE_BYTES, sdO = sQ + TILE_BYTES;
@@ -406,9 +410,11 @@ attn_bwd_kernel(const AttnParams p) {
 #pragma unroll
       for (int kk = 0; kk < D / 16; ++kk)
         umma_f16_ss(tmem + C_S, desc_kmajor(sQ, kk), desc_kmajor(sK, kk), idesc_ss, kk > 0 ? 1u : 0u);
+      if constexpr (!COMPACT) {
 #pragma unroll
-      for (int kk = 0; kk < D / 16; ++kk)
-        umma_f16_ss(tmem + C_DP, desc_kmajor(sdO, kk), desc_kmajor(sV, kk), idesc_ss, kk > 0 ? 1u : 0u);
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_f16_ss(tmem + C_DP, desc_kmajor(sdO, kk), desc_kmajor(sV, kk), idesc_ss, kk > 0 ? 1u : 0u);
+      }
       umma_commit(bar);
     }
     const size_t stat_idx = (static_cast<size_t>(b) * p.H + h) * p.T + (q_ok ? q : 0);
@@ -420,32 +426,82 @@ attn_bwd_kernel(const AttnParams p) {
     tcgen05_fence_after();
 
     const bool diag = (qt == kt);
-#pragma unroll 1
-    for (int c = 0; c < TK / 32; ++c) {
-      uint32_t rs[32], rd[32];
-      tmem_ld_32x32b_x32(t_lane + C_S + c * 32, rs);
-      tmem_ld_32x32b_x32(t_lane + C_DP + c * 32, rd);
-      tmem_ld_wait();
-      uint32_t pk[16], dk[16];
-      const uint32_t kb = keep_bits(k0 + c * 32, q, diag, q_ok, p.T, mask_row);
+    if constexpr (COMPACT) {
+      // P from S (kept packed in registers and written to smem), then dP into the same columns
+      uint32_t pkeep[TK / 2];
 #pragma unroll
-      for (int j = 0; j < 32; j += 2) {
-        float pv[2], dsv[2];
+      for (int c = 0; c < TK / 32; ++c) {
+        uint32_t rs[32];
+        tmem_ld_32x32b_x32(t_lane + C_S + c * 32, rs);
+        tmem_ld_wait();
+        const uint32_t kb = keep_bits(k0 + c * 32, q, diag, q_ok, p.T, mask_row);
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          const float e = exp2f(__uint_as_float(rs[j + u]) * sl2 - lse_l2);
-          const float pr = ((kb >> (j + u)) & 1u) ? e : 0.f;
-          pv[u] = pr;
-          dsv[u] = pr * (__uint_as_float(rd[j + u]) - delta) * p.scale;
+        for (int j = 0; j < 32; j += 2) {
+          const float e0 = exp2f(__uint_as_float(rs[j]) * sl2 - lse_l2);
+          const float e1 = exp2f(__uint_as_float(rs[j + 1]) * sl2 - lse_l2);
+          pkeep[c * 16 + (j >> 1)] = pack_bf16x2(((kb >> j) & 1u) ? e0 : 0.f, ((kb >> (j + 1)) & 1u) ? e1 : 0.f);
         }
-        pk[j >> 1] = pack_bf16x2(pv[0], pv[1]);
-        dk[j >> 1] = pack_bf16x2(dsv[0], dsv[1]);
-      }
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        const uint32_t off = (c * 4 + g) * CHUNK_STRIDE + tid * 16;
-        st_shared_v4(sP + off, pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
-        st_shared_v4(sdS + off, dk[4 * g], dk[4 * g + 1], dk[4 * g + 2], dk[4 * g + 3]);
+        for (int g = 0; g < 4; ++g)
+          st_shared_v4(sP + (c * 4 + g) * CHUNK_STRIDE + tid * 16, pkeep[c * 16 + 4 * g], pkeep[c * 16 + 4 * g + 1],
+                       pkeep[c * 16 + 4 * g + 2], pkeep[c * 16 + 4 * g + 3]);
+      }
+      tcgen05_fence_before();
+      __syncthreads();                     // every thread has read S: dP may overwrite the columns
+      if (tid == 0) {
+        tcgen05_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_f16_ss(tmem + C_DP, desc_kmajor(sdO, kk), desc_kmajor(sV, kk), idesc_ss, kk > 0 ? 1u : 0u);
+        umma_commit(bar);
+      }
+      if (!mbar_wait(bar, phase, abort_flag, p.err_word, ERR_ATTN_BWD)) { ok = false; }
+      phase ^= 1;
+      if (!__syncthreads_and(ok)) { ok = false; break; }
+      tcgen05_fence_after();
+#pragma unroll
+      for (int c = 0; c < TK / 32; ++c) {
+        uint32_t rd[32], dk[16];
+        tmem_ld_32x32b_x32(t_lane + C_DP + c * 32, rd);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          const float2 pr = unpack_bf16x2(pkeep[c * 16 + (j >> 1)]);
+          dk[j >> 1] = pack_bf16x2(pr.x * (__uint_as_float(rd[j]) - delta) * p.scale,
+                                   pr.y * (__uint_as_float(rd[j + 1]) - delta) * p.scale);
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          st_shared_v4(sdS + (c * 4 + g) * CHUNK_STRIDE + tid * 16, dk[4 * g], dk[4 * g + 1], dk[4 * g + 2], dk[4 * g + 3]);
+      }
+    } else {
+#pragma unroll 1
+      for (int c = 0; c < TK / 32; ++c) {
+        uint32_t rs[32], rd[32];
+        tmem_ld_32x32b_x32(t_lane + C_S + c * 32, rs);
+        tmem_ld_32x32b_x32(t_lane + C_DP + c * 32, rd);
+        tmem_ld_wait();
+        uint32_t pk[16], dk[16];
+        const uint32_t kb = keep_bits(k0 + c * 32, q, diag, q_ok, p.T, mask_row);
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          float pv[2], dsv[2];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const float e = exp2f(__uint_as_float(rs[j + u]) * sl2 - lse_l2);
+            const float pr = ((kb >> (j + u)) & 1u) ? e : 0.f;
+            pv[u] = pr;
+            dsv[u] = pr * (__uint_as_float(rd[j + u]) - delta) * p.scale;
+          }
+          pk[j >> 1] = pack_bf16x2(pv[0], pv[1]);
+          dk[j >> 1] = pack_bf16x2(dsv[0], dsv[1]);
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const uint32_t off = (c * 4 + g) * CHUNK_STRIDE + tid * 16;
+          st_shared_v4(sP + off, pk[4 * g], pk[4 * g + 1], pk[4 * g + 2], pk[4 * g + 3]);
+          st_shared_v4(sdS + off, dk[4 * g], dk[4 * g + 1], dk[4 * g + 2], dk[4 * g + 3]);
+        }
       }
     }
     tcgen05_fence_before();
