@@ -213,6 +213,17 @@ def run_ours(args):
         host_losses.append(loss.item())      # D2H read of the step's result, every step
 
     ms_e2e = timed(e2e_timed, args.steps, device)
+
+    # exposed communication per step = step time minus the same step with the all-reduces skipped
+    exposed_comm_ms = None
+    if n > 1 and hasattr(strategy, "reducer"):
+        strategy.reducer.skip_comm = True
+        strategy._graphed = None                      # re-capture without the collective kernels
+        for i in range(6):
+            dev_step(i)
+        torch.cuda.synchronize(device)
+        ms_nocomm = timed(dev_step, args.steps, device)
+        exposed_comm_ms = max(ms_total - ms_nocomm, 0.0) / args.steps
     tokens_per_step = CFG["batch_size"] * (CFG["sequence_length"] - 1) * n
     value = tokens_per_step * args.steps / ms_total * 1e3
     e2e_value = tokens_per_step * args.steps / ms_e2e * 1e3
@@ -221,7 +232,8 @@ def run_ours(args):
     if rank == 0:
         extra = {"cuda_graph": bool(getattr(strategy, "use_graph", False)),
                  "final_loss": host_losses[-1] if host_losses else None,
-                 "comm": getattr(strategy, "comm_kind", None)}
+                 "comm": getattr(strategy, "comm_kind", None),
+                 "exposed_comm_ms_per_step": exposed_comm_ms}
         print(json.dumps(result_line("ours", value, ms_total / args.steps, e2e_value, n, args.steps, args.warmup,
                                      clocks, launches, extra, h2d, 4)), flush=True)
     if dist.is_initialized():

@@ -72,6 +72,7 @@ class GradReducer:
         self.comm_stream = torch.cuda.Stream(arena.device) if self.cuda else None
         self.works = []
         self.active = False
+        self.skip_comm = False      # measurement only: run the step without the all-reduces
         native.grad_ready_hooks.append(self.on_grad_ready)
         for p in arena.params:
             p.register_post_accumulate_grad_hook(self.on_grad_ready)
@@ -99,7 +100,7 @@ class GradReducer:
         self.launched[b] = True
         self.order.append(b)
         lo, hi, _ = self.buckets[b]
-        if self.world == 1:
+        if self.world == 1 or self.skip_comm:
             return
         if self.transport == "symm":
             ev = torch.cuda.Event()
@@ -140,7 +141,7 @@ class GradReducer:
         self.works = []
         self.active = False
         ranged = (optimizer is not None and getattr(optimizer, "native", False) and self.cuda and self.world > 1
-                  and len(self.order) > 1 and all(self.events[b] is not None for b in self.order))
+                  and not self.skip_comm and len(self.order) > 1 and all(self.events[b] is not None for b in self.order))
         if not ranged:
             if self.cuda and self.world > 1:
                 torch.cuda.current_stream().wait_stream(self.comm_stream)
