@@ -571,7 +571,7 @@ __device__ __forceinline__ void cp_async_16(uint32_t smem_dst, const void* gsrc)
 }
 
 // One block per row.  The logits row (bf16, <= 113 KB) is staged in shared memory with cp.async (no
-// register staging, so two rows per SM overlap each other's phases), reduced (max / argmax /
+// register staging, so two rows per SM overlap each other's phases), reduced (packed-bf16 max,
 // sum-exp) and - when write_grad - overwritten in place in global memory with
 // dlogits = (softmax - onehot) * scale.  exp() is evaluated once per element: p = exp(l - max) is
 // written back to the staged row as bf16 and reused by the gradient pass.
@@ -587,9 +587,7 @@ ce_fwd_bwd_kernel(bf16* __restrict__ logits, const int64_t* __restrict__ targets
   const int tgt = static_cast<int>(tgt64);
   const int nvec = ld >> 3;
   __shared__ float s_f[CE_THREADS / 32];
-  __shared__ int s_i[CE_THREADS / 32];
   __shared__ float s_bcast[2];
-  __shared__ int s_arg;
 
   if (!valid) {  // ignored row: no loss, zero gradient
     if (write_grad)
@@ -604,61 +602,72 @@ ce_fwd_bwd_kernel(bf16* __restrict__ logits, const int64_t* __restrict__ targets
   asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
 
-  float mx = -INFINITY;
-  int arg = 0;
+  // pad columns [vocab, ld) -> -inf in the staged row (each thread patches the vectors it copied
+  // itself), so the passes below run unpredicated and the pad gradient comes out as exact zeros
+  for (int c = vocab >> 3; c < nvec; ++c) {
+    if (c % CE_THREADS != static_cast<int>(threadIdx.x)) continue;
+    unsigned short* e = reinterpret_cast<unsigned short*>(srow + c);
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (c * 8 + j >= vocab) e[j] = 0xFF80u;   // bf16 -inf
+  }
+
+  // pass 1: row max with packed bf16x2 max (one instruction per two logits)
+  __nv_bfloat162 m2 = __floats2bfloat162_rn(-INFINITY, -INFINITY);
   for (int c = threadIdx.x; c < nvec; c += CE_THREADS) {
     const uint4 u = srow[c];
     const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
-    for (int t = 0; t < 4; ++t) {
-      const float2 f = unpack_bf16x2(w[t]);
-      const int col = c * 8 + 2 * t;
-      if (col < vocab && f.x > mx) { mx = f.x; arg = col; }
-      if (col + 1 < vocab && f.y > mx) { mx = f.y; arg = col + 1; }
-    }
+    for (int t = 0; t < 4; ++t) m2 = __hmax2(m2, *reinterpret_cast<const __nv_bfloat162*>(&w[t]));
   }
-  // block argmax (ties -> lowest index, like torch.argmax)
+  float mx = fmaxf(__low2float(m2), __high2float(m2));
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const float om = __shfl_xor_sync(0xffffffffu, mx, o);
-    const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
-    if (om > mx || (om == mx && oa < arg)) { mx = om; arg = oa; }
-  }
-  if (lane == 0) { s_f[warp] = mx; s_i[warp] = arg; }
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (lane == 0) s_f[warp] = mx;
   __syncthreads();
   if (warp == 0) {
-    float m2 = lane < CE_THREADS / 32 ? s_f[lane] : -INFINITY;
-    int a2 = lane < CE_THREADS / 32 ? s_i[lane] : 0x7fffffff;
+    float t2 = lane < CE_THREADS / 32 ? s_f[lane] : -INFINITY;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float om = __shfl_xor_sync(0xffffffffu, m2, o);
-      const int oa = __shfl_xor_sync(0xffffffffu, a2, o);
-      if (om > m2 || (om == m2 && oa < a2)) { m2 = om; a2 = oa; }
-    }
-    if (lane == 0) { s_bcast[0] = m2; s_arg = a2; }
+    for (int o = 16; o > 0; o >>= 1) t2 = fmaxf(t2, __shfl_xor_sync(0xffffffffu, t2, o));
+    if (lane == 0) s_bcast[0] = t2;
   }
   __syncthreads();
   const float row_max = s_bcast[0];
+  // prediction correct <=> the target holds the max and no lower index ties it (torch.argmax
+  // returns the first maximum).  Only rows whose target logit equals the max pay for the scan.
+  bool correct = false;
+  if (tgt_logit == row_max) {           // block-uniform
+    int earlier = 0;
+    const int cend = tgt >> 3;
+    for (int c = threadIdx.x; c <= cend; c += CE_THREADS) {
+      const bf16* e = reinterpret_cast<const bf16*>(srow + c);
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        earlier |= (c * 8 + j < tgt && __bfloat162float(e[j]) == row_max) ? 1 : 0;
+    }
+    correct = __syncthreads_or(earlier) == 0;
+  }
   const float kLog2e = 1.4426950408889634f;
   const float mscaled = row_max * kLog2e;
 
-  float sum = 0.f;
+  // pass 2: p = exp(l - max), summed in fp32 and written back to the staged row as bf16
+  float sum0 = 0.f, sum1 = 0.f;
   for (int c = threadIdx.x; c < nvec; c += CE_THREADS) {
     const uint4 u = srow[c];
     uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
       const float2 f = unpack_bf16x2(w[t]);
-      const int col = c * 8 + 2 * t;
-      const float p0 = col < vocab ? exp2f(f.x * kLog2e - mscaled) : 0.f;
-      const float p1 = col + 1 < vocab ? exp2f(f.y * kLog2e - mscaled) : 0.f;
-      sum += p0 + p1;
+      const float p0 = exp2f(fmaf(f.x, kLog2e, -mscaled));
+      const float p1 = exp2f(fmaf(f.y, kLog2e, -mscaled));
+      sum0 += p0;
+      sum1 += p1;
       w[t] = pack_bf16x2(p0, p1);
     }
     srow[c] = make_uint4(w[0], w[1], w[2], w[3]);   // same thread re-reads it below: no sync needed
   }
-  sum = warp_sum(sum);
+  float sum = warp_sum(sum0 + sum1);
   if (lane == 0) s_f[warp] = sum;
   __syncthreads();
   if (warp == 0) {
@@ -671,25 +680,27 @@ ce_fwd_bwd_kernel(bf16* __restrict__ logits, const int64_t* __restrict__ targets
   if (threadIdx.x == 0) {
     const float lse = row_max + logf(total);
     atomicAdd(stats + 1, lse - tgt_logit);
-    if (s_arg == tgt) atomicAdd(stats + 2, 1.0f);
+    if (correct) atomicAdd(stats + 2, 1.0f);
   }
   if (!write_grad) return;
   const float n_valid = fmaxf(stats[0], 1.0f);
   const float scale = grad_scale / n_valid;
   const float pscale = scale / total;
+  // pass 3: dlogits = p * scale / sum, streamed straight to global; the target column is fixed up
+  // afterwards by the thread that stored its vector (program order on one address)
   for (int c = threadIdx.x; c < nvec; c += CE_THREADS) {
     const uint4 u = srow[c];
     uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
       const float2 f = unpack_bf16x2(w[t]);
-      const int col = c * 8 + 2 * t;
-      float g0 = f.x * pscale, g1 = f.y * pscale;
-      if (col == tgt) g0 -= scale;
-      if (col + 1 == tgt) g1 -= scale;
-      w[t] = pack_bf16x2(g0, g1);
+      w[t] = pack_bf16x2(f.x * pscale, f.y * pscale);
     }
     reinterpret_cast<uint4*>(lr)[c] = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  if ((tgt >> 3) % CE_THREADS == static_cast<int>(threadIdx.x)) {
+    const float pt = __bfloat162float(reinterpret_cast<const bf16*>(srow)[tgt]);
+    lr[tgt] = __float2bfloat16(pt * pscale - scale);
   }
 }
 
