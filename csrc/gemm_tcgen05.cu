@@ -47,6 +47,7 @@ struct GemmParams {
   const bf16* mask_src;
   int act, out_fp32, accumulate;
   int tma_store;  // 1: epilogue stages tiles in smem and writes them with TMA (coalesced, clipped)
+  int n_fastest;  // tile order: 0 = consecutive CTAs walk down M (share the B tile), 1 = walk along N (share A)
   long long* dbg;  // optional per-CTA phase timestamps (16 slots per CTA), bring-up only
   int* err_word;
   // Fused all-gather of the B operand (FSDP, b200_ag_gemm_bf16): before its B tiles are read, the
@@ -64,7 +65,9 @@ enum : int { ERR_GEMM_PRODUCER = 101, ERR_GEMM_MMA = 102, ERR_GEMM_EPILOGUE = 10
              ERR_GEMM_AG_WAIT = 105 };
 
 
-constexpr int STAGING_BYTES = 4 * 4096;  // one 32-row x 128-byte swizzled tile per epilogue warp
+constexpr int STAGING_BYTES = 4 * 4096;  // one 32-row x 128-byte swizzled tile per epilogue warp (x NSTG buffers)
+// staging buffers per epilogue warp: with two, a warp fills one while the TMA engine still reads the other
+template <int BN, int CG> constexpr int staging_bufs() { return (CG == 2 || BN == 128) ? 2 : 1; }
 constexpr int AG_SLICE = 16384;           // bounce buffer of the gather warp (fused all-gather)
 
 __device__ __forceinline__ long long global_ns() {
@@ -83,13 +86,20 @@ __device__ __forceinline__ long long global_ns() {
 
 enum : int { EPI_BIAS = 1, EPI_RELU = 2, EPI_AUX = 4, EPI_MASK = 8, EPI_RES = 16, EPI_F32 = 32, EPI_ACC = 64 };
 
-template <int BN, int STAGES, int MIN_CTAS, int EPI>
+// CG = 1: one CTA per 128 x BN tile (tcgen05 cta_group::1).
+// CG = 2: a CTA pair (cluster of 2 = the two SMs of a TPC) per 256 x BN tile (cta_group::2): each CTA
+//         stages its own 128 rows of A and HALF of the B tile, the leader's single thread issues
+//         M = 256 MMAs that read both CTAs' shared memory and write both CTAs' TMEM.  Per FLOP a CTA
+//         pulls 1/3 less operand data out of L2, which is what bounds the short-K GEMMs here.
+template <int BN, int STAGES, int MIN_CTAS, int EPI, int CG>
 __global__ void __launch_bounds__(GEMM_THREADS, MIN_CTAS)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
-  constexpr int B_STAGE_BYTES = BN * BK * 2;
+  constexpr int B_ROWS = BN / CG;                 // rows of the B tile staged by this CTA
+  constexpr int B_STAGE_BYTES = B_ROWS * BK * 2;
   constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   constexpr uint32_t TMEM_COLS = 2 * BN;
+  constexpr int NSTG = staging_bufs<BN, CG>();
 
   // 128B-swizzled TMA/UMMA tiles need 1024-byte alignment; the dynamic smem window of a kernel
   // without static smem starts 1024-aligned (checked below, reported through the error word).
@@ -98,7 +108,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t sA = smem_base;
   const uint32_t sB = smem_base + STAGES * A_STAGE_BYTES;
   const uint32_t sStage = smem_base + STAGES * STAGE_BYTES;
-  const uint32_t sBounce = sStage + STAGING_BYTES;
+  const uint32_t sBounce = sStage + NSTG * STAGING_BYTES;
   const uint32_t bars = sBounce + AG_SLICE;  // 8-byte mbarriers
   const uint32_t full_bar = bars;
   const uint32_t empty_bar = bars + 8 * STAGES;
@@ -106,7 +116,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t tempty_bar = tfull_bar + 16;
   const uint32_t gather_bar = tempty_bar + 16;
   uint32_t* tmem_ptr_smem =
-      reinterpret_cast<uint32_t*>(smem_raw + STAGES * STAGE_BYTES + STAGING_BYTES + AG_SLICE + 16 * STAGES + 40);
+      reinterpret_cast<uint32_t*>(smem_raw + STAGES * STAGE_BYTES + NSTG * STAGING_BYTES + AG_SLICE + 16 * STAGES + 40);
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
   if ((smem_base & 1023u) != 0u) {
     if (threadIdx.x == 0) atomicCAS(p.err_word, 0, ERR_GEMM_SMEM_ALIGN);
@@ -115,6 +125,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   const int warp_idx = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int cta_rank = (CG == 2) ? static_cast<int>(cluster_ctarank()) : 0;
+  const int unit = blockIdx.x / CG;               // CTA (CG = 1) or CTA pair (CG = 2) index
+  const int num_units = gridDim.x / CG;
 
   if (threadIdx.x == 0) {
     DBG_STAMP(0);
@@ -126,7 +139,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(tfull_bar + 8 * i, 1);
-      mbar_init(tempty_bar + 8 * i, 4);
+      mbar_init(tempty_bar + 8 * i, 4 * CG);   // the epilogue warps of both CTAs of a pair
     }
     mbar_init(gather_bar, 1);
     fence_barrier_init();
@@ -135,11 +148,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tma_prefetch_desc(&tmC);
   }
   if (warp_idx == 1) {
-    tmem_alloc(smem_u32(tmem_ptr_smem), TMEM_COLS);
-    tmem_relinquish();
+    if constexpr (CG == 2) {
+      tmem_alloc_2sm(smem_u32(tmem_ptr_smem), TMEM_COLS);
+      tmem_relinquish_2sm();
+    } else {
+      tmem_alloc(smem_u32(tmem_ptr_smem), TMEM_COLS);
+      tmem_relinquish();
+    }
   }
   tcgen05_fence_before();
   __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all();   // the peer's barriers exist before anything arrives on them
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
   if (threadIdx.x == 0) DBG_STAMP(1);
@@ -158,11 +177,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       uint32_t stage = 0, phase = 0;
       bool ok = true;
       int ag_tile_seen = -1;
-      for (int tile = blockIdx.x; tile < total_tiles && ok; tile += gridDim.x) {
+      for (int tile = unit; tile < total_tiles && ok; tile += num_units) {
         const int split = tile % p.k_splits;
         const int t2 = tile / p.k_splits;
-        const int m0 = (t2 % p.num_m_tiles) * BM;
-        const int n0 = (t2 / p.num_m_tiles) * BN;
+        const int m0 = (p.n_fastest ? t2 / p.num_n_tiles : t2 % p.num_m_tiles) * (BM * CG) + cta_rank * BM;
+        const int n0 = (p.n_fastest ? t2 % p.num_n_tiles : t2 / p.num_m_tiles) * BN;
+        const int nb0 = n0 + cta_rank * B_ROWS;   // first B row staged by this CTA
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -171,17 +191,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             break;
           }
           const uint32_t fb = full_bar + 8 * stage;
-          mbar_arrive_expect_tx(fb, STAGE_BYTES);
+          // CG = 2: the bytes of both CTAs are reported to the leader's barrier, armed by the leader
+          if (CG == 1 || cta_rank == 0) mbar_arrive_expect_tx(fb, CG * STAGE_BYTES);
           const int k0 = kb * BK;
           const uint32_t a_dst = sA + stage * A_STAGE_BYTES;
           const uint32_t b_dst = sB + stage * B_STAGE_BYTES;
+          auto load = [&](uint32_t dst, const CUtensorMap* tm, int c0, int c1) {
+            if constexpr (CG == 2) tma_load_2d_2sm(dst, tm, fb, c0, c1);
+            else tma_load_2d(dst, tm, fb, c0, c1);
+          };
           if (!p.a_mn) {
-            tma_load_2d(a_dst, &tmA, fb, k0, m0);
+            load(a_dst, &tmA, k0, m0);
           } else {
 #pragma unroll
-            for (int j = 0; j < BM / 64; ++j) tma_load_2d(a_dst + j * 8192, &tmA, fb, m0 + 64 * j, k0);
+            for (int j = 0; j < BM / 64; ++j) load(a_dst + j * 8192, &tmA, m0 + 64 * j, k0);
           }
-          if (p.ag_bytes > 0 && ag_tile_seen != n0) {
+          if (CG == 1 && p.ag_bytes > 0 && ag_tile_seen != n0) {
             // the gather warps of all CTAs pull W from the peers tile by tile: wait for this n-tile
             const int j = n0 / BN;
             const long long left = p.ag_bytes - static_cast<long long>(j) * p.ag_tile_bytes;
@@ -201,12 +226,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             ag_tile_seen = n0;
           }
           if (!p.b_mn) {
-            tma_load_2d(b_dst, &tmB, fb, k0, n0);
+            load(b_dst, &tmB, k0, nb0);
           } else {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j) tma_load_2d(b_dst + j * 8192, &tmB, fb, n0 + 64 * j, k0);
+            for (int j = 0; j < B_ROWS / 64; ++j) load(b_dst + j * 8192, &tmB, nb0 + 64 * j, k0);
           }
-          if (kb == kb0 && tile == (int)blockIdx.x) DBG_STAMP(2);
+          if (kb == kb0 && tile == unit) DBG_STAMP(2);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -218,7 +243,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint32_t stage = 0, phase = 0;
     int lt = 0;
     bool ok = true;
-    for (int tile = blockIdx.x; tile < total_tiles && ok; tile += gridDim.x, ++lt) {
+    for (int tile = unit; tile < total_tiles && ok && (CG == 1 || cta_rank == 0); tile += num_units, ++lt) {
       const int split = tile % p.k_splits;
       const int kb0 = split * p.kb_per_split;
       const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
@@ -240,14 +265,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           for (int kk = 0; kk < BK / UMMA_K; ++kk) {
             const uint64_t ad = umma_desc_at(p.a_desc_base, a_src + kk * p.a_kstep);
             const uint64_t bd = umma_desc_at(p.b_desc_base, b_src + kk * p.b_kstep);
-            umma_f16_ss(tmem_d, ad, bd, p.idesc, (kb > kb0 || kk > 0) ? 1u : 0u);
+            if constexpr (CG == 2) umma_f16_ss_2sm(tmem_d, ad, bd, p.idesc, (kb > kb0 || kk > 0) ? 1u : 0u);
+            else umma_f16_ss(tmem_d, ad, bd, p.idesc, (kb > kb0 || kk > 0) ? 1u : 0u);
           }
-          umma_commit(empty_bar + 8 * stage);  // frees the smem slot when these MMAs retire
+          // frees the smem slot (in both CTAs of a pair) when these MMAs retire
+          if constexpr (CG == 2) umma_commit_2sm(empty_bar + 8 * stage);
+          else umma_commit(empty_bar + 8 * stage);
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
-      if (ok && lane == 0) umma_commit(tfull_bar + 8 * as);  // accumulator ready for the epilogue
+      if (ok && lane == 0) {  // accumulator ready for the epilogue (of both CTAs of a pair)
+        if constexpr (CG == 2) umma_commit_2sm(tfull_bar + 8 * as);
+        else umma_commit(tfull_bar + 8 * as);
+      }
       if (lane == 0 && lt == 0) DBG_STAMP(4);
       __syncwarp();
     }
@@ -255,7 +286,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // ===================== gather warp (fused all-gather of the B operand) =====================
     // One lane moves this CTA's share of W with the TMA engine: 16 KB slices, peer shard -> smem bounce
     // buffer -> local full buffer, round-robin over the CTAs in n-tile order so the first tiles land first.
-    if (lane == 0 && p.ag_bytes > 0) {
+    if (CG == 1 && lane == 0 && p.ag_bytes > 0) {
       const long long nslices = (p.ag_bytes + AG_SLICE - 1) / AG_SLICE;
       uint32_t gphase = 0;
       bool ok = true;
@@ -297,10 +328,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int swz = lane & 7;
     uint32_t nstore = 0;  // TMA stores issued by this warp (selects the staging buffer)
     int lt = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+    for (int tile = unit; tile < total_tiles; tile += num_units, ++lt) {
       const int t2 = tile / p.k_splits;
-      const int m0 = (t2 % p.num_m_tiles) * BM;
-      const int n0 = (t2 / p.num_m_tiles) * BN;
+      const int m0 = (p.n_fastest ? t2 / p.num_n_tiles : t2 % p.num_m_tiles) * (BM * CG) + cta_rank * BM;
+      const int n0 = (p.n_fastest ? t2 % p.num_n_tiles : t2 / p.num_m_tiles) * BN;
       const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
       const int row = m0 + q * 32 + lane;
       const bool row_ok = row < p.M;
@@ -364,7 +395,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (c == BN / 32 - 1) {  // accumulator fully in registers: hand the TMEM buffer back early
           tcgen05_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(tempty_bar + 8 * as);
+          if (lane == 0) {
+            if constexpr (CG == 2) mbar_arrive_leader(tempty_bar + 8 * as);
+            else mbar_arrive(tempty_bar + 8 * as);
+          }
         }
         float v[32];
 #pragma unroll
@@ -408,10 +442,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         // stage: fp32 -> one 32x32 tile per chunk; bf16 -> two chunks fill one 32x64 tile
         constexpr bool kStoreEvery = E_F32;
         const bool first_half = kStoreEvery || (c & 1) == 0;
-        const uint32_t stage_buf = stage_base;
+        const uint32_t stage_buf = stage_base + (nstore % NSTG) * STAGING_BYTES;
         const uint32_t my_row = stage_buf + lane * 128;
-        if (first_half) {  // the store issued two stores ago must be done reading this buffer
-          if (lane == 0) tma_store_wait_read0();
+        if (first_half) {  // the store issued NSTG stores ago must be done reading this buffer
+          if (lane == 0) {
+            if constexpr (NSTG == 2) tma_store_wait_read1();
+            else tma_store_wait_read0();
+          }
           __syncwarp();
         }
         if constexpr (E_F32) {
@@ -460,9 +497,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   }
   if (threadIdx.x == 0) DBG_STAMP(8);
+  if constexpr (CG == 2) cluster_sync_all();   // nobody frees TMEM / leaves while the peer may still touch it
   if (warp_idx == 1) {
     tcgen05_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if constexpr (CG == 2) tmem_dealloc_2sm(tmem_base, TMEM_COLS);
+    else tmem_dealloc(tmem_base, TMEM_COLS);
     if (lane == 0) DBG_STAMP(9);
     if (lane == 0) DBG_STAMP_NS(13);
   }
@@ -525,23 +564,28 @@ long long* g_gemm_dbg = nullptr;
 // programmatic dependent launch of the GEMM kernels: measured gain 0.4 % of a step, so opt-in (B200GPT_PDL=1)
 bool g_gemm_pdl = []() { const char* e = getenv("B200GPT_PDL"); return e != nullptr && e[0] == '1'; }();
 
+// CTA-pair (cta_group::2) GEMMs are the default for 256-wide tiles; B200GPT_GEMM_2SM=0 turns them off
+bool g_gemm_2sm = []() { const char* e = getenv("B200GPT_GEMM_2SM"); return e == nullptr || e[0] != '0'; }();
+
 struct GemmOverrides {
   int a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep;  // < 0 => default
   int force_bn, force_splits;
   int no_tma_store;
 };
 
-template <int BN, int STAGES, int MIN_CTAS, int EPI>
+template <int BN, int STAGES, int MIN_CTAS, int EPI, int CG>
 int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p,
            int grid, cudaStream_t stream) {
-  constexpr int smem = STAGES * (A_STAGE_BYTES + BN * BK * 2) + STAGING_BYTES + AG_SLICE + 16 * STAGES + 40 + 16;
+  constexpr int smem = STAGES * (A_STAGE_BYTES + (BN / CG) * BK * 2) + staging_bufs<BN, CG>() * STAGING_BYTES + AG_SLICE +
+                       16 * STAGES + 40 + 16;
+  static_assert(smem <= 227 * 1024, "gemm: shared memory budget exceeded");
   static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!configured[dev & 63]) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI>,
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI>,
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG>,
                                          cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     configured[dev & 63] = true;
   }
@@ -550,21 +594,32 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tm
   cfg.blockDim = dim3(GEMM_THREADS);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (g_gemm_pdl && CG == 1) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (CG == 2) {   // CTA pair: a cluster of two CTAs is placed on the two SMs of one TPC
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 2;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = g_gemm_pdl ? 1 : 0;
-  B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI>, tmA, tmB, tmC, p));
+  cfg.numAttrs = na;
+  B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG>, tmA, tmB, tmC, p));
   return 0;
 }
 
 // the epilogue combinations the framework uses (one pruned kernel each)
-template <int BN, int STAGES, int MIN_CTAS>
+template <int BN, int STAGES, int MIN_CTAS, int CG>
 int launch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
                const GemmParams& p, int grid, cudaStream_t st) {
   switch (epi) {
-#define B200_EPI_CASE(E) case (E): return launch<BN, STAGES, MIN_CTAS, (E)>(tmA, tmB, tmC, p, grid, st);
+#define B200_EPI_CASE(E) case (E): return launch<BN, STAGES, MIN_CTAS, (E), CG>(tmA, tmB, tmC, p, grid, st);
     B200_EPI_CASE(0)                                                   // plain bf16 (QKV, dgrad, logits)
     B200_EPI_CASE(EPI_BIAS)                                            // + bias
     B200_EPI_CASE(EPI_BIAS | EPI_RELU)                                 // MLP up
@@ -595,9 +650,16 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   if (bn == 0) bn = (N >= 256) ? 256 : 128;  // 128x256 tiles read 25% less operand data from L2 per FLOP
   B200_REQUIRE(bn == 128 || bn == 256, "gemm: tile N %d not supported", bn);
 
+  // CTA pairs (cta_group::2, 256 x 256 tiles): cfg bit 10 forces them on, bit 11 off
+  const bool fused_ag = ag != nullptr && ag->bytes > 0;
+  int cg = (bn == 256 && M > BM && !fused_ag && g_gemm_2sm) ? 2 : 1;
+  if (cfg & 0x400) cg = 2;
+  if (cfg & 0x800) cg = 1;
+  B200_REQUIRE(cg == 1 || (bn == 256 && !fused_ag), "gemm: CTA pairs need 256-wide tiles and no fused all-gather");
+
   GemmParams p{};
   p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.ldr = ldr;
-  p.num_m_tiles = ceil_div(M, BM);
+  p.num_m_tiles = ceil_div(M, BM * cg);
   p.num_n_tiles = ceil_div(N, bn);
   p.kb_total = ceil_div(K, BK);
   const int tiles = p.num_m_tiles * p.num_n_tiles;
@@ -605,7 +667,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   int splits = 1;
   const bool plain = (bias == nullptr && residual == nullptr && act == 0 && aux_out == nullptr &&
                       mask_src == nullptr);
-  const int slots = sms * ((bn == 128) ? 2 : 1);
+  const int slots = sms * ((bn == 128) ? 2 : 1) / cg;
   if (accumulate && out_fp32 && plain && tiles < slots) {
     splits = slots / tiles;
     const int max_splits = p.kb_total / 4 > 0 ? p.kb_total / 4 : 1;
@@ -617,7 +679,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   p.kb_per_split = ceil_div(p.kb_total, splits);
   p.k_splits = ceil_div(p.kb_total, p.kb_per_split);
 
-  p.idesc = umma_idesc_bf16(BM, bn, a_mn, b_mn);
+  p.idesc = umma_idesc_bf16(BM * cg, bn, a_mn, b_mn);
   // K-major SW128: 8-row groups 1024 B apart (SBO), LBO unused (1); K advance = 32 B in the row.
   // MN-major SW128: 64-wide MN groups one TMA box (8192 B) apart (LBO), 8-k groups 1024 B apart (SBO);
   //                 K advance of 16 = two k groups = 2048 B.
@@ -663,7 +725,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   if (!a_mn) rc = get_tmap(&tmA, A, K, M, lda, BK, BM);
   else       rc = get_tmap(&tmA, A, M, K, lda, 64, BK);
   if (rc != 0) return rc;
-  if (!b_mn) rc = get_tmap(&tmB, B, K, N, ldb, BK, bn);
+  if (!b_mn) rc = get_tmap(&tmB, B, K, N, ldb, BK, bn / cg);
   else       rc = get_tmap(&tmB, B, N, K, ldb, 64, BK);
   if (rc != 0) return rc;
 
@@ -679,18 +741,20 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
                      (reinterpret_cast<uintptr_t>(aux_out) & 15) == 0,
                  "gemm: residual / mask / aux epilogues need N %% 32 == 0 and 16-byte aligned rows (N=%d)", N);
   p.tma_store = 1;
+  p.n_fastest = (cfg & 0x1000) && !fused_ag ? 1 : 0;
   rc = get_tmap(&tmC, C, N, M, ldc, out_fp32 ? 32 : 64, 32, esz);
   if (rc != 0) return rc;
   const int total = tiles * p.k_splits;
   const int ctas_per_sm = (bn == 128) ? 2 : 1;
-  const int cap = sms * ctas_per_sm;
-  const int grid = total < cap ? total : cap;
+  const int cap = sms * ctas_per_sm / cg;
+  const int grid = (total < cap ? total : cap) * cg;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int epi = (bias ? EPI_BIAS : 0) | (act == 1 ? EPI_RELU : 0) | (aux_out ? EPI_AUX : 0) |
                   (mask_src ? EPI_MASK : 0) | (residual ? EPI_RES : 0) | (out_fp32 ? EPI_F32 : 0) |
                   (accumulate ? EPI_ACC : 0);
-  if (bn == 128) return launch_epi<128, 2, 2>(epi, tmA, tmB, tmC, p, grid, st);
-  return launch_epi<256, 4, 1>(epi, tmA, tmB, tmC, p, grid, st);
+  if (bn == 128) return launch_epi<128, 2, 2, 1>(epi, tmA, tmB, tmC, p, grid, st);
+  if (cg == 2) return launch_epi<256, 5, 1, 2>(epi, tmA, tmB, tmC, p, grid, st);
+  return launch_epi<256, 4, 1, 1>(epi, tmA, tmB, tmC, p, grid, st);
 }
 
 }  // namespace
@@ -734,7 +798,7 @@ int b200_gemm_debug(const void* A, const void* B, void* C, int M, int N, int K, 
                     int b_lbo, int b_sbo, int b_kstep, int force_bn, int force_splits, void* stream) {
   GemmOverrides ov{a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep, force_bn & 0xffff, force_splits, (force_bn >> 16) & 1};
   return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, nullptr, nullptr, 0, 0, 1,
-                   force_splits > 1 ? 1 : 0, nullptr, nullptr, 0, &ov, stream);
+                   force_splits > 1 ? 1 : 0, nullptr, nullptr, ((force_bn >> 17) & 1) ? 0x400 : 0x800, &ov, stream);
 }
 
 }  // extern "C"
