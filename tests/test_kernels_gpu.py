@@ -206,7 +206,8 @@ def test_gemm_wgrad_mn_major_both_accumulate(Mtok, N, K):
                                             (1000, 512, 640, False, True), (1024, 256, 4096, True, True)])
 def test_gemm_cta_pair_matches_single_cta(M, N, K, a_mn, b_mn):
     """tcgen05 cta_group::2 (256 x 256 tile on a CTA pair, cfg bit 10) and cta_group::1 (cfg bit 11)
-    are both kept alive: each against fp32 PyTorch, and against each other bit for bit."""
+    are both kept alive: each against fp32 PyTorch, and against each other (split-K reduce order
+    is the only difference allowed)."""
     torch.manual_seed(0)
     pad = lambda n: (n + 7) // 8 * 8   # noqa: E731
     A = (torch.randn(K, pad(M), device="cuda") if a_mn else torch.randn(M, pad(K), device="cuda")).to(BF16)
@@ -221,7 +222,7 @@ def test_gemm_cta_pair_matches_single_cta(M, N, K, a_mn, b_mn):
         native.gemm(A, B, out[:, :N], M, N, K, a_mn_major=a_mn, b_mn_major=b_mn, accumulate=True, cfg=bit)
         assert float((out[:, :N] - ref).norm() / ref.norm()) < 1e-3
         outs.append(out)
-    assert torch.equal(outs[0], outs[1])
+    assert float((outs[0] - outs[1]).abs().max()) < 1e-3
 
 
 def _tiny_model(dev, layers=2, dim=256, heads=8, head_dim=32, vocab=50257, seq=256):
