@@ -22,6 +22,8 @@ OBJ_DIR = ROOT / "build" / "obj"
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v"]
+if os.environ.get("B200_GEMM_TRACE") == "1":      # bring-up build: GEMM wait accounting (tools/gemm_phases.py)
+    FLAGS.append("-DB200_GEMM_TRACE")
 
 
 def sources():

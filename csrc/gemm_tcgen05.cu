@@ -69,6 +69,15 @@ constexpr int STAGING_BYTES = 4 * 4096;  // one 32-row x 128-byte swizzled tile 
 // staging buffers per epilogue warp: with two, a warp fills one while the TMA engine still reads the other
 template <int BN, int CG> constexpr int staging_bufs() { return (CG == 2 || BN == 128) ? 2 : 1; }
 constexpr int AG_SLICE = 16384;           // bounce buffer of the gather warp (fused all-gather)
+// the fused all-gather (single-CTA kernels only) needs the bounce buffer; CTA pairs spend it on a deeper ring
+template <int CG> constexpr int ag_bounce_bytes() { return CG == 2 ? 0 : AG_SLICE; }
+// Wait accounting (tools/gemm_phases.py) costs ~1 % of a training step even when the debug buffer is
+// null, so it is only compiled in with -DB200_GEMM_TRACE (B200_GEMM_TRACE=1 python -m csrc.build).
+#ifdef B200_GEMM_TRACE
+#define TRACE_ON(p) ((p).dbg != nullptr)
+#else
+#define TRACE_ON(p) false
+#endif
 
 __device__ __forceinline__ long long global_ns() {
   long long t;
@@ -109,14 +118,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t sB = smem_base + STAGES * A_STAGE_BYTES;
   const uint32_t sStage = smem_base + STAGES * STAGE_BYTES;
   const uint32_t sBounce = sStage + NSTG * STAGING_BYTES;
-  const uint32_t bars = sBounce + AG_SLICE;  // 8-byte mbarriers
+  const uint32_t bars = sBounce + ag_bounce_bytes<CG>();  // 8-byte mbarriers
   const uint32_t full_bar = bars;
   const uint32_t empty_bar = bars + 8 * STAGES;
   const uint32_t tfull_bar = bars + 16 * STAGES;
   const uint32_t tempty_bar = tfull_bar + 16;
   const uint32_t gather_bar = tempty_bar + 16;
   uint32_t* tmem_ptr_smem =
-      reinterpret_cast<uint32_t*>(smem_raw + STAGES * STAGE_BYTES + NSTG * STAGING_BYTES + AG_SLICE + 16 * STAGES + 40);
+      reinterpret_cast<uint32_t*>(smem_raw + STAGES * STAGE_BYTES + NSTG * STAGING_BYTES + ag_bounce_bytes<CG>() +
+                                  16 * STAGES + 40);
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
   if ((smem_base & 1023u) != 0u) {
     if (threadIdx.x == 0) atomicCAS(p.err_word, 0, ERR_GEMM_SMEM_ALIGN);
@@ -177,6 +187,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       uint32_t stage = 0, phase = 0;
       bool ok = true;
       int ag_tile_seen = -1;
+      long long w_empty = 0;   // bring-up: cycles this producer spent waiting for a free smem slot
       for (int tile = unit; tile < total_tiles && ok; tile += num_units) {
         const int split = tile % p.k_splits;
         const int t2 = tile / p.k_splits;
@@ -186,10 +197,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
         for (int kb = kb0; kb < kb1; ++kb) {
+          const long long tw0 = TRACE_ON(p) ? clock64() : 0;
           if (!mbar_wait(empty_bar + 8 * stage, phase ^ 1, abort_flag, p.err_word, ERR_GEMM_PRODUCER)) {
             ok = false;
             break;
           }
+          if (TRACE_ON(p)) w_empty += clock64() - tw0;
           const uint32_t fb = full_bar + 8 * stage;
           // CG = 2: the bytes of both CTAs are reported to the leader's barrier, armed by the leader
           if (CG == 1 || cta_rank == 0) mbar_arrive_expect_tx(fb, CG * STAGE_BYTES);
@@ -236,6 +249,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       }
       DBG_STAMP(10);
+      if (TRACE_ON(p)) p.dbg[blockIdx.x * 32 + 17] = w_empty;
     }
     __syncwarp();  // lanes 1..31 must not reach the CTA barrier before lane 0 (bar.sync counts warps)
   } else if (warp_idx == 1) {
@@ -243,19 +257,24 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint32_t stage = 0, phase = 0;
     int lt = 0;
     bool ok = true;
+    long long w_full = 0, w_tempty = 0;   // bring-up: cycles waiting for operands / for a drained accumulator
     for (int tile = unit; tile < total_tiles && ok && (CG == 1 || cta_rank == 0); tile += num_units, ++lt) {
       const int split = tile % p.k_splits;
       const int kb0 = split * p.kb_per_split;
       const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
       const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
+      long long tw0 = TRACE_ON(p) ? clock64() : 0;
       if (!mbar_wait(tempty_bar + 8 * as, aph ^ 1, abort_flag, p.err_word, ERR_GEMM_MMA)) break;
+      if (TRACE_ON(p)) w_tempty += clock64() - tw0;
       tcgen05_fence_after();
       const uint32_t tmem_d = tmem_base + as * BN;
       for (int kb = kb0; kb < kb1; ++kb) {
+        tw0 = TRACE_ON(p) ? clock64() : 0;
         if (!mbar_wait(full_bar + 8 * stage, phase, abort_flag, p.err_word, ERR_GEMM_MMA)) {
           ok = false;
           break;
         }
+        if (TRACE_ON(p)) w_full += clock64() - tw0;
         tcgen05_fence_after();
         if (lane == 0 && kb == kb0 && lt == 0) DBG_STAMP(3);
         if (lane == 0) {
@@ -281,6 +300,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       if (lane == 0 && lt == 0) DBG_STAMP(4);
       __syncwarp();
+    }
+    if (TRACE_ON(p) && lane == 0 && (CG == 1 || cta_rank == 0)) {
+      p.dbg[blockIdx.x * 32 + 14] = w_full;
+      p.dbg[blockIdx.x * 32 + 15] = w_tempty;
     }
   } else if (warp_idx == 6) {
     // ===================== gather warp (fused all-gather of the B operand) =====================
@@ -328,6 +351,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int swz = lane & 7;
     uint32_t nstore = 0;  // TMA stores issued by this warp (selects the staging buffer)
     int lt = 0;
+    long long w_tfull = 0, w_stage = 0;   // bring-up: cycles waiting for the MMAs / for a free staging buffer
     for (int tile = unit; tile < total_tiles; tile += num_units, ++lt) {
       const int t2 = tile / p.k_splits;
       const int m0 = (p.n_fastest ? t2 / p.num_n_tiles : t2 % p.num_m_tiles) * (BM * CG) + cta_rank * BM;
@@ -353,7 +377,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int j = 0; j < 4; ++j)
           nmsk[j] = row_ok ? __ldg(reinterpret_cast<const uint4*>(msk_row + n0) + j) : make_uint4(0u, 0u, 0u, 0u);
       }
+      const long long tw0 = TRACE_ON(p) ? clock64() : 0;
       if (!mbar_wait(tfull_bar + 8 * as, aph, abort_flag, p.err_word, ERR_GEMM_EPILOGUE)) break;
+      if (TRACE_ON(p)) w_tfull += clock64() - tw0;
       tcgen05_fence_after();
       if (warp_idx == 2 && lane == 0 && lt == 0) DBG_STAMP(5);
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
@@ -445,11 +471,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const uint32_t stage_buf = stage_base + (nstore % NSTG) * STAGING_BYTES;
         const uint32_t my_row = stage_buf + lane * 128;
         if (first_half) {  // the store issued NSTG stores ago must be done reading this buffer
+          const long long ts0 = TRACE_ON(p) ? clock64() : 0;
           if (lane == 0) {
             if constexpr (NSTG == 2) tma_store_wait_read1();
             else tma_store_wait_read0();
           }
           __syncwarp();
+          if (TRACE_ON(p)) w_stage += clock64() - ts0;
         }
         if constexpr (E_F32) {
 #pragma unroll
@@ -481,6 +509,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
     }
     if (warp_idx == 2 && lane == 0) DBG_STAMP(6);
+    if (TRACE_ON(p) && warp_idx == 2 && lane == 0) {
+      p.dbg[blockIdx.x * 32 + 16] = w_tfull;
+      p.dbg[blockIdx.x * 32 + 18] = w_stage;
+    }
     if (lane == 0) tma_store_wait_all();
     __syncwarp();
     if (warp_idx == 2 && lane == 0) DBG_STAMP(7);
@@ -576,8 +608,8 @@ struct GemmOverrides {
 template <int BN, int STAGES, int MIN_CTAS, int EPI, int CG>
 int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p,
            int grid, cudaStream_t stream) {
-  constexpr int smem = STAGES * (A_STAGE_BYTES + (BN / CG) * BK * 2) + staging_bufs<BN, CG>() * STAGING_BYTES + AG_SLICE +
-                       16 * STAGES + 40 + 16;
+  constexpr int smem = STAGES * (A_STAGE_BYTES + (BN / CG) * BK * 2) + staging_bufs<BN, CG>() * STAGING_BYTES +
+                       ag_bounce_bytes<CG>() + 16 * STAGES + 40 + 16;
   static_assert(smem <= 227 * 1024, "gemm: shared memory budget exceeded");
   static bool configured[64] = {false};
   int dev = 0;
@@ -753,7 +785,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
                   (mask_src ? EPI_MASK : 0) | (residual ? EPI_RES : 0) | (out_fp32 ? EPI_F32 : 0) |
                   (accumulate ? EPI_ACC : 0);
   if (bn == 128) return launch_epi<128, 2, 2, 1>(epi, tmA, tmB, tmC, p, grid, st);
-  if (cg == 2) return launch_epi<256, 5, 1, 2>(epi, tmA, tmB, tmC, p, grid, st);
+  if (cg == 2) return launch_epi<256, 6, 1, 2>(epi, tmA, tmB, tmC, p, grid, st);
   return launch_epi<256, 4, 1, 1>(epi, tmA, tmB, tmC, p, grid, st);
 }
 

@@ -25,6 +25,7 @@ grad_ready_hooks: List[Callable[[torch.nn.Parameter], None]] = []
 # per-parameter override of where the bf16 weights come from (FSDP installs gathered buffers)
 import os as _os
 _LM_CHUNK_ROWS = int(_os.environ.get("B200GPT_LM_CHUNK", "4096"))  # rows of logits kept in flight (L2 resident)
+_LM_SUB_ROWS = int(_os.environ.get("B200GPT_LM_SUB", "0"))     # rows per logits-GEMM + CE sub-chunk (0 = whole chunk)
 
 
 _SCRATCH = {}
@@ -539,9 +540,15 @@ class _LMHeadCE(torch.autograd.Function):
         gw = grad_of(weight) if (want_grad and weight.requires_grad) else None
         for r0 in range(0, M, rows):
             r = min(rows, M - r0)
-            gemm(x2[r0:r0 + r], wb, logits, r, V, D, ag=fused_gather_args([weight]) if r0 == 0 else None)
-            call("b200_ce_fwd_bwd", logits.data_ptr(), t.data_ptr() + 8 * r0, stats.data_ptr(),
-                 r, V, ld, ignore_index, int(want_grad), float(grad_scale), stream())
+            # logits GEMM + in-place CE in sub-chunks small enough that the CE pass reads the logits
+            # the GEMM just wrote out of L2 rather than HBM; dX / dW then run over the whole chunk
+            sub = _LM_SUB_ROWS if _LM_SUB_ROWS > 0 else r
+            for s0 in range(0, r, sub):
+                sr = min(sub, r - s0)
+                gemm(x2[r0 + s0:r0 + s0 + sr], wb, logits[s0:s0 + sr], sr, V, D,
+                     ag=fused_gather_args([weight]) if (r0 == 0 and s0 == 0) else None)
+                call("b200_ce_fwd_bwd", logits.data_ptr() + 2 * s0 * ld, t.data_ptr() + 8 * (r0 + s0), stats.data_ptr(),
+                     sr, V, ld, ignore_index, int(want_grad), float(grad_scale), stream())
             if want_grad:
                 gemm(logits, wb, dx32[r0:r0 + r], r, D, V, b_mn_major=True, accumulate=True)  # dX = dL . W
                 if gw is not None:

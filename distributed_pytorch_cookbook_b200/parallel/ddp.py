@@ -143,7 +143,7 @@ class GradReducer:
         ranged = (optimizer is not None and getattr(optimizer, "native", False) and self.cuda and self.world > 1
                   and not self.skip_comm and len(self.order) > 1 and all(self.events[b] is not None for b in self.order))
         if not ranged:
-            if self.cuda and self.world > 1:
+            if self.cuda and self.world > 1 and not self.skip_comm:
                 torch.cuda.current_stream().wait_stream(self.comm_stream)
             if optimizer is not None:
                 optimizer.step()
