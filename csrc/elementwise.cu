@@ -159,7 +159,7 @@ layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
 // issued before the first use (the kernel is latency bound: a row is only 1.5 KB), values stay in
 // registers for the single pass, and the dres (residual-branch gradient) add is folded in.
 template <int NV, int R>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)   // <= 128 registers: two blocks (16 warps) per SM keep twice the rows in flight
 layernorm_bwd_small_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
                            const float* __restrict__ gamma, const float* __restrict__ mean_in,
                            const float* __restrict__ rstd_in, const float* __restrict__ dres,

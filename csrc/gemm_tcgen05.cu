@@ -28,7 +28,11 @@ namespace {
 constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int UMMA_K = 16;
-constexpr int GEMM_THREADS = 224;  // TMA producer, MMA issuer, 4 epilogue warps, gather warp (fused all-gather)
+constexpr int GEMM_THREADS = 224;  // CG = 1: TMA producer, MMA issuer, 4 epilogue warps, gather warp (fused all-gather)
+// CTA pairs run 8 epilogue warps (two per TMEM lane quarter, each taking half of the tile's columns): with
+// K = 256 a tile's MMAs last ~2 K cycles, less than 4 warps need for a bias/mask/residual epilogue
+template <int CG> constexpr int epilogue_warps() { return CG == 2 ? 8 : 4; }
+template <int CG> constexpr int gemm_threads() { return CG == 2 ? 32 * (2 + epilogue_warps<2>()) : GEMM_THREADS; }
 constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KB
 
 struct GemmParams {
@@ -45,6 +49,7 @@ struct GemmParams {
   void* C;
   bf16* aux_out;
   const bf16* mask_src;
+  float* colsum;  // EPI_CSUM: colsum[n] += sum over rows of the (bf16-rounded) output - the bias gradient of the layer that produced mask_src
   int act, out_fp32, accumulate;
   int tma_store;  // 1: epilogue stages tiles in smem and writes them with TMA (coalesced, clipped)
   int n_fastest;  // tile order: 0 = consecutive CTAs walk down M (share the B tile), 1 = walk along N (share A)
@@ -65,9 +70,11 @@ enum : int { ERR_GEMM_PRODUCER = 101, ERR_GEMM_MMA = 102, ERR_GEMM_EPILOGUE = 10
              ERR_GEMM_AG_WAIT = 105 };
 
 
-constexpr int STAGING_BYTES = 4 * 4096;  // one 32-row x 128-byte swizzled tile per epilogue warp (x NSTG buffers)
+// one 32-row x 128-byte swizzled staging tile per epilogue warp (x NSTG buffers)
+template <int CG> constexpr int staging_bytes() { return epilogue_warps<CG>() * 4096; }
 // staging buffers per epilogue warp: with two, a warp fills one while the TMA engine still reads the other
-template <int BN, int CG> constexpr int staging_bufs() { return (CG == 2 || BN == 128) ? 2 : 1; }
+// (CTA pairs hide that wait behind the second warp of the lane quarter instead)
+template <int BN, int CG> constexpr int staging_bufs() { return (CG == 1 && BN == 128) ? 2 : 1; }
 constexpr int AG_SLICE = 16384;           // bounce buffer of the gather warp (fused all-gather)
 // the fused all-gather (single-CTA kernels only) needs the bounce buffer; CTA pairs spend it on a deeper ring
 template <int CG> constexpr int ag_bounce_bytes() { return CG == 2 ? 0 : AG_SLICE; }
@@ -93,7 +100,8 @@ __device__ __forceinline__ long long global_ns() {
     if (p.dbg != nullptr) p.dbg[blockIdx.x * 32 + (slot)] = clock64();                    \
   } while (0)
 
-enum : int { EPI_BIAS = 1, EPI_RELU = 2, EPI_AUX = 4, EPI_MASK = 8, EPI_RES = 16, EPI_F32 = 32, EPI_ACC = 64 };
+enum : int { EPI_BIAS = 1, EPI_RELU = 2, EPI_AUX = 4, EPI_MASK = 8, EPI_RES = 16, EPI_F32 = 32, EPI_ACC = 64,
+             EPI_CSUM = 128 };
 
 // CG = 1: one CTA per 128 x BN tile (tcgen05 cta_group::1).
 // CG = 2: a CTA pair (cluster of 2 = the two SMs of a TPC) per 256 x BN tile (cta_group::2): each CTA
@@ -101,7 +109,7 @@ enum : int { EPI_BIAS = 1, EPI_RELU = 2, EPI_AUX = 4, EPI_MASK = 8, EPI_RES = 16
 //         M = 256 MMAs that read both CTAs' shared memory and write both CTAs' TMEM.  Per FLOP a CTA
 //         pulls 1/3 less operand data out of L2, which is what bounds the short-K GEMMs here.
 template <int BN, int STAGES, int MIN_CTAS, int EPI, int CG>
-__global__ void __launch_bounds__(GEMM_THREADS, MIN_CTAS)
+__global__ void __launch_bounds__(gemm_threads<CG>(), MIN_CTAS)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
   constexpr int B_ROWS = BN / CG;                 // rows of the B tile staged by this CTA
@@ -109,6 +117,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   constexpr uint32_t TMEM_COLS = 2 * BN;
   constexpr int NSTG = staging_bufs<BN, CG>();
+  constexpr int STAGING_BYTES = staging_bytes<CG>();
+  constexpr int EPW = epilogue_warps<CG>();
 
   // 128B-swizzled TMA/UMMA tiles need 1024-byte alignment; the dynamic smem window of a kernel
   // without static smem starts 1024-aligned (checked below, reported through the error word).
@@ -149,7 +159,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(tfull_bar + 8 * i, 1);
-      mbar_init(tempty_bar + 8 * i, 4 * CG);   // the epilogue warps of both CTAs of a pair
+      mbar_init(tempty_bar + 8 * i, EPW * CG);   // the epilogue warps of both CTAs of a pair
     }
     mbar_init(gather_bar, 1);
     fence_barrier_init();
@@ -305,7 +315,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       p.dbg[blockIdx.x * 32 + 14] = w_full;
       p.dbg[blockIdx.x * 32 + 15] = w_tempty;
     }
-  } else if (warp_idx == 6) {
+  } else if (CG == 1 && warp_idx == 6) {
     // ===================== gather warp (fused all-gather of the B operand) =====================
     // One lane moves this CTA's share of W with the TMA engine: 16 KB slices, peer shard -> smem bounce
     // buffer -> local full buffer, round-robin over the CTAs in n-tile order so the first tiles land first.
@@ -338,16 +348,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     __syncwarp();
   } else {
-    // ===================== epilogue (4 warps) =====================
+    // ===================== epilogue (4 warps; 8 in a CTA pair) =====================
     // TMEM -> registers -> (bias / ReLU / aux / mask / residual, selected at compile time by EPI) ->
     // 128B-swizzled smem tile -> TMA store (or TMA reduce-add).  Global traffic is whole 128-byte
     // rows, M/N tails are clipped by the tensor map, and the residual / mask operands of chunk
     // c+1 are prefetched under chunk c.
     constexpr bool E_BIAS = (EPI & EPI_BIAS) != 0, E_RELU = (EPI & EPI_RELU) != 0, E_AUX = (EPI & EPI_AUX) != 0,
                    E_MASK = (EPI & EPI_MASK) != 0, E_RES = (EPI & EPI_RES) != 0, E_F32 = (EPI & EPI_F32) != 0,
-                   E_ACC = (EPI & EPI_ACC) != 0;
+                   E_ACC = (EPI & EPI_ACC) != 0, E_CSUM = (EPI & EPI_CSUM) != 0;
     const int q = warp_idx & 3;  // TMEM lane quarter this warp may access
-    const uint32_t stage_base = sStage + q * 4096;
+    const int ew = warp_idx - 2;  // epilogue warp index
+    constexpr int NCH = (BN / 32) / (EPW / 4);   // 32-column chunks per warp
+    const int cbase = (ew >> 2) * NCH;           // first chunk of this warp (second warp of a quarter: upper half)
+    const uint32_t stage_base = sStage + ew * 4096;
     const int swz = lane & 7;
     uint32_t nstore = 0;  // TMA stores issued by this warp (selects the staging buffer)
     int lt = 0;
@@ -355,7 +368,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     for (int tile = unit; tile < total_tiles; tile += num_units, ++lt) {
       const int t2 = tile / p.k_splits;
       const int m0 = (p.n_fastest ? t2 / p.num_n_tiles : t2 % p.num_m_tiles) * (BM * CG) + cta_rank * BM;
-      const int n0 = (p.n_fastest ? t2 % p.num_n_tiles : t2 / p.num_m_tiles) * BN;
+      const int n0 = (p.n_fastest ? t2 % p.num_n_tiles : t2 / p.num_m_tiles) * BN + cbase * 32;  // this warp's first column
       const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
       const int row = m0 + q * 32 + lane;
       const bool row_ok = row < p.M;
@@ -370,23 +383,23 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if constexpr (E_RES) {
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-          nres[j] = row_ok ? __ldg(reinterpret_cast<const float4*>(res_row + n0) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+          nres[j] = (row_ok && n0 < p.N) ? __ldg(reinterpret_cast<const float4*>(res_row + n0) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
       if constexpr (E_MASK) {
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-          nmsk[j] = row_ok ? __ldg(reinterpret_cast<const uint4*>(msk_row + n0) + j) : make_uint4(0u, 0u, 0u, 0u);
+          nmsk[j] = (row_ok && n0 < p.N) ? __ldg(reinterpret_cast<const uint4*>(msk_row + n0) + j) : make_uint4(0u, 0u, 0u, 0u);
       }
       const long long tw0 = TRACE_ON(p) ? clock64() : 0;
       if (!mbar_wait(tfull_bar + 8 * as, aph, abort_flag, p.err_word, ERR_GEMM_EPILOGUE)) break;
       if (TRACE_ON(p)) w_tfull += clock64() - tw0;
       tcgen05_fence_after();
       if (warp_idx == 2 && lane == 0 && lt == 0) DBG_STAMP(5);
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + cbase * 32;
       uint32_t rr[2][32];  // TMEM loads are software-pipelined: chunk c+1 is in flight under chunk c
       tmem_ld_32x32b_x32(taddr, rr[0]);
 #pragma unroll
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = 0; c < NCH; ++c) {
         uint32_t* r = rr[c & 1];
         [[maybe_unused]] float4 res[8];
         [[maybe_unused]] uint4 msk[4];
@@ -400,7 +413,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 4; ++j) msk[j] = nmsk[j];
         }
-        if (c + 1 < BN / 32) {   // host guarantees N % 32 == 0 whenever res / mask / aux are used
+        if (c + 1 < NCH) {   // host guarantees N % 32 == 0 whenever res / mask / aux are used
           const int ncol0 = col0 + 32;
           if constexpr (E_BIAS) nbias = (ncol0 + lane < p.N) ? __ldg(p.bias + ncol0 + lane) : 0.f;
           if constexpr (E_RES) {
@@ -417,8 +430,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
         }
         tmem_ld_wait_dep(r);
-        if (c + 1 < BN / 32) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, rr[(c + 1) & 1]);
-        if (c == BN / 32 - 1) {  // accumulator fully in registers: hand the TMEM buffer back early
+        if (c + 1 < NCH) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, rr[(c + 1) & 1]);
+        if (c == NCH - 1) {  // accumulator fully in registers: hand the TMEM buffer back early
           tcgen05_fence_before();
           __syncwarp();
           if (lane == 0) {
@@ -505,6 +518,26 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             tma_store_commit();
           }
           ++nstore;
+        }
+        if constexpr (E_CSUM) {
+          // column sums of this warp's 32 x 32 block by a butterfly transpose-reduce (31 shuffles): lane l
+          // ends up with the sum of column l over the warp's 32 rows (rows past M are exact zeros: their
+          // A rows were zero-filled by TMA), then one fire-and-forget reduction per lane
+          if constexpr (!E_F32) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __bfloat162float(__float2bfloat16_rn(v[j]));   // what the consumer of the bf16 output sees
+          }
+#pragma unroll
+          for (int sft = 16; sft >= 1; sft >>= 1) {
+            const bool up = (lane & sft) != 0;
+#pragma unroll
+            for (int j = 0; j < sft; ++j) {
+              const float send = up ? v[j] : v[j + sft];
+              const float keep = up ? v[j + sft] : v[j];
+              v[j] = keep + __shfl_xor_sync(0xffffffffu, send, sft);
+            }
+          }
+          if (col0 + lane < p.N) atomicAdd(p.colsum + col0 + lane, v[0]);
         }
       }
     }
@@ -608,7 +641,7 @@ struct GemmOverrides {
 template <int BN, int STAGES, int MIN_CTAS, int EPI, int CG>
 int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p,
            int grid, cudaStream_t stream) {
-  constexpr int smem = STAGES * (A_STAGE_BYTES + (BN / CG) * BK * 2) + staging_bufs<BN, CG>() * STAGING_BYTES +
+  constexpr int smem = STAGES * (A_STAGE_BYTES + (BN / CG) * BK * 2) + staging_bufs<BN, CG>() * staging_bytes<CG>() +
                        ag_bounce_bytes<CG>() + 16 * STAGES + 40 + 16;
   static_assert(smem <= 227 * 1024, "gemm: shared memory budget exceeded");
   static bool configured[64] = {false};
@@ -623,7 +656,7 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tm
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.blockDim = dim3(gemm_threads<CG>());
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
@@ -656,6 +689,7 @@ int launch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
     B200_EPI_CASE(EPI_BIAS)                                            // + bias
     B200_EPI_CASE(EPI_BIAS | EPI_RELU)                                 // MLP up
     B200_EPI_CASE(EPI_MASK)                                            // dgrad fused with the ReLU mask
+    B200_EPI_CASE(EPI_MASK | EPI_CSUM)                                 // ... and with the bias gradient of that layer
     B200_EPI_CASE(EPI_F32)                                             // plain fp32
     B200_EPI_CASE(EPI_F32 | EPI_ACC)                                   // wgrad / split-K (TMA reduce-add)
     B200_EPI_CASE(EPI_F32 | EPI_BIAS)
@@ -672,7 +706,7 @@ int launch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
 int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
               int a_mn, int b_mn, const float* bias, const float* residual, int ldr, int act,
               int out_fp32, int accumulate, void* aux_out, const void* mask_src, int cfg,
-              const GemmOverrides* ov, void* stream, const AgArgs* ag = nullptr) {
+              const GemmOverrides* ov, void* stream, const AgArgs* ag = nullptr, float* colsum = nullptr) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
   B200_REQUIRE(!accumulate || out_fp32, "gemm: accumulate needs an fp32 output");
   B200_REQUIRE(act == 0 || act == 1, "gemm: activation %d not supported (0 none, 1 relu)", act);
@@ -732,6 +766,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   p.bias = bias; p.residual = residual; p.C = C;
   p.aux_out = reinterpret_cast<bf16*>(aux_out);
   p.mask_src = reinterpret_cast<const bf16*>(mask_src);
+  p.colsum = colsum;
   p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate;
   p.err_word = b200_error_word();
   p.dbg = g_gemm_dbg;
@@ -783,7 +818,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int epi = (bias ? EPI_BIAS : 0) | (act == 1 ? EPI_RELU : 0) | (aux_out ? EPI_AUX : 0) |
                   (mask_src ? EPI_MASK : 0) | (residual ? EPI_RES : 0) | (out_fp32 ? EPI_F32 : 0) |
-                  (accumulate ? EPI_ACC : 0);
+                  (accumulate ? EPI_ACC : 0) | (colsum ? EPI_CSUM : 0);
   if (bn == 128) return launch_epi<128, 2, 2, 1>(epi, tmA, tmB, tmC, p, grid, st);
   if (cg == 2) return launch_epi<256, 6, 1, 2>(epi, tmA, tmB, tmC, p, grid, st);
   return launch_epi<256, 4, 1, 1>(epi, tmA, tmB, tmC, p, grid, st);
@@ -816,6 +851,16 @@ int b200_ag_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K
             static_cast<long long>(shard_bytes), ag_sync, ag_sync_tiles};
   return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, 0, 0, bias, residual, ldr, act, out_fp32, 0, aux_out, nullptr,
                    0, nullptr, stream, &ag);
+}
+
+// Masked dgrad with the bias gradient fused in (MLP backward, reference models/gpt.py:33-41):
+//   C[M,N] (bf16) = (A[M,K] . B) * (mask_src > 0)     and     colsum[n] += sum_m C[m,n]
+// so the [tokens, 4*dim] activation gradient is written once and never re-read for its column sums.
+int b200_gemm_mask_colsum_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                               int b_mn_major, const void* mask_src, float* colsum, int cfg, void* stream) {
+  B200_REQUIRE(mask_src != nullptr && colsum != nullptr, "gemm_mask_colsum: mask_src and colsum are required");
+  return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, 0, b_mn_major, nullptr, nullptr, 0, 0, 0, 0, nullptr, mask_src,
+                   cfg, nullptr, stream, nullptr, colsum);
 }
 
 int b200_gemm_set_debug_buffer(void* buf) {

@@ -40,6 +40,7 @@ _SIGS = {
     "b200_ce_fwd_bwd": [P, P, P, I, I, I, I, I, Fl, P],
     "b200_gemm_bf16": [P, P, P, I, I, I, I, I, I, I, I, P, P, I, I, I, I, P, P, I, P],
     "b200_gemm_debug": [P, P, P] + [I] * 16 + [P],
+    "b200_gemm_mask_colsum_bf16": [P, P, P, I, I, I, I, I, I, I, P, P, I, P],
     "b200_attn_fwd": [P, P, P, I, I, I, I, Fl, P, P],
     "b200_attn_bwd": [P, P, P, P, P, P, P, I, I, I, I, Fl, P, P],
     "b200_allreduce": [P, P, P, I, I, L, L, Fl, I, I, P],

@@ -194,9 +194,9 @@ class _MLP(torch.autograd.Function):
     """relu(relu(x W1^T + b1) W2^T + b2) [+ residual] as one autograd node (reference gpt.py:33-41).
 
     Forward is two epilogue-fused GEMMs.  Backward fuses the first ReLU's mask into the dgrad GEMM
-    that produces its input gradient (``mask_src`` epilogue: dZ1 = (dZ2 W2) * (u > 0)), so the
-    [tokens, 4*dim] activation gradient is written once, already masked, and only a column-sum
-    pass is left for the bias gradient.
+    that produces its input gradient (``mask_src`` epilogue: dZ1 = (dZ2 W2) * (u > 0)) together with
+    the bias gradient db1 (column sums by a warp butterfly in the same epilogue), so the
+    [tokens, 4*dim] activation gradient is written once, already masked, and never re-read.
     """
 
     @staticmethod
@@ -231,8 +231,9 @@ class _MLP(torch.autograd.Function):
              int(dy2.dtype == torch.float32), sc.data_ptr(), cnt.data_ptr(), stream())
         gemm(dz2, u, grad_of(w2), N, F1, M, a_mn_major=True, b_mn_major=True, accumulate=True)     # dW2 += dZ2^T u
         dz1 = torch.empty((M, F1), dtype=BF16, device=dy.device)
-        gemm(dz2, w2b, dz1, M, F1, N, b_mn_major=True, mask_src=u)                                # dZ1 = (dZ2 W2) * (u > 0)
-        call("b200_colsum_bf16", dz1.data_ptr(), grad_of(b1).data_ptr(), M, F1, F1, sc.data_ptr(), cnt.data_ptr(), stream())
+        # dZ1 = (dZ2 W2) * (u > 0), with db1 += column sums of dZ1 folded into the same epilogue
+        call("b200_gemm_mask_colsum_bf16", dz2.data_ptr(), w2b.data_ptr(), dz1.data_ptr(), M, F1, N, dz2.stride(0),
+             w2b.stride(0), dz1.stride(0), 1, u.data_ptr(), grad_of(b1).data_ptr(), 0, stream())
         gemm(dz1, x2, grad_of(w1), F1, K, M, a_mn_major=True, b_mn_major=True, accumulate=True)    # dW1 += dZ1^T x
         dx = None
         if ctx.needs_input_grad[0]:

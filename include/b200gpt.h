@@ -67,6 +67,12 @@ int b200_count_valid(const int64_t* targets, float* stats, int ignore_index, int
 int b200_ce_fwd_bwd(void* logits_bf16, const int64_t* targets, float* stats, int rows, int vocab, int ld,
                     int ignore_index, int write_grad, float grad_scale, void* stream);
 
+/* Masked dgrad GEMM with the bias gradient fused into its epilogue (MLP backward of reference
+ * models/gpt.py:33-41): C (bf16) = (A . B) * (mask_src > 0), colsum[n] += sum over rows of C.  colsum is
+ * accumulated with fp32 reductions, like every other gradient of this library. */
+int b200_gemm_mask_colsum_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                               int b_mn_major, const void* mask_src, float* colsum, int cfg, void* stream);
+
 /* C[M,N] (+)= A[M,K] . B[N,K]^T on tcgen05 with a fused epilogue  (models/gpt.py:29-38,60-64,102,219)
  * a/b_mn_major: 0 = operand stored [rows][K]; 1 = stored [K][rows] (dgrad / wgrad, no transposes).
  * epilogue order: +bias -> act(1=ReLU) -> aux_out(bf16) -> *(mask_src>0) -> +residual(fp32) -> store. */

@@ -225,6 +225,27 @@ def test_gemm_cta_pair_matches_single_cta(M, N, K, a_mn, b_mn):
     assert float((outs[0] - outs[1]).abs().max()) < 1e-3
 
 
+@pytest.mark.parametrize("M,N,K", [(16320, 1024, 256), (700, 512, 256), (4096, 256, 1024)])
+def test_gemm_masked_dgrad_with_fused_bias_gradient(M, N, K):
+    """b200_gemm_mask_colsum_bf16: dZ1 = (dZ2 . W2) * (u > 0) and db1 += colsum(dZ1) in one launch."""
+    from distributed_pytorch_cookbook_b200.ops.native import call, stream
+    torch.manual_seed(0)
+    dz2 = torch.randn(M, K, device="cuda").to(BF16)
+    W = (torch.randn(K, N, device="cuda") / K ** 0.5).to(BF16)          # stored [K, N]: MN-major B
+    u = torch.randn(M, N, device="cuda").to(BF16)
+    db0 = torch.randn(N, device="cuda")
+    db = db0.clone()
+    out = torch.empty(M, N, device="cuda", dtype=BF16)
+    for cfg in (0x800, 0x400):                                          # single CTA and CTA pair
+        db.copy_(db0)
+        call("b200_gemm_mask_colsum_bf16", dz2.data_ptr(), W.data_ptr(), out.data_ptr(), M, N, K, K, N, N, 1,
+             u.data_ptr(), db.data_ptr(), cfg, stream())
+        ref = (dz2.float() @ W.float()) * (u.float() > 0)
+        assert torch.allclose(out.float(), ref, atol=3e-2, rtol=2e-2)
+        ref_db = db0 + out.float().sum(0)                               # exactly what the kernel promises
+        assert torch.allclose(db, ref_db, atol=2e-2, rtol=2e-3)
+
+
 def _tiny_model(dev, layers=2, dim=256, heads=8, head_dim=32, vocab=50257, seq=256):
     from distributed_pytorch_cookbook_b200 import TransformerDecoderLM
     torch.manual_seed(0)
