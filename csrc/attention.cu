@@ -18,7 +18,8 @@
 // columns = next MN group).  No tile is ever transposed.
 //
 // Forward, per CTA = (batch, head, 128-query tile): for each key tile up to the diagonal:
-//   S = Q K^T (TMEM) -> online softmax in registers -> P (bf16, smem) -> PV = P V (TMEM) ->
+//   S = Q K^T (TMEM) -> online softmax in registers -> P (bf16, back into TMEM) -> PV = P V (A operand
+//   from TMEM) ->
 //   O = O * alpha + PV in registers.  Writes O (bf16) and LSE (fp32).
 // Backward, per CTA = (batch, head, 128-key tile): loops over the query tiles at or below the
 // diagonal; S and dP = dO V^T into TMEM, P and dS = P * (dP - delta) * scale to smem, then
@@ -113,6 +114,7 @@ struct AttnParams {
   float* dq_acc;       // [B, T, H*D] fp32 scratch
   const uint8_t* key_mask;  // [B, T] 1 = padding, nullable
   int B, T, H;
+  int tile_in_z;       // backward: key-tile index comes from blockIdx.z (see attn_bwd_kernel)
   float scale;
   int* err_word;
   long long* dbg;  // optional per-CTA phase timestamps (32 slots), bring-up only
@@ -143,17 +145,25 @@ template <int D>
 __global__ void __launch_bounds__(ATTN_THREADS)
 attn_fwd_kernel(const AttnParams p) {
   constexpr int TILE_BYTES = TQ * D * 2;
-  constexpr uint32_t TMEM_COLS = 256;  // S: [0,128)  PV: [128,128+D)
+  // Tensor memory: S = Q K^T in columns [0,128) (fp32).  Each thread turns its S row into P (bf16, two keys
+  // per 32-bit column) and stores it back over the columns it has already consumed, [0,64); the PV MMAs
+  // take P straight from tensor memory (A operand in TMEM) and write to [PV_COL, PV_COL + D).  P never
+  // touches shared memory, and for D <= 64 a CTA needs 128 columns and 3 * 128 * D * 2 bytes of smem, so
+  // four CTAs fit an SM.
+  constexpr uint32_t PV_COL = (D <= 64) ? 64 : 128;
+  constexpr uint32_t TMEM_COLS = (D <= 64) ? 128 : 256;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 127u) & ~127u;
-  const uint32_t sQ = base, sK = sQ + TILE_BYTES, sV = sK + TILE_BYTES, sP = sV + TILE_BYTES;
-  const uint32_t bar = sP + TQ * TK * 2;
+  const uint32_t sQ = base, sK = sQ + TILE_BYTES, sV = sK + TILE_BYTES;
+  const uint32_t bar = sV + TILE_BYTES;
   uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + 3 * TILE_BYTES + TQ * TK * 2 + 8);
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + 3 * TILE_BYTES + 8);
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
 
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  // grid = (H, B, query tiles): z is the slowest launch dimension, so the late query tiles (most key tiles)
+  // of every (batch, head) are scheduled first and the short ones fill the tail
+  const int qt = gridDim.z - 1 - blockIdx.z, h = blockIdx.x, b = blockIdx.y;
   const int HD = p.H * D;
   const size_t row_stride = static_cast<size_t>(3) * HD;
   const bf16* qkv_b = p.qkv + static_cast<size_t>(b) * p.T * row_stride;
@@ -231,7 +241,7 @@ attn_fwd_kernel(const AttnParams p) {
     const float m_safe = (m_new == -INFINITY) ? 0.f : m_new;
     const float alpha = exp2f((m_run - m_safe) * kLog2e);  // m_run = -inf -> 0
     const float m_l2 = m_safe * kLog2e;
-    // pass B: p = exp(s - m), row sum, P tile to smem (bf16)
+    // pass B: p = exp(s - m), row sum, P (bf16) back into tensor memory
     float l_tile = 0.f;
 #pragma unroll 1
     for (int c = 0; c < TK / 32; ++c) {
@@ -254,22 +264,19 @@ attn_fwd_kernel(const AttnParams p) {
         l_tile += back.x + back.y;
         pk[j >> 1] = packed;
       }
-#pragma unroll
-      for (int g = 0; g < 4; ++g)  // 4 chunks of 8 keys
-        st_shared_v4(sP + (c * 4 + g) * CHUNK_STRIDE + tid * 16, pk[4 * g], pk[4 * g + 1], pk[4 * g + 2],
-                     pk[4 * g + 3]);
+      tmem_st_32x32b_x16(t_lane + c * 16, pk);   // keys [32c, 32c+32) -> columns [16c, 16c+16): already consumed
     }
+    tmem_st_wait();
     l_run = l_run * alpha + l_tile;
     m_run = m_new;
     tcgen05_fence_before();
-    fence_proxy_async_smem();
     __syncthreads();
     if (kt < 2) ADBG(5 + 6 * kt);
     if (tid == 0) {
       tcgen05_fence_after();
 #pragma unroll
       for (int kk = 0; kk < TK / 16; ++kk)
-        umma_f16_ss(tmem + TK, desc_kmajor(sP, kk), desc_mnmajor(sV, kk), idesc_pv, kk > 0 ? 1u : 0u);
+        umma_f16_ts(tmem + PV_COL, tmem + kk * 8, desc_mnmajor(sV, kk), idesc_pv, kk > 0 ? 1u : 0u);
       umma_commit(bar);
     }
     if (!mbar_wait(bar, phase, abort_flag, p.err_word, ERR_ATTN_FWD)) { ok = false; }
@@ -280,7 +287,7 @@ attn_fwd_kernel(const AttnParams p) {
 #pragma unroll
     for (int c = 0; c < D / 32; ++c) {
       uint32_t r[32];
-      tmem_ld_32x32b_x32(t_lane + TK + c * 32, r);
+      tmem_ld_32x32b_x32(t_lane + PV_COL + c * 32, r);
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 32; ++j) o[c * 32 + j] = o[c * 32 + j] * alpha + __uint_as_float(r[j]);
@@ -362,7 +369,11 @@ attn_bwd_kernel(const AttnParams p) {
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
 
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  // short sequences: grid = (H, B, key tiles), so the early key tiles (most query tiles to visit) are all
+  // scheduled first; long ones: grid = (key tiles, H, B), the key tiles of one head run together and share
+  // its Q / dO in L2
+  const bool kz = p.tile_in_z != 0;
+  const int kt = kz ? blockIdx.z : blockIdx.x, h = kz ? blockIdx.x : blockIdx.y, b = kz ? blockIdx.y : blockIdx.z;
   const int HD = p.H * D;
   const size_t row_stride = static_cast<size_t>(3) * HD;
   const bf16* qkv_b = p.qkv + static_cast<size_t>(b) * p.T * row_stride;
@@ -595,7 +606,7 @@ attn_dq_convert_kernel(const float* __restrict__ dq_acc, bf16* __restrict__ dqkv
 
 template <int D>
 int fwd_launch(const AttnParams& p, cudaStream_t st) {
-  constexpr int smem = 3 * TQ * D * 2 + TQ * TK * 2 + 8 + 16 + 128;
+  constexpr int smem = 3 * TQ * D * 2 + 8 + 16 + 128;
   static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -603,7 +614,7 @@ int fwd_launch(const AttnParams& p, cudaStream_t st) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured[dev & 63] = true;
   }
-  dim3 grid(ceil_div(p.T, TQ), p.H, p.B);
+  dim3 grid(p.H, p.B, ceil_div(p.T, TQ));
   attn_fwd_kernel<D><<<grid, ATTN_THREADS, smem, st>>>(p);
   B200_LAUNCH_CHECK();
   return 0;
@@ -629,8 +640,11 @@ int bwd_launch(const AttnParams& p, cudaStream_t st) {
     attn_delta_kernel<D><<<grid, 256, 0, st>>>(p.out, p.dout, p.delta, p.B, p.T, p.H);
     B200_LAUNCH_CHECK();
   }
-  dim3 grid(ceil_div(p.T, TK), p.H, p.B);
-  attn_bwd_kernel<D><<<grid, ATTN_THREADS, smem, st>>>(p);
+  const int nkt = ceil_div(p.T, TK);
+  AttnParams pb = p;
+  pb.tile_in_z = nkt <= 2 ? 1 : 0;
+  dim3 grid = pb.tile_in_z ? dim3(p.H, p.B, nkt) : dim3(nkt, p.H, p.B);
+  attn_bwd_kernel<D><<<grid, ATTN_THREADS, smem, st>>>(pb);
   B200_LAUNCH_CHECK();
   {
     const int64_t total = rows * (HD / 4);
