@@ -9,7 +9,9 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
 so = ROOT / "distributed_pytorch_cookbook_b200" / "_C" / "libb200gpt.so"
 out = subprocess.run(["cuobjdump", "-sass", str(so)], capture_output=True, text=True).stdout
-pats = {"tcgen05.mma": r"\bUTC[A-Z]*MMA", "tcgen05.ld": r"\bLDTM", "tcgen05.alloc": r"UTCATOMSWS", "tcgen05.commit": r"UTCBAR",
+pats = {"tcgen05.mma.cta_group::2": r"\bUTC[A-Z]*MMA\.2CTA", "TMA load .cta_group::2": r"UTMALDG\.[0-9A-Z]*\.2CTA",
+        "commit multicast": r"UTCBAR\.2CTA\.MULTICAST", "tcgen05.st": r"\bSTTM", "tcgen05.mma A-from-TMEM": r"\bUTC[A-Z]*MMA[.A-Z0-9]*\s+tmem\[",
+        "tcgen05.mma": r"\bUTC[A-Z]*MMA", "tcgen05.ld": r"\bLDTM", "tcgen05.alloc": r"UTCATOMSWS", "tcgen05.commit": r"UTCBAR",
         "TMA load": r"UTMALDG", "TMA store": r"UTMASTG", "TMA reduce": r"UTMAREDG", "mbarrier": r"SYNCS\.",
         "multimem.ld_reduce": r"LDG[A-Z.]*MC|LDGMC", "multimem.st": r"STG[A-Z.]*MC|STGMC|REDG[A-Z.]*MC",
         "HMMA (legacy)": r"\bHMMA", "cp.async": r"LDGSTS"}
