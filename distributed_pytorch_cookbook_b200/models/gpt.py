@@ -117,6 +117,29 @@ class SelfAttention(nn.Module):
         return o if residual is None else o + residual
 
 
+    def forward_cached(self, x: torch.Tensor, past=None):
+        """Incremental decoding: attend the ``S`` new positions of ``x`` to the cached keys / values
+        plus themselves.  Returns ``(out, (k, v))`` with k, v ``[N, h, L, d]`` covering all ``L``
+        positions so far.  Same maths as ``forward`` (reference gpt.py:75-103), without recomputing
+        the prefix - the reference's ``generate`` has no cache (utils.py:63-65)."""
+        N, S, _ = x.shape
+        h, d = self.heads, self.head_dim
+        q = self.to_q(x).view(N, S, h, d).transpose(1, 2)
+        k = self.to_k(x).view(N, S, h, d).transpose(1, 2)
+        v = self.to_v(x).view(N, S, h, d).transpose(1, 2)
+        if past is not None:
+            k = torch.cat([past[0], k], dim=2)
+            v = torch.cat([past[1], v], dim=2)
+        L = k.shape[2]
+        logits = (q @ k.transpose(-1, -2)) * self.attn_scale
+        if S > 1:   # new position i (absolute L - S + i) sees keys 0 .. L - S + i
+            causal = torch.ones(S, L, device=x.device, dtype=torch.bool).tril_(diagonal=L - S)
+            logits = logits + torch.where(causal, 0.0, -1e9).to(logits.dtype)
+        o = F.softmax(logits, dim=-1) @ v
+        o = o.transpose(1, 2).reshape(N, S, h * d)
+        return self.dropout(self.to_out(o)), (k, v)
+
+
 class DecoderLayer(nn.Module):
     """Pre-LN block ``x = attn(norm1(x)) + x; x = fc(norm2(x)) + x`` (reference :108-135)."""
 
@@ -139,6 +162,13 @@ class DecoderLayer(nn.Module):
         x = self.attn(self.norm1(x), mask) + x
         x = self.fc(self.norm2(x)) + x
         return x
+
+
+    def forward_cached(self, x: torch.Tensor, past=None):
+        a, present = self.attn.forward_cached(self.norm1(x), past)
+        x = a + x
+        x = self.fc(self.norm2(x)) + x
+        return x, present
 
 
 class TransformerDecoder(nn.Module):
@@ -219,6 +249,18 @@ class TransformerDecoderLM(nn.Module):
         if ops.use_native(x):
             return ops.linear(x, self.lm_head.weight, None)
         return self.lm_head(x)
+
+    @torch.no_grad()
+    def forward_cached(self, input_ids: torch.Tensor, position_ids: torch.Tensor, past=None):
+        """Logits for the new positions only, given the per-layer key/value cache ``past`` returned
+        by the previous call (``None`` for the prompt).  -> ``(logits [N, S_new, vocab], past)``."""
+        with ops.force_reference():      # single-token steps: plain PyTorch maths, any device / dtype
+            x = self.embeddings(input_ids, position_ids)
+            present = []
+            for i, layer in enumerate(self.decoder.layers):
+                x, kv = layer.forward_cached(x, None if past is None else past[i])
+                present.append(kv)
+            return self.lm_head(self.norm_out(x)), present
 
     def loss(self, input_ids: torch.Tensor, position_ids: torch.Tensor, targets: torch.Tensor,
              mask: Optional[torch.Tensor] = None, ignore_index: int = -100):

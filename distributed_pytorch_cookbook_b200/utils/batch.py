@@ -50,18 +50,26 @@ def prepare_batch_device(input_ids: torch.Tensor, pad_id: int,
 
 
 @torch.inference_mode()
-def generate(model, prompt: str, tokenizer, device, max_new_tokens: int = 20):
-    """Greedy (argmax) decoding, reference utils.py:42-91: re-runs the whole prefix each
-    step (no KV cache), stops at EOS, prompt truncated to 256 tokens."""
+def generate(model, prompt: str, tokenizer, device, max_new_tokens: int = 20, use_cache: bool = False):
+    """Greedy (argmax) decoding, reference utils.py:42-91: stops at EOS, prompt truncated to 256
+    tokens.  Like the reference it re-runs the whole prefix each step by default; ``use_cache=True``
+    keeps per-layer keys / values (``TransformerDecoderLM.forward_cached``) and feeds one token per
+    step - same tokens, O(L) instead of O(L^2) work per step."""
     batch = tokenizer([prompt], truncation=True, max_length=256, return_tensors="pt")
     input_ids = batch["input_ids"].to(device)
     sequence_length = input_ids.shape[1]
     position_ids = torch.arange(sequence_length, device=device).unsqueeze(0)
     max_pos = getattr(model, "max_position_embeddings", None)
+    cached = use_cache and hasattr(model, "forward_cached")
+    past = None
     for _ in range(max_new_tokens):
         if max_pos is not None and sequence_length >= max_pos:
             break
-        logits = model(input_ids=input_ids, position_ids=position_ids)
+        if cached:
+            new = slice(0, None) if past is None else slice(-1, None)
+            logits, past = model.forward_cached(input_ids[:, new], position_ids[:, new], past)
+        else:
+            logits = model(input_ids=input_ids, position_ids=position_ids)
         new_token = logits[0, -1].argmax(dim=-1)
         if int(new_token) == tokenizer.eos_token_id:
             break

@@ -114,6 +114,27 @@ def test_generate_matches_reference_tokens():
         ref_utils.generate(ref, "x", _Tok(), torch.device("cpu"), max_new_tokens=8)
 
 
+def test_generate_with_kv_cache_yields_the_same_tokens_and_logits():
+    """use_cache=True (per-layer key/value cache, one token per step) against the reference-style
+    full-prefix recompute: identical greedy tokens, and step logits equal to the full forward's."""
+    from distributed_pytorch_cookbook_b200.utils import generate
+    torch.manual_seed(0)
+    m = TransformerDecoderLM(**CFG).eval()
+    dev = torch.device("cpu")
+    assert generate(m, "x", _Tok(), dev, max_new_tokens=12, use_cache=True) == \
+        generate(m, "x", _Tok(), dev, max_new_tokens=12, use_cache=False)
+    ids = torch.randint(0, CFG["vocab_size"], (2, 9))
+    pos = torch.arange(9).unsqueeze(0).repeat(2, 1)
+    with torch.no_grad():
+        full = m(ids, pos)
+    logits, past = m.forward_cached(ids[:, :6], pos[:, :6])
+    assert torch.allclose(logits, full[:, :6], atol=1e-5)
+    for t in range(6, 9):
+        logits, past = m.forward_cached(ids[:, t:t + 1], pos[:, t:t + 1], past)
+        assert torch.allclose(logits[:, 0], full[:, t], atol=1e-5)
+    assert past[0][0].shape == (2, CFG["heads"], 9, CFG["head_dim"])
+
+
 def test_checkpoint_round_trip_and_prefix_stripping(tmp_path):
     torch.manual_seed(0)
     m = TransformerDecoderLM(**CFG)
