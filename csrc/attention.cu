@@ -61,12 +61,12 @@ __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t tile, int kk) {
 // Asynchronous copies (cp.async, 16 B each, zero-fill through src-size 0): a thread fires all its
 // copies back to back and the caller waits once with load_tiles_wait(), so a tile costs one
 // global-memory latency instead of one per 16-byte chunk.
-template <int D>
+template <int D, int NT = ATTN_THREADS>
 __device__ __forceinline__ void load_tile(uint32_t smem_dst, const bf16* __restrict__ g, int nvalid,
                                           size_t row_stride) {
   constexpr int CPR = D / 8;  // 16-byte chunks per row
 #pragma unroll
-  for (int c = threadIdx.x; c < TQ * CPR; c += ATTN_THREADS) {
+  for (int c = threadIdx.x; c < TQ * CPR; c += NT) {
     const int row = c / CPR, kc = c % CPR;
     const bool ok = row < nvalid;
     const bf16* src = g + static_cast<size_t>(ok ? row : 0) * row_stride + kc * 8;
@@ -348,8 +348,13 @@ attn_delta_kernel(const bf16* __restrict__ out, const bf16* __restrict__ dout, f
   }
 }
 
+// 256 threads: threads t and t + 128 share score row t (same TMEM lane) and split its 128 keys - and the
+// D output columns of dQ / dK / dV - in halves.  The softmax statistics are inputs here (lse, delta), so the
+// two halves never have to talk to each other, and the exp / pack / store work per thread is halved.
+constexpr int ATTN_BWD_THREADS = 256;
+
 template <int D>
-__global__ void __launch_bounds__(ATTN_THREADS)
+__global__ void __launch_bounds__(ATTN_BWD_THREADS, (128 + 2 * D) <= 256 ? 2 : 1)
 attn_bwd_kernel(const AttnParams p) {
   constexpr int TILE_BYTES = TQ * D * 2;
   constexpr int SS_BYTES = TQ * TK * 2;
@@ -368,7 +373,9 @@ attn_bwd_kernel(const AttnParams p) {
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + 4 * TILE_BYTES + 2 * SS_BYTES + 8);
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
 
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x & 127, warp = (threadIdx.x >> 5) & 3;   // score row / TMEM lane quarter
+  const int half = threadIdx.x >> 7;                                   // which half of the keys / columns
+  constexpr int CH = TK / 32 / 2;                                      // 32-key chunks per thread
   // short sequences: grid = (H, B, key tiles), so the early key tiles (most query tiles to visit) are all
   // scheduled first; long ones: grid = (key tiles, H, B), the key tiles of one head run together and share
   // its Q / dO in L2
@@ -381,17 +388,17 @@ attn_bwd_kernel(const AttnParams p) {
   const int k0 = kt * TK;
   const int nq_tiles = (p.T + TQ - 1) / TQ;
 
-  if (tid == 0) {
+  if (threadIdx.x == 0) {
     *abort_flag = 0;
     mbar_init(bar, 1);
     fence_barrier_init();
   }
-  if (warp == 0) {
+  if (threadIdx.x < 32) {
     tmem_alloc(smem_u32(tmem_ptr_smem), TMEM_COLS);
     tmem_relinquish();
   }
-  load_tile<D>(sK, qkv_b + static_cast<size_t>(k0) * row_stride + HD + h * D, min(TK, p.T - k0), row_stride);
-  load_tile<D>(sV, qkv_b + static_cast<size_t>(k0) * row_stride + 2 * HD + h * D, min(TK, p.T - k0), row_stride);
+  load_tile<D, ATTN_BWD_THREADS>(sK, qkv_b + static_cast<size_t>(k0) * row_stride + HD + h * D, min(TK, p.T - k0), row_stride);
+  load_tile<D, ATTN_BWD_THREADS>(sV, qkv_b + static_cast<size_t>(k0) * row_stride + 2 * HD + h * D, min(TK, p.T - k0), row_stride);
   load_tiles_wait();
   tcgen05_fence_before();
   __syncthreads();
@@ -411,12 +418,12 @@ attn_bwd_kernel(const AttnParams p) {
     const int q = q0 + tid;
     const bool q_ok = q < p.T;
     __syncthreads();
-    load_tile<D>(sQ, qkv_b + static_cast<size_t>(q0) * row_stride + h * D, min(TQ, p.T - q0), row_stride);
-    load_tile<D>(sdO, dout_b + static_cast<size_t>(q0) * HD + h * D, min(TQ, p.T - q0), HD);
+    load_tile<D, ATTN_BWD_THREADS>(sQ, qkv_b + static_cast<size_t>(q0) * row_stride + h * D, min(TQ, p.T - q0), row_stride);
+    load_tile<D, ATTN_BWD_THREADS>(sdO, dout_b + static_cast<size_t>(q0) * HD + h * D, min(TQ, p.T - q0), HD);
     load_tiles_wait();
     fence_proxy_async_smem();
     __syncthreads();
-    if (tid == 0) {
+    if (threadIdx.x == 0) {
       tcgen05_fence_after();
 #pragma unroll
       for (int kk = 0; kk < D / 16; ++kk)
@@ -439,9 +446,10 @@ attn_bwd_kernel(const AttnParams p) {
     const bool diag = (qt == kt);
     if constexpr (COMPACT) {
       // P from S (kept packed in registers and written to smem), then dP into the same columns
-      uint32_t pkeep[TK / 2];
+      uint32_t pkeep[CH * 16];
 #pragma unroll
-      for (int c = 0; c < TK / 32; ++c) {
+      for (int cc = 0; cc < CH; ++cc) {
+        const int c = half * CH + cc;
         uint32_t rs[32];
         tmem_ld_32x32b_x32(t_lane + C_S + c * 32, rs);
         tmem_ld_wait();
@@ -450,16 +458,16 @@ attn_bwd_kernel(const AttnParams p) {
         for (int j = 0; j < 32; j += 2) {
           const float e0 = exp2f(__uint_as_float(rs[j]) * sl2 - lse_l2);
           const float e1 = exp2f(__uint_as_float(rs[j + 1]) * sl2 - lse_l2);
-          pkeep[c * 16 + (j >> 1)] = pack_bf16x2(((kb >> j) & 1u) ? e0 : 0.f, ((kb >> (j + 1)) & 1u) ? e1 : 0.f);
+          pkeep[cc * 16 + (j >> 1)] = pack_bf16x2(((kb >> j) & 1u) ? e0 : 0.f, ((kb >> (j + 1)) & 1u) ? e1 : 0.f);
         }
 #pragma unroll
         for (int g = 0; g < 4; ++g)
-          st_shared_v4(sP + (c * 4 + g) * CHUNK_STRIDE + tid * 16, pkeep[c * 16 + 4 * g], pkeep[c * 16 + 4 * g + 1],
-                       pkeep[c * 16 + 4 * g + 2], pkeep[c * 16 + 4 * g + 3]);
+          st_shared_v4(sP + (c * 4 + g) * CHUNK_STRIDE + tid * 16, pkeep[cc * 16 + 4 * g], pkeep[cc * 16 + 4 * g + 1],
+                       pkeep[cc * 16 + 4 * g + 2], pkeep[cc * 16 + 4 * g + 3]);
       }
       tcgen05_fence_before();
       __syncthreads();                     // every thread has read S: dP may overwrite the columns
-      if (tid == 0) {
+      if (threadIdx.x == 0) {
         tcgen05_fence_after();
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
@@ -471,13 +479,14 @@ attn_bwd_kernel(const AttnParams p) {
       if (!__syncthreads_and(ok)) { ok = false; break; }
       tcgen05_fence_after();
 #pragma unroll
-      for (int c = 0; c < TK / 32; ++c) {
+      for (int cc = 0; cc < CH; ++cc) {
+        const int c = half * CH + cc;
         uint32_t rd[32], dk[16];
         tmem_ld_32x32b_x32(t_lane + C_DP + c * 32, rd);
         tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 32; j += 2) {
-          const float2 pr = unpack_bf16x2(pkeep[c * 16 + (j >> 1)]);
+          const float2 pr = unpack_bf16x2(pkeep[cc * 16 + (j >> 1)]);
           dk[j >> 1] = pack_bf16x2(pr.x * (__uint_as_float(rd[j]) - delta) * p.scale,
                                    pr.y * (__uint_as_float(rd[j + 1]) - delta) * p.scale);
         }
@@ -487,7 +496,8 @@ attn_bwd_kernel(const AttnParams p) {
       }
     } else {
 #pragma unroll 1
-      for (int c = 0; c < TK / 32; ++c) {
+      for (int cc = 0; cc < CH; ++cc) {
+        const int c = half * CH + cc;
         uint32_t rs[32], rd[32];
         tmem_ld_32x32b_x32(t_lane + C_S + c * 32, rs);
         tmem_ld_32x32b_x32(t_lane + C_DP + c * 32, rd);
@@ -518,7 +528,7 @@ attn_bwd_kernel(const AttnParams p) {
     tcgen05_fence_before();
     fence_proxy_async_smem();
     __syncthreads();
-    if (tid == 0) {
+    if (threadIdx.x == 0) {
       tcgen05_fence_after();
       const uint32_t acc0 = (qt > kt) ? 1u : 0u;
 #pragma unroll
@@ -538,14 +548,15 @@ attn_bwd_kernel(const AttnParams p) {
     tcgen05_fence_after();
     float* dq_row = p.dq_acc + (static_cast<size_t>(b) * p.T + (q_ok ? q : 0)) * HD + h * D;
 #pragma unroll
-    for (int c = 0; c < D / 32; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32b_x32(t_lane + C_S + c * 32, r);
+    for (int c = 0; c < D / 32; ++c) {   // this thread's D / 2 columns, 16 at a time
+      const int col = half * (D / 2) + c * 16;
+      uint32_t r[16];
+      tmem_ld_32x32b_x16(t_lane + C_S + col, r);
       tmem_ld_wait();
       if (q_ok) {
 #pragma unroll
-        for (int j = 0; j < 32; j += 4)
-          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dq_row + c * 32 + j),
+        for (int j = 0; j < 16; j += 4)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dq_row + col + j),
                        "f"(__uint_as_float(r[j])), "f"(__uint_as_float(r[j + 1])),
                        "f"(__uint_as_float(r[j + 2])), "f"(__uint_as_float(r[j + 3]))
                        : "memory");
@@ -560,20 +571,21 @@ attn_bwd_kernel(const AttnParams p) {
     bf16* dk_row = p.dqkv + (static_cast<size_t>(b) * p.T + (key < p.T ? key : 0)) * row_stride + HD + h * D;
     bf16* dv_row = dk_row + HD;
 #pragma unroll
-    for (int c = 0; c < D / 32; ++c) {
-      uint32_t rk[32], rv[32];
-      tmem_ld_32x32b_x32(t_lane + C_DK + c * 32, rk);
-      tmem_ld_32x32b_x32(t_lane + C_DV + c * 32, rv);
+    for (int c = 0; c < D / 32; ++c) {   // this thread's D / 2 columns, 16 at a time
+      const int col = half * (D / 2) + c * 16;
+      uint32_t rk[16], rv[16];
+      tmem_ld_32x32b_x16(t_lane + C_DK + col, rk);
+      tmem_ld_32x32b_x16(t_lane + C_DV + col, rv);
       tmem_ld_wait();
       if (key < p.T) {
 #pragma unroll
-        for (int j = 0; j < 32; j += 8) {
-          *reinterpret_cast<uint4*>(dk_row + c * 32 + j) = make_uint4(
+        for (int j = 0; j < 16; j += 8) {
+          *reinterpret_cast<uint4*>(dk_row + col + j) = make_uint4(
               pack_bf16x2(__uint_as_float(rk[j]), __uint_as_float(rk[j + 1])),
               pack_bf16x2(__uint_as_float(rk[j + 2]), __uint_as_float(rk[j + 3])),
               pack_bf16x2(__uint_as_float(rk[j + 4]), __uint_as_float(rk[j + 5])),
               pack_bf16x2(__uint_as_float(rk[j + 6]), __uint_as_float(rk[j + 7])));
-          *reinterpret_cast<uint4*>(dv_row + c * 32 + j) = make_uint4(
+          *reinterpret_cast<uint4*>(dv_row + col + j) = make_uint4(
               pack_bf16x2(__uint_as_float(rv[j]), __uint_as_float(rv[j + 1])),
               pack_bf16x2(__uint_as_float(rv[j + 2]), __uint_as_float(rv[j + 3])),
               pack_bf16x2(__uint_as_float(rv[j + 4]), __uint_as_float(rv[j + 5])),
@@ -584,7 +596,7 @@ attn_bwd_kernel(const AttnParams p) {
   }
   tcgen05_fence_before();
   __syncthreads();
-  if (warp == 0) {
+  if (threadIdx.x < 32) {
     tcgen05_fence_after();
     tmem_dealloc(tmem, TMEM_COLS);
   }
@@ -644,7 +656,7 @@ int bwd_launch(const AttnParams& p, cudaStream_t st) {
   AttnParams pb = p;
   pb.tile_in_z = nkt <= 2 ? 1 : 0;
   dim3 grid = pb.tile_in_z ? dim3(p.H, p.B, nkt) : dim3(nkt, p.H, p.B);
-  attn_bwd_kernel<D><<<grid, ATTN_THREADS, smem, st>>>(pb);
+  attn_bwd_kernel<D><<<grid, ATTN_BWD_THREADS, smem, st>>>(pb);
   B200_LAUNCH_CHECK();
   {
     const int64_t total = rows * (HD / 4);

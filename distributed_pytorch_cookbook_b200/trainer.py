@@ -190,7 +190,7 @@ class Trainer:
         gen_model.eval()
         print("Argmax sampling from model")
         for p in PROMPTS:
-            print(generate(gen_model, p, tokenizer, self.device))
+            print(generate(gen_model, p, tokenizer, self.device, use_cache=True))   # same tokens as the reference's full re-run
 
 
 class SingleStrategy:
