@@ -387,6 +387,8 @@ attn_bwd_kernel(const AttnParams p) {
   const bf16* dout_b = p.dout + static_cast<size_t>(b) * p.T * HD;
   const int k0 = kt * TK;
   const int nq_tiles = (p.T + TQ - 1) / TQ;
+  ADBG(0);
+  ADBG_NS(24);
 
   if (threadIdx.x == 0) {
     *abort_flag = 0;
@@ -410,10 +412,12 @@ attn_bwd_kernel(const AttnParams p) {
   const uint32_t idesc_dq = umma_idesc_bf16(TQ, D, 0, 1);     // dQ: K-major x MN-major, N = D
   const float sl2 = p.scale * kLog2e;
   const uint8_t* mask_row = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
+  ADBG(1);
 
   uint32_t phase = 0;
   bool ok = true;
   for (int qt = kt; qt < nq_tiles && ok; ++qt) {
+    const int it = qt - kt;   // bring-up stamps cover the first two iterations
     const int q0 = qt * TQ;
     const int q = q0 + tid;
     const bool q_ok = q < p.T;
@@ -423,6 +427,7 @@ attn_bwd_kernel(const AttnParams p) {
     load_tiles_wait();
     fence_proxy_async_smem();
     __syncthreads();
+    if (it < 2) ADBG(2 + 8 * it);
     if (threadIdx.x == 0) {
       tcgen05_fence_after();
 #pragma unroll
@@ -442,6 +447,7 @@ attn_bwd_kernel(const AttnParams p) {
     phase ^= 1;
     if (!__syncthreads_and(ok)) { ok = false; break; }
     tcgen05_fence_after();
+    if (it < 2) ADBG(3 + 8 * it);
 
     const bool diag = (qt == kt);
     if constexpr (COMPACT) {
@@ -467,6 +473,7 @@ attn_bwd_kernel(const AttnParams p) {
       }
       tcgen05_fence_before();
       __syncthreads();                     // every thread has read S: dP may overwrite the columns
+      if (it < 2) ADBG(4 + 8 * it);
       if (threadIdx.x == 0) {
         tcgen05_fence_after();
 #pragma unroll
@@ -478,6 +485,7 @@ attn_bwd_kernel(const AttnParams p) {
       phase ^= 1;
       if (!__syncthreads_and(ok)) { ok = false; break; }
       tcgen05_fence_after();
+      if (it < 2) ADBG(5 + 8 * it);
 #pragma unroll
       for (int cc = 0; cc < CH; ++cc) {
         const int c = half * CH + cc;
@@ -528,6 +536,7 @@ attn_bwd_kernel(const AttnParams p) {
     tcgen05_fence_before();
     fence_proxy_async_smem();
     __syncthreads();
+    if (it < 2) ADBG(6 + 8 * it);
     if (threadIdx.x == 0) {
       tcgen05_fence_after();
       const uint32_t acc0 = (qt > kt) ? 1u : 0u;
@@ -546,6 +555,7 @@ attn_bwd_kernel(const AttnParams p) {
     phase ^= 1;
     if (!__syncthreads_and(ok)) { ok = false; break; }
     tcgen05_fence_after();
+    if (it < 2) ADBG(7 + 8 * it);
     float* dq_row = p.dq_acc + (static_cast<size_t>(b) * p.T + (q_ok ? q : 0)) * HD + h * D;
 #pragma unroll
     for (int c = 0; c < D / 32; ++c) {   // this thread's D / 2 columns, 16 at a time
@@ -563,7 +573,9 @@ attn_bwd_kernel(const AttnParams p) {
       }
     }
     tcgen05_fence_before();
+    if (it < 2) ADBG(8 + 8 * it);
   }
+  ADBG(20);
 
   // dK / dV for this key tile: row = key
   const int key = k0 + tid;
@@ -600,6 +612,8 @@ attn_bwd_kernel(const AttnParams p) {
     tcgen05_fence_after();
     tmem_dealloc(tmem, TMEM_COLS);
   }
+  ADBG(21);
+  ADBG_NS(25);
 }
 
 // dq fp32 scratch [B*T, H*D] -> bf16 q section of dqkv [B*T, 3*H*D]
@@ -711,6 +725,7 @@ int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const floa
   p.key_mask = reinterpret_cast<const uint8_t*>(key_mask);
   p.B = B; p.T = T; p.H = H; p.scale = scale;
   p.err_word = b200_error_word();
+  p.dbg = g_attn_dbg;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (D == 32) return bwd_launch<32>(p, st);
   if (D == 64) return bwd_launch<64>(p, st);
