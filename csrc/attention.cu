@@ -127,6 +127,10 @@ __device__ __forceinline__ long long attn_global_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
+// Phase stamps (tools/attn_phases.py, tools/attn_bwd_phases.py) cost registers in kernels that sit at their
+// occupancy cap (3.7 us per backward launch), so they are only compiled into the bring-up build
+// (B200_GEMM_TRACE=1 python -m csrc.build).
+#ifdef B200_GEMM_TRACE
 #define ADBG(slot)                                                                                    \
   do {                                                                                                \
     if (p.dbg != nullptr && threadIdx.x == 0)                                                         \
@@ -137,6 +141,10 @@ __device__ __forceinline__ long long attn_global_ns() {
     if (p.dbg != nullptr && threadIdx.x == 0)                                                         \
       p.dbg[((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 32 + (slot)] = attn_global_ns(); \
   } while (0)
+#else
+#define ADBG(slot) do { } while (0)
+#define ADBG_NS(slot) do { } while (0)
+#endif
 
 // ------------------------------------------------------------------------------------------
 // forward
@@ -401,7 +409,11 @@ attn_bwd_kernel(const AttnParams p) {
   }
   load_tile<D, ATTN_BWD_THREADS>(sK, qkv_b + static_cast<size_t>(k0) * row_stride + HD + h * D, min(TK, p.T - k0), row_stride);
   load_tile<D, ATTN_BWD_THREADS>(sV, qkv_b + static_cast<size_t>(k0) * row_stride + 2 * HD + h * D, min(TK, p.T - k0), row_stride);
+  // the first query tile's Q / dO ride on the same global-memory latency as K / V
+  load_tile<D, ATTN_BWD_THREADS>(sQ, qkv_b + static_cast<size_t>(k0) * row_stride + h * D, min(TQ, p.T - k0), row_stride);
+  load_tile<D, ATTN_BWD_THREADS>(sdO, dout_b + static_cast<size_t>(k0) * HD + h * D, min(TQ, p.T - k0), HD);
   load_tiles_wait();
+  fence_proxy_async_smem();
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
@@ -417,16 +429,18 @@ attn_bwd_kernel(const AttnParams p) {
   uint32_t phase = 0;
   bool ok = true;
   for (int qt = kt; qt < nq_tiles && ok; ++qt) {
-    const int it = qt - kt;   // bring-up stamps cover the first two iterations
+    [[maybe_unused]] const int it = qt - kt;   // bring-up stamps cover the first two iterations
     const int q0 = qt * TQ;
     const int q = q0 + tid;
     const bool q_ok = q < p.T;
-    __syncthreads();
-    load_tile<D, ATTN_BWD_THREADS>(sQ, qkv_b + static_cast<size_t>(q0) * row_stride + h * D, min(TQ, p.T - q0), row_stride);
-    load_tile<D, ATTN_BWD_THREADS>(sdO, dout_b + static_cast<size_t>(q0) * HD + h * D, min(TQ, p.T - q0), HD);
-    load_tiles_wait();
-    fence_proxy_async_smem();
-    __syncthreads();
+    if (qt > kt) {   // (the diagonal tile was loaded with K / V above)
+      __syncthreads();
+      load_tile<D, ATTN_BWD_THREADS>(sQ, qkv_b + static_cast<size_t>(q0) * row_stride + h * D, min(TQ, p.T - q0), row_stride);
+      load_tile<D, ATTN_BWD_THREADS>(sdO, dout_b + static_cast<size_t>(q0) * HD + h * D, min(TQ, p.T - q0), HD);
+      load_tiles_wait();
+      fence_proxy_async_smem();
+      __syncthreads();
+    }
     if (it < 2) ADBG(2 + 8 * it);
     if (threadIdx.x == 0) {
       tcgen05_fence_after();

@@ -1,4 +1,4 @@
-"""Per-CTA phase timestamps of the attention backward kernel (bring-up): default GPT shape."""
+"""Per-CTA phase timestamps of the attention backward kernel (bring-up; needs the trace build: B200_GEMM_TRACE=1 python -m csrc.build): default GPT shape."""
 import sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))

@@ -1,4 +1,4 @@
-"""Per-CTA phase timestamps of the attention forward kernel (bring-up)."""
+"""Per-CTA phase timestamps of the attention forward kernel (bring-up; needs the trace build: B200_GEMM_TRACE=1 python -m csrc.build)."""
 import sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
