@@ -24,7 +24,9 @@ BF16 = torch.bfloat16
 grad_ready_hooks: List[Callable[[torch.nn.Parameter], None]] = []
 # per-parameter override of where the bf16 weights come from (FSDP installs gathered buffers)
 import os as _os
-_LM_CHUNK_ROWS = int(_os.environ.get("B200GPT_LM_CHUNK", "4096"))  # rows of logits kept in flight (L2 resident)
+# rows of bf16 logits in flight (one reused buffer of rows x vocab; 16384 rows = 1.6 GB at vocab 50257).  Bigger
+# chunks mean fewer, larger GEMMs and fewer read-modify-write passes over dW: 4.93 -> 4.86 ms/step from 4096 to 16384.
+_LM_CHUNK_ROWS = int(_os.environ.get("B200GPT_LM_CHUNK", "16384"))
 _LM_SUB_ROWS = int(_os.environ.get("B200GPT_LM_SUB", "0"))     # rows per logits-GEMM + CE sub-chunk (0 = whole chunk)
 
 
@@ -511,14 +513,15 @@ def attention(qkv, heads, head_dim, scale, key_mask=None):
 
 # ----------------------------------------------------------------------------------------
 class _LMHeadCE(torch.autograd.Function):
-    """Fused LM head + cross-entropy (+ argmax accuracy) without [tokens, vocab] logits.
+    """Fused LM head + cross-entropy (+ argmax accuracy) with one bf16 logits buffer reused in place.
 
-    Rows are processed in chunks: a tcgen05 GEMM writes a bf16 logits chunk that stays in
-    the 126 MB L2, one pass of ``b200_ce_fwd_bwd`` turns it in place into dlogits (softmax -
-    onehot, already scaled by grad_scale / n_valid) while accumulating loss / correct counts,
-    and two more GEMMs consume it from L2 for dX and dW.  The gradient is therefore produced
-    in the forward pass; backward only hands dX over.  The incoming gradient of the loss must
-    be ``grad_scale`` (1.0 for plain training; pipeline engines pass 1/num_microbatches).
+    Rows are processed in chunks of ``B200GPT_LM_CHUNK`` rows through one reused bf16 buffer: a
+    tcgen05 GEMM writes the logits chunk, one pass of ``b200_ce_fwd_bwd`` turns it in place into
+    dlogits (softmax - onehot, already scaled by grad_scale / n_valid) while accumulating loss /
+    correct counts, and two more GEMMs consume it for dX and dW - no fp32 logits, no separate
+    softmax / log-softmax tensors.  The gradient is therefore produced in the forward pass; backward
+    only hands dX over.  The incoming gradient of the loss must be ``grad_scale`` (1.0 for plain
+    training; pipeline engines pass 1/num_microbatches).
     """
 
     @staticmethod

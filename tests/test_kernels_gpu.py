@@ -316,6 +316,31 @@ def test_training_reduces_loss_with_fused_adamw_and_graph():
     assert losses[-1] < losses[0] - 1.0, losses
 
 
+def test_lmhead_ce_chunking_is_invisible(monkeypatch):
+    """The fused LM head + CE gives the same loss / counts / gradients whether the rows go through the
+    logits buffer in one chunk or in several (B200GPT_LM_CHUNK) or in GEMM+CE sub-chunks (B200GPT_LM_SUB)."""
+    torch.manual_seed(0)
+    M, Dm, V = 1000, 256, 5003
+    x0 = torch.randn(M, Dm, device="cuda").to(BF16)
+    w = torch.nn.Parameter(torch.randn(V, Dm, device="cuda") * 0.05)
+    tgt = torch.randint(0, V, (M,), device="cuda")
+    tgt[:7] = -100
+    results = []
+    for chunk, sub in ((16384, 0), (384, 0), (512, 128)):
+        monkeypatch.setattr(native, "_LM_CHUNK_ROWS", chunk)
+        monkeypatch.setattr(native, "_LM_SUB_ROWS", sub)
+        x = x0.clone().requires_grad_(True)
+        w.grad = None
+        loss, n_valid, n_correct = native.lmhead_cross_entropy(x, w, tgt)
+        loss.backward()
+        results.append((float(loss), int(n_valid), int(n_correct), x.grad.float().clone(), native.grad_of(w).clone()))
+    base = results[0]
+    for r in results[1:]:
+        assert abs(r[0] - base[0]) < 1e-4 and r[1] == base[1] and r[2] == base[2]
+        assert torch.allclose(r[3], base[3], atol=2e-3, rtol=2e-2)
+        assert torch.allclose(r[4], base[4], atol=1e-4, rtol=1e-3)
+
+
 @pytest.mark.parametrize("B,T,H,D,masked", [(2, 255, 8, 32, False), (2, 100, 2, 64, True), (1, 300, 2, 128, False),
                                             (64, 255, 8, 32, False), (1, 1023, 2, 128, True)])
 def test_flash_attention_fwd_bwd(B, T, H, D, masked):
