@@ -540,7 +540,11 @@ class _LMHeadCE(torch.autograd.Function):
         logits = torch.empty((rows, ld), dtype=BF16, device=dev)
         # dX is reduced over the vocabulary (K = 50257): few output tiles, long K -> split-K with
         # fp32 atomics into a zeroed buffer, cast to bf16 once at the end
-        dx32 = torch.zeros((M, D), dtype=torch.float32, device=dev) if want_grad else None
+        # (a single chunk with enough row tiles to fill the SMs un-split writes dX as bf16 straight from
+        # the GEMM epilogue: nothing to accumulate, no zero fill, no cast)
+        one_chunk = M <= rows and M >= 8192
+        dx32 = torch.zeros((M, D), dtype=torch.float32, device=dev) if (want_grad and not one_chunk) else None
+        dx = torch.empty((M, D), dtype=BF16, device=dev) if (want_grad and one_chunk) else None
         gw = grad_of(weight) if (want_grad and weight.requires_grad) else None
         for r0 in range(0, M, rows):
             r = min(rows, M - r0)
@@ -554,14 +558,18 @@ class _LMHeadCE(torch.autograd.Function):
                 call("b200_ce_fwd_bwd", logits.data_ptr() + 2 * s0 * ld, t.data_ptr() + 8 * (r0 + s0), stats.data_ptr(),
                      sr, V, ld, ignore_index, int(want_grad), float(grad_scale), stream())
             if want_grad:
-                gemm(logits, wb, dx32[r0:r0 + r], r, D, V, b_mn_major=True, accumulate=True)  # dX = dL . W
+                if one_chunk:
+                    gemm(logits, wb, dx, r, D, V, b_mn_major=True)                             # dX = dL . W
+                else:
+                    gemm(logits, wb, dx32[r0:r0 + r], r, D, V, b_mn_major=True, accumulate=True)
                 if gw is not None:
                     gemm(logits, x2[r0:r0 + r], gw, V, D, r, a_mn_major=True, b_mn_major=True,
                          accumulate=True)                                       # dW += dL^T . X
         if gw is not None:
             _notify(weight)
         loss = stats[1] / stats[0].clamp(min=1.0)
-        dx = dx32.to(BF16) if want_grad else None
+        if dx32 is not None:
+            dx = dx32.to(BF16)
         ctx.save_for_backward(dx)
         ctx.x_shape, ctx.in_dtype = x.shape, x.dtype
         ctx.mark_non_differentiable(stats)

@@ -341,6 +341,25 @@ def test_lmhead_ce_chunking_is_invisible(monkeypatch):
         assert torch.allclose(r[4], base[4], atol=1e-4, rtol=1e-3)
 
 
+def test_lmhead_ce_large_single_chunk_against_fp32():
+    """>= 8192 rows in one chunk: dX comes straight out of the un-split dgrad GEMM as bf16."""
+    from distributed_pytorch_cookbook_b200 import ops
+    torch.manual_seed(0)
+    M, Dm, V = 8448, 256, 1003
+    x = torch.randn(M, Dm, device="cuda").to(BF16).requires_grad_(True)
+    w = torch.nn.Parameter(torch.randn(V, Dm, device="cuda") * 0.05)
+    tgt = torch.randint(0, V, (M,), device="cuda")
+    loss, n_valid, _ = native.lmhead_cross_entropy(x, w, tgt)
+    loss.backward()
+    x32 = x.detach().float().requires_grad_(True)
+    w32 = w.detach().to(BF16).float().requires_grad_(True)
+    ref, nv, _ = ops.lmhead_cross_entropy_reference(x32, w32, tgt)
+    ref.backward()
+    assert abs(float(loss) - float(ref)) < 2e-3 and int(n_valid) == int(nv)
+    assert float((x.grad.float() - x32.grad).norm() / x32.grad.norm()) < 2e-2
+    assert float((native.grad_of(w) - w32.grad).norm() / w32.grad.norm()) < 2e-2
+
+
 @pytest.mark.parametrize("B,T,H,D,masked", [(2, 255, 8, 32, False), (2, 100, 2, 64, True), (1, 300, 2, 128, False),
                                             (64, 255, 8, 32, False), (1, 1023, 2, 128, True)])
 def test_flash_attention_fwd_bwd(B, T, H, D, masked):
