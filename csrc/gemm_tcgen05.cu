@@ -1,17 +1,24 @@
 // Persistent, warp-specialised bf16 GEMM for sm_100a: TMA -> 128B-swizzled smem ring ->
-// tcgen05.mma (cta_group::1, 128 x BN x 16, fp32 accumulators double-buffered in TMEM) ->
-// tcgen05.ld epilogue with fused bias / ReLU / ReLU-mask / fp32 residual / cast / split-K
-// reduction.  One kernel serves forward (K-major x K-major), dgrad (K-major x MN-major) and
-// wgrad (MN-major x MN-major): operand major-ness only changes the TMA box shape and the
-// UMMA descriptors, so no tensor is ever transposed in memory.
+// tcgen05.mma (fp32 accumulators double-buffered in TMEM) -> tcgen05.ld epilogue with fused bias /
+// ReLU / ReLU-mask / fp32 residual / bias-gradient column sums / cast / split-K reduction.  One
+// kernel serves forward (K-major x K-major), dgrad (K-major x MN-major) and wgrad (MN-major x
+// MN-major): operand major-ness only changes the TMA box shape and the UMMA descriptors, so no
+// tensor is ever transposed in memory.
 //
 //   C[M,N] (+)= A[M,K] . B[N,K]^T        K = reduction extent
 //   K-major  operand: memory is [rows][K]  (row stride ld)   -> one TMA box {64 k, rows}
 //   MN-major operand: memory is [K][rows]  (row stride ld)   -> rows/64 TMA boxes {64 rows, 64 k}
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer,
-// warps 2..5 = epilogue (TMEM lane quarter = warp_idx % 4).  All waits are bounded
-// (common.cuh: mbar_wait) so a protocol bug surfaces as an error code, never as a hung GPU.
+// Two tile engines (template parameter CG):
+//   CG = 2  CTA pair (cluster of 2, the two SMs of a TPC) per 256 x 256 tile, tcgen05 cta_group::2:
+//           each CTA stages its 128 rows of A and half of B, the leader issues M = 256 MMAs and
+//           multicast commits.  320 threads: warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer
+//           (leader only), warps 2..9 epilogue (two per TMEM lane quarter, half of the columns each).
+//   CG = 1  one CTA per 128 x 256 (or 128 x 128, 2 CTAs/SM) tile, cta_group::1.  224 threads: warp 0
+//           TMA producer, warp 1 MMA issuer, warps 2..5 epilogue, warp 6 gather warp of the fused
+//           FSDP all-gather (b200_ag_gemm_bf16).
+// All waits are bounded (common.cuh: mbar_wait) so a protocol bug surfaces as an error code, never
+// as a hung GPU.
 //
 // Serves reference call sites models/gpt.py:60-64,71-73,102 (projections), :29-38 (MLP),
 // :219,231 (LM head) and every backward GEMM autograd derives from them (SURVEY K3,K5-K9).
