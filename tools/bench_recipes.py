@@ -161,6 +161,8 @@ def main():
                 step(i)
             torch.cuda.synchronize(dev)
         if rank == 0:
+            if os.environ.get("TRACE_OUT"):     # chrome trace of the 3 profiled steps (per-stream timeline)
+                prof.export_chrome_trace(os.environ["TRACE_OUT"])
             rows = sorted(prof.key_averages(), key=lambda e: -e.device_time_total)
             tot = sum(e.device_time_total for e in rows)
             print(f"total device time {tot/3:.1f} us/step (sum over streams)")
