@@ -94,3 +94,23 @@ def test_main_single_trains_on_cpu(tmp_path):
     rows = [json.loads(l) for l in (tmp_path / "m.jsonl").read_text().splitlines()]
     train = [r["loss"] for r in rows if r["phase"] == "train"]
     assert train and train[-1] < 6.5   # ln(300) = 5.7; it must at least be finite and sane
+
+
+def test_resume_continues_from_the_checkpoint(tmp_path):
+    """--resume (additive flag): the second run starts from the first run's weights, so its
+    first validation loss equals the first run's last one instead of the random-init loss."""
+    base = [sys.executable, str(ROOT / "main-single.py"), "--synthetic", "--synthetic_samples", "64",
+            "--batch_size", "4", "--sequence_length", "16", "--dim", "32", "--head_dim", "8", "--heads", "4",
+            "--num_layers", "2", "--vocab_size", "300", "--epochs", "1", "--num_workers", "0", "--no_generate"]
+    r1 = subprocess.run(base + ["--learning_rate", "1e-2", "--max_steps", "12", "--checkpoint_dir", str(tmp_path / "a"),
+                                "--metrics_jsonl", str(tmp_path / "a.jsonl")],
+                        capture_output=True, text=True, cwd=ROOT, timeout=300)
+    assert r1.returncode == 0, r1.stderr[-2000:]
+    ck = next((tmp_path / "a").glob("checkpoint-*.pt"))
+    # second run: zero learning rate, so its validation loss is exactly that of the loaded weights
+    r2 = subprocess.run(base + ["--learning_rate", "0", "--max_steps", "12", "--resume", str(ck), "--no_save",
+                                "--metrics_jsonl", str(tmp_path / "b.jsonl")],
+                        capture_output=True, text=True, cwd=ROOT, timeout=300)
+    assert r2.returncode == 0, r2.stderr[-2000:]
+    val = lambda p: [json.loads(l) for l in p.read_text().splitlines() if json.loads(l)["phase"] == "val"][-1]["loss"]  # noqa: E731
+    assert abs(val(tmp_path / "a.jsonl") - val(tmp_path / "b.jsonl")) < 1e-4
