@@ -69,6 +69,25 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// LM head (b200_lmhead_gemm_bf16 / b200_lmhead_finish): the softmax of a logits row is evaluated
+// relative to a shift that is known before the GEMM runs, so the row needs no second pass.
+// |x . w| <= |x| |w|: with U = xnorm * wmax (+ rounding slack) every logit of the row is <= U.  `gap` is
+// the smallest (U - row max) the previous call observed (0 at first), so U - gap estimates the largest
+// logit and shift = U - gap - 40 puts exp(max - shift) near e^40: far from bf16 / fp32 overflow (e^88)
+// and underflow (e^-87) on both sides.  The estimate is only a performance matter: b200_lmhead_finish
+// checks every row's true maximum against its shift and recomputes the rows that fell outside the
+// window.  Both users must compute the same bits: no contraction.
+__device__ __forceinline__ float lm_row_shift(float xnorm, float wmax, float gap) {
+  return __fadd_rn(__fsub_rn(__fmul_rn(__fmul_rn(xnorm, wmax), 1.0002f), gap), -39.75f);
+}
+constexpr float kLmWindowLo = -45.0f;   // row max - shift below this: too much of the row underflows
+constexpr float kLmWindowHi = 62.0f;    // above this: the row scale 1/sum leaves the bf16 range
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

@@ -2,8 +2,10 @@
 // LayerNorm fp32 -> bf16 (fwd/bwd with dgamma/dbeta), fused multi-tensor AdamW over the flat
 // arena (writes the bf16 compute copy in the same pass), ReLU-backward + bias-gradient, and the
 // in-place cross-entropy forward+backward over a bf16 logits chunk (loss, argmax accuracy and
-// dlogits in one pass).  All are vectorised (16-byte accesses) and sized against the measured
-// HBM roofline; none needs scratch memory.
+// dlogits in one pass), plus the small kernels around the softmax-epilogue LM-head GEMM.  All are
+// vectorised (16-byte accesses) and sized against the measured HBM roofline.  The column reductions
+// (bias / gamma / beta gradients) use a caller-provided scratch of 16 replica rows and a ticket
+// counter; b200_relu_bwd_static at the end of the file carries that scratch inside the library.
 //
 // Reference call sites: models/gpt.py:185 (embeddings), :119,122,217 (LayerNorm), :35,38
 // (ReLU), main-single.py:42,99-101 (AdamW + GradScaler), :95-96,127-131 (CE + accuracy).
@@ -704,6 +706,199 @@ ce_fwd_bwd_kernel(bf16* __restrict__ logits, const int64_t* __restrict__ targets
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// LM head around the softmax-epilogue GEMM (b200_lmhead_gemm_bf16, csrc/gemm_tcgen05.cu):
+//   begin   count the valid targets, zero the statistics, rotate the gap estimate
+//   norms   l2 norm of every activation row; largest l2 norm of a weight row
+//   [GEMM]  E = exp(logit - shift), (sum, max) partials per row and column span, target logits
+//   finish  per row: total sum / max -> loss, accuracy, row scale of the gradient, E[target] -= sum (the
+//           "- onehot" of softmax - onehot), scaled activations for the weight-gradient GEMM; rows whose
+//           maximum fell outside the shift's window are recomputed exactly, here, by their warp.
+// lmstate (4 floats that live with the weight): [0] wmax  [1] gap used by this call  [2] smallest gap seen
+// by this call (the next call's estimate)  [3] rows recomputed by this call.
+// ------------------------------------------------------------------------------------------
+__global__ void lm_begin_kernel(const int64_t* __restrict__ targets, float* __restrict__ stats,
+                                float* __restrict__ lmstate, int ignore_index, int64_t n) {
+  __shared__ int sm[32];
+  int c = 0;
+  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) c += (targets[i] != ignore_index) ? 1 : 0;
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) t += sm[w];
+    stats[0] = static_cast<float>(t);
+    stats[1] = 0.f;
+    stats[2] = 0.f;
+    stats[3] = 0.f;
+    const float seen = lmstate[2];
+    if (isfinite(seen) && seen >= 0.f) lmstate[1] = seen;   // no valid row last time: keep the estimate
+    lmstate[0] = 0.f;
+    lmstate[2] = INFINITY;
+    lmstate[3] = 0.f;
+  }
+}
+
+__device__ __forceinline__ float dot8_bf16(const uint4 a, const uint4 b, float acc) {
+  const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    const float2 fa = unpack_bf16x2(aw[t]), fb = unpack_bf16x2(bw[t]);
+    acc = fmaf(fa.x, fb.x, acc);
+    acc = fmaf(fa.y, fb.y, acc);
+  }
+  return acc;
+}
+
+// one warp per row: rows [0, M) are activations (norm -> xnorm), rows [M, M + V) weights (max norm -> lmstate[0])
+__global__ void __launch_bounds__(256)
+lm_norms_kernel(const bf16* __restrict__ X, int ldx, const bf16* __restrict__ W, int ldw, int M, int V, int D,
+                float* __restrict__ xnorm, float* __restrict__ lmstate) {
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  float wmax = 0.f;
+  for (int r = warp; r < M + V; r += nwarps) {
+    const bf16* src = r < M ? X + static_cast<size_t>(r) * ldx : W + static_cast<size_t>(r - M) * ldw;
+    float acc = 0.f;
+    for (int d = lane * 8; d < D; d += 256) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(src + d));
+      acc = dot8_bf16(v, v, acc);
+    }
+    acc = sqrtf(warp_sum(acc));
+    if (r < M) {
+      if (lane == 0) xnorm[r] = acc;
+    } else {
+      wmax = fmaxf(wmax, acc);
+    }
+  }
+  if (lane == 0 && wmax > 0.f) atomicMax(reinterpret_cast<int*>(lmstate), __float_as_int(wmax));   // positive floats order like ints
+}
+
+constexpr int LMF_ROWS = 64;   // rows per block of lm_finish_kernel
+
+__global__ void __launch_bounds__(256)
+lm_finish_kernel(const float2* __restrict__ part, int num_parts, int M, const float* __restrict__ xnorm,
+                 const float* __restrict__ tgt_val, const int64_t* __restrict__ targets, int ignore_index,
+                 float* __restrict__ stats, float* __restrict__ lmstate, bf16* __restrict__ E, int lde, int V,
+                 const bf16* __restrict__ X, int ldx, int D, const bf16* __restrict__ W, int ldw,
+                 bf16* __restrict__ Xs, float* __restrict__ rscale, float grad_scale, int write_grad) {
+  __shared__ float sh_sum[4][LMF_ROWS], sh_max[4][LMF_ROWS];
+  __shared__ float sh_red[3][8];
+  const int row0 = blockIdx.x * LMF_ROWS;
+  {   // phase 1: total (sum, max) of each row; consecutive threads read consecutive rows of one span
+    const int r = threadIdx.x & (LMF_ROWS - 1), kg = threadIdx.x / LMF_ROWS;
+    float s = 0.f, m = -INFINITY;
+    if (row0 + r < M) {
+      for (int k = kg; k < num_parts; k += 4) {
+        const float2 pr = __ldg(part + static_cast<size_t>(k) * M + row0 + r);
+        s += pr.x;
+        m = fmaxf(m, pr.y);
+      }
+    }
+    sh_sum[kg][r] = s;
+    sh_max[kg][r] = m;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const float wmax = lmstate[0], gap_used = lmstate[1];
+  const float n_valid = fmaxf(stats[0], 1.0f);
+  constexpr float kLog2e = 1.4426950408889634f;
+  float loss_acc = 0.f, corr_acc = 0.f, gap_acc = INFINITY, bad_acc = 0.f;
+  for (int rr = warp; rr < LMF_ROWS; rr += 8) {
+    const int row = row0 + rr;
+    if (row >= M) break;
+    float s = (sh_sum[0][rr] + sh_sum[1][rr]) + (sh_sum[2][rr] + sh_sum[3][rr]);
+    float m = fmaxf(fmaxf(sh_max[0][rr], sh_max[1][rr]), fmaxf(sh_max[2][rr], sh_max[3][rr]));
+    const float xn = xnorm[row];
+    const float ubound = __fmul_rn(__fmul_rn(xn, wmax), 1.0002f);
+    float shift = lm_row_shift(xn, wmax, gap_used);
+    const long long t64 = targets[row];
+    const bool valid = t64 != ignore_index && t64 >= 0 && t64 < V;
+    const int tgt = valid ? static_cast<int>(t64) : -1;
+    float tl = valid ? tgt_val[row] : 0.f;
+    const float a = m - shift;
+    const bool good = isfinite(s) && s > 0.f && a >= kLmWindowLo && a <= kLmWindowHi;
+    if (!good) {
+      // the shift estimate missed this row (or the row holds non-finite values): redo it exactly with
+      // shift = row max.  Every lane takes its own vocabulary entries; x is read through L1, W through L2.
+      const bf16* xr = X + static_cast<size_t>(row) * ldx;
+      float mx = -INFINITY;
+      for (int j = lane; j < V; j += 32) {
+        const bf16* wr = W + static_cast<size_t>(j) * ldw;
+        float acc = 0.f;
+        for (int d = 0; d < D; d += 8)
+          acc = dot8_bf16(__ldg(reinterpret_cast<const uint4*>(xr + d)), __ldg(reinterpret_cast<const uint4*>(wr + d)), acc);
+        mx = fmaxf(mx, acc);
+      }
+      mx = warp_max(mx);
+      float ssum = 0.f, tfound = -INFINITY;
+      for (int j = lane; j < V; j += 32) {
+        const bf16* wr = W + static_cast<size_t>(j) * ldw;
+        float acc = 0.f;
+        for (int d = 0; d < D; d += 8)
+          acc = dot8_bf16(__ldg(reinterpret_cast<const uint4*>(xr + d)), __ldg(reinterpret_cast<const uint4*>(wr + d)), acc);
+        const float e = fast_exp2((acc - mx) * kLog2e);
+        ssum += e;
+        if (j == tgt) tfound = acc;
+        if (write_grad) E[static_cast<size_t>(row) * lde + j] = __float2bfloat16(e);
+      }
+      s = warp_sum(ssum);
+      tfound = warp_max(tfound);
+      m = mx;
+      shift = mx;
+      if (valid) tl = tfound;
+      bad_acc += 1.f;
+      __syncwarp();
+    }
+    if (valid) {
+      loss_acc += (shift + logf(s)) - tl;
+      corr_acc += (tl >= m) ? 1.f : 0.f;
+      if (isfinite(m)) gap_acc = fminf(gap_acc, fmaxf(ubound - m, 0.f));
+    }
+    if (write_grad) {
+      const float r = valid ? grad_scale / (n_valid * s) : 0.f;
+      if (lane == 0) {
+        rscale[row] = r;
+        // softmax - onehot: (E[t] - sum) / sum = p[t] - 1
+        if (valid) E[static_cast<size_t>(row) * lde + tgt] = __float2bfloat16(fast_exp2((tl - shift) * kLog2e) - s);
+      }
+      const bf16* xr = X + static_cast<size_t>(row) * ldx;
+      bf16* xs = Xs + static_cast<size_t>(row) * D;
+      for (int d = lane * 8; d < D; d += 256) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(xr + d));
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        uint32_t o[4];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const float2 f = unpack_bf16x2(w[t]);
+          o[t] = pack_bf16x2(f.x * r, f.y * r);
+        }
+        *reinterpret_cast<uint4*>(xs + d) = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+    }
+  }
+  if (lane == 0) {
+    sh_red[0][warp] = loss_acc;
+    sh_red[1][warp] = corr_acc;
+    sh_red[2][warp] = gap_acc;
+  }
+  if (lane == 0 && bad_acc > 0.f) atomicAdd(lmstate + 3, bad_acc);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float l = 0.f, c = 0.f, g = INFINITY;
+    for (int w = 0; w < 8; ++w) {
+      l += sh_red[0][w];
+      c += sh_red[1][w];
+      g = fminf(g, sh_red[2][w]);
+    }
+    atomicAdd(stats + 1, l);
+    if (c > 0.f) atomicAdd(stats + 2, c);
+    if (isfinite(g)) atomicMin(reinterpret_cast<int*>(lmstate + 2), __float_as_int(g));
+  }
+}
+
 inline int grid_for(int64_t work_items, int threads, int max_blocks_per_sm = 8) {
   int64_t blocks = ceil_div64(work_items, threads);
   const int64_t cap = static_cast<int64_t>(b200_num_sms()) * max_blocks_per_sm;
@@ -868,6 +1063,50 @@ int b200_colsum_bf16(const void* x, float* out_accum, int rows, int cols, int ld
 
 int b200_count_valid(const int64_t* targets, float* stats, int ignore_index, int64_t n, void* stream) {
   count_valid_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(targets, stats, ignore_index, n);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// LM head, step 1 of 4 (reference main-single.py:95-96 F.cross_entropy(ignore_index=-100)): stats[0] = number of
+// targets != ignore_index, stats[1..3] = 0, and the per-weight state `lmstate` (4 floats, zero-initialised once by
+// the caller and then left alone) is rotated for this call.
+int b200_lmhead_begin(const int64_t* targets, float* stats, float* lmstate, int ignore_index, int64_t n,
+                      void* stream) {
+  B200_REQUIRE(stats != nullptr && lmstate != nullptr, "lmhead_begin: stats and lmstate are required");
+  lm_begin_kernel<<<1, 1024, 0, static_cast<cudaStream_t>(stream)>>>(targets, stats, lmstate, ignore_index, n);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// step 2: xnorm[m] = |X[m,:]|, lmstate[0] = max_v |W[v,:]| (bf16 operands, fp32 math)
+int b200_lmhead_norms(const void* X, int ldx, const void* W, int ldw, int M, int V, int D, float* xnorm,
+                      float* lmstate, void* stream) {
+  B200_REQUIRE(D % 8 == 0 && ldx % 8 == 0 && ldw % 8 == 0, "lmhead_norms: D / ldx / ldw must be multiples of 8");
+  B200_REQUIRE(((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(W)) & 15) == 0,
+               "lmhead_norms: operands must be 16-byte aligned");
+  const int grid = grid_for(static_cast<int64_t>(M + V) * 32, 256, 8);
+  lm_norms_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const bf16*>(X), ldx, reinterpret_cast<const bf16*>(W), ldw, M, V, D, xnorm, lmstate);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// step 4 (step 3 is b200_lmhead_gemm_bf16): stats[1] += sum of row losses, stats[2] += rows whose target holds the
+// row maximum; with write_grad: rscale[m] = grad_scale / (n_valid * sum_m) (0 for ignored rows),
+// E[m, target] -= sum_m, Xs[m,:] = rscale[m] * X[m,:], so that afterwards
+//   dX = diag(rscale) . (E . W)      (b200_gemm_rowscale_bf16)      dW += E^T . Xs      (b200_gemm_bf16).
+int b200_lmhead_finish(const void* part, int num_parts, int M, const float* xnorm, const float* tgt_val,
+                       const int64_t* targets, int ignore_index, float* stats, float* lmstate, void* E, int lde,
+                       int V, const void* X, int ldx, int D, const void* W, int ldw, void* Xs, float* rscale,
+                       float grad_scale, int write_grad, void* stream) {
+  B200_REQUIRE(D % 8 == 0 && ldx % 8 == 0 && ldw % 8 == 0, "lmhead_finish: D / ldx / ldw must be multiples of 8");
+  B200_REQUIRE(!write_grad || (E != nullptr && Xs != nullptr && rscale != nullptr),
+               "lmhead_finish: gradient outputs missing");
+  if (M == 0) return 0;
+  lm_finish_kernel<<<ceil_div(M, LMF_ROWS), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const float2*>(part), num_parts, M, xnorm, tgt_val, targets, ignore_index, stats, lmstate,
+      reinterpret_cast<bf16*>(E), lde, V, reinterpret_cast<const bf16*>(X), ldx, D, reinterpret_cast<const bf16*>(W),
+      ldw, reinterpret_cast<bf16*>(Xs), rscale, grad_scale, write_grad);
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -71,6 +71,14 @@ struct GemmParams {
   long long ag_off, ag_bytes, ag_shard_bytes;
   int* ag_sync;                    // [1] exited-CTA tickets, [2 + j] slices landed for n-tile j (all zero between launches)
   int ag_tile_bytes;               // bytes of W per n-tile (BN * K * 2), a multiple of AG_SLICE
+  // EPI_RSCALE: row_a[m] multiplies output row m.  EPI_SMAX (LM head, see b200_lmhead_gemm_bf16): row_a[m] is
+  // the l2 norm of A's row m, wmax[0] the largest l2 norm of a B row, wmax[1] the gap estimate; the epilogue
+  // stores exp(c[m,n] - lm_row_shift(...)) and leaves (sum, max) partials per row and column span in part.
+  const float* row_a;
+  const float* wmax;
+  float2* part;                    // [num_parts][M]
+  const int64_t* targets;          // [M] column whose raw value is copied to tgt_val[m] (out of range: none)
+  float* tgt_val;
 };
 
 enum : int { ERR_GEMM_PRODUCER = 101, ERR_GEMM_MMA = 102, ERR_GEMM_EPILOGUE = 103, ERR_GEMM_SMEM_ALIGN = 104,
@@ -108,7 +116,7 @@ __device__ __forceinline__ long long global_ns() {
   } while (0)
 
 enum : int { EPI_BIAS = 1, EPI_RELU = 2, EPI_AUX = 4, EPI_MASK = 8, EPI_RES = 16, EPI_F32 = 32, EPI_ACC = 64,
-             EPI_CSUM = 128 };
+             EPI_CSUM = 128, EPI_SMAX = 256, EPI_NOSTORE = 512, EPI_RSCALE = 1024 };
 
 // CG = 1: one CTA per 128 x BN tile (tcgen05 cta_group::1).
 // CG = 2: a CTA pair (cluster of 2 = the two SMs of a TPC) per 256 x BN tile (cta_group::2): each CTA
@@ -362,7 +370,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // c+1 are prefetched under chunk c.
     constexpr bool E_BIAS = (EPI & EPI_BIAS) != 0, E_RELU = (EPI & EPI_RELU) != 0, E_AUX = (EPI & EPI_AUX) != 0,
                    E_MASK = (EPI & EPI_MASK) != 0, E_RES = (EPI & EPI_RES) != 0, E_F32 = (EPI & EPI_F32) != 0,
-                   E_ACC = (EPI & EPI_ACC) != 0, E_CSUM = (EPI & EPI_CSUM) != 0;
+                   E_ACC = (EPI & EPI_ACC) != 0, E_CSUM = (EPI & EPI_CSUM) != 0, E_SMAX = (EPI & EPI_SMAX) != 0,
+                   E_NOSTORE = (EPI & EPI_NOSTORE) != 0, E_RSCALE = (EPI & EPI_RSCALE) != 0;
+    constexpr float kLog2e = 1.4426950408889634f;
     const int q = warp_idx & 3;  // TMEM lane quarter this warp may access
     const int ew = warp_idx - 2;  // epilogue warp index
     constexpr int NCH = (BN / 32) / (EPW / 4);   // 32-column chunks per warp
@@ -385,6 +395,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       [[maybe_unused]] float4 nres[8];
       [[maybe_unused]] uint4 nmsk[4];
       [[maybe_unused]] float nbias = 0.f;
+      // EPI_RSCALE: this row's scale.  EPI_SMAX: this row's shift in log2 units, its target column and the
+      // running (sum of stored values, max of raw values) over the columns this warp owns in the tile
+      [[maybe_unused]] float rowa = 0.f;
+      [[maybe_unused]] int tgt = -1;
+      [[maybe_unused]] float s_sum[4] = {0.f, 0.f, 0.f, 0.f};
+      [[maybe_unused]] float s_max = -INFINITY;
+      if constexpr (E_RSCALE) rowa = row_ok ? __ldg(p.row_a + row) : 0.f;
+      if constexpr (E_SMAX) {
+        rowa = lm_row_shift(row_ok ? __ldg(p.row_a + row) : 0.f, __ldg(p.wmax), __ldg(p.wmax + 1)) * kLog2e;
+        if (row_ok && p.targets != nullptr) {
+          const long long t64 = p.targets[row];
+          tgt = (t64 >= 0 && t64 < p.N) ? static_cast<int>(t64) : -1;
+        }
+      }
       // prefetch the epilogue operands of chunk 0 while the MMAs of this tile are still running
       if constexpr (E_BIAS) nbias = (n0 + lane < p.N) ? __ldg(p.bias + n0 + lane) : 0.f;
       if constexpr (E_RES) {
@@ -485,6 +509,32 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             v[4 * j] += res[j].x; v[4 * j + 1] += res[j].y; v[4 * j + 2] += res[j].z; v[4 * j + 3] += res[j].w;
           }
         }
+        if constexpr (E_RSCALE) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] *= rowa;
+        }
+        if constexpr (E_SMAX) {
+          if (col0 + 32 > p.N) {   // columns past N (zero-filled B rows) must not count
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j >= p.N) v[j] = -INFINITY;
+          }
+          if (tgt >= col0 && tgt < col0 + 32) {   // rare: this thread holds its row's target column
+            float tv = 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j == tgt) tv = v[j];
+            p.tgt_val[row] = tv;
+          }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) s_max = fmaxf(s_max, v[j]);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            v[j] = fast_exp2(fmaf(v[j], kLog2e, -rowa));
+            s_sum[j & 3] += v[j];
+          }
+        }
+        if constexpr (!E_NOSTORE) {
         // stage: fp32 -> one 32x32 tile per chunk; bf16 -> two chunks fill one 32x64 tile
         constexpr bool kStoreEvery = E_F32;
         const bool first_half = kStoreEvery || (c & 1) == 0;
@@ -526,6 +576,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
           ++nstore;
         }
+        }  // !E_NOSTORE
         if constexpr (E_CSUM) {
           // column sums of this warp's 32 x 32 block by a butterfly transpose-reduce (31 shuffles): lane l
           // ends up with the sum of column l over the warp's 32 rows (rows past M are exact zeros: their
@@ -546,6 +597,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
           if (col0 + lane < p.N) atomicAdd(p.colsum + col0 + lane, v[0]);
         }
+      }
+      if constexpr (E_SMAX) {   // one (sum, max) partial per row and per NCH * 32-column span, coalesced over the warp
+        if (row_ok)
+          p.part[static_cast<size_t>(n0 / (NCH * 32)) * p.M + row] =
+              make_float2((s_sum[0] + s_sum[1]) + (s_sum[2] + s_sum[3]), s_max);
       }
     }
     if (warp_idx == 2 && lane == 0) DBG_STAMP(6);
@@ -639,6 +695,18 @@ bool g_gemm_pdl = []() { const char* e = getenv("B200GPT_PDL"); return e != null
 // CTA-pair (cta_group::2) GEMMs are the default for 256-wide tiles; B200GPT_GEMM_2SM=0 turns them off
 bool g_gemm_2sm = []() { const char* e = getenv("B200GPT_GEMM_2SM"); return e == nullptr || e[0] != '0'; }();
 
+// extra epilogue operands of the LM-head kernels
+struct EpiExtra {
+  const float* row_a;
+  const float* wmax;
+  float2* part;
+  const int64_t* targets;
+  float* tgt_val;
+  int smax, nostore, rscale;
+  int* num_parts_out;   // host: number of column spans (rows of `part`) the launch wrote
+  int max_parts;
+};
+
 struct GemmOverrides {
   int a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep;  // < 0 => default
   int force_bn, force_splits;
@@ -704,6 +772,9 @@ int launch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
     B200_EPI_CASE(EPI_F32 | EPI_RES)
     B200_EPI_CASE(EPI_F32 | EPI_BIAS | EPI_RELU | EPI_RES)             // MLP down + residual (inference)
     B200_EPI_CASE(EPI_F32 | EPI_BIAS | EPI_RELU | EPI_AUX | EPI_RES)   // MLP down + residual (training)
+    B200_EPI_CASE(EPI_SMAX)                                            // LM head: exp(logit - shift) + row statistics
+    B200_EPI_CASE(EPI_SMAX | EPI_NOSTORE)                              // ... statistics only (evaluation)
+    B200_EPI_CASE(EPI_RSCALE)                                          // per-row scale (LM head dX)
 #undef B200_EPI_CASE
     default:
       return b200_set_error(-1, "gemm: epilogue combination 0x%x is not instantiated", epi);
@@ -713,7 +784,8 @@ int launch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
 int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
               int a_mn, int b_mn, const float* bias, const float* residual, int ldr, int act,
               int out_fp32, int accumulate, void* aux_out, const void* mask_src, int cfg,
-              const GemmOverrides* ov, void* stream, const AgArgs* ag = nullptr, float* colsum = nullptr) {
+              const GemmOverrides* ov, void* stream, const AgArgs* ag = nullptr, float* colsum = nullptr,
+              const EpiExtra* ex = nullptr) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
   B200_REQUIRE(!accumulate || out_fp32, "gemm: accumulate needs an fp32 output");
   B200_REQUIRE(act == 0 || act == 1, "gemm: activation %d not supported (0 none, 1 relu)", act);
@@ -777,6 +849,21 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate;
   p.err_word = b200_error_word();
   p.dbg = g_gemm_dbg;
+  const bool nostore = ex != nullptr && ex->nostore;
+  if (ex != nullptr) {
+    B200_REQUIRE(plain && !out_fp32 && !accumulate && colsum == nullptr && splits == 1,
+                 "gemm: softmax / row-scale epilogues take a plain bf16 output");
+    p.row_a = ex->row_a; p.wmax = ex->wmax; p.part = ex->part; p.targets = ex->targets; p.tgt_val = ex->tgt_val;
+    if (ex->smax) {
+      const int span = (cg == 2) ? bn / 2 : bn;   // columns one epilogue warp owns in a tile
+      const int parts = p.num_n_tiles * (bn / span);
+      B200_REQUIRE(parts <= ex->max_parts, "lmhead_gemm: %d column spans exceed the partial buffer (%d)", parts, ex->max_parts);
+      B200_REQUIRE(ex->row_a && ex->wmax && ex->part && ex->tgt_val, "lmhead_gemm: missing statistics buffers");
+      if (ex->num_parts_out) *ex->num_parts_out = parts;
+    } else {
+      B200_REQUIRE(ex->row_a != nullptr, "gemm: row scale vector missing");
+    }
+  }
   if (ag != nullptr && ag->bytes > 0) {
     B200_REQUIRE(!b_mn && splits == 1, "ag_gemm: B must be a K-major weight and the GEMM un-split");
     B200_REQUIRE(ag->off % 16 == 0 && ag->bytes % 16 == 0 && ag->shard_bytes % 16 == 0 && ag->shard_bytes > 0,
@@ -806,7 +893,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   // output through TMA when the layout allows it (16-byte aligned base and row stride)
   CUtensorMap tmC = tmA;
   const int esz = out_fp32 ? 4 : 2;
-  B200_REQUIRE((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (static_cast<int64_t>(ldc) * esz) % 16 == 0,
+  B200_REQUIRE(nostore || ((reinterpret_cast<uintptr_t>(C) & 15) == 0 && (static_cast<int64_t>(ldc) * esz) % 16 == 0),
                "gemm: output must be 16-byte aligned with a 16-byte multiple row stride (ldc=%d)", ldc);
   if (residual != nullptr || mask_src != nullptr || aux_out != nullptr)
     B200_REQUIRE(N % 32 == 0 && ldc % 8 == 0 && (residual == nullptr || ldr % 4 == 0) &&
@@ -816,8 +903,10 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
                  "gemm: residual / mask / aux epilogues need N %% 32 == 0 and 16-byte aligned rows (N=%d)", N);
   p.tma_store = 1;
   p.n_fastest = (cfg & 0x1000) && !fused_ag ? 1 : 0;
-  rc = get_tmap(&tmC, C, N, M, ldc, out_fp32 ? 32 : 64, 32, esz);
-  if (rc != 0) return rc;
+  if (!nostore) {
+    rc = get_tmap(&tmC, C, N, M, ldc, out_fp32 ? 32 : 64, 32, esz);
+    if (rc != 0) return rc;
+  }
   const int total = tiles * p.k_splits;
   const int ctas_per_sm = (bn == 128) ? 2 : 1;
   const int cap = sms * ctas_per_sm / cg;
@@ -825,7 +914,8 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int epi = (bias ? EPI_BIAS : 0) | (act == 1 ? EPI_RELU : 0) | (aux_out ? EPI_AUX : 0) |
                   (mask_src ? EPI_MASK : 0) | (residual ? EPI_RES : 0) | (out_fp32 ? EPI_F32 : 0) |
-                  (accumulate ? EPI_ACC : 0) | (colsum ? EPI_CSUM : 0);
+                  (accumulate ? EPI_ACC : 0) | (colsum ? EPI_CSUM : 0) | ((ex && ex->smax) ? EPI_SMAX : 0) |
+                  (nostore ? EPI_NOSTORE : 0) | ((ex && ex->rscale) ? EPI_RSCALE : 0);
   if (bn == 128) return launch_epi<128, 2, 2, 1>(epi, tmA, tmB, tmC, p, grid, st);
   if (cg == 2) return launch_epi<256, 6, 1, 2>(epi, tmA, tmB, tmC, p, grid, st);
   return launch_epi<256, 4, 1, 1>(epi, tmA, tmB, tmC, p, grid, st);
@@ -868,6 +958,31 @@ int b200_gemm_mask_colsum_bf16(const void* A, const void* B, void* C, int M, int
   B200_REQUIRE(mask_src != nullptr && colsum != nullptr, "gemm_mask_colsum: mask_src and colsum are required");
   return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, 0, b_mn_major, nullptr, nullptr, 0, 0, 0, 0, nullptr, mask_src,
                    cfg, nullptr, stream, nullptr, colsum);
+}
+
+// LM head, forward (reference models/gpt.py:219,231 + F.cross_entropy main-single.py:95-96): the logits
+// GEMM whose epilogue turns each logit into E = exp(logit - shift[m]) straight out of tensor memory, where
+// shift[m] = lm_row_shift(xnorm[m], lmstate[0], lmstate[1]) is fixed before the kernel starts (see common.cuh),
+// so the softmax needs no second pass over the row: the kernel stores E as bf16 (or nothing at all when
+// E_out is null: evaluation) and leaves, per row and per column span, (sum of E, max logit) in part[span][M],
+// plus the raw target logit in tgt_val[m].  b200_lmhead_finish turns these into loss / accuracy / the
+// gradient's row scale.  *num_parts (host int) receives the number of spans written (<= max_parts).
+int b200_lmhead_gemm_bf16(const void* X, const void* W, void* E_out, int M, int V, int K, int ldx, int ldw, int lde,
+                          const float* xnorm, const float* lmstate, void* part, int max_parts, int* num_parts,
+                          const int64_t* targets, float* tgt_val, int cfg, void* stream) {
+  EpiExtra ex{xnorm, lmstate, reinterpret_cast<float2*>(part), targets, tgt_val, 1, E_out == nullptr ? 1 : 0, 0,
+              num_parts, max_parts};
+  return gemm_impl(X, W, E_out, M, V, K, ldx, ldw, lde, 0, 0, nullptr, nullptr, 0, 0, 0, 0, nullptr, nullptr, cfg,
+                   nullptr, stream, nullptr, nullptr, &ex);
+}
+
+// C[M,N] (bf16) = diag(row_scale) . (A . op(B)): plain GEMM with a per-row factor in the epilogue (LM head dX:
+// the softmax normalisation 1/sum and the loss scale are per-row constants that commute with the GEMM).
+int b200_gemm_rowscale_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                            int b_mn_major, const float* row_scale, int cfg, void* stream) {
+  EpiExtra ex{row_scale, nullptr, nullptr, nullptr, nullptr, 0, 0, 1, nullptr, 0};
+  return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, 0, b_mn_major, nullptr, nullptr, 0, 0, 0, 0, nullptr, nullptr, cfg,
+                   nullptr, stream, nullptr, nullptr, &ex);
 }
 
 int b200_gemm_set_debug_buffer(void* buf) {

@@ -38,6 +38,11 @@ _SIGS = {
     "b200_count_valid": [P, P, I, L, P],
     "b200_device_error": [P, I],
     "b200_ce_fwd_bwd": [P, P, P, I, I, I, I, I, Fl, P],
+    "b200_lmhead_begin": [P, P, P, I, L, P],
+    "b200_lmhead_norms": [P, I, P, I, I, I, I, P, P, P],
+    "b200_lmhead_gemm_bf16": [P, P, P, I, I, I, I, I, I, P, P, P, I, P, P, P, I, P],
+    "b200_lmhead_finish": [P, I, I, P, P, P, I, P, P, P, I, I, P, I, I, P, I, P, P, Fl, I, P],
+    "b200_gemm_rowscale_bf16": [P, P, P, I, I, I, I, I, I, I, P, I, P],
     "b200_gemm_bf16": [P, P, P, I, I, I, I, I, I, I, I, P, P, I, I, I, I, P, P, I, P],
     "b200_gemm_debug": [P, P, P] + [I] * 16 + [P],
     "b200_gemm_mask_colsum_bf16": [P, P, P, I, I, I, I, I, I, I, P, P, I, P],

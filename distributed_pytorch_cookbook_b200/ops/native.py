@@ -23,6 +23,7 @@ from ._lib import call, ptr, stream
 BF16 = torch.bfloat16
 grad_ready_hooks: List[Callable[[torch.nn.Parameter], None]] = []
 # per-parameter override of where the bf16 weights come from (FSDP installs gathered buffers)
+import ctypes as _ctypes
 import os as _os
 # rows of bf16 logits in flight (one reused buffer of rows x vocab; 16384 rows = 1.6 GB at vocab 50257).  Bigger
 # chunks mean fewer, larger GEMMs and fewer read-modify-write passes over dW: 4.93 -> 4.86 ms/step from 4096 to 16384.
@@ -86,6 +87,20 @@ def _as_bf16_2d(x: torch.Tensor) -> torch.Tensor:
     return x2.contiguous()
 
 
+def _tma_rows(t: torch.Tensor) -> torch.Tensor:
+    """A 2-D tensor the TMA engine can address: unit column stride, 16-byte aligned base and row pitch.
+    Anything else (e.g. bf16 rows of 50257 elements) is copied into rows padded to the next 16 bytes."""
+    esz = t.element_size()
+    if t.stride(1) == 1 and (t.stride(0) * esz) % 16 == 0 and t.data_ptr() % 16 == 0:
+        return t
+    per = 16 // esz
+    ld = (t.shape[1] + per - 1) // per * per
+    buf = torch.empty((t.shape[0], ld), dtype=t.dtype, device=t.device)
+    out = buf[:, :t.shape[1]]
+    out.copy_(t)
+    return out
+
+
 def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int, *,
          a_mn_major: bool = False, b_mn_major: bool = False, lda=None, ldb=None,
          bias=None, residual=None, act: int = 0, accumulate: bool = False,
@@ -140,7 +155,11 @@ class _Linear(torch.autograd.Function):
         M, K = x2.shape
         wb = bf16_of(weight)
         N = wb.shape[0]
-        out = torch.empty((M, N), dtype=torch.float32 if out_fp32 else BF16, device=x.device)
+        # rows are padded to 16 bytes when N is not (vocab 50257: reference gpt.py:231 returns [.., vocab] logits);
+        # the caller sees the [:, :N] view
+        per = 4 if out_fp32 else 8
+        out = torch.empty((M, (N + per - 1) // per * per), dtype=torch.float32 if out_fp32 else BF16,
+                          device=x.device)[:, :N]
         res2 = residual.reshape(M, N) if residual is not None else None
         need_aux = act != 0 and residual is not None and grad_on
         aux = torch.empty((M, N), dtype=BF16, device=x.device) if need_aux else None
@@ -160,11 +179,11 @@ class _Linear(torch.autograd.Function):
         M, K = x2.shape
         N = wb.shape[0]
         dy2 = dy.reshape(M, N)
-        if not dy2.is_contiguous():
-            dy2 = dy2.contiguous()
         dres = dy if ctx.has_res else None
         need_dz = ctx.act != 0 or dy2.dtype != BF16 or bias is not None
         if need_dz:
+            if not dy2.is_contiguous():
+                dy2 = dy2.contiguous()
             dz = torch.empty((M, N), dtype=BF16, device=dy.device)
             dbias = grad_of(bias) if (bias is not None and bias.requires_grad) else None
             sc, cnt = colsum_scratch(dy.device)
@@ -172,6 +191,7 @@ class _Linear(torch.autograd.Function):
                  int(dy2.dtype == torch.float32), sc.data_ptr(), cnt.data_ptr(), stream())
         else:
             dz = dy2
+        dz = _tma_rows(dz)
         dx = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty((M, K), dtype=BF16, device=dy.device)
@@ -512,20 +532,41 @@ def attention(qkv, heads, head_dim, scale, key_mask=None):
 
 
 # ----------------------------------------------------------------------------------------
-class _LMHeadCE(torch.autograd.Function):
-    """Fused LM head + cross-entropy (+ argmax accuracy) with one bf16 logits buffer reused in place.
+_LM_FUSED = _os.environ.get("B200GPT_LM_FUSED", "1") != "0"     # 0: the older logits-buffer + in-place CE path
+_LM_CHECKS_LEFT = [2]                                             # un-captured backward calls that verify dloss
 
-    Rows are processed in chunks of ``B200GPT_LM_CHUNK`` rows through one reused bf16 buffer: a
-    tcgen05 GEMM writes the logits chunk, one pass of ``b200_ce_fwd_bwd`` turns it in place into
-    dlogits (softmax - onehot, already scaled by grad_scale / n_valid) while accumulating loss /
-    correct counts, and two more GEMMs consume it for dX and dW - no fp32 logits, no separate
-    softmax / log-softmax tensors.  The gradient is therefore produced in the forward pass; backward
-    only hands dX over.  The incoming gradient of the loss must be ``grad_scale`` (1.0 for plain
-    training; pipeline engines pass 1/num_microbatches).
+
+def lm_state(weight: torch.Tensor) -> torch.Tensor:
+    """The 4 floats the LM-head kernels keep with a weight: [max row norm, softmax-shift gap in use, gap
+    observed by the last call, rows the last call had to recompute] (csrc/elementwise.cu)."""
+    st = getattr(weight, "_b200_lmstate", None)
+    if st is None or st.device != weight.device:
+        st = torch.zeros(4, dtype=torch.float32, device=weight.device)
+        weight._b200_lmstate = st
+    return st
+
+
+class _LMHeadCE(torch.autograd.Function):
+    """Fused LM head + cross-entropy (+ argmax accuracy); the logits never exist in memory.
+
+    ``b200_lmhead_gemm_bf16`` computes the logits tile by tile in tensor memory and its epilogue turns
+    them straight into ``E = exp(logit - shift[row])`` (bf16) plus per-row (sum, max) statistics and
+    the target logit; the shift is fixed before the GEMM from ``|x| * max|w|`` and the gap observed on the
+    previous call, so no second pass over a row is needed (rows the estimate misses are recomputed
+    exactly by ``b200_lmhead_finish``).  ``finish`` produces loss / accuracy and the per-row factor
+    ``grad_scale / (n_valid * sum)``; the gradients are then two GEMMs over E:
+    ``dX = diag(rscale) (E' W)`` and ``dW += E'^T (rscale * X)`` with ``E' = E - sum * onehot``.
+    E (rows x vocab bf16, one reused chunk of ``B200GPT_LM_CHUNK`` rows) is written once and read
+    twice; evaluation stores nothing.  The gradient is produced in the forward pass; backward only
+    hands dX over, so the incoming gradient of the loss must equal ``grad_scale`` (1.0 for plain
+    training; pipeline engines pass 1/num_microbatches) - verified on the first un-captured calls
+    and always under ``B200GPT_DEBUG=1``.
     """
 
     @staticmethod
     def forward(ctx, x, weight, targets, ignore_index, grad_scale, params, grad_on):
+        if not _LM_FUSED:
+            return _lmhead_ce_unfused(ctx, x, weight, targets, ignore_index, grad_scale, grad_on)
         x2 = _as_bf16_2d(x)
         M, D = x2.shape
         wb = bf16_of(weight)
@@ -533,45 +574,55 @@ class _LMHeadCE(torch.autograd.Function):
         ld = (V + 127) // 128 * 128
         t = targets.reshape(-1).contiguous()
         dev = x.device
-        stats = torch.zeros(4, dtype=torch.float32, device=dev)  # n_valid, loss_sum, n_correct
-        call("b200_count_valid", t.data_ptr(), stats.data_ptr(), ignore_index, M, stream())
+        st = stream()
+        stats = torch.empty(4, dtype=torch.float32, device=dev)  # n_valid, loss_sum, n_correct
+        lmstate = lm_state(weight)
+        call("b200_lmhead_begin", t.data_ptr(), stats.data_ptr(), lmstate.data_ptr(), ignore_index, M, st)
+        xnorm = torch.empty(M, dtype=torch.float32, device=dev)
+        call("b200_lmhead_norms", x2.data_ptr(), x2.stride(0), wb.data_ptr(), wb.stride(0), M, V, D,
+             xnorm.data_ptr(), lmstate.data_ptr(), st)
         want_grad = grad_on and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1])
         rows = min(_LM_CHUNK_ROWS, M)
-        logits = torch.empty((rows, ld), dtype=BF16, device=dev)
-        # dX is reduced over the vocabulary (K = 50257): few output tiles, long K -> split-K with
-        # fp32 atomics into a zeroed buffer, cast to bf16 once at the end
-        # (a single chunk with enough row tiles to fill the SMs un-split writes dX as bf16 straight from
-        # the GEMM epilogue: nothing to accumulate, no zero fill, no cast)
-        one_chunk = M <= rows and M >= 8192
-        dx32 = torch.zeros((M, D), dtype=torch.float32, device=dev) if (want_grad and not one_chunk) else None
-        dx = torch.empty((M, D), dtype=BF16, device=dev) if (want_grad and one_chunk) else None
-        gw = grad_of(weight) if (want_grad and weight.requires_grad) else None
+        max_parts = (V + 127) // 128 + 2
+        part = torch.empty((max_parts, rows, 2), dtype=torch.float32, device=dev)
+        tgt_val = torch.empty(rows, dtype=torch.float32, device=dev)
+        E = xs = rscale = dx = None
+        gw = None
+        if want_grad:
+            E = torch.empty((rows, ld), dtype=BF16, device=dev)
+            xs = torch.empty((rows, D), dtype=BF16, device=dev)
+            rscale = torch.empty(rows, dtype=torch.float32, device=dev)
+            dx = torch.empty((M, D), dtype=BF16, device=dev)
+            gw = grad_of(weight) if weight.requires_grad else None
+        nparts = _ctypes.c_int(0)
         for r0 in range(0, M, rows):
             r = min(rows, M - r0)
-            # logits GEMM + in-place CE in sub-chunks small enough that the CE pass reads the logits
-            # the GEMM just wrote out of L2 rather than HBM; dX / dW then run over the whole chunk
-            sub = _LM_SUB_ROWS if _LM_SUB_ROWS > 0 else r
-            for s0 in range(0, r, sub):
-                sr = min(sub, r - s0)
-                gemm(x2[r0 + s0:r0 + s0 + sr], wb, logits[s0:s0 + sr], sr, V, D,
-                     ag=fused_gather_args([weight]) if (r0 == 0 and s0 == 0) else None)
-                call("b200_ce_fwd_bwd", logits.data_ptr() + 2 * s0 * ld, t.data_ptr() + 8 * (r0 + s0), stats.data_ptr(),
-                     sr, V, ld, ignore_index, int(want_grad), float(grad_scale), stream())
+            xc = x2[r0:r0 + r]
+            call("b200_lmhead_gemm_bf16", xc.data_ptr(), wb.data_ptr(), ptr(E), r, V, D, xc.stride(0), wb.stride(0), ld,
+                 xnorm.data_ptr() + 4 * r0, lmstate.data_ptr(), part.data_ptr(), max_parts, _ctypes.addressof(nparts),
+                 t.data_ptr() + 8 * r0, tgt_val.data_ptr(), 0, st)
+            call("b200_lmhead_finish", part.data_ptr(), nparts.value, r, xnorm.data_ptr() + 4 * r0, tgt_val.data_ptr(),
+                 t.data_ptr() + 8 * r0, ignore_index, stats.data_ptr(), lmstate.data_ptr(), ptr(E), ld, V,
+                 xc.data_ptr(), xc.stride(0), D, wb.data_ptr(), wb.stride(0), ptr(xs), ptr(rscale),
+                 float(grad_scale), int(want_grad), st)
             if want_grad:
-                if one_chunk:
-                    gemm(logits, wb, dx, r, D, V, b_mn_major=True)                             # dX = dL . W
+                Ec = E[:r]
+                if r >= 8192:
+                    # enough row tiles to fill the SMs: dX straight to bf16, row scale in the epilogue
+                    call("b200_gemm_rowscale_bf16", Ec.data_ptr(), wb.data_ptr(), dx.data_ptr() + 2 * r0 * D, r, D, V,
+                         ld, wb.stride(0), D, 1, rscale.data_ptr(), 0, st)
                 else:
-                    gemm(logits, wb, dx32[r0:r0 + r], r, D, V, b_mn_major=True, accumulate=True)
+                    # few output tiles, K = vocab: split-K into fp32 (TMA reduce-add), scale + cast afterwards
+                    dx32 = torch.zeros((r, D), dtype=torch.float32, device=dev)
+                    gemm(Ec, wb, dx32, r, D, V, b_mn_major=True, accumulate=True)
+                    dx[r0:r0 + r] = (dx32 * rscale[:r, None]).to(BF16)
                 if gw is not None:
-                    gemm(logits, x2[r0:r0 + r], gw, V, D, r, a_mn_major=True, b_mn_major=True,
-                         accumulate=True)                                       # dW += dL^T . X
+                    gemm(Ec, xs[:r], gw, V, D, r, a_mn_major=True, b_mn_major=True, accumulate=True)   # dW += E'^T . Xs
         if gw is not None:
             _notify(weight)
         loss = stats[1] / stats[0].clamp(min=1.0)
-        if dx32 is not None:
-            dx = dx32.to(BF16)
         ctx.save_for_backward(dx)
-        ctx.x_shape, ctx.in_dtype = x.shape, x.dtype
+        ctx.x_shape, ctx.in_dtype, ctx.grad_scale = x.shape, x.dtype, float(grad_scale)
         ctx.mark_non_differentiable(stats)
         return loss, stats
 
@@ -580,10 +631,65 @@ class _LMHeadCE(torch.autograd.Function):
         (dx,) = ctx.saved_tensors
         if dx is None:
             return None, None, None, None, None, None, None
+        debug = _os.environ.get("B200GPT_DEBUG") == "1"
+        if (debug or _LM_CHECKS_LEFT[0] > 0) and not torch.cuda.is_current_stream_capturing():
+            _LM_CHECKS_LEFT[0] -= 1
+            got = float(dloss)
+            if abs(got - ctx.grad_scale) > 1e-6 * max(1.0, abs(ctx.grad_scale)):
+                raise RuntimeError(
+                    f"lmhead_cross_entropy: loss.backward() arrived with gradient {got} but the op was told "
+                    f"grad_scale={ctx.grad_scale}; its weight gradient is produced in the forward pass, so pass the "
+                    "factor you scale the loss by as grad_scale=")
         dx = dx.view(ctx.x_shape)
         if ctx.in_dtype != BF16:
             dx = dx.to(ctx.in_dtype)
         return dx, None, None, None, None, None, None
+
+
+def _lmhead_ce_unfused(ctx, x, weight, targets, ignore_index, grad_scale, grad_on):
+    """B200GPT_LM_FUSED=0: logits chunk -> in-place ``b200_ce_fwd_bwd`` -> dX / dW GEMMs (the pre-fusion path,
+    kept as the A/B baseline of the fused kernels; vocabularies up to 57856)."""
+    x2 = _as_bf16_2d(x)
+    M, D = x2.shape
+    wb = bf16_of(weight)
+    V = wb.shape[0]
+    ld = (V + 127) // 128 * 128
+    t = targets.reshape(-1).contiguous()
+    dev = x.device
+    stats = torch.zeros(4, dtype=torch.float32, device=dev)  # n_valid, loss_sum, n_correct
+    call("b200_count_valid", t.data_ptr(), stats.data_ptr(), ignore_index, M, stream())
+    want_grad = grad_on and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1])
+    rows = min(_LM_CHUNK_ROWS, M)
+    logits = torch.empty((rows, ld), dtype=BF16, device=dev)
+    one_chunk = M <= rows and M >= 8192
+    dx32 = torch.zeros((M, D), dtype=torch.float32, device=dev) if (want_grad and not one_chunk) else None
+    dx = torch.empty((M, D), dtype=BF16, device=dev) if (want_grad and one_chunk) else None
+    gw = grad_of(weight) if (want_grad and weight.requires_grad) else None
+    for r0 in range(0, M, rows):
+        r = min(rows, M - r0)
+        sub = _LM_SUB_ROWS if _LM_SUB_ROWS > 0 else r
+        for s0 in range(0, r, sub):
+            sr = min(sub, r - s0)
+            gemm(x2[r0 + s0:r0 + s0 + sr], wb, logits[s0:s0 + sr], sr, V, D)
+            call("b200_ce_fwd_bwd", logits.data_ptr() + 2 * s0 * ld, t.data_ptr() + 8 * (r0 + s0), stats.data_ptr(),
+                 sr, V, ld, ignore_index, int(want_grad), float(grad_scale), stream())
+        if want_grad:
+            if one_chunk:
+                gemm(logits, wb, dx, r, D, V, b_mn_major=True)                             # dX = dL . W
+            else:
+                gemm(logits[:r], wb, dx32[r0:r0 + r], r, D, V, b_mn_major=True, accumulate=True)
+            if gw is not None:
+                gemm(logits[:r], x2[r0:r0 + r], gw, V, D, r, a_mn_major=True, b_mn_major=True,
+                     accumulate=True)                                       # dW += dL^T . X
+    if gw is not None:
+        _notify(weight)
+    loss = stats[1] / stats[0].clamp(min=1.0)
+    if dx32 is not None:
+        dx = dx32.to(BF16)
+    ctx.save_for_backward(dx)
+    ctx.x_shape, ctx.in_dtype, ctx.grad_scale = x.shape, x.dtype, float(grad_scale)
+    ctx.mark_non_differentiable(stats)
+    return loss, stats
 
 
 def lmhead_cross_entropy(x, weight, targets, ignore_index=-100, grad_scale: float = 1.0):

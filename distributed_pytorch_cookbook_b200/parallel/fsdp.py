@@ -203,10 +203,16 @@ class FSDPStrategy:
         fa = os.environ.get("B200GPT_FUSED_AG", "")
         wide = int(getattr(model, "dim", 0) or 0) >= 1024
         self.fused_ag = transport == "symm" and (fa == "1" or (fa != "0" and wide))
+        for g in self.groups:
+            g.fused = False
         if self.fused_ag:
+            head = self.units[-1]
             for g in self.groups:
-                if g.kind != "big":
+                # the LM-head weight is consumed by the softmax-epilogue GEMM, which has no gather warp: its
+                # group is pulled on the side stream one unit ahead like the small groups
+                if g.kind != "big" or any(g is h for h in head):
                     continue
+                g.fused = True
                 g.peers_dev = torch.tensor([pp + 2 * g.shard_base for pp in self.shard_bf16_buf.peer_ptrs],
                                            dtype=torch.int64, device=dev)
                 g.ag_sync = torch.zeros(2 + 1024, dtype=torch.int32, device=dev)
@@ -268,7 +274,7 @@ class FSDPStrategy:
                 g.event.record(self.comm_stream)
 
     def _ensure(self, g: ShardGroup):
-        if self.fused_ag and g.kind == "big":
+        if g.fused:
             return                                        # gathered inside the consuming GEMMs
         if g.gathered_version != self.version:
             self._gather(g)

@@ -67,6 +67,32 @@ int b200_count_valid(const int64_t* targets, float* stats, int ignore_index, int
 int b200_ce_fwd_bwd(void* logits_bf16, const int64_t* targets, float* stats, int rows, int vocab, int ld,
                     int ignore_index, int write_grad, float grad_scale, void* stream);
 
+/* Fused LM head + cross entropy (models/gpt.py:219,231 + main-single.py:95-96,127-131).  The logits are never
+ * written: the logits GEMM's epilogue stores E = exp(logit - shift[m]) (bf16) with a shift fixed before the GEMM
+ * (upper bound |x||w| of the row's logits minus an observed gap), and leaves per-row statistics; `finish` derives
+ * loss / accuracy and prepares the two gradient GEMMs, recomputing exactly any row the shift estimate missed.
+ *   b200_lmhead_begin   stats[0] = #targets != ignore_index, stats[1..3] = 0, rotate lmstate
+ *   b200_lmhead_norms   xnorm[m] = |X[m,:]|, lmstate[0] = max_v |W[v,:]|
+ *   b200_lmhead_gemm_bf16  E (NULL: statistics only), part[span][M] = (sum E, max logit), tgt_val[m]
+ *   b200_lmhead_finish  stats[1] += loss sum, stats[2] += #correct, rscale, E[m,target] -= sum_m, Xs = rscale * X
+ *   then  dX = b200_gemm_rowscale_bf16(E, W, rscale)   and   dW += E^T . Xs  (b200_gemm_bf16)
+ * lmstate: 4 floats that live with the weight (zero once, then leave alone): wmax, gap in use, gap observed,
+ * rows recomputed by the last call.  part: max_parts x M float2 with max_parts >= ceil(V / 128) + 2. */
+int b200_lmhead_begin(const int64_t* targets, float* stats, float* lmstate, int ignore_index, int64_t n,
+                      void* stream);
+int b200_lmhead_norms(const void* X_bf16, int ldx, const void* W_bf16, int ldw, int M, int V, int D, float* xnorm,
+                      float* lmstate, void* stream);
+int b200_lmhead_gemm_bf16(const void* X, const void* W, void* E_out, int M, int V, int K, int ldx, int ldw, int lde,
+                          const float* xnorm, const float* lmstate, void* part, int max_parts, int* num_parts,
+                          const int64_t* targets, float* tgt_val, int cfg, void* stream);
+int b200_lmhead_finish(const void* part, int num_parts, int M, const float* xnorm, const float* tgt_val,
+                       const int64_t* targets, int ignore_index, float* stats, float* lmstate, void* E, int lde,
+                       int V, const void* X, int ldx, int D, const void* W, int ldw, void* Xs, float* rscale,
+                       float grad_scale, int write_grad, void* stream);
+/* C (bf16) = diag(row_scale) . (A . op(B)) */
+int b200_gemm_rowscale_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                            int b_mn_major, const float* row_scale, int cfg, void* stream);
+
 /* Masked dgrad GEMM with the bias gradient fused into its epilogue (MLP backward of reference
  * models/gpt.py:33-41): C (bf16) = (A . B) * (mask_src > 0), colsum[n] += sum over rows of C.  colsum is
  * accumulated with fp32 reductions, like every other gradient of this library. */

@@ -360,6 +360,137 @@ def test_lmhead_ce_large_single_chunk_against_fp32():
     assert float((native.grad_of(w) - w32.grad).norm() / w32.grad.norm()) < 2e-2
 
 
+def _lm_reference(x, w, tgt):
+    from distributed_pytorch_cookbook_b200 import ops
+    x32 = x.detach().float().requires_grad_(True)
+    w32 = w.detach().to(BF16).float().requires_grad_(True)
+    ref, nv, nc = ops.lmhead_cross_entropy_reference(x32, w32, tgt)
+    ref.backward()
+    return float(ref), int(nv), int(nc), x32.grad, w32.grad
+
+
+def _rel(a, b):
+    return float((a.float() - b.float()).norm() / b.float().norm().clamp(min=1e-20))
+
+
+@pytest.mark.parametrize("M,Dm,V,xs", [(16320, 256, 50257, 1.0), (1000, 256, 5003, 1.0), (300, 512, 1000, 6.0),
+                                         (129, 64, 257, 1.0)])
+def test_lmhead_fused_softmax_epilogue_against_fp32(M, Dm, V, xs):
+    """Softmax-epilogue LM head (no logits in memory): loss, counts, dX and dW against fp32 PyTorch on the
+    same bf16 operands, with ignored rows, a vocabulary tail and logits of very different magnitude."""
+    torch.manual_seed(1)
+    x = (torch.randn(M, Dm, device="cuda") * xs).to(BF16).requires_grad_(True)
+    w = torch.nn.Parameter(torch.randn(V, Dm, device="cuda") * 0.05)
+    tgt = torch.randint(0, V, (M,), device="cuda")
+    tgt[3:9] = -100
+    tgt[-1] = V - 1
+    for it in range(2):      # second call runs with the gap observed by the first
+        x.grad = None
+        w.grad = None
+        loss, n_valid, n_correct = native.lmhead_cross_entropy(x, w, tgt)
+        loss.backward()
+        ref, nv, nc, dx32, dw32 = _lm_reference(x, w, tgt)
+        assert abs(float(loss) - ref) < 2e-3 * max(1.0, abs(ref)), (it, float(loss), ref)
+        assert int(n_valid) == nv == M - 6
+        assert abs(int(n_correct) - nc) <= max(1, nc // 50), (int(n_correct), nc)
+        assert _rel(x.grad, dx32) < 2e-2, (it, _rel(x.grad, dx32))
+        assert _rel(native.grad_of(w), dw32) < 2e-2, (it, _rel(native.grad_of(w), dw32))
+        assert float(x.grad[3:9].abs().max()) == 0.0          # ignored rows get no gradient
+    st = native.lm_state(w).tolist()
+    assert st[3] == 0.0 and st[1] >= 0.0, st                  # nothing had to be recomputed
+    assert _dev_err() == 0
+
+
+def test_lmhead_rows_outside_the_shift_window_are_recomputed():
+    """A wrong gap estimate (here: absurdly large, so every exp overflows) must only cost time: finish
+    recomputes the rows exactly, and the next call runs with the gap that was observed."""
+    torch.manual_seed(2)
+    M, Dm, V = 200, 256, 3001
+    x = torch.randn(M, Dm, device="cuda").to(BF16).requires_grad_(True)
+    w = torch.nn.Parameter(torch.randn(V, Dm, device="cuda") * 0.05)
+    tgt = torch.randint(0, V, (M,), device="cuda")
+    tgt[:4] = -100
+    ref, nv, nc, dx32, dw32 = _lm_reference(x, w, tgt)
+    st = native.lm_state(w)
+    for poison, expect_bad in ((900.0, M), (None, 0), (-1.0, 0)):
+        if poison is not None and poison > 0:
+            st[2] = poison
+        x.grad = None
+        w.grad = None
+        loss, n_valid, n_correct = native.lmhead_cross_entropy(x, w, tgt)
+        loss.backward()
+        torch.cuda.synchronize()
+        assert st[3].item() == expect_bad, (poison, st.tolist())
+        assert abs(float(loss) - ref) < 2e-3 * max(1.0, abs(ref)), (poison, float(loss), ref)
+        assert abs(int(n_correct) - nc) <= 1 and int(n_valid) == nv
+        assert _rel(x.grad, dx32) < 2e-2 and _rel(native.grad_of(w), dw32) < 2e-2
+    # evaluation (no gradient, nothing stored) agrees too, also from a poisoned estimate
+    st[2] = 900.0
+    with torch.no_grad():
+        l2, nv2, nc2 = native.lmhead_cross_entropy(x.detach(), w, tgt)
+    assert abs(float(l2) - ref) < 2e-3 * max(1.0, abs(ref)) and int(nv2) == nv and abs(int(nc2) - nc) <= 1
+    assert _dev_err() == 0
+
+
+def test_lmhead_fused_and_unfused_paths_agree(monkeypatch):
+    torch.manual_seed(3)
+    M, Dm, V = 2048, 256, 50257
+    x0 = torch.randn(M, Dm, device="cuda").to(BF16)
+    w = torch.nn.Parameter(torch.randn(V, Dm, device="cuda") * 0.03)
+    tgt = torch.randint(0, V, (M,), device="cuda")
+    out = []
+    for fused in (True, False):
+        monkeypatch.setattr(native, "_LM_FUSED", fused)
+        x = x0.clone().requires_grad_(True)
+        w.grad = None
+        loss, nv, nc = native.lmhead_cross_entropy(x, w, tgt, grad_scale=0.5)
+        (loss * 0.5).backward()
+        out.append((float(loss), int(nv), int(nc), x.grad.clone(), native.grad_of(w).clone()))
+    a, b = out
+    assert abs(a[0] - b[0]) < 2e-3 and a[1] == b[1] and abs(a[2] - b[2]) <= 2
+    assert _rel(a[3], b[3]) < 2e-2 and _rel(a[4], b[4]) < 2e-2
+
+
+def test_lmhead_wrong_loss_gradient_is_detected(monkeypatch):
+    """The op bakes grad_scale into the gradients it produces in forward; a caller that scales the loss by
+    something else must hear about it (first un-captured calls, or always with B200GPT_DEBUG=1)."""
+    monkeypatch.setenv("B200GPT_DEBUG", "1")
+    x = torch.randn(64, 64, device="cuda").to(BF16).requires_grad_(True)
+    w = torch.nn.Parameter(torch.randn(300, 64, device="cuda") * 0.05)
+    tgt = torch.randint(0, 300, (64,), device="cuda")
+    loss, _, _ = native.lmhead_cross_entropy(x, w, tgt)
+    with pytest.raises(RuntimeError, match="grad_scale"):
+        (loss * 0.25).backward()
+
+
+def test_model_forward_returns_logits_at_odd_vocab():
+    """Reference-style ``model(input_ids, position_ids)`` (gpt.py:221-231) under bf16 autocast at vocab 50257:
+    the logits rows are not a multiple of 16 bytes, the op pads them and returns the [.., vocab] view; its
+    backward and greedy generation without the cache go through the same path."""
+    from distributed_pytorch_cookbook_b200 import ops
+    dev = torch.device("cuda")
+    V = 50257
+    model = _tiny_model(dev, layers=1, vocab=V)
+    ids = torch.randint(0, V, (2, 37), device=dev)
+    pos = torch.arange(37, device=dev).unsqueeze(0).repeat(2, 1)
+    with torch.autocast("cuda", dtype=BF16):
+        logits = model(ids, pos)
+    assert logits.shape == (2, 37, V) and logits.dtype == BF16
+    with ops.force_reference():
+        ref = model(ids, pos)
+    assert float((logits.float() - ref).abs().max()) < 0.08 * max(1.0, float(ref.abs().max()))
+    tgt = torch.randint(0, V, (2, 37), device=dev)
+    with torch.autocast("cuda", dtype=BF16):
+        loss = F.cross_entropy(model(ids, pos).float().view(-1, V), tgt.view(-1))
+    loss.backward()
+    g = model.lm_head.weight.grad.clone()
+    model.zero_grad(set_to_none=True)
+    with ops.force_reference():
+        F.cross_entropy(model(ids, pos).view(-1, V), tgt.view(-1)).backward()
+    assert _rel(g, model.lm_head.weight.grad) < 3e-2
+    assert _dev_err() == 0
+
+
 @pytest.mark.parametrize("B,T,H,D,masked", [(2, 255, 8, 32, False), (2, 100, 2, 64, True), (1, 300, 2, 128, False),
                                             (64, 255, 8, 32, False), (1, 1023, 2, 128, True)])
 def test_flash_attention_fwd_bwd(B, T, H, D, masked):
