@@ -251,6 +251,52 @@ rs_adamw_kernel(const CommCtx c, int64_t shard_off, int64_t shard_n, float scale
 }
 
 // ------------------------------------------------------------------------------------------
+// reduce-scatter alone: out[i] = scale * sum over ranks of grad[shard_off + i].  Meant for a SMALL grid
+// (<= 16 blocks): with NVLS the switch does the additions and one multimem.ld_reduce brings 16 reduced
+// bytes, so a handful of blocks with 8 loads in flight per thread saturate what a training step needs,
+// and the compute kernels keep their SMs.  The optimizer then runs on `out` as an ordinary kernel.
+template <bool USE_MC>
+__global__ void __launch_bounds__(512)
+reduce_scatter_kernel(const CommCtx c, int64_t shard_off, int64_t shard_n, float scale, float* __restrict__ out,
+                      int end_barrier) {
+  __shared__ int s_fail;
+  if (!block_barrier(c, &s_fail)) return;           // every rank's gradients of this range are complete
+  const int64_t nvec = shard_n >> 2;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  constexpr int U = 8;
+  for (int64_t i0 = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i0 < nvec; i0 += stride * U) {
+    float4 g[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = i0 + u * stride;
+      g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (i < nvec) {
+        if (USE_MC) {
+          g[u] = mc_ld_reduce_f32x4(reinterpret_cast<const float*>(c.mc) + shard_off + 4 * i);
+        } else {
+#pragma unroll 1
+          for (int p = 0; p < c.world; ++p) {
+            const int peer = (c.rank + p) % c.world;
+            const float4 v = ld_sys_f32x4(reinterpret_cast<const float*>(c.bufs[peer]) + shard_off + 4 * i);
+            g[u].x += v.x; g[u].y += v.y; g[u].z += v.z; g[u].w += v.w;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = i0 + u * stride;
+      if (i < nvec)
+        reinterpret_cast<float4*>(out)[i] = make_float4(g[u].x * scale, g[u].y * scale, g[u].z * scale, g[u].w * scale);
+    }
+  }
+  if (end_barrier) {   // nobody overwrites its gradients (next step) while a peer still reads them
+    __threadfence_system();
+    block_barrier(c, &s_fail);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // all-gather (pull): dst[p * shard_bytes + i] = peer p's src shard, 16-byte vectors.
 __global__ void __launch_bounds__(512)
 allgather_kernel(const CommCtx c, int64_t src_off_bytes, int64_t shard_bytes, uint8_t* dst,
@@ -335,6 +381,27 @@ int b200_rs_adamw(const void* grad_bufs_dev, void* grad_mc_ptr, const void* flag
     rs_adamw_kernel<true><<<nblocks, 512, 0, st>>>(c, shard_off, shard_n, scale, a, end_barrier);
   else
     rs_adamw_kernel<false><<<nblocks, 512, 0, st>>>(c, shard_off, shard_n, scale, a, end_barrier);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// Reduce-scatter of this rank's shard into a local fp32 buffer (FSDP post-backward reduce-scatter,
+// main-fsdp.py:138-140), for callers that run the optimizer as a separate kernel: small grid, no AdamW
+// traffic inside the kernel that spins on the peers.
+int b200_reduce_scatter(const void* grad_bufs_dev, void* grad_mc_ptr, const void* flags_dev, int rank, int world,
+                        int64_t shard_off, int64_t shard_n, float scale, float* out, int end_barrier, int nblocks,
+                        int channel_base, void* stream) {
+  B200_REQUIRE(shard_n % 4 == 0 && shard_off % 4 == 0, "reduce_scatter: offset/count must be multiples of 4");
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(out) & 15) == 0, "reduce_scatter: output must be 16-byte aligned");
+  if (shard_n == 0) return 0;
+  CommCtx c;
+  int rc = make_ctx(&c, grad_bufs_dev, grad_mc_ptr, flags_dev, rank, world, channel_base, nblocks);
+  if (rc != 0) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (grad_mc_ptr != nullptr)
+    reduce_scatter_kernel<true><<<nblocks, 512, 0, st>>>(c, shard_off, shard_n, scale, out, end_barrier);
+  else
+    reduce_scatter_kernel<false><<<nblocks, 512, 0, st>>>(c, shard_off, shard_n, scale, out, end_barrier);
   B200_LAUNCH_CHECK();
   return 0;
 }

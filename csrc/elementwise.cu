@@ -820,7 +820,10 @@ lm_finish_kernel(const float2* __restrict__ part, int num_parts, int M, const fl
     float tl = valid ? tgt_val[row] : 0.f;
     const float a = m - shift;
     const bool good = isfinite(s) && s > 0.f && a >= kLmWindowLo && a <= kLmWindowHi;
-    if (!good) {
+    // NaN in the row (NaN activations or weights) cannot be repaired by recomputing it: let it through, the
+    // loss comes out NaN like the reference's
+    const bool hopeless = s != s || m != m || m == INFINITY;
+    if (!good && !hopeless) {
       // the shift estimate missed this row (or the row holds non-finite values): redo it exactly with
       // shift = row max.  Every lane takes its own vocabulary entries; x is read through L1, W through L2.
       const bf16* xr = X + static_cast<size_t>(row) * ldx;

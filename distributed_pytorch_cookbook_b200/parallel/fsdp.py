@@ -170,6 +170,12 @@ class FSDPStrategy:
         self.shard_bf16, self.shard_bf16_buf = alloc(Gs, bf16, True) if self.native else (None, None)
         self.hyper = torch.tensor([self.lr, 0.0, 0.0, 0.0], dtype=f32, device=dev)
         self.host_step = 0
+        import os
+        # B200GPT_FSDP_RS=fused: the one-kernel reduce-scatter + AdamW (b200_rs_adamw, up to 64 resident blocks);
+        # default: small-grid b200_reduce_scatter into a shard-sized buffer + b200_adamw behind it
+        self.rs_split = transport == "symm" and os.environ.get("B200GPT_FSDP_RS", "split") != "fused"
+        self.rs_blocks = int(os.environ.get("B200GPT_FSDP_RS_BLOCKS", "8"))
+        self.shard_grad = torch.zeros(Gs, dtype=f32, device=dev) if self.rs_split else None
 
         # re-point parameters / gradients at the flat buffers and cut the shards
         self.group_of = {}
@@ -195,7 +201,6 @@ class FSDPStrategy:
                 self.master_dev.copy_(self.master, non_blocking=True)
         # fused all-gather: big (bf16) groups are not gathered by a separate kernel - the first GEMM that
         # consumes each weight pulls it from the peers' shards itself (b200_ag_gemm_bf16)
-        import os
         # All-gather inside the consuming GEMM (b200_ag_gemm_bf16) or as a pull kernel on the side stream.  The
         # fused form runs on single-CTA tiles (it needs the gather warp), which costs more than it hides when the
         # weights are small: measured at 4 GPUs, default GPT 5.26 ms fused vs 5.09 ms unfused, 1.4 B model 90.6 vs
@@ -315,6 +320,19 @@ class FSDPStrategy:
             self.comm_stream.wait_event(ev)
             ctx = torch.cuda.stream(self.comm_stream)
         with ctx:
+            if self.comm_kind == "symm" and self.rs_split:
+                # reduce-scatter on a small grid (the switch adds; <= 16 blocks leave the SMs to the compute
+                # kernels), then AdamW on the reduced shard as an ordinary kernel behind it
+                pb = self.shard_bf16.data_ptr() + 2 * sb if g.kind == "big" else None
+                nblocks = max(1, min(self.rs_blocks, (sn * 4) >> 20))           # ~1 MiB of shard per block
+                st = self.comm_stream.cuda_stream
+                _lib.call("b200_reduce_scatter", self.grads_buf.ptrs_dev, self.grads_buf.mc_ptr or None,
+                          self.symm.flags.ptrs_dev, self.rank, self.world, lo, sn, 1.0 / self.world,
+                          self.shard_grad.data_ptr() + 4 * sb, 1, nblocks, CH_RS_ADAMW, st)
+                _lib.call("b200_adamw", self.master.data_ptr() + 4 * sb, self.shard_grad.data_ptr() + 4 * sb,
+                          self.exp_avg.data_ptr() + 4 * sb, self.exp_avg_sq.data_ptr() + 4 * sb, pb, sn,
+                          self.hyper.data_ptr(), b1, b2, self.eps, self.wd, st)
+                return
             if self.comm_kind == "symm":
                 pb = self.shard_bf16.data_ptr() + 2 * sb if g.kind == "big" else None
                 nblocks = max(2, min(64, (sn * 4) >> 17))                        # ~128 KiB of shard per block
@@ -371,6 +389,11 @@ class FSDPStrategy:
                 self._reduce_and_step(g)
         self.active = False
         if self.device.type == "cuda":
+            if self.rs_split and self.fused_ag:
+                # the next step's GEMMs pull the peers' bf16 shards without a barrier of their own: every rank's
+                # AdamW kernels (queued on the side stream above) must have finished first
+                with torch.cuda.stream(self.comm_stream):
+                    self.symm.barrier()
             torch.cuda.current_stream().wait_stream(self.comm_stream)
         self.version += 1                                  # shards changed: gathered copies are stale
         return loss.detach()

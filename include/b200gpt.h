@@ -145,6 +145,11 @@ int b200_rs_adamw(const void* grad_bufs_dev, void* grad_mc_ptr, const void* flag
                   int64_t shard_off, int64_t shard_n, float scale, float* p, float* m, float* v,
                   void* p_bf16, const float* hyper, float beta1, float beta2, float eps, float wd,
                   int end_barrier, int nblocks, int channel_base, void* stream);
+/* reduce-scatter alone: out[i] = scale * sum_ranks grad[shard_off + i], for a small grid (<= 16 blocks; the
+ * switch adds), followed by b200_adamw on `out` as an ordinary kernel  (main-fsdp.py:138-140) */
+int b200_reduce_scatter(const void* grad_bufs_dev, void* grad_mc_ptr, const void* flags_dev, int rank, int world,
+                        int64_t shard_off, int64_t shard_n, float scale, float* out, int end_barrier, int nblocks,
+                        int channel_base, void* stream);
 /* pull all-gather: dst[peer * shard_bytes ...] = peer's bytes [src_off, src_off + shard_bytes)
  * (FSDP pre-forward unshard, main-fsdp.py:131) */
 int b200_allgather(const void* src_bufs_dev, const void* flags_dev, int rank, int world,
