@@ -91,6 +91,20 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def timed_blocks(fn, steps: int, device, sampler=None, min_total_s: float = 1.0, max_blocks: int = 40):
+    """The K-step timed region, repeated: every block is ``timed`` (barrier + synchronize on both sides, CUDA
+    events, max over ranks) over exactly K steps; blocks are added until at least ``min_total_s`` of device time
+    has been measured.  Returns the per-block times in ms.  One clock sampler spans all blocks."""
+    out = []
+    ctx = sampler if sampler is not None else _Null()
+    with ctx:
+        while True:
+            out.append(timed(fn, steps, device))
+            if sum(out) >= min_total_s * 1e3 or len(out) >= max_blocks:
+                break
+    return out
+
+
 def timed(fn, steps: int, device, sampler=None):
     """barrier + sync, K x fn under CUDA events, sync + barrier; returns ms (max over ranks)."""
     if dist.is_initialized():
@@ -130,7 +144,9 @@ def host_batches(n: int, seed: int):
     return out
 
 
-def result_line(impl, value, ms, e2e_value, n, steps, warmup, clocks, launches, extra_cfg, h2d, d2h):
+def result_line(impl, value, ms, e2e_value, n, steps, warmup, clocks, launches, details, h2d, d2h):
+    """``config`` holds only what both arms share (model / batch / sequence / parallelism); everything that is
+    specific to an arm (graph capture, transport, compile mode, losses, block statistics) goes to ``details``."""
     baseline = None  # BASELINE.md publishes no number ("none published")
     line = {
         "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": n, "steps": steps, "warmup": warmup,
@@ -143,8 +159,8 @@ def result_line(impl, value, ms, e2e_value, n, steps, warmup, clocks, launches, 
                    "parallelism": "single" if n == 1 else f"dp{n}",
                    "optimizer": "AdamW lr1e-4 (step inside timed region)",
                    "l2": "no flush: per-step working set (0.5 GB params+optimizer state, >1 GB activations) "
-                         "exceeds the 126 MB L2",
-                   **extra_cfg},
+                         "exceeds the 126 MB L2"},
+        "details": details,
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches,
@@ -200,9 +216,10 @@ def run_ours(args):
         strategy.train_step(b, t, amp=True)
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
-    ms_total = timed(dev_step, args.steps, device, sampler)
+    blocks = timed_blocks(dev_step, args.steps, device, sampler, args.min_seconds)
+    ms_total = statistics.median(blocks)
     clocks = sampler.summary() if sampler is not None else None
-    launches = (_lib.launch_count() - launches0)
+    launches = (_lib.launch_count() - launches0) // len(blocks)
     if per_step_launches:
         launches = per_step_launches * args.steps
 
@@ -224,8 +241,9 @@ def run_ours(args):
             loss_ev[i & 1].synchronize()
             host_losses.append(float(loss_host[i & 1]))
 
-    ms_e2e = timed(e2e_timed, args.steps, device)
-    assert len(host_losses) == args.steps
+    e2e_blocks = timed_blocks(e2e_timed, args.steps, device, None, args.min_seconds)
+    ms_e2e = statistics.median(e2e_blocks)
+    assert len(host_losses) == args.steps * len(e2e_blocks)
 
     # exposed communication per step = step time minus the same step with the all-reduces skipped
     exposed_comm_ms = None
@@ -236,7 +254,7 @@ def run_ours(args):
             for i in range(6):
                 dev_step(i)
             torch.cuda.synchronize(device)
-            ms_nocomm = timed(dev_step, args.steps, device)
+            ms_nocomm = statistics.median(timed_blocks(dev_step, args.steps, device, None, args.min_seconds / 2))
             exposed_comm_ms = max(ms_total - ms_nocomm, 0.0) / args.steps
         except Exception as e:  # noqa: BLE001  (measurement extra: never lose the headline line)
             print(f"[bench] exposed-communication measurement failed: {e}", file=sys.stderr, flush=True)
@@ -245,16 +263,108 @@ def run_ours(args):
     e2e_value = tokens_per_step * args.steps / ms_e2e * 1e3
     h2d = sum(v.numel() * v.element_size() for v in prepare_batch(batches[0], pad, "cpu")[0].values()) + \
         CFG["batch_size"] * (CFG["sequence_length"] - 1) * 8
+    details = {"cuda_graph": bool(getattr(strategy, "use_graph", False)),
+               "final_loss": host_losses[-1] if host_losses else None,
+               "comm": getattr(strategy, "comm_kind", None),
+               "exposed_comm_ms_per_step": exposed_comm_ms,
+               "timed_blocks": len(blocks), "timed_seconds": sum(blocks) / 1e3,
+               "ms_per_step_min": min(blocks) / args.steps, "ms_per_step_max": max(blocks) / args.steps,
+               "e2e_ms_per_step": ms_e2e / args.steps}
+    if hasattr(strategy, "close"):
+        strategy.close()
+    del strategy, model, dev_batches
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
+    line = result_line("ours", value, ms_total / args.steps, e2e_value, n, args.steps, args.warmup,
+                       clocks, launches, details, h2d, 4)
+    if n > 1 and not args.no_selfcheck:
+        line["selfcheck"] = selfcheck(device)
+    if n > 1 and not args.no_recipes:
+        line["recipes"] = run_recipes("ours", n, args)
     if rank == 0:
-        extra = {"cuda_graph": bool(getattr(strategy, "use_graph", False)),
-                 "final_loss": host_losses[-1] if host_losses else None,
-                 "comm": getattr(strategy, "comm_kind", None),
-                 "exposed_comm_ms_per_step": exposed_comm_ms}
-        print(json.dumps(result_line("ours", value, ms_total / args.steps, e2e_value, n, args.steps, args.warmup,
-                                     clocks, launches, extra, h2d, 4)), flush=True)
+        print(json.dumps(line), flush=True)
     if dist.is_initialized():
         dist.barrier()
         dist.destroy_process_group()
+
+
+def selfcheck(device):
+    """Multi-GPU correctness the 1-GPU test tier cannot see: the same 3 training steps (default GPT, fixed seed,
+    one batch per rank) through (a) DDP on the own NVLink all-reduce, (b) DDP on NCCL, (c) FSDP on the own
+    reduce-scatter / all-gather kernels.  All three must report the same losses."""
+    from distributed_pytorch_cookbook_b200.ops import _lib
+    from distributed_pytorch_cookbook_b200.parallel.ddp import DDPStrategy
+    from distributed_pytorch_cookbook_b200.parallel.fsdp import FSDPStrategy
+    from distributed_pytorch_cookbook_b200.trainer import build_model
+    from distributed_pytorch_cookbook_b200.utils import prepare_batch, seed_everything
+    import ctypes
+    rank = dist.get_rank()
+    out = {}
+    try:
+        batches = host_batches(3, seed=500 + rank)
+        runs = {}
+        for name, make, comm in (("ddp_symm", DDPStrategy, "symm"), ("ddp_nccl", DDPStrategy, "nccl"),
+                                 ("fsdp_symm", FSDPStrategy, "symm")):
+            seed_everything(0)
+            ns = SimpleNamespace(**CFG, disable_amp=False, disable_cuda_graph=False, bucket_mb=4.0, comm=comm,
+                                 epochs=1, cpu_offload=False)
+            st = make()
+            st.setup(build_model(ns, CFG["vocab_size"]), ns, device)
+            st.train()
+            losses = []
+            for b in batches:
+                bb, t = prepare_batch(b, 2, device)
+                losses.append(st.train_step(bb, t, amp=True).float().reshape(1).clone())
+            ls = torch.cat(losses)
+            dist.all_reduce(ls)
+            runs[name] = (ls / dist.get_world_size()).tolist()
+            st.close()
+            del st
+            torch.cuda.synchronize(device)
+        err = ctypes.c_int(0)
+        _lib.call("b200_device_error", ctypes.addressof(err), 0)
+        ref = runs["ddp_nccl"]
+        out = {"losses": runs, "device_error": err.value,
+               "max_abs_diff_vs_nccl": {k: max(abs(a - b) for a, b in zip(v, ref)) for k, v in runs.items()}}
+        out["ok"] = bool(err.value == 0 and all(d < 2e-2 for d in out["max_abs_diff_vs_nccl"].values())
+                         and all(x == x for v in runs.values() for x in v))
+    except Exception as e:  # noqa: BLE001
+        out = {"ok": False, "error": repr(e)[:300]}
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_recipes(impl, n, args):
+    """BASELINE.json configs 3-5 on the same N ranks, after the headline run: FSDP on the ~1.3 B GPT, the GPipe /
+    1F1B pipeline (stages = N up to 4) and pipeline x DDP (2 stages x N/2).  Same timing rules as the headline
+    (tools/bench_recipes.py: warm-up, barrier + synchronize, CUDA events, max over ranks, AdamW inside)."""
+    sys.path.insert(0, str(ROOT / "tools"))
+    from bench_recipes import run_recipe
+    plan = [("fsdp_1p3b", dict(recipe="fsdp", model="1.3b", steps=8, warmup=5, measure_exposed=impl == "ours"))]
+    if n <= 4:
+        plan.append((f"pipe_{n}stage_m{n}", dict(recipe="pipe", steps=20, warmup=6, schedule="1f1b", microbatches=n)))
+        plan.append((f"pipe_{n}stage_m{2 * n}", dict(recipe="pipe", steps=20, warmup=6, schedule="1f1b", microbatches=2 * n)))
+    if n >= 4:
+        plan.append((f"pipe_ddp_2x{n // 2}", dict(recipe="pipe-ddp", steps=20, warmup=6, schedule="1f1b", microbatches=4)))
+    out = {}
+    for name, kw in plan:
+        if args.recipes != "all" and name.split("_")[0] not in args.recipes.split(","):
+            continue
+        try:
+            r = run_recipe(impl=impl, **kw)
+            out[name] = {k: r.get(k) for k in ("ms_per_step", "tokens_per_s", "loss_after", "comm", "stages", "dp",
+                                               "microbatches", "schedule", "global_batch", "seq_len", "model",
+                                               "compute_only_ms_per_step", "exposed_comm_ms_per_step") if r.get(k) is not None}
+        except Exception as e:  # noqa: BLE001
+            out[name] = {"error": repr(e)[:300]}
+            try:
+                dist.barrier()
+            except Exception:
+                pass
+    return out
 
 
 # ------------------------------------------------------------------------------------------
@@ -322,30 +432,38 @@ def run_reference(args):
         torch.cuda.synchronize(device)
         dev_batches = [ref.utils.prepare_batch(b, pad, device) for b in batches]
         sampler = ClockSampler(local_rank) if rank == 0 else None
-        ms_dev = timed(lambda i: step(*dev_batches[i % len(dev_batches)], False), args.steps, device, sampler)
+        dev_blocks = timed_blocks(lambda i: step(*dev_batches[i % len(dev_batches)], False), args.steps, device,
+                                  sampler, args.min_seconds)
+        ms_dev = statistics.median(dev_blocks)
         if sampler is not None:
             clocks = sampler.summary()
 
         def e2e(i):
             b, t = ref.utils.prepare_batch(batches[i % len(batches)], pad, device)
             step(b, t, True)
-        ms_e2e = timed(e2e, args.steps, device)
-        results["compile" if use_compile and compiled_ok else "eager"] = (ms_dev, ms_e2e)
+        ms_e2e = statistics.median(timed_blocks(e2e, args.steps, device, None, args.min_seconds))
+        results["compile" if use_compile and compiled_ok else "eager"] = (ms_dev, ms_e2e, len(dev_blocks))
         del model, optim, sp_model
         torch.cuda.empty_cache()
 
     tokens_per_step = CFG["batch_size"] * (CFG["sequence_length"] - 1) * n
     timed_modes = {k: v for k, v in results.items() if isinstance(v, tuple)}
     best = min(timed_modes, key=lambda k: timed_modes[k][0])
-    ms_dev, ms_e2e = timed_modes[best]
+    ms_dev, ms_e2e, nblocks = timed_modes[best]
+    extra = {"reference_mode": best,
+             "all_modes_ms_per_step": {k: v[0] / args.steps for k, v in timed_modes.items()},
+             "repairs_applied_in_memory": ref.repairs, "compile_error": results.get("compile_error"),
+             "timed_blocks": nblocks, "e2e_ms_per_step": ms_e2e / args.steps}
+    h2d = 3 * CFG["batch_size"] * (CFG["sequence_length"] - 1) * 8 + CFG["batch_size"] * (CFG["sequence_length"] - 1)
+    line = result_line("reference", tokens_per_step * args.steps / ms_dev * 1e3, ms_dev / args.steps,
+                       tokens_per_step * args.steps / ms_e2e * 1e3, n, args.steps, args.warmup, clocks,
+                       0, extra, h2d, 4)
+    if n > 1 and not args.no_recipes:
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
+        line["recipes"] = run_recipes("reference", n, args)
     if rank == 0:
-        extra = {"reference_mode": best,
-                 "all_modes_ms_per_step": {k: v[0] / args.steps for k, v in timed_modes.items()},
-                 "repairs_applied_in_memory": ref.repairs, "compile_error": results.get("compile_error")}
-        h2d = 3 * CFG["batch_size"] * (CFG["sequence_length"] - 1) * 8 + CFG["batch_size"] * (CFG["sequence_length"] - 1)
-        line = result_line("reference", tokens_per_step * args.steps / ms_dev * 1e3, ms_dev / args.steps,
-                           tokens_per_step * args.steps / ms_e2e * 1e3, n, args.steps, args.warmup, clocks,
-                           0, extra, h2d, 4)
         print(json.dumps(line), flush=True)
     if dist.is_initialized():
         dist.barrier()
@@ -361,6 +479,12 @@ def main():
     ap.add_argument("--ref-compile", dest="ref_compile", choices=["both", "on", "off"], default="both")
     ap.add_argument("--bucket_mb", type=float, default=4.0)
     ap.add_argument("--comm", choices=["auto", "symm", "nccl"], default="auto")
+    ap.add_argument("--min-seconds", dest="min_seconds", type=float, default=1.0,
+                    help="repeat the K-step timed block until this much device time has been measured (median reported)")
+    ap.add_argument("--no-recipes", dest="no_recipes", action="store_true",
+                    help="N > 1: skip the FSDP-1.3B / pipeline / pipeline x DDP recipes after the headline run")
+    ap.add_argument("--recipes", default="all", help="comma list out of fsdp,pipe (pipe covers pipe and pipe_ddp)")
+    ap.add_argument("--no-selfcheck", dest="no_selfcheck", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank, _, n = world()

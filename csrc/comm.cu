@@ -235,6 +235,8 @@ rs_adamw_kernel(const CommCtx c, int64_t shard_off, int64_t shard_n, float scale
           mp[j] = a.beta1 * mp[j] + (1.0f - a.beta1) * gj;
           vp[j] = a.beta2 * vp[j] + (1.0f - a.beta2) * gj * gj;
           pp[j] -= step_size * mp[j] / (sqrtf(vp[j]) * bc2_rsqrt + a.eps);
+        } else {
+          atomicAdd(const_cast<float*>(a.hyper) + 2, 1.0f);   // skipped element, see adamw_kernel
         }
       }
       reinterpret_cast<float4*>(a.p)[i] = pv;

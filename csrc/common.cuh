@@ -74,6 +74,23 @@ __device__ __forceinline__ float fast_exp2(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// GELU and its derivative, erf form (F.gelu default, act code 2) or tanh form (approximate="tanh", act code 3)
+__device__ __forceinline__ float gelu_fwd(float x, int act) {
+  if (act == 3) {
+    const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
+    return 0.5f * x * (1.0f + tanhf(u));
+  }
+  return 0.5f * x * (1.0f + erff(x * 0.7071067811865476f));
+}
+__device__ __forceinline__ float gelu_grad(float x, int act) {
+  if (act == 3) {
+    const float x2 = x * x;
+    const float t = tanhf(0.7978845608028654f * (x + 0.044715f * x * x2));
+    return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * 0.7978845608028654f * (1.0f + 0.134145f * x2);
+  }
+  return 0.5f * (1.0f + erff(x * 0.7071067811865476f)) + x * 0.3989422804014327f * __expf(-0.5f * x * x);
+}
+
 // LM head (b200_lmhead_gemm_bf16 / b200_lmhead_finish): the softmax of a logits row is evaluated
 // relative to a shift that is known before the GEMM runs, so the row needs no second pass.
 // |x . w| <= |x| |w|: with U = xnorm * wmax (+ rounding slack) every logit of the row is <= U.  `gap` is

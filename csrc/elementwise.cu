@@ -436,12 +436,17 @@ adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restri
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const float gj = gp[j];
-      if (isfinite(gj)) {  // GradScaler-style skip of non-finite gradients, without a host sync
+      if (isfinite(gj)) {
         pp[j] *= decay;
         mp[j] = beta1 * mp[j] + (1.0f - beta1) * gj;
         vp[j] = beta2 * vp[j] + (1.0f - beta2) * gj * gj;
         const float denom = sqrtf(vp[j]) * bc2_rsqrt + eps;
         pp[j] -= step_size * mp[j] / denom;
+      } else {
+        // A non-finite gradient element leaves its parameter and moments untouched and is counted in hyper[2].
+        // Deliberate deviation from the reference's GradScaler (main-single.py:99-101), which drops the WHOLE
+        // step on any inf/nan after a host round trip: here the finite elements still update, nothing syncs.
+        atomicAdd(const_cast<float*>(hyper) + 2, 1.0f);
       }
     }
     reinterpret_cast<float4*>(p)[i] = pv;
@@ -454,6 +459,7 @@ adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restri
   for (int64_t i = (nvec << 2) + blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
        i += stride) {
     const float gj = g[i];
+    if (!isfinite(gj)) atomicAdd(const_cast<float*>(hyper) + 2, 1.0f);
     if (isfinite(gj)) {
       float pj = p[i] * decay;
       const float mj = beta1 * m[i] + (1.0f - beta1) * gj;
@@ -488,7 +494,8 @@ template <bool DY_FP32>
 __global__ void __launch_bounds__(256)
 relu_bwd_kernel(const void* __restrict__ dy_, const bf16* __restrict__ y_act, bf16* __restrict__ dz,
                 float* __restrict__ dbias, int rows, int cols, int ld, float* __restrict__ scratch,
-                int* __restrict__ counter) {
+                int* __restrict__ counter, int act = 1) {
+  // act 1: y_act is the ReLU output (mask = y > 0); act 2 / 3: y_act is the GELU pre-activation (factor gelu'(z))
   const int cg = blockIdx.x * 32 + threadIdx.x;  // column group (8 columns)
   const int col = cg * 8;
   const bool col_ok = col < cols;
@@ -516,8 +523,13 @@ relu_bwd_kernel(const void* __restrict__ dy_, const bf16* __restrict__ y_act, bf
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
           const float2 f = unpack_bf16x2(w[t]);
-          if (!(f.x > 0.f)) v[2 * t] = 0.f;
-          if (!(f.y > 0.f)) v[2 * t + 1] = 0.f;
+          if (act >= 2) {
+            v[2 * t] *= gelu_grad(f.x, act);
+            v[2 * t + 1] *= gelu_grad(f.y, act);
+          } else {
+            if (!(f.x > 0.f)) v[2 * t] = 0.f;
+            if (!(f.y > 0.f)) v[2 * t + 1] = 0.f;
+          }
         }
       }
       if (dz != nullptr)
@@ -1048,6 +1060,27 @@ int b200_relu_bwd(const void* dy, const void* y_act, void* dz, float* dbias, int
     relu_bwd_kernel<false><<<grid, block, 0, st>>>(dy, reinterpret_cast<const bf16*>(y_act),
                                                    reinterpret_cast<bf16*>(dz), dbias, rows, cols, cols, scratch,
                                                    counter);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// dz = dy * act'(.) as bf16, dbias += column sums of dz: act 1 = ReLU (y_or_z = activated output), 2 / 3 = GELU erf /
+// tanh form (y_or_z = pre-activation).  b200_relu_bwd is the act = 1 case.  (reference models/gpt.py:14-15,35,38)
+int b200_act_bwd(const void* dy, const void* y_or_z, void* dz, float* dbias, int rows, int cols, int dy_fp32, int act,
+                 float* scratch, int* counter, void* stream) {
+  B200_REQUIRE(cols % 8 == 0, "act_bwd: cols %d must be a multiple of 8", cols);
+  B200_REQUIRE(act >= 1 && act <= 3, "act_bwd: activation %d not supported (1 relu, 2 gelu, 3 gelu-tanh)", act);
+  B200_REQUIRE(dbias == nullptr || (scratch != nullptr && counter != nullptr),
+               "act_bwd: bias gradient needs scratch (16 x cols floats) and a counter");
+  if (rows == 0) return 0;
+  dim3 grid(ceil_div(cols / 8, 32), ceil_div(rows, RELU_ROWS)), block(32, 8);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dy_fp32)
+    relu_bwd_kernel<true><<<grid, block, 0, st>>>(dy, reinterpret_cast<const bf16*>(y_or_z), reinterpret_cast<bf16*>(dz),
+                                                  dbias, rows, cols, cols, scratch, counter, act);
+  else
+    relu_bwd_kernel<false><<<grid, block, 0, st>>>(dy, reinterpret_cast<const bf16*>(y_or_z), reinterpret_cast<bf16*>(dz),
+                                                   dbias, rows, cols, cols, scratch, counter, act);
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -116,7 +116,7 @@ __device__ __forceinline__ long long global_ns() {
   } while (0)
 
 enum : int { EPI_BIAS = 1, EPI_RELU = 2, EPI_AUX = 4, EPI_MASK = 8, EPI_RES = 16, EPI_F32 = 32, EPI_ACC = 64,
-             EPI_CSUM = 128, EPI_SMAX = 256, EPI_NOSTORE = 512, EPI_RSCALE = 1024 };
+             EPI_CSUM = 128, EPI_SMAX = 256, EPI_NOSTORE = 512, EPI_RSCALE = 1024, EPI_GELU = 2048 };
 
 // CG = 1: one CTA per 128 x BN tile (tcgen05 cta_group::1).
 // CG = 2: a CTA pair (cluster of 2 = the two SMs of a TPC) per 256 x BN tile (cta_group::2): each CTA
@@ -371,7 +371,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     constexpr bool E_BIAS = (EPI & EPI_BIAS) != 0, E_RELU = (EPI & EPI_RELU) != 0, E_AUX = (EPI & EPI_AUX) != 0,
                    E_MASK = (EPI & EPI_MASK) != 0, E_RES = (EPI & EPI_RES) != 0, E_F32 = (EPI & EPI_F32) != 0,
                    E_ACC = (EPI & EPI_ACC) != 0, E_CSUM = (EPI & EPI_CSUM) != 0, E_SMAX = (EPI & EPI_SMAX) != 0,
-                   E_NOSTORE = (EPI & EPI_NOSTORE) != 0, E_RSCALE = (EPI & EPI_RSCALE) != 0;
+                   E_NOSTORE = (EPI & EPI_NOSTORE) != 0, E_RSCALE = (EPI & EPI_RSCALE) != 0,
+                   E_GELU = (EPI & EPI_GELU) != 0;
     constexpr float kLog2e = 1.4426950408889634f;
     const int q = warp_idx & 3;  // TMEM lane quarter this warp may access
     const int ew = warp_idx - 2;  // epilogue warp index
@@ -477,11 +478,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += __shfl_sync(0xffffffffu, biasv, j);
         }
-        if constexpr (E_RELU) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
-        }
-        if constexpr (E_AUX) {
+        auto store_aux = [&]() {
           if (row_ok && col0 < p.N) {
             bf16* dst = p.aux_out + static_cast<size_t>(row) * p.ldc + col0;
 #pragma unroll
@@ -490,7 +487,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                   make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
                              pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
           }
+        };
+        if constexpr (E_RELU) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
         }
+        if constexpr (E_GELU && !E_MASK) {
+          if constexpr (E_AUX) store_aux();   // GELU: the backward pass needs the pre-activation
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = gelu_fwd(v[j], p.act);
+        }
+        if constexpr (E_AUX && !(E_GELU && !E_MASK)) store_aux();   // ReLU: copy of the activated output (its own mask)
         if constexpr (E_MASK) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -498,8 +505,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
             for (int t = 0; t < 4; ++t) {
               const float2 f = unpack_bf16x2(w[t]);
-              if (!(f.x > 0.0f)) v[8 * j + 2 * t] = 0.0f;
-              if (!(f.y > 0.0f)) v[8 * j + 2 * t + 1] = 0.0f;
+              if constexpr (E_GELU) {   // mask_src holds the pre-activation: multiply by gelu'(z)
+                v[8 * j + 2 * t] *= gelu_grad(f.x, p.act);
+                v[8 * j + 2 * t + 1] *= gelu_grad(f.y, p.act);
+              } else {
+                if (!(f.x > 0.0f)) v[8 * j + 2 * t] = 0.0f;
+                if (!(f.y > 0.0f)) v[8 * j + 2 * t + 1] = 0.0f;
+              }
             }
           }
         }
@@ -775,6 +787,12 @@ int launch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
     B200_EPI_CASE(EPI_SMAX)                                            // LM head: exp(logit - shift) + row statistics
     B200_EPI_CASE(EPI_SMAX | EPI_NOSTORE)                              // ... statistics only (evaluation)
     B200_EPI_CASE(EPI_RSCALE)                                          // per-row scale (LM head dX)
+    B200_EPI_CASE(EPI_BIAS | EPI_GELU)                                 // GELU MLP up (inference)
+    B200_EPI_CASE(EPI_BIAS | EPI_GELU | EPI_AUX)                       // GELU MLP up (training: + pre-activation)
+    B200_EPI_CASE(EPI_F32 | EPI_BIAS | EPI_GELU | EPI_RES)             // GELU MLP down + residual (inference)
+    B200_EPI_CASE(EPI_F32 | EPI_BIAS | EPI_GELU | EPI_AUX | EPI_RES)   // GELU MLP down + residual (training)
+    B200_EPI_CASE(EPI_MASK | EPI_GELU)                                 // dgrad times gelu'(pre-activation)
+    B200_EPI_CASE(EPI_MASK | EPI_GELU | EPI_CSUM)                      // ... and the bias gradient
 #undef B200_EPI_CASE
     default:
       return b200_set_error(-1, "gemm: epilogue combination 0x%x is not instantiated", epi);
@@ -788,7 +806,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
               const EpiExtra* ex = nullptr) {
   B200_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
   B200_REQUIRE(!accumulate || out_fp32, "gemm: accumulate needs an fp32 output");
-  B200_REQUIRE(act == 0 || act == 1, "gemm: activation %d not supported (0 none, 1 relu)", act);
+  B200_REQUIRE(act >= 0 && act <= 3, "gemm: activation %d not supported (0 none, 1 relu, 2 gelu, 3 gelu-tanh)", act);
 
   int bn = (cfg & 0x3ff);
   if (ov && ov->force_bn > 0) bn = ov->force_bn;
@@ -812,6 +830,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   int splits = 1;
   const bool plain = (bias == nullptr && residual == nullptr && act == 0 && aux_out == nullptr &&
                       mask_src == nullptr);
+  B200_REQUIRE(mask_src == nullptr || act != 1, "gemm: a mask epilogue takes act 0 (ReLU mask) or 2 / 3 (GELU derivative)");
   const int slots = sms * ((bn == 128) ? 2 : 1) / cg;
   if (accumulate && out_fp32 && plain && tiles < slots) {
     splits = slots / tiles;
@@ -912,7 +931,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
   const int cap = sms * ctas_per_sm / cg;
   const int grid = (total < cap ? total : cap) * cg;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int epi = (bias ? EPI_BIAS : 0) | (act == 1 ? EPI_RELU : 0) | (aux_out ? EPI_AUX : 0) |
+  const int epi = (bias ? EPI_BIAS : 0) | (act == 1 ? EPI_RELU : 0) | (act >= 2 ? EPI_GELU : 0) | (aux_out ? EPI_AUX : 0) |
                   (mask_src ? EPI_MASK : 0) | (residual ? EPI_RES : 0) | (out_fp32 ? EPI_F32 : 0) |
                   (accumulate ? EPI_ACC : 0) | (colsum ? EPI_CSUM : 0) | ((ex && ex->smax) ? EPI_SMAX : 0) |
                   (nostore ? EPI_NOSTORE : 0) | ((ex && ex->rscale) ? EPI_RSCALE : 0);
@@ -983,6 +1002,16 @@ int b200_gemm_rowscale_bf16(const void* A, const void* B, void* C, int M, int N,
   EpiExtra ex{row_scale, nullptr, nullptr, nullptr, nullptr, 0, 0, 1, nullptr, 0};
   return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, 0, b_mn_major, nullptr, nullptr, 0, 0, 0, 0, nullptr, nullptr, cfg,
                    nullptr, stream, nullptr, nullptr, &ex);
+}
+
+// Same with the activation selectable: act 0 / 1 = ReLU (mask_src = activated output), 2 / 3 = GELU erf / tanh form
+// (mask_src = pre-activation, the product is taken with gelu'(mask_src)).  Reference models/gpt.py:14-15 takes any
+// activation callable; F.gelu is the other one this library fuses.
+int b200_gemm_dact_colsum_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                               int b_mn_major, const void* mask_src, float* colsum, int act, int cfg, void* stream) {
+  B200_REQUIRE(mask_src != nullptr, "gemm_dact_colsum: mask_src is required");
+  return gemm_impl(A, B, C, M, N, K, lda, ldb, ldc, 0, b_mn_major, nullptr, nullptr, 0, act >= 2 ? act : 0, 0, 0, nullptr,
+                   mask_src, cfg, nullptr, stream, nullptr, colsum);
 }
 
 int b200_gemm_set_debug_buffer(void* buf) {

@@ -33,10 +33,19 @@ from .. import ops
 
 
 def _act_name(fn: Callable) -> Optional[str]:
-    if fn is F.relu or fn is torch.relu:
+    """Name of an activation the native MLP kernels fuse (ReLU, GELU in its erf and tanh forms); ``None`` for any
+    other callable, which then runs through PyTorch (reference gpt.py:14-15 accepts any callable)."""
+    import functools
+    if fn is F.relu or fn is torch.relu or isinstance(fn, nn.ReLU):
         return "relu"
     if fn is F.gelu:
         return "gelu"
+    if isinstance(fn, nn.GELU):
+        return "gelu_tanh" if fn.approximate == "tanh" else "gelu"
+    if isinstance(fn, functools.partial) and fn.func is F.gelu and not fn.args:
+        appr = fn.keywords.get("approximate", "none")
+        if set(fn.keywords) <= {"approximate"}:
+            return "gelu_tanh" if appr == "tanh" else "gelu"
     return None
 
 
@@ -62,9 +71,9 @@ class FeedForward(nn.Module):
 
     def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
         act = _act_name(self.activation)
-        if ops.use_native(x) and act == "relu" and self.bias and self.dropout.p == 0.0:
+        if ops.use_native(x) and act is not None and self.bias and self.dropout.p == 0.0:
             return ops.mlp(x, self.up_proj.weight, self.up_proj.bias, self.down_proj.weight, self.down_proj.bias,
-                           residual=residual)
+                           residual=residual, activation=act)
         if ops.use_native(x) and act == "relu" and self.dropout.p == 0.0:
             h = ops.linear(x, self.up_proj.weight, self.up_proj.bias, activation=act)
             return ops.linear(h, self.down_proj.weight, self.down_proj.bias, activation=act,

@@ -107,9 +107,9 @@ def linear(x, weight, bias=None, activation: Optional[str] = None, residual=None
     return native.linear(x, weight, bias, activation, residual, out_fp32)
 
 
-def mlp(x, w1, b1, w2, b2, residual=None):
+def mlp(x, w1, b1, w2, b2, residual=None, activation: str = "relu"):
     from . import native
-    return native.mlp(x, w1, b1, w2, b2, residual)
+    return native.mlp(x, w1, b1, w2, b2, residual, activation)
 
 
 def linear_qkv(x, wq, wk, wv):

@@ -33,6 +33,8 @@ _SIGS = {
     "b200_adamw_tick": [P, P],
     "b200_cast_bf16": [P, P, L, P],
     "b200_relu_bwd": [P, P, P, P, I, I, I, P, P, P],
+    "b200_act_bwd": [P, P, P, P, I, I, I, I, P, P, P],
+    "b200_gemm_dact_colsum_bf16": [P, P, P, I, I, I, I, I, I, I, P, P, I, I, P],
     "b200_colsum_bf16": [P, P, I, I, I, P, P, P],
     "b200_relu_bwd_static": [P, P, P, P, I, I, I, P],
     "b200_count_valid": [P, P, I, L, P],

@@ -136,7 +136,7 @@ def fused_gather_args(weights):
     if info is None:
         return None
     eng, grp, off0, _ = info
-    if not eng.fused_ag or all(getattr(w, "_b200_ag_version", -1) == eng.version for w in weights):
+    if not eng.fused_ag or not grp.fused or all(getattr(w, "_b200_ag_version", -1) == eng.version for w in weights):
         return None
     last = weights[-1]._b200_ag
     end = last[2] + last[3]
@@ -212,36 +212,48 @@ def linear(x, weight, bias=None, activation: Optional[str] = None, residual=None
 
 
 # ----------------------------------------------------------------------------------------
-class _MLP(torch.autograd.Function):
-    """relu(relu(x W1^T + b1) W2^T + b2) [+ residual] as one autograd node (reference gpt.py:33-41).
+ACT_CODES = {"relu": 1, "gelu": 2, "gelu_tanh": 3}
 
-    Forward is two epilogue-fused GEMMs.  Backward fuses the first ReLU's mask into the dgrad GEMM
-    that produces its input gradient (``mask_src`` epilogue: dZ1 = (dZ2 W2) * (u > 0)) together with
-    the bias gradient db1 (column sums by a warp butterfly in the same epilogue), so the
-    [tokens, 4*dim] activation gradient is written once, already masked, and never re-read.
+
+class _MLP(torch.autograd.Function):
+    """act(act(x W1^T + b1) W2^T + b2) [+ residual] as one autograd node (reference gpt.py:33-41; the
+    activation is a constructor argument there, :14-15 - ReLU, GELU erf form and GELU tanh form are fused).
+
+    Forward is two epilogue-fused GEMMs.  Backward fuses the first activation's derivative into the dgrad
+    GEMM that produces its input gradient (``mask_src`` epilogue: dZ1 = (dZ2 W2) * act'(.)) together with
+    the bias gradient db1 (column sums by a warp butterfly in the same epilogue), so the [tokens, 4*dim]
+    activation gradient is written once, already masked, and never re-read.  ReLU's derivative is read off
+    the activated output; GELU's needs the pre-activation, which the forward GEMM then stores next to its
+    output (``aux_out``).
     """
 
     @staticmethod
-    def forward(ctx, x, w1, b1, w2, b2, residual, params, grad_on):
+    def forward(ctx, x, w1, b1, w2, b2, residual, params, grad_on, act):
         lead = x.shape[:-1]
         x2 = _as_bf16_2d(x)
         M, K = x2.shape
         w1b, w2b = bf16_of(w1), bf16_of(w2)
         F1, N = w1b.shape[0], w2b.shape[0]
+        gelu = act >= 2
         u = torch.empty((M, F1), dtype=BF16, device=x.device)
-        gemm(x2, w1b, u, M, F1, K, bias=b1, act=1, ag=fused_gather_args([w1]))
+        z1 = torch.empty((M, F1), dtype=BF16, device=x.device) if (gelu and grad_on) else None
+        gemm(x2, w1b, u, M, F1, K, bias=b1, act=act, aux_out=z1, ag=fused_gather_args([w1]))
         res2 = residual.reshape(M, N) if residual is not None else None
         out = torch.empty((M, N), dtype=torch.float32 if residual is not None else BF16, device=x.device)
-        aux = torch.empty((M, N), dtype=BF16, device=x.device) if (residual is not None and grad_on) else None
-        gemm(u, w2b, out, M, N, F1, bias=b2, residual=res2, act=1, aux_out=aux, ag=fused_gather_args([w2]))
-        ctx.params, ctx.has_res, ctx.in_dtype = params, residual is not None, x.dtype
-        ctx.save_for_backward(x2, w1b, w2b, u, aux if aux is not None else out)
+        # second activation's backward operand: ReLU -> the activated output itself (bf16 copy when the output is the
+        # fp32 residual sum), GELU -> the pre-activation
+        need_aux = grad_on and (residual is not None or gelu)
+        aux = torch.empty((M, N), dtype=BF16, device=x.device) if need_aux else None
+        gemm(u, w2b, out, M, N, F1, bias=b2, residual=res2, act=act, aux_out=aux, ag=fused_gather_args([w2]))
+        ctx.params, ctx.has_res, ctx.in_dtype, ctx.act = params, residual is not None, x.dtype, act
+        ctx.save_for_backward(x2, w1b, w2b, u, aux if aux is not None else out, z1)
         return out.view(*lead, N)
 
     @staticmethod
     def backward(ctx, dy):
-        x2, w1b, w2b, u, y_act = ctx.saved_tensors
+        x2, w1b, w2b, u, y_act, z1 = ctx.saved_tensors
         w1, b1, w2, b2 = ctx.params
+        act = ctx.act
         M, K = x2.shape
         F1, N = w1b.shape[0], w2b.shape[0]
         dy2 = dy.reshape(M, N)
@@ -249,13 +261,13 @@ class _MLP(torch.autograd.Function):
             dy2 = dy2.contiguous()
         sc, cnt = colsum_scratch(dy.device)
         dz2 = torch.empty((M, N), dtype=BF16, device=dy.device)
-        call("b200_relu_bwd", dy2.data_ptr(), y_act.data_ptr(), dz2.data_ptr(), grad_of(b2).data_ptr(), M, N,
-             int(dy2.dtype == torch.float32), sc.data_ptr(), cnt.data_ptr(), stream())
+        call("b200_act_bwd", dy2.data_ptr(), y_act.data_ptr(), dz2.data_ptr(), grad_of(b2).data_ptr(), M, N,
+             int(dy2.dtype == torch.float32), act, sc.data_ptr(), cnt.data_ptr(), stream())
         gemm(dz2, u, grad_of(w2), N, F1, M, a_mn_major=True, b_mn_major=True, accumulate=True)     # dW2 += dZ2^T u
         dz1 = torch.empty((M, F1), dtype=BF16, device=dy.device)
-        # dZ1 = (dZ2 W2) * (u > 0), with db1 += column sums of dZ1 folded into the same epilogue
-        call("b200_gemm_mask_colsum_bf16", dz2.data_ptr(), w2b.data_ptr(), dz1.data_ptr(), M, F1, N, dz2.stride(0),
-             w2b.stride(0), dz1.stride(0), 1, u.data_ptr(), grad_of(b1).data_ptr(), 0, stream())
+        # dZ1 = (dZ2 W2) * act'(.), with db1 += column sums of dZ1 folded into the same epilogue
+        call("b200_gemm_dact_colsum_bf16", dz2.data_ptr(), w2b.data_ptr(), dz1.data_ptr(), M, F1, N, dz2.stride(0),
+             w2b.stride(0), dz1.stride(0), 1, (z1 if act >= 2 else u).data_ptr(), grad_of(b1).data_ptr(), act, 0, stream())
         gemm(dz1, x2, grad_of(w1), F1, K, M, a_mn_major=True, b_mn_major=True, accumulate=True)    # dW1 += dZ1^T x
         dx = None
         if ctx.needs_input_grad[0]:
@@ -265,11 +277,11 @@ class _MLP(torch.autograd.Function):
             if ctx.in_dtype != BF16:
                 dx = dx.to(ctx.in_dtype)
         _notify(w2, b2, w1, b1)
-        return dx, None, None, None, None, (dy if ctx.has_res else None), None, None
+        return dx, None, None, None, None, (dy if ctx.has_res else None), None, None, None
 
 
-def mlp(x, w1, b1, w2, b2, residual=None):
-    return _MLP.apply(x, w1, b1, w2, b2, residual, (w1, b1, w2, b2), torch.is_grad_enabled())
+def mlp(x, w1, b1, w2, b2, residual=None, activation: str = "relu"):
+    return _MLP.apply(x, w1, b1, w2, b2, residual, (w1, b1, w2, b2), torch.is_grad_enabled(), ACT_CODES[activation])
 
 
 # ----------------------------------------------------------------------------------------

@@ -5,8 +5,13 @@ Reference: ``torch.optim.AdamW(model.parameters(), lr)`` (main-single.py:42) => 
 GradScaler (main-single.py:78,99-101) that for bf16 only adds an unscale pass, an inf check
 and a host sync per step.  Here ONE kernel launch (``b200_adamw``, csrc/elementwise.cu)
 updates all parameters, writes the bf16 compute copies in the same pass, reads lr/step from
-device memory (so it replays inside a CUDA graph) and skips the update when the gradient
-is non-finite (the GradScaler's only useful effect) without a host round trip.
+device memory (so it replays inside a CUDA graph).  Non-finite gradients: the reference's GradScaler
+skips the *whole* optimizer step when any gradient element is inf/nan, at the price of a host sync per
+step; this kernel skips *per element* - that parameter and its moments keep their values, every finite
+element still updates, the step counter still advances - and counts the skipped elements in
+``hyper[2]`` (``skipped_elements()``), with no host round trip.  A deliberate deviation: under bf16
+autocast (no loss scaling needed) non-finite gradients mean the run is already in trouble, and the
+counter makes that visible without stalling every healthy step.
 On CPU (or when the library is absent) the same maths runs through ``torch.optim.AdamW``.
 """
 from __future__ import annotations
@@ -29,7 +34,7 @@ class FusedAdamW:
         self.native = device.type == "cuda" and _lib.available()
         if self.native:
             self.arena = arena if arena is not None else ParamArena(self.params, device, grad_alloc=grad_alloc)
-            # hyper[0] = lr, hyper[1] = step (float, exact up to 2^24 steps), hyper[2] = skipped steps
+            # hyper[0] = lr, hyper[1] = step (float, exact up to 2^24 steps), hyper[2] = gradient elements skipped so far
             self.hyper = torch.tensor([lr, 0.0, 0.0, 0.0], dtype=torch.float32, device=device)
             self.torch_opt = None
         else:
@@ -68,6 +73,10 @@ class FusedAdamW:
                   a.bf16.data_ptr() + 2 * lo, hi - lo, self.hyper.data_ptr(),
                   self.betas[0], self.betas[1], self.eps, self.weight_decay, s)
 
+    def skipped_elements(self) -> int:
+        """Gradient elements the kernel has skipped as non-finite since the start (host sync)."""
+        return int(self.hyper[2]) if self.native else 0
+
     def state_dict(self):
         if self.native:
             a = self.arena
@@ -76,12 +85,16 @@ class FusedAdamW:
         return {"native": False, "torch": self.torch_opt.state_dict()}
 
     def load_state_dict(self, sd):
+        """Moments and step counter come from ``sd``; the learning rate stays the one this run was started with."""
         if self.native and sd.get("native"):
             self.hyper.copy_(sd["hyper"])
+            self.hyper[0] = self.lr
             self.arena.exp_avg.copy_(sd["exp_avg"])
             self.arena.exp_avg_sq.copy_(sd["exp_avg_sq"])
         elif not self.native and not sd.get("native"):
             self.torch_opt.load_state_dict(sd["torch"])
+            for g in self.torch_opt.param_groups:
+                g["lr"] = self.lr
         else:
             raise ValueError("optimizer state was saved by the other back-end")
 

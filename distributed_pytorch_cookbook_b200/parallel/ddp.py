@@ -77,6 +77,10 @@ class GradReducer:
         for p in arena.params:
             p.register_post_accumulate_grad_hook(self.on_grad_ready)
 
+    def close(self):
+        if self.on_grad_ready in native.grad_ready_hooks:
+            native.grad_ready_hooks.remove(self.on_grad_ready)
+
     # ------------------------------------------------------------------------------
     def begin(self):
         self.remaining = [len(idxs) for _, _, idxs in self.buckets]
@@ -241,13 +245,22 @@ class DDPStrategy:
         return nullcontext()
 
     def _raw_step(self, input_ids, position_ids, targets, mask, amp):
+        from ..utils import nvtx
         self.optim.zero_grad()
         self.reducer.begin()
-        with self._autocast(amp):
+        with self._autocast(amp), nvtx.phase("forward"):
             loss, _, _ = self.model.loss(input_ids, position_ids, targets, mask=mask)
-        loss.backward()
-        self.reducer.finish(self.optim)       # joins communication and runs the (ranged) optimizer step
+        with nvtx.phase("backward + bucket all-reduce"):
+            loss.backward()
+        with nvtx.phase("grad-sync tail + optimizer"):
+            self.reducer.finish(self.optim)       # joins communication and runs the (ranged) optimizer step
         return loss.detach()
+
+    def optimizer_state(self):
+        return self.optim.state_dict()
+
+    def load_optimizer_state(self, sd):
+        self.optim.load_state_dict(sd)
 
     def train_step(self, batch, targets, amp=True):
         if self.use_graph and amp:
@@ -274,6 +287,10 @@ class DDPStrategy:
 
     def generation_model(self):
         return self.model
+
+    def close(self):
+        self.reducer.close()
+        self._graphed = None
 
     def state_dict(self):
         from ..utils import canonical_state_dict

@@ -231,6 +231,7 @@ class FSDPStrategy:
             g.gathered_version = 0
             g.event = None
         self.active = False
+        self.skip_comm = False
         # forward pre-hooks: make the unit's weights resident (and prefetch the next unit)
         for ui, mods in enumerate(plan_units(self.model)):
             mods[0].register_forward_pre_hook(lambda m, inp, ui=ui: self._pre_forward(ui))
@@ -254,6 +255,8 @@ class FSDPStrategy:
         shard_view = shard[g.shard_base:g.shard_base + g.shard_n]
         if self.world == 1:
             full_view.copy_(shard_view)
+            return
+        if self.skip_comm:                                # measurement only: no traffic, the weights go stale
             return
         cuda = self.device.type == "cuda"
         ctx = nullcontext()
@@ -320,6 +323,12 @@ class FSDPStrategy:
             self.comm_stream.wait_event(ev)
             ctx = torch.cuda.stream(self.comm_stream)
         with ctx:
+            if self.skip_comm:                            # measurement only: AdamW on the shard's local gradients
+                pb = self.shard_bf16.data_ptr() + 2 * sb if g.kind == "big" else None
+                _lib.call("b200_adamw", self.master.data_ptr() + 4 * sb, self.grads.data_ptr() + 4 * lo,
+                          self.exp_avg.data_ptr() + 4 * sb, self.exp_avg_sq.data_ptr() + 4 * sb, pb, sn,
+                          self.hyper.data_ptr(), b1, b2, self.eps, self.wd, self.comm_stream.cuda_stream)
+                return
             if self.comm_kind == "symm" and self.rs_split:
                 # reduce-scatter on a small grid (the switch adds; <= 16 blocks leave the SMs to the compute
                 # kernels), then AdamW on the reduced shard as an ordinary kernel behind it
@@ -381,15 +390,17 @@ class FSDPStrategy:
         for g in self.groups:
             g.ready = 0
         self.active = True
-        with self._autocast(amp):
+        from ..utils import nvtx
+        with self._autocast(amp), nvtx.phase("forward (+ all-gather)"):
             loss, _, _ = self.model.loss(input_ids, position_ids, targets, mask=mask)
-        loss.backward()
+        with nvtx.phase("backward (+ reduce-scatter + AdamW)"):
+            loss.backward()
         for g in self.groups:                              # parameters that received no gradient
             if g.ready >= 0:
                 self._reduce_and_step(g)
         self.active = False
         if self.device.type == "cuda":
-            if self.rs_split and self.fused_ag:
+            if self.rs_split and self.fused_ag and not self.skip_comm:
                 # the next step's GEMMs pull the peers' bf16 shards without a barrier of their own: every rank's
                 # AdamW kernels (queued on the side stream above) must have finished first
                 with torch.cuda.stream(self.comm_stream):
@@ -422,6 +433,38 @@ class FSDPStrategy:
     def launches_per_step(self):
         return self._graphed.native_calls_per_replay if (self._graphed and self._graphed.graph) else None
 
+    def set_skip_comm(self, on: bool):
+        """Measurement aid (bench: exposed communication): run the same step with every collective left out -
+        no gathers (weights go stale), AdamW on the local gradients of the own shard, plain CTA-pair GEMMs.
+        Symmetric-memory transport on CUDA only; the captured graph is dropped and re-captured."""
+        assert self.comm_kind == "symm", "skip_comm is a measurement aid of the symmetric-memory transport"
+        self.skip_comm = on
+        for g in self.groups:
+            if hasattr(g, "peers_dev"):
+                g.fused = self.fused_ag and not on
+        self._graphed = None
+
+    def optimizer_state(self):
+        """This rank's shard of the optimizer state (fp32 master shard, moments, step)."""
+        return {"fsdp": True, "world": self.world, "rank": self.rank, "hyper": self.hyper.cpu(),
+                "host_step": self.host_step, "master": self.master.detach().cpu().clone(),
+                "exp_avg": self.exp_avg.detach().cpu().clone(), "exp_avg_sq": self.exp_avg_sq.detach().cpu().clone()}
+
+    def load_optimizer_state(self, sd):
+        if not sd.get("fsdp") or sd["world"] != self.world or sd["rank"] != self.rank:
+            raise ValueError("FSDP optimizer state belongs to a different rank / world size")
+        self.hyper.copy_(sd["hyper"])
+        self.hyper[0] = self.lr
+        self.host_step = int(sd["host_step"])
+        self.exp_avg.copy_(sd["exp_avg"])
+        self.exp_avg_sq.copy_(sd["exp_avg_sq"])
+
+    def close(self):
+        """Detach from the process-wide gradient-ready hook list (benchmarks run several strategies in one process)."""
+        if self._on_grad_ready in native.grad_ready_hooks:
+            native.grad_ready_hooks.remove(self._on_grad_ready)
+        self._graphed = None
+
     # ------------------------------------------------------------------------------
     def gather_full_fp32(self):
         """Collective: bring every fp32 master shard into ``param.data`` (full model on every rank) -
@@ -431,6 +474,11 @@ class FSDPStrategy:
         for g in self.groups:
             self._gather(g, torch.float32)
             if self._gather_dtype(g) == torch.float32:
+                g.gathered_version = self.version
+            elif not g.fused:
+                # the bf16 copy too: a forward that only some ranks run afterwards (rank-0 generation) must not
+                # find a stale group and start a collective gather on its own
+                self._gather(g)
                 g.gathered_version = self.version
         if self.device.type == "cuda":
             torch.cuda.current_stream().wait_stream(self.comm_stream)

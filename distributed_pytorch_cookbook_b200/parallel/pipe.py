@@ -319,6 +319,18 @@ class PipeStrategy:
     def all_reduce_mean(self, t):
         return t                                   # eval_step already returned group-wide values
 
+    def close(self):
+        if self.reducer is not None:
+            self.reducer.close()
+
+    static_batches = True      # micro-batches travel between stages in fixed-shape buffers
+
+    def optimizer_state(self):
+        return self.optim.state_dict()
+
+    def load_optimizer_state(self, sd):
+        self.optim.load_state_dict(sd)
+
     def generation_model(self):
         return None                                # generation needs all stages; see gather_full_model()
 

@@ -26,6 +26,7 @@ from .data import (PinnedPrefetcher, ShardedSampler, SyntheticTokenDataset, Synt
 from .models import TransformerDecoderLM
 from .utils import (JsonlLogger, StepTimer, generate, load_checkpoint, prepare_batch,
                     save_checkpoint, seed_everything)
+from .utils import nvtx
 
 PRINT_FREQ = 8
 PROMPTS = ("The big brown cat ", "One day, ", "She said ")
@@ -55,7 +56,26 @@ def build_model(args, vocab_size: int) -> TransformerDecoderLM:
                                 max_position_embeddings=args.sequence_length)
 
 
-def build_data(args, rank: int = 0, world: int = 1, data_parallel: bool = False):
+def check_device_error(where: str = ""):
+    """Raise if a kernel reported a failure through the device error word (a bounded wait that timed out: a
+    cross-GPU barrier whose peer never arrived, a GEMM pipeline stage that never filled).  Such a kernel has
+    returned early - the collective or tile it stood for did not happen - so continuing would train on
+    unreduced gradients.  The condition is fatal: the caller should let the exception end the process
+    (torchrun then tears the other ranks down)."""
+    from .ops import _lib
+    if not (_lib.loaded() and torch.cuda.is_available() and _lib.has("b200_device_error")):
+        return
+    import ctypes
+    code = ctypes.c_int(0)
+    _lib.call("b200_device_error", ctypes.addressof(code), 0)
+    if code.value != 0:
+        kinds = {101: "GEMM producer wait", 102: "GEMM MMA wait", 103: "GEMM epilogue wait", 104: "GEMM smem alignment",
+                 105: "fused all-gather wait", 301: "cross-GPU signal", 302: "cross-GPU wait (a peer never arrived)"}
+        raise RuntimeError(f"device error {code.value} ({kinds.get(code.value, 'kernel-side wait timed out')}) "
+                           f"detected {where}: a kernel gave up waiting and skipped its work; aborting the run")
+
+
+def build_data(args, rank: int = 0, world: int = 1, data_parallel: bool = False, static_batches: bool = False):
     """tokenizer + train/val datasets + loaders (+ samplers when data-parallel)."""
     synthetic = getattr(args, "synthetic", False)
     if synthetic:
@@ -77,8 +97,10 @@ def build_data(args, rank: int = 0, world: int = 1, data_parallel: bool = False)
     workers = 0 if synthetic else args.num_workers
     train_loader = make_loader(train, args.batch_size, sampler=tsamp, shuffle=tsamp is None,
                                num_workers=workers, drop_last=True)
+    # the reference's validation loader keeps the last partial batch (main-single.py:65-71); only engines that move
+    # fixed-shape micro-batches between stages (pipeline) need full batches
     val_loader = make_loader(val, args.batch_size, sampler=vsamp, shuffle=False,
-                             num_workers=workers, drop_last=True)
+                             num_workers=workers, drop_last=static_batches)
     return tokenizer, train_loader, val_loader, tsamp
 
 
@@ -100,18 +122,26 @@ class Trainer:
     def run(self):
         args = self.args
         seed_everything(getattr(args, "seed", 0))
+        nvtx.enable(getattr(args, "profile", False))
+        if nvtx.enabled():
+            args.disable_cuda_graph = True      # phases are only visible when the step is not one graph launch
         tokenizer, train_loader, val_loader, tsamp = build_data(
-            args, self.rank, self.world, self.data_parallel)
+            args, self.rank, self.world, self.data_parallel,
+            static_batches=getattr(self.strategy, "static_batches", False))
         self.tokenizer = tokenizer
         model = build_model(args, tokenizer.vocab_size)
+        resume_extra = None
         if getattr(args, "resume", None):
-            load_checkpoint(model, args.resume)
+            _, resume_extra = load_checkpoint(model, args.resume, rank=self._global_rank())
         self.strategy.setup(model, args, self.device)
+        start_epoch = 0
+        if resume_extra is not None:
+            start_epoch = self._restore(resume_extra)
         amp = not args.disable_amp
         timer = StepTimer(self.device)
         tokens_per_step = args.batch_size * (args.sequence_length - 1) * (self.world if self.data_parallel else 1)
 
-        for ei in range(args.epochs):
+        for ei in range(start_epoch, args.epochs):
             if tsamp is not None:
                 tsamp.set_epoch(ei)
             pb = _tqdm(PinnedPrefetcher(train_loader, self.device), disable=not self.main)
@@ -123,11 +153,13 @@ class Trainer:
                 if getattr(args, "max_steps", 0) and i >= args.max_steps:
                     break
                 batch, targets = prepare_batch(batch, tokenizer.pad_token_id, self.device)
-                loss = self.strategy.train_step(batch, targets, amp=amp)
+                with nvtx.phase("train_step"):
+                    loss = self.strategy.train_step(batch, targets, amp=amp)
                 window.append(loss)
                 if i > 0 and not i % PRINT_FREQ:
                     ms = timer.stop_ms() / len(window)
                     mean = float(torch.stack([w.detach().float() for w in window]).mean())
+                    check_device_error(f"at epoch {ei + 1} step {i}")     # the loss read-back above already synchronised
                     pb.set_description(f"[training] Epoch {ei+1}/{args.epochs} | loss: {mean:.3f}")
                     self.metrics.log(phase="train", epoch=ei, step=i, loss=mean, ms_per_step=ms,
                                      tokens_per_s=tokens_per_step / ms * 1e3)
@@ -135,20 +167,56 @@ class Trainer:
                     timer.start()
 
             self.validate(ei, val_loader, amp=True)  # reference validates under autocast always (:119)
+            check_device_error(f"after epoch {ei + 1}")
             if not getattr(args, "no_generate", False):
                 self.sample(tokenizer)
             if dist.is_initialized():
                 dist.barrier()
+            self.epochs_done = ei + 1
 
         path = None
         if not getattr(args, "no_save", False):
             if dist.is_initialized():
                 dist.barrier()
+            check_device_error("before saving the checkpoint")
             state = self.strategy.state_dict()  # collective for FSDP / pipeline
             if self.main:
                 path = save_checkpoint(state, getattr(args, "checkpoint_dir", "checkpoints"))
+            self._save_resume_state(path)
         self.metrics.close()
         return path
+
+    # ------------------------------------------------------------------------------
+    def _global_rank(self) -> int:
+        return dist.get_rank() if dist.is_initialized() else 0
+
+    def _save_resume_state(self, path):
+        """Optimizer moments + step counter + epochs done, one ``<checkpoint>.resume.rank<r>`` per rank (FSDP
+        shards and pipeline stages own different slices of the optimizer state).  The weights file itself stays
+        the plain state_dict the reference loads."""
+        from pathlib import Path
+        if not hasattr(self.strategy, "optimizer_state"):
+            return
+        name = [str(path) if path is not None else None]
+        if dist.is_initialized():
+            dist.broadcast_object_list(name, src=0)
+        if name[0] is None:
+            return
+        extra = {"optimizer": self.strategy.optimizer_state(), "epochs_done": getattr(self, "epochs_done", 0),
+                 "world": dist.get_world_size() if dist.is_initialized() else 1}
+        torch.save(extra, Path(name[0] + f".resume.rank{self._global_rank()}"))
+
+    def _restore(self, extra) -> int:
+        world = dist.get_world_size() if dist.is_initialized() else 1
+        if extra.get("world") != world or not hasattr(self.strategy, "load_optimizer_state"):
+            if self.main:
+                print("[resume] optimizer state was saved for a different layout; continuing from the weights only",
+                      flush=True)
+            return 0
+        self.strategy.load_optimizer_state(extra["optimizer"])
+        if self.main:
+            print(f"[resume] optimizer state restored ({extra.get('epochs_done', 0)} epochs done)", flush=True)
+        return int(extra.get("epochs_done", 0)) if getattr(self.args, "resume_epochs", False) else 0
 
     # ------------------------------------------------------------------------------
     @torch.no_grad()
@@ -219,11 +287,19 @@ class SingleStrategy:
     def _raw_step(self, input_ids, position_ids, targets, mask, amp):
         ctx = torch.autocast(device_type="cuda", dtype=torch.bfloat16) if (amp and self.device.type == "cuda") else nullcontext()
         self.optim.zero_grad()
-        with ctx:
+        with ctx, nvtx.phase("forward"):
             loss, _, _ = self.model.loss(input_ids, position_ids, targets, mask=mask)
-        loss.backward()
-        self.optim.step()
+        with nvtx.phase("backward"):
+            loss.backward()
+        with nvtx.phase("optimizer"):
+            self.optim.step()
         return loss.detach()
+
+    def optimizer_state(self):
+        return self.optim.state_dict()
+
+    def load_optimizer_state(self, sd):
+        self.optim.load_state_dict(sd)
 
     def train_step(self, batch, targets, amp=True):
         if self.use_graph:

@@ -6,8 +6,10 @@ wraps the model first, its files carry ``_orig_mod.`` / ``module.`` prefixes.  W
 save the un-prefixed fp32 key set of ``TransformerDecoderLM`` so that
 ``TransformerDecoderLM(...).load_state_dict(torch.load(path))`` works in the reference,
 and our loader strips the wrapper prefixes so reference-produced files load here.
-Resume (optimizer state, step) is additive: stored beside the weights under ``"__extra__"``-free
-separate file so the weights file stays reference-loadable.
+Resume state (optimizer moments, step counter, epochs done) is additive: the Trainer writes it beside the
+weights as ``<checkpoint>.resume.rank<r>`` (one per rank - FSDP shards and pipeline stages own different
+slices), so the weights file stays reference-loadable; ``load_checkpoint`` hands the rank's file back and
+``--resume`` restores it when the world layout matches (weights only otherwise).
 """
 from __future__ import annotations
 
@@ -59,8 +61,9 @@ def save_checkpoint(state_or_model, directory="checkpoints", name: Optional[str]
     return path
 
 
-def load_checkpoint(model, path, strict: bool = True, map_location="cpu"):
-    """Load a checkpoint written by us or by any of the reference's recipes."""
+def load_checkpoint(model, path, strict: bool = True, map_location="cpu", rank: int = 0):
+    """Load a checkpoint written by us or by any of the reference's recipes.  -> (load result, resume state of
+    ``rank`` or None)."""
     state = torch.load(path, map_location=map_location, weights_only=True)
     state = strip_prefixes(state)
     m = getattr(model, "module", model)
@@ -70,6 +73,8 @@ def load_checkpoint(model, path, strict: bool = True, map_location="cpu"):
     for p in m.parameters():
         if hasattr(p, "_b200_bf16_version"):
             p._b200_bf16_version = -1
-    resume = Path(path).with_suffix(".resume.pt")
+    resume = Path(str(path) + f".resume.rank{rank}")
+    if not resume.exists():
+        resume = Path(path).with_suffix(".resume.pt")
     extra = torch.load(resume, map_location=map_location, weights_only=False) if resume.exists() else None
     return result, extra

@@ -34,13 +34,19 @@ def build_parser(recipe: str = "single") -> argparse.ArgumentParser:
     x.add_argument("--vocab_size", type=int, default=50257)
     x.add_argument("--max_steps", type=int, default=0, help="stop each epoch after N steps (0 = all)")
     x.add_argument("--seed", type=int, default=0)
-    x.add_argument("--resume", type=str, default=None, help="checkpoint to load before training")
+    x.add_argument("--resume", type=str, default=None,
+                   help="checkpoint to load before training; the optimizer state saved next to it "
+                        "(<file>.resume.rank<r>) is restored when the world layout matches")
+    x.add_argument("--resume_epochs", action="store_true",
+                   help="with --resume: also skip the epochs the checkpoint had already completed")
     x.add_argument("--checkpoint_dir", type=str, default="checkpoints")
     x.add_argument("--no_save", action="store_true")
     x.add_argument("--no_generate", action="store_true")
     x.add_argument("--metrics_jsonl", type=str, default=None)
     x.add_argument("--disable_cuda_graph", action="store_true")
-    x.add_argument("--profile", action="store_true", help="emit NVTX ranges around step phases")
+    x.add_argument("--profile", action="store_true",
+                   help="NVTX ranges around train_step / forward / backward / grad-sync / optimizer "
+                        "(runs the step eagerly instead of as one CUDA graph so the ranges bracket kernels)")
     if recipe in ("ddp", "pipe-ddp"):
         x.add_argument("--bucket_mb", type=float, default=4.0)
         x.add_argument("--comm", choices=["auto", "symm", "nccl"], default="auto",

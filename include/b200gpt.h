@@ -37,7 +37,9 @@ int b200_layernorm_bwd(const void* dy_bf16, const float* x, const float* gamma, 
                        const float* rstd, const float* dres, float* dx, void* dx_bf16, float* dgamma,
                        float* dbeta, int rows, int dim, float* scratch, int* counter, void* stream);
 
-/* fused AdamW over a flat arena; hyper = {lr, step, ..} in device memory  (main-single.py:42,99-101) */
+/* fused AdamW over a flat arena; hyper = {lr, step, skipped, -} in device memory  (main-single.py:42,99-101).
+ * Non-finite gradient elements are skipped one by one (parameter and moments keep their values) and counted in
+ * hyper[2]; the reference's GradScaler instead drops the whole step after a host sync - a deliberate deviation. */
 int b200_adamw(float* p, const float* g, float* m, float* v, void* p_bf16, int64_t n,
                const float* hyper, float beta1, float beta2, float eps, float wd, void* stream);
 int b200_adamw_tick(float* hyper, void* stream);
@@ -47,6 +49,10 @@ int b200_cast_bf16(const float* in, void* out_bf16, int64_t n, void* stream);
 /* scratch: [16][cols] floats + one int counter (same contract as b200_layernorm_bwd) */
 int b200_relu_bwd(const void* dy, const void* y_act_bf16, void* dz_bf16, float* dbias, int rows, int cols,
                   int dy_is_fp32, float* scratch, int* counter, void* stream);
+/* same with the activation selectable: act 1 ReLU (y_or_z = activated output), 2 / 3 GELU erf / tanh form
+ * (y_or_z = pre-activation)  (models/gpt.py:14-15: activation is a constructor argument) */
+int b200_act_bwd(const void* dy, const void* y_or_z_bf16, void* dz_bf16, float* dbias, int rows, int cols,
+                 int dy_is_fp32, int act, float* scratch, int* counter, void* stream);
 int b200_colsum_bf16(const void* x_bf16, float* out_accum, int rows, int cols, int ld, float* scratch,
                      int* counter, void* stream);
 /* No counterpart in the reference (an addition of this library).  Same result as b200_relu_bwd, for
@@ -99,9 +105,15 @@ int b200_gemm_rowscale_bf16(const void* A, const void* B, void* C, int M, int N,
 int b200_gemm_mask_colsum_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
                                int b_mn_major, const void* mask_src, float* colsum, int cfg, void* stream);
 
+/* same, activation selectable: act 0 / 1 ReLU mask (mask_src = activated output), 2 / 3 GELU (mask_src = pre-activation,
+ * C = (A . B) * gelu'(mask_src)); colsum may be NULL */
+int b200_gemm_dact_colsum_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                               int b_mn_major, const void* mask_src, float* colsum, int act, int cfg, void* stream);
+
 /* C[M,N] (+)= A[M,K] . B[N,K]^T on tcgen05 with a fused epilogue  (models/gpt.py:29-38,60-64,102,219)
  * a/b_mn_major: 0 = operand stored [rows][K]; 1 = stored [K][rows] (dgrad / wgrad, no transposes).
- * epilogue order: +bias -> act(1=ReLU) -> aux_out(bf16) -> *(mask_src>0) -> +residual(fp32) -> store. */
+ * epilogue order: +bias -> act (1 ReLU, 2 GELU erf form, 3 GELU tanh form) -> *(mask_src>0) -> +residual(fp32) -> store;
+ * aux_out (bf16) receives the activated value for ReLU and the PRE-activation for GELU (what each backward needs). */
 int b200_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb,
                    int ldc, int a_mn_major, int b_mn_major, const float* bias, const float* residual,
                    int ldr, int act, int out_fp32, int accumulate, void* aux_out_bf16,

@@ -114,3 +114,30 @@ def test_resume_continues_from_the_checkpoint(tmp_path):
     assert r2.returncode == 0, r2.stderr[-2000:]
     val = lambda p: [json.loads(l) for l in p.read_text().splitlines() if json.loads(l)["phase"] == "val"][-1]["loss"]  # noqa: E731
     assert abs(val(tmp_path / "a.jsonl") - val(tmp_path / "b.jsonl")) < 1e-4
+    # the optimizer state travels next to the weights (one file per rank) and is picked up again
+    assert Path(str(ck) + ".resume.rank0").exists()
+    assert "[resume] optimizer state restored" in r2.stdout
+
+
+def test_resume_restores_adamw_moments_and_step():
+    """Strategy-level round trip: after loading the saved optimizer state a second strategy takes exactly the
+    step the first one would have taken next (moments and bias-correction step, not just the weights)."""
+    import copy
+    from types import SimpleNamespace
+    import torch
+    from distributed_pytorch_cookbook_b200.trainer import SingleStrategy, build_model
+    ns = SimpleNamespace(dim=32, head_dim=8, heads=4, num_layers=2, sequence_length=16, learning_rate=1e-2,
+                         disable_amp=True, disable_cuda_graph=True)
+    torch.manual_seed(0)
+    a = SingleStrategy(); a.setup(build_model(ns, 100), ns, "cpu"); a.train()
+    ids = torch.randint(0, 100, (4, 15)); pos = torch.arange(15).unsqueeze(0).repeat(4, 1)
+    batch = {"input_ids": ids, "position_ids": pos}
+    for _ in range(3):
+        a.train_step(batch, ids, amp=False)
+    weights, opt = copy.deepcopy(a.model.state_dict()), copy.deepcopy(a.optimizer_state())
+    b = SingleStrategy(); m = build_model(ns, 100); m.load_state_dict(weights); b.setup(m, ns, "cpu"); b.train()
+    b.load_optimizer_state(opt)
+    la, lb = a.train_step(batch, ids, amp=False), b.train_step(batch, ids, amp=False)
+    assert float(la) == float(lb)
+    for (k, x), (_, y) in zip(a.model.state_dict().items(), b.model.state_dict().items()):
+        assert torch.equal(x, y), k

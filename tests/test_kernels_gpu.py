@@ -360,6 +360,54 @@ def test_lmhead_ce_large_single_chunk_against_fp32():
     assert float((native.grad_of(w) - w32.grad).norm() / w32.grad.norm()) < 2e-2
 
 
+@pytest.mark.parametrize("act", ["relu", "gelu", "gelu_tanh"])
+@pytest.mark.parametrize("with_res", [True, False])
+def test_fused_mlp_activations_against_fp32(act, with_res):
+    """The MLP node (two GEMM epilogues, act' folded into the dgrad epilogue) for ReLU / GELU / tanh-GELU against
+    fp32 PyTorch on the same bf16-rounded operands: output, dX, dW1, db1, dW2, db2, residual gradient."""
+    torch.manual_seed(4)
+    M, D, Fd = 1000, 256, 1024
+    fn = {"relu": F.relu, "gelu": F.gelu, "gelu_tanh": lambda t: F.gelu(t, approximate="tanh")}[act]
+    x = torch.randn(M, D, device="cuda").to(BF16).requires_grad_(True)
+    res = torch.randn(M, D, device="cuda").requires_grad_(True) if with_res else None
+    w1 = torch.nn.Parameter(torch.randn(Fd, D, device="cuda") * 0.06)
+    b1 = torch.nn.Parameter(torch.randn(Fd, device="cuda") * 0.1)
+    w2 = torch.nn.Parameter(torch.randn(D, Fd, device="cuda") * 0.03)
+    b2 = torch.nn.Parameter(torch.randn(D, device="cuda") * 0.1)
+    out = native.mlp(x, w1, b1, w2, b2, residual=res, activation=act)
+    dy = torch.randn_like(out, dtype=torch.float32)
+    out.float().backward(dy)
+    got = [out.float(), x.grad.float(), native.grad_of(w1).clone(), native.grad_of(b1).clone(),
+           native.grad_of(w2).clone(), native.grad_of(b2).clone()] + ([res.grad] if with_res else [])
+    x32 = x.detach().float().requires_grad_(True)
+    p32 = [t.detach().to(BF16).float().requires_grad_(True) if t.ndim == 2 else t.detach().clone().requires_grad_(True)
+           for t in (w1, b1, w2, b2)]
+    r32 = res.detach().clone().requires_grad_(True) if with_res else None
+    h = fn(F.linear(x32, p32[0], p32[1]))
+    ref = fn(F.linear(h, p32[2], p32[3]))
+    if with_res:
+        ref = ref + r32
+    ref.backward(dy)
+    want = [ref, x32.grad, p32[0].grad, p32[1].grad, p32[2].grad, p32[3].grad] + ([r32.grad] if with_res else [])
+    names = ["out", "dx", "dw1", "db1", "dw2", "db2", "dres"]
+    for n, g, w in zip(names, got, want):
+        assert _rel(g, w) < 2.5e-2, (act, n, _rel(g, w))
+
+
+def test_gelu_model_takes_the_native_path():
+    """A GELU FeedForward under bf16 autocast runs on the fused kernels (no silent drop to eager PyTorch)."""
+    from distributed_pytorch_cookbook_b200.models.gpt import FeedForward
+    torch.manual_seed(0)
+    ff = FeedForward(256, activation=F.gelu).cuda()
+    x = torch.randn(4, 50, 256, device="cuda")
+    before = _lib.launch_count()
+    with torch.autocast("cuda", dtype=BF16):
+        y = ff(x)
+    assert _lib.launch_count() - before >= 2
+    ref = ff(x)
+    assert _rel(y, ref) < 2e-2
+
+
 def _lm_reference(x, w, tgt):
     from distributed_pytorch_cookbook_b200 import ops
     x32 = x.detach().float().requires_grad_(True)

@@ -39,23 +39,15 @@ def timed(fn, steps, dev):
     return float(ms)
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--recipe", choices=["fsdp", "pipe", "pipe-ddp"], required=True)
-    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--model", choices=list(MODELS), default="default")
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=4)
-    ap.add_argument("--schedule", default="1f1b")
-    ap.add_argument("--microbatches", type=int, default=0)
-    ap.add_argument("--comm", default="auto")
-    ap.add_argument("--no_graph", action="store_true")
-    ap.add_argument("--profile", action="store_true")
-    a = ap.parse_args()
-    rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
-    dev = torch.device(f"cuda:{local}")
-    torch.cuda.set_device(dev)
-    dist.init_process_group("nccl", device_id=dev)
+def run_recipe(recipe, impl="ours", model="default", steps=10, warmup=4, schedule="1f1b", microbatches=0,
+               comm="auto", no_graph=False, profile_steps=False, measure_exposed=False):
+    """One recipe on the already-initialised default process group (device = cuda:LOCAL_RANK).
+    Returns the result dict on every rank (timing is the max over ranks)."""
+    import gc
+    rank, world = dist.get_rank(), dist.get_world_size()
+    dev = torch.device(f"cuda:{torch.cuda.current_device()}")
+    a = SimpleNamespace(recipe=recipe, impl=impl, model=model, steps=steps, warmup=warmup, schedule=schedule,
+                        microbatches=microbatches, comm=comm, no_graph=no_graph, profile=profile_steps)
     cfg = MODELS[a.model]
     B, S, V = cfg["batch_size"], cfg["sequence_length"], cfg["vocab_size"]
     dp = world if a.recipe == "fsdp" else (world // 2 if a.recipe == "pipe-ddp" else 1)
@@ -65,6 +57,7 @@ def main():
     ids = [torch.randint(0, V, (B, S - 1), generator=g).to(dev) for _ in range(4)]
     pos = torch.arange(S - 1, device=dev).unsqueeze(0).repeat(B, 1)
     extra = {}
+    st = None
     torch.manual_seed(0)
     if a.impl == "ours":
         from distributed_pytorch_cookbook_b200.trainer import build_model
@@ -144,15 +137,18 @@ def main():
 
             def step(i):
                 optim.zero_grad()
+                ls = []
                 if pp_rank == 0:
                     sched.step(ids[i % 4])
                 elif pp_rank == stages - 1:
-                    sched.step(target=ids[i % 4], losses=[])
+                    sched.step(target=ids[i % 4], losses=ls)
                 else:
                     sched.step()
                 optim.step()
+                return torch.stack([l.detach().float() for l in ls]).mean() if ls else torch.full((), -1e30, device=dev)
+    last = None
     for i in range(a.warmup):
-        step(i)
+        last = step(i)
     if a.profile:
         from torch.profiler import ProfilerActivity, profile
         torch.cuda.synchronize(dev); dist.barrier()
@@ -170,12 +166,60 @@ def main():
                 print(f"{e.device_time_total/3:10.1f} us/step n/step={e.count/3:6.1f} avg={e.device_time_total/e.count:9.1f}  {e.key[:100]}")
         dist.barrier()
     ms = timed(step, a.steps, dev)
+    last = step(0)
+    loss = None
+    if torch.is_tensor(last):
+        lt = last.detach().float().reshape(1).clone()
+        dist.all_reduce(lt, op=dist.ReduceOp.MAX)       # pipeline: only some ranks hold it; NaN propagates
+        loss = float(lt)
     tokens = B * (S - 1) * dp
+    out = {"recipe": a.recipe, "impl": a.impl, "model": a.model, "n_gpus": world, "stages": stages, "dp": dp,
+           "microbatches": M, "schedule": a.schedule if a.recipe != "fsdp" else None,
+           "ms_per_step": ms / a.steps, "tokens_per_s": tokens * a.steps / ms * 1e3,
+           "global_batch": B * dp, "seq_len": S, "loss_after": loss, **extra}
+    if measure_exposed and st is not None and hasattr(st, "set_skip_comm"):
+        # the same step with every collective skipped (each rank updates its shard from its local gradients):
+        # what is left of the difference is communication that compute did not hide
+        try:
+            st.set_skip_comm(True)
+            for i in range(3):
+                step(i)
+            ms_nc = timed(step, a.steps, dev)
+            out["compute_only_ms_per_step"] = ms_nc / a.steps
+            out["exposed_comm_ms_per_step"] = max(ms - ms_nc, 0.0) / a.steps
+        except Exception as e:  # noqa: BLE001
+            out["exposed_comm_error"] = repr(e)[:200]
+    if st is not None and hasattr(st, "close"):
+        st.close()
+    del st, step
+    gc.collect()
+    torch.cuda.empty_cache()
+    dist.barrier()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--recipe", choices=["fsdp", "pipe", "pipe-ddp"], required=True)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--model", choices=list(MODELS), default="default")
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=4)
+    ap.add_argument("--schedule", default="1f1b")
+    ap.add_argument("--microbatches", type=int, default=0)
+    ap.add_argument("--comm", default="auto")
+    ap.add_argument("--no_graph", action="store_true")
+    ap.add_argument("--profile", action="store_true")
+    ap.add_argument("--exposed", action="store_true")
+    a = ap.parse_args()
+    rank, local = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
+    dev = torch.device(f"cuda:{local}")
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    out = run_recipe(a.recipe, a.impl, a.model, a.steps, a.warmup, a.schedule, a.microbatches, a.comm, a.no_graph,
+                     a.profile, a.exposed)
     if rank == 0:
-        print(json.dumps({"recipe": a.recipe, "impl": a.impl, "model": a.model, "n_gpus": world, "stages": stages, "dp": dp,
-                          "microbatches": M, "schedule": a.schedule if a.recipe != "fsdp" else None,
-                          "ms_per_step": ms / a.steps, "tokens_per_s": tokens * a.steps / ms * 1e3,
-                          "global_batch": B * dp, "seq_len": S, **extra}), flush=True)
+        print(json.dumps(out), flush=True)
     dist.barrier()
     dist.destroy_process_group()
 
