@@ -357,7 +357,8 @@ def run_recipes(impl, n, args):
             r = run_recipe(impl=impl, **kw)
             out[name] = {k: r.get(k) for k in ("ms_per_step", "tokens_per_s", "loss_after", "comm", "stages", "dp",
                                                "microbatches", "schedule", "global_batch", "seq_len", "model",
-                                               "compute_only_ms_per_step", "exposed_comm_ms_per_step") if r.get(k) is not None}
+                                               "compute_only_ms_per_step", "exposed_comm_ms_per_step", "exposed_comm_error")
+                         if r.get(k) is not None}
         except Exception as e:  # noqa: BLE001
             out[name] = {"error": repr(e)[:300]}
             try:

@@ -390,8 +390,11 @@ def test_fused_mlp_activations_against_fp32(act, with_res):
     ref.backward(dy)
     want = [ref, x32.grad, p32[0].grad, p32[1].grad, p32[2].grad, p32[3].grad] + ([r32.grad] if with_res else [])
     names = ["out", "dx", "dw1", "db1", "dw2", "db2", "dres"]
+    # ReLU's derivative is a step: a pre-activation whose bf16 rounding changes sign flips a whole mask bit, which the
+    # smooth GELUs do not suffer from
+    tol = 6e-2 if act == "relu" else 2.5e-2
     for n, g, w in zip(names, got, want):
-        assert _rel(g, w) < 2.5e-2, (act, n, _rel(g, w))
+        assert _rel(g, w) < tol, (act, n, _rel(g, w))
 
 
 def test_gelu_model_takes_the_native_path():
