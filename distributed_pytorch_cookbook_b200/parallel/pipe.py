@@ -110,36 +110,64 @@ def schedule_actions(kind: str, stage: int, num_stages: int, num_microbatches: i
     return acts
 
 
-class _P2P:
-    """Batched isend/irecv between neighbouring stages (ranks given as global ranks)."""
+class _Link:
+    """One direction of one stage boundary.
 
-    def __init__(self, prev_rank: Optional[int], next_rank: Optional[int], shape, wire_dtype, device, group=None):
-        self.prev, self.next, self.shape, self.dtype, self.device, self.group = \
-            prev_rank, next_rank, tuple(shape), wire_dtype, device, group
+    Every boundary gets two 2-rank process groups, one per direction (activations forward, gradients
+    backward).  A group then has exactly one sender and one receiver whose operations match in issue order,
+    and traffic of the opposite direction lives on a different communicator, so no ordering between a
+    stage's sends and receives can deadlock and nothing has to be issued as a blocking batch.  On CUDA the
+    operations are issued from the link's own stream: a send waits (event) for the kernel that produced
+    its buffer and the compute stream goes on; a receive is posted ahead of time and the compute stream
+    waits for it only when the data is needed (``Work.wait`` is a stream-level wait for NCCL).
+    Reference intent: main-pipe.py:79-83,162 (legacy Pipe moves micro-batches on copy streams).
+    """
 
-    def _buf(self):
-        return torch.empty(self.shape, dtype=self.dtype, device=self.device)
+    def __init__(self, group, peer: int, device):
+        self.group, self.peer = group, peer
+        self.cuda = torch.device(device).type == "cuda"
+        self.stream = torch.cuda.Stream(device) if self.cuda else None
+        self.pending = []                       # (work, tensor) of sends not joined yet
 
-    def _run(self, ops):
-        if not ops:
-            return
-        for w in dist.batch_isend_irecv(ops):
+    def order_after_compute(self):
+        """Operations issued from now on start after everything the compute stream has queued so far."""
+        if self.cuda:
+            self.stream.wait_stream(torch.cuda.current_stream())
+
+    def send(self, t: torch.Tensor):
+        if self.cuda:
+            ev = torch.cuda.Event()
+            ev.record()
+            self.stream.wait_event(ev)
+            with torch.cuda.stream(self.stream):
+                w = dist.isend(t, dst=self.peer, group=self.group)
+        else:
+            w = dist.isend(t, dst=self.peer, group=self.group)
+        self.pending.append((w, t))
+
+    def post_recv(self, buf: torch.Tensor):
+        if self.cuda:
+            with torch.cuda.stream(self.stream):
+                return dist.irecv(buf, src=self.peer, group=self.group)
+        return dist.irecv(buf, src=self.peer, group=self.group)
+
+    def join(self):
+        """Buffers of finished sends may be reused after this (stream-level on CUDA, blocking on gloo)."""
+        for w, _ in self.pending:
             w.wait()
+        self.pending = []
 
-    def exchange(self, send_next=None, send_prev=None, recv_prev=False, recv_next=False):
-        ops, from_prev, from_next = [], None, None
-        if send_prev is not None and self.prev is not None:
-            ops.append(dist.P2POp(dist.isend, send_prev.to(self.dtype).contiguous(), self.prev, self.group))
-        if recv_prev and self.prev is not None:
-            from_prev = self._buf()
-            ops.append(dist.P2POp(dist.irecv, from_prev, self.prev, self.group))
-        if send_next is not None and self.next is not None:
-            ops.append(dist.P2POp(dist.isend, send_next.to(self.dtype).contiguous(), self.next, self.group))
-        if recv_next and self.next is not None:
-            from_next = self._buf()
-            ops.append(dist.P2POp(dist.irecv, from_next, self.next, self.group))
-        self._run(ops)
-        return from_prev, from_next
+
+class _Slot:
+    """Per-micro-batch state of a stage: wire buffers, the autograd endpoints of the live forward, the static
+    loss / count tensors of the last stage and, in graph mode, the captured forward / backward graphs."""
+
+    def __init__(self):
+        self.act_in = self.out_wire = self.grad_in = self.gin_wire = None
+        self.x_in = self.out = None
+        self.loss = self.n_valid = self.n_correct = None
+        self.fgraph = self.bgraph = None
+        self.recompute = False
 
 
 class PipeStrategy:
@@ -147,11 +175,24 @@ class PipeStrategy:
 
     Rank layout for pp x dp: ``rank = pp_rank * dp_size + dp_rank`` - neighbouring stages of one
     replica are ``dp_size`` ranks apart, the replicas of one stage are consecutive ranks.
+
+    Execution: every stage walks its GPipe / 1F1B action list (``schedule_actions``).  Receives of all
+    micro-batches are posted up front on the link streams, sends leave from the link streams behind an
+    event, so transfers overlap the stage's compute.  On CUDA (native kernels) each micro-batch's forward
+    and backward are captured once as CUDA graphs (shapes are static) and replayed - at the default model
+    size a micro-batch is a few dozen 5-10 us kernels and the host would otherwise be the bottleneck.
+    ``checkpoint`` = never | except_last | always re-runs a micro-batch's forward inside its backward instead
+    of keeping its activations (legacy Pipe default ``except_last``, main-pipe.py:79-83).
     """
 
-    def __init__(self, num_stages: int = 0, num_microbatches: int = 0, schedule: str = "gpipe", dp_size: int = 1):
+    static_batches = True      # micro-batches travel between stages in fixed-shape buffers
+
+    def __init__(self, num_stages: int = 0, num_microbatches: int = 0, schedule: str = "gpipe", dp_size: int = 1,
+                 checkpoint: str = "never"):
         self.num_stages, self.num_microbatches, self.schedule, self.dp_size = \
             num_stages, num_microbatches, schedule, dp_size
+        assert checkpoint in ("never", "except_last", "always")
+        self.checkpoint = checkpoint
         self.comm_kind = None
 
     # ------------------------------------------------------------------------------
@@ -163,13 +204,34 @@ class PipeStrategy:
         self.S, self.M = S, (self.num_microbatches or S)       # reference: chunks = num_stages
         self.pp_rank, self.dp_rank = rank // self.dp_size, rank % self.dp_size
         self.args = args
+        self.checkpoint = getattr(args, "checkpoint", None) or self.checkpoint
+        dp = self.dp_size
         # process groups: every rank must create every group, in the same order
         self.dp_group = None
-        if self.dp_size > 1:
+        if dp > 1:
             for s in range(S):
-                g = dist.new_group([s * self.dp_size + d for d in range(self.dp_size)])
+                g = dist.new_group([s * dp + d for d in range(dp)])
                 if s == self.pp_rank:
                     self.dp_group = g
+        # one 2-rank group per stage boundary, direction and replica, and one from the last stage to the first
+        # (the loss travels there; stage 0 finishes every step last, so it never waits for it)
+        self.fwd_in = self.fwd_out = self.bwd_in = self.bwd_out = self.loss_link = None
+        for d in range(dp):
+            for l in range(S - 1):
+                a, b = l * dp + d, (l + 1) * dp + d
+                gf, gb = dist.new_group([a, b]), dist.new_group([a, b])
+                if rank == a:
+                    self.fwd_out, self.bwd_in = _Link(gf, b, self.device), _Link(gb, b, self.device)
+                if rank == b:
+                    self.fwd_in, self.bwd_out = _Link(gf, a, self.device), _Link(gb, a, self.device)
+            if S > 1:
+                a, b = d, (S - 1) * dp + d
+                gl = dist.new_group([a, b])
+                if rank == a:
+                    self.loss_link = _Link(gl, b, self.device)
+                if rank == b:
+                    self.loss_link = _Link(gl, a, self.device)
+        self.links = [l for l in (self.fwd_in, self.fwd_out, self.bwd_in, self.bwd_out, self.loss_link) if l is not None]
         self.stage = PipelineStage(model, self.pp_rank, S).to(self.device)
         cuda = self.device.type == "cuda"
         self.native_ok = cuda and _lib.available() and not args.disable_amp
@@ -178,7 +240,7 @@ class PipeStrategy:
         symm = None
         grad_alloc, holder = None, {}
         transport = "gloo" if not cuda else "nccl"
-        if self.dp_size > 1:
+        if dp > 1:
             from ..runtime.symm import SymmContext, symmetric_memory_available
             want = getattr(args, "comm", "auto")
             if self.native_ok and want in ("auto", "symm") and symmetric_memory_available(self.device):
@@ -193,22 +255,40 @@ class PipeStrategy:
                     if want == "symm":
                         raise
                     print(f"[pipe-ddp] symmetric memory unavailable ({e!r}); using NCCL", flush=True)
-        self.comm_kind = f"p2p:{'nccl' if cuda else 'gloo'}" + (f"+dp:{transport}" if self.dp_size > 1 else "")
+        self.comm_kind = f"p2p:{'nccl' if cuda else 'gloo'}" + (f"+dp:{transport}" if dp > 1 else "")
         self.arena = ParamArena(params, self.device, with_bf16=self.native_ok, with_moments=self.native_ok,
                                 grad_alloc=grad_alloc)
         self.optim = FusedAdamW(params, lr=args.learning_rate, device=self.device, arena=self.arena)
-        if self.dp_size > 1:
+        if dp > 1:
             from .ddp import GradReducer
             self.reducer = GradReducer(self.arena, self.dp_group, getattr(args, "bucket_mb", 4.0), transport,
                                        symm, holder.get("buf"))
         self.mb = args.batch_size // self.M
         assert self.mb * self.M == args.batch_size, "batch_size must be divisible by the number of micro-batches"
-        T = args.sequence_length - 1
-        wire = torch.bfloat16 if (cuda and not args.disable_amp) else torch.float32
-        prev_rank = rank - self.dp_size if self.pp_rank > 0 else None
-        next_rank = rank + self.dp_size if self.pp_rank < S - 1 else None
-        self.p2p = _P2P(prev_rank, next_rank, (self.mb, T, model.dim), wire, self.device)
+        self.T = args.sequence_length - 1
+        self.wire = torch.bfloat16 if (cuda and not args.disable_amp) else torch.float32
         self.has_loss = self.stage.is_last
+        self.use_graph = self.native_ok and not getattr(args, "disable_cuda_graph", False)
+        self.graph_warmup = 2                  # eager steps before the per-micro-batch graphs are captured
+        self.steps_done = 0
+        self.slots: List[_Slot] = []
+        self._static = {}
+        self._pool = None
+        self._cap_stream = None
+        self._warm_links()
+
+    def _warm_links(self):
+        """Create the link communicators now, boundary by boundary from the first stage on (a chain, so the lazy
+        NCCL initialisation of one link never waits on a rank that is itself waiting on an earlier link)."""
+        one = torch.zeros(1, dtype=torch.float32, device=self.device)
+        for link, sending in ((self.fwd_in, False), (self.bwd_out, True), (self.fwd_out, True), (self.bwd_in, False)):
+            if link is None:
+                continue
+            (dist.send if sending else dist.recv)(one, link.peer, group=link.group)
+        if self.loss_link is not None:
+            (dist.send if self.stage.is_last else dist.recv)(one, self.loss_link.peer, group=self.loss_link.group)
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
 
     def train(self):
         self.stage.train()
@@ -222,96 +302,196 @@ class PipeStrategy:
         return nullcontext()
 
     # ------------------------------------------------------------------------------
+    def _make_slots(self, dim: int):
+        st, dev = self.stage, self.device
+        shape = (self.mb, self.T, dim)
+        for k in range(self.M):
+            sl = _Slot()
+            if not st.is_first:
+                sl.act_in = torch.zeros(shape, dtype=self.wire, device=dev)
+                sl.gin_wire = torch.zeros(shape, dtype=self.wire, device=dev)
+            if not st.is_last:
+                sl.out_wire = torch.zeros(shape, dtype=self.wire, device=dev)
+                sl.grad_in = torch.zeros(shape, dtype=self.wire, device=dev)
+            sl.recompute = self.checkpoint == "always" or (self.checkpoint == "except_last" and k < self.M - 1)
+            self.slots.append(sl)
+
     def _micro(self, t, i):
         return None if t is None else t[i * self.mb:(i + 1) * self.mb]
 
-    def _forward(self, i, recv, batch, targets, amp, train=True):
+    def _run_forward(self, sl: _Slot, i: int, batch, targets, amp: bool, grad: bool):
+        """Forward of micro-batch i on this stage.  grad=False: nothing is kept for a backward pass."""
         st = self.stage
-        with self._autocast(amp):
+        with self._autocast(amp), (nullcontext() if grad else torch.no_grad()):
             if st.is_first:
                 x_in = None
                 x = st.forward_hidden(None, self._micro(batch["input_ids"], i), self._micro(batch["position_ids"], i),
                                       self._micro(batch.get("mask"), i))
             else:
-                x_in = recv.float()
-                if train:
+                x_in = sl.act_in.float()
+                if x_in is sl.act_in:             # fp32 wire: the autograd leaf must not be the receive buffer itself
+                    x_in = x_in.clone()
+                if grad:
                     x_in.requires_grad_(True)
                 x = st.forward_hidden(x_in, mask=self._micro(batch.get("mask"), i))
             if st.is_last:
                 loss, n_valid, n_correct = st.loss(x, self._micro(targets, i), grad_scale=1.0 / self.M)
-                return x_in, loss, (loss.detach(), n_valid, n_correct)
-        return x_in, x, None
+                out = loss
+                for name, v in (("loss", loss.detach()), ("n_valid", n_valid), ("n_correct", n_correct)):
+                    v = v.float() if torch.is_tensor(v) else torch.tensor(float(v), device=self.device)
+                    cur = getattr(sl, name)
+                    if cur is None:
+                        setattr(sl, name, v.clone())
+                    else:
+                        cur.copy_(v)
+            else:
+                out = x
+                sl.out_wire.copy_(x.detach())
+        if grad:
+            sl.x_in, sl.out = x_in, out
+        return out
 
-    def _backward(self, x_in, out, grad_from_next):
-        if self.stage.is_last:
-            (out * (1.0 / self.M)).backward()
+    def _run_backward(self, sl: _Slot, i: int, batch, targets, amp: bool):
+        st = self.stage
+        if sl.recompute:                       # activation checkpointing: redo the forward, now with autograd
+            self._run_forward(sl, i, batch, targets, amp, grad=True)
+        if st.is_last:
+            (sl.out * (1.0 / self.M)).backward()
         else:
-            torch.autograd.backward(out, grad_from_next.to(out.dtype))
-        return None if x_in is None else x_in.grad
+            torch.autograd.backward(sl.out, sl.grad_in.to(sl.out.dtype))
+        if not st.is_first:
+            sl.gin_wire.copy_(sl.x_in.grad)
+        sl.x_in = sl.out = None
+
+    def _capture(self, fn):
+        """Capture ``fn`` into a CUDA graph (shared memory pool, no device-wide synchronisation: transfers of
+        other micro-batches are in flight on the link streams while a stage captures)."""
+        if self._cap_stream is None:
+            self._cap_stream = torch.cuda.Stream(self.device)
+            self._pool = torch.cuda.graph_pool_handle()
+        g = torch.cuda.CUDAGraph()
+        cur = torch.cuda.current_stream()
+        self._cap_stream.wait_stream(cur)
+        with torch.cuda.stream(self._cap_stream):
+            g.capture_begin(pool=self._pool, capture_error_mode="thread_local")
+            try:
+                fn()
+            finally:
+                g.capture_end()
+        cur.wait_stream(self._cap_stream)
+        return g
+
+    def _forward_action(self, sl, i, batch, targets, amp, graphed):
+        grad = not sl.recompute
+        if not graphed:
+            self._run_forward(sl, i, batch, targets, amp, grad)
+            return
+        if sl.fgraph is None:
+            sl.fgraph = self._capture(lambda: self._run_forward(sl, i, batch, targets, amp, grad))
+        sl.fgraph.replay()
+
+    def _backward_action(self, sl, i, batch, targets, amp, graphed):
+        if not graphed:
+            self._run_backward(sl, i, batch, targets, amp)
+            return
+        if sl.bgraph is None:
+            sl.bgraph = self._capture(lambda: self._run_backward(sl, i, batch, targets, amp))
+        sl.bgraph.replay()
+
+    def _static_inputs(self, batch, targets):
+        """Graph mode: the captured kernels read the batch from fixed addresses."""
+        out = {}
+        for name, t in (("input_ids", batch["input_ids"]), ("position_ids", batch["position_ids"]), ("targets", targets)):
+            buf = self._static.get(name)
+            if buf is None or buf.shape != t.shape:
+                buf = self._static[name] = torch.empty_like(t, device=self.device)
+            buf.copy_(t, non_blocking=True)
+            out[name] = buf
+        return {"input_ids": out["input_ids"], "position_ids": out["position_ids"]}, out["targets"]
 
     def train_step(self, batch, targets, amp=True):
-        M, S = self.M, self.S
+        from ..utils import nvtx
+        M, S, st = self.M, self.S, self.stage
+        graphed = self.use_graph and amp and self.steps_done >= self.graph_warmup
+        capturing = graphed and (not self.slots or self.slots[0].fgraph is None)
+        if not self.slots:
+            self._make_slots(st.dim)
+        if graphed:
+            batch, targets = self._static_inputs(batch, targets)   # the key-padding mask is a no-op for the loss: dropped
         self.optim.zero_grad()
         if self.reducer is not None:
             self.reducer.begin()
             self.reducer.active = False              # grads accumulate over micro-batches: reduce at the end
-        warm = M if self.schedule == "gpipe" else min(S - self.pp_rank - 1, M)
-        remaining = M - warm
-        inflight, stats = [], []
-        f = 0
-        recv = None
-        for _ in range(warm):
-            recv, _ = self.p2p.exchange(recv_prev=True)
-            x_in, out, st = self._forward(f, recv, batch, targets, amp)
-            self.p2p.exchange(send_next=None if self.stage.is_last else out.detach())
-            inflight.append((x_in, out)); stats.append(st); f += 1
-        if remaining > 0:
-            recv, _ = self.p2p.exchange(recv_prev=True)
-        for k in range(remaining):
-            x_in, out, st = self._forward(f, recv, batch, targets, amp)
-            inflight.append((x_in, out)); stats.append(st); f += 1
-            _, g = self.p2p.exchange(send_next=None if self.stage.is_last else out.detach(), recv_next=True)
-            bx, bout = inflight.pop(0)
-            gin = self._backward(bx, bout, g)
-            if k == remaining - 1:
-                self.p2p.exchange(send_prev=gin)
+        for l in self.links:
+            l.order_after_compute()
+        # receives are posted ahead of the compute that needs them; in the step that captures the graphs they are
+        # posted one at a time instead (capture must not sit behind a receive that depends on this stage's own work)
+        acts = grads = None
+        if not capturing:
+            acts = [self.fwd_in.post_recv(sl.act_in) for sl in self.slots] if not st.is_first else None
+            grads = [self.bwd_in.post_recv(sl.grad_in) for sl in self.slots] if not st.is_last else None
+        for kind, i in schedule_actions(self.schedule, self.pp_rank, S, M):
+            sl = self.slots[i]
+            if kind == "F":
+                if not st.is_first:
+                    (acts[i] if acts is not None else self.fwd_in.post_recv(sl.act_in)).wait()
+                with nvtx.phase(f"forward mb{i}"):
+                    self._forward_action(sl, i, batch, targets, amp, graphed)
+                if not st.is_last:
+                    self.fwd_out.send(sl.out_wire)
             else:
-                recv, _ = self.p2p.exchange(send_prev=gin, recv_prev=True)
-        while inflight:
-            _, g = self.p2p.exchange(recv_next=True)
-            bx, bout = inflight.pop(0)
-            gin = self._backward(bx, bout, g)
-            self.p2p.exchange(send_prev=gin)
-        if self.reducer is not None:
-            self.reducer.active = True
-            self.reducer.finish()
-        self.optim.step()
-        if self.stage.is_last:
-            loss = torch.stack([s[0].float() for s in stats]).mean()
-        else:
-            loss = torch.zeros((), device=self.device)
-        # every rank reports the same loss (the trainer prints on rank 0): broadcast from the last stage
-        src = (S - 1) * self.dp_size + self.dp_rank
-        if self.dp_size == 1:
-            dist.broadcast(loss, src=src)
-        else:
-            dist.all_reduce(loss)
+                if not st.is_last:
+                    (grads[i] if grads is not None else self.bwd_in.post_recv(sl.grad_in)).wait()
+                with nvtx.phase(f"backward mb{i}"):
+                    self._backward_action(sl, i, batch, targets, amp, graphed)
+                if not st.is_first:
+                    self.bwd_out.send(sl.gin_wire)
+        with nvtx.phase("grad-sync + optimizer"):
+            if self.reducer is not None:
+                self.reducer.active = True
+                self.reducer.finish()
+            self.optim.step()
+        self.steps_done += 1
+        # the loss goes from the last stage to the first (rank 0 prints); other stages report 0
+        loss = torch.zeros((), dtype=torch.float32, device=self.device)
+        if st.is_last:
+            loss = torch.stack([sl.loss for sl in self.slots]).mean()
+            if self.loss_link is not None:
+                self._loss_out = loss.reshape(1).clone()
+                self.loss_link.send(self._loss_out)
+        elif st.is_first and self.loss_link is not None:
+            buf = torch.zeros(1, dtype=torch.float32, device=self.device)
+            self.loss_link.post_recv(buf).wait()
+            loss = buf[0]
+        for l in self.links:
+            l.join()
+        if st.is_first and self.dp_size > 1:
+            loss = loss.clone()
+            dist.all_reduce(loss, group=self.dp_group)
             loss = loss / self.dp_size
         return loss.detach()
 
     @torch.no_grad()
     def eval_step(self, batch, targets, amp=True):
-        stats = []
+        st = self.stage
+        if not self.slots:
+            self._make_slots(st.dim)
+        for l in self.links:
+            l.order_after_compute()
         for i in range(self.M):
-            recv, _ = self.p2p.exchange(recv_prev=True)
-            _, out, st = self._forward(i, recv, batch, targets, amp, train=False)
-            self.p2p.exchange(send_next=None if self.stage.is_last else out)
-            stats.append(st)
+            sl = self.slots[i]
+            if not st.is_first:
+                self.fwd_in.post_recv(sl.act_in).wait()
+            self._run_forward(sl, i, batch, targets, amp, grad=False)
+            if not st.is_last:
+                self.fwd_out.send(sl.out_wire)
+        for l in self.links:
+            l.join()
         res = torch.zeros(3, device=self.device)
-        if self.stage.is_last:
-            res[0] = torch.stack([s[0].float() for s in stats]).mean()
-            res[1] = torch.stack([s[1].float() for s in stats]).sum()
-            res[2] = torch.stack([s[2].float() for s in stats]).sum()
+        if st.is_last:
+            res[0] = torch.stack([sl.loss for sl in self.slots]).mean()
+            res[1] = torch.stack([sl.n_valid for sl in self.slots]).sum()
+            res[2] = torch.stack([sl.n_correct for sl in self.slots]).sum()
         dist.all_reduce(res)                      # only last-stage ranks contribute
         res = res / self.dp_size if self.dp_size > 1 else res
         return res[0], res[1], res[2]
@@ -322,8 +502,7 @@ class PipeStrategy:
     def close(self):
         if self.reducer is not None:
             self.reducer.close()
-
-    static_batches = True      # micro-batches travel between stages in fixed-shape buffers
+        self.slots = []
 
     def optimizer_state(self):
         return self.optim.state_dict()
@@ -331,10 +510,27 @@ class PipeStrategy:
     def load_optimizer_state(self, sd):
         self.optim.load_state_dict(sd)
 
-    def generation_model(self):
-        return None                                # generation needs all stages; see gather_full_model()
-
     # ------------------------------------------------------------------------------
+    def gather_full_model(self):
+        """Collective: rank 0 gets a complete, up-to-date copy of the model (its own ``TransformerDecoderLM``
+        object with every stage's weights loaded), the other ranks ``None``.  Used for the per-epoch sample
+        generation of the reference (main-pipe.py:210-214), which needs all stages in one place."""
+        sd = self.state_dict()
+        if dist.get_rank() != 0:
+            return None
+        if getattr(self, "_gen_model", None) is None:
+            import copy
+            full = self.stage._full
+            self._gen_model = copy.deepcopy(full).to("cpu").float().to(self.device)
+        self._gen_model.load_state_dict(sd)
+        for p in self._gen_model.parameters():
+            if hasattr(p, "_b200_bf16_version"):
+                p._b200_bf16_version = -1
+        return self._gen_model
+
+    def generation_model(self):
+        return self.gather_full_model()
+
     def state_dict(self):
         """Canonical checkpoint: every stage sends its (key, tensor) pairs to rank 0 (collective)."""
         mine = [(k, v.detach().float().cpu()) for k, v in self.stage.canonical_items()] if self.dp_rank == 0 else []

@@ -57,4 +57,7 @@ def build_parser(recipe: str = "single") -> argparse.ArgumentParser:
         x.add_argument("--num_stages", type=int, default=0, help="0 = world size (pipe) / 2 (pipe-ddp)")
         x.add_argument("--num_microbatches", type=int, default=0, help="0 = num_stages (reference chunks=num_stages)")
         x.add_argument("--schedule", choices=["gpipe", "1f1b"], default="gpipe")
+        x.add_argument("--checkpoint", choices=["never", "except_last", "always"], default="never",
+                       help="activation checkpointing per micro-batch: re-run its forward inside its backward "
+                            "(legacy Pipe's default was except_last, reference main-pipe.py:79-83)")
     return parser

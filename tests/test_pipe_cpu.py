@@ -71,12 +71,13 @@ def _data(steps, batch):
     return ids, pos
 
 
-def _pipe_worker(rank, world, schedule, stages, dp, microbatches):
+def _pipe_worker(rank, world, schedule, stages, dp, microbatches, checkpoint="never"):
     from distributed_pytorch_cookbook_b200 import TransformerDecoderLM
     from distributed_pytorch_cookbook_b200.parallel.pipe import PipeStrategy
     torch.manual_seed(0)
     model = TransformerDecoderLM(**CFG)
-    strat = PipeStrategy(num_stages=stages, num_microbatches=microbatches, schedule=schedule, dp_size=dp)
+    strat = PipeStrategy(num_stages=stages, num_microbatches=microbatches, schedule=schedule, dp_size=dp,
+                         checkpoint=checkpoint)
     strat.setup(model, _args(), "cpu")
     ids, pos = _data(3, 8 * dp)
     losses = []
@@ -86,6 +87,15 @@ def _pipe_worker(rank, world, schedule, stages, dp, microbatches):
         losses.append(float(strat.train_step({"input_ids": x, "position_ids": pos[:8]}, x, amp=False)))
     ev = strat.eval_step({"input_ids": ids[0, :8], "position_ids": pos[:8]}, ids[0, :8], amp=False)
     sd = strat.state_dict()
+    gen = strat.generation_model()          # collective; rank 0 gets the assembled model
+    if rank == 0:
+        assert gen is not None
+        for k, v in gen.state_dict().items():
+            assert torch.equal(v.cpu(), sd[k]), k
+        with torch.no_grad():
+            assert gen(ids[0, :2], pos[:2]).shape == (2, 12, CFG["vocab_size"])
+    else:
+        assert gen is None
     return ({k: v.numpy().copy() for k, v in sd.items()} if sd is not None else None, losses,
             [float(e) for e in ev])
 
@@ -108,9 +118,13 @@ def _single_reference(dp):
     return ref, losses, [float(e) for e in ev]
 
 
-@pytest.mark.parametrize("schedule,stages,dp,mb", [("gpipe", 2, 1, 2), ("1f1b", 4, 1, 4), ("1f1b", 2, 2, 4)])
-def test_pipeline_matches_single_process(schedule, stages, dp, mb):
-    outs = run_distributed(_pipe_worker, stages * dp, schedule, stages, dp, mb)
+@pytest.mark.parametrize("schedule,stages,dp,mb,ckpt", [("gpipe", 2, 1, 2, "never"), ("1f1b", 4, 1, 4, "never"),
+                                                          ("1f1b", 2, 2, 4, "never"), ("1f1b", 3, 1, 4, "except_last"),
+                                                          ("gpipe", 2, 1, 4, "always")])
+def test_pipeline_matches_single_process(schedule, stages, dp, mb, ckpt):
+    """GPipe / 1F1B, more micro-batches than stages, pp x dp, and activation checkpointing (forward re-run inside the
+    backward) all train exactly like one process; rank 0 can assemble the full model for generation."""
+    outs = run_distributed(_pipe_worker, stages * dp, schedule, stages, dp, mb, ckpt)
     ref, ref_losses, ref_eval = _single_reference(dp)
     sd = outs[0][0]
     assert list(sd.keys()) == list(ref.state_dict().keys())
