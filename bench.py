@@ -182,7 +182,7 @@ def run_ours(args):
     assert _lib.available(), f"native sm_100a library not loaded: {_lib.load_error()}"
     seed_everything(0)
     ns = SimpleNamespace(**CFG, disable_amp=False, disable_cuda_graph=False, bucket_mb=args.bucket_mb,
-                         comm=args.comm, epochs=1)
+                         comm=args.comm, epochs=1, comm_dtype=args.comm_dtype)
     model = build_model(ns, CFG["vocab_size"])
     if n == 1:
         strategy = SingleStrategy()
@@ -480,6 +480,7 @@ def main():
     ap.add_argument("--ref-compile", dest="ref_compile", choices=["both", "on", "off"], default="both")
     ap.add_argument("--bucket_mb", type=float, default=4.0)
     ap.add_argument("--comm", choices=["auto", "symm", "nccl"], default="auto")
+    ap.add_argument("--comm_dtype", choices=["fp32", "bf16"], default="fp32")
     ap.add_argument("--min-seconds", dest="min_seconds", type=float, default=1.0,
                     help="repeat the K-step timed block until this much device time has been measured (median reported)")
     ap.add_argument("--no-recipes", dest="no_recipes", action="store_true",

@@ -32,6 +32,10 @@ enum : int { ERR_COMM_SIGNAL = 301, ERR_COMM_WAIT = 302 };
 #define B200_COMM_TIMEOUT_CYCLES 40000000000LL  // ~20 s: ranks may be skewed by whole steps
 #endif
 
+// bound of every cross-GPU spin, in SM cycles; b200_set_comm_timeout_ms changes it for the current device (tests
+// shorten it to prove that a missing peer is reported instead of hanging)
+__device__ long long g_comm_timeout_cycles = B200_COMM_TIMEOUT_CYCLES;
+
 struct CommCtx {
   void* const* bufs;        // device array [world] of peer base pointers (data buffer)
   void* mc;                 // multicast base pointer of the same buffer, or nullptr
@@ -64,12 +68,13 @@ __device__ bool block_barrier(const CommCtx& c, int* s_fail) {
     uint32_t* remote = c.flags[peer] + ch * MAX_WORLD + c.rank;
     uint32_t* local = c.flags[c.rank] + ch * MAX_WORLD + peer;
     const long long t0 = clock64();
+    const long long limit = g_comm_timeout_cycles;
     bool ok = true;
     while (cas_release_sys(remote, 0u, 1u) != 0u) {
-      if (clock64() - t0 > B200_COMM_TIMEOUT_CYCLES) { ok = false; atomicCAS(c.err_word, 0, ERR_COMM_SIGNAL); break; }
+      if (clock64() - t0 > limit) { ok = false; atomicCAS(c.err_word, 0, ERR_COMM_SIGNAL); break; }
     }
     while (ok && cas_acquire_sys(local, 1u, 0u) != 1u) {
-      if (clock64() - t0 > B200_COMM_TIMEOUT_CYCLES) { ok = false; atomicCAS(c.err_word, 0, ERR_COMM_WAIT); break; }
+      if (clock64() - t0 > limit) { ok = false; atomicCAS(c.err_word, 0, ERR_COMM_WAIT); break; }
     }
     if (!ok) *s_fail = 1;
   }
@@ -174,6 +179,92 @@ allreduce_kernel(const CommCtx c, int64_t off, int64_t n, float scale) {
   }
   __threadfence_system();
   block_barrier(c, &s_fail);                       // every rank's slice has landed everywhere
+}
+
+// ------------------------------------------------------------------------------------------
+// All-reduce with bf16 on the wire (fp32 accumulation in the switch): halves the NVLink bytes of a bucket.
+// The fp32 gradients stay where they are; `stage` is a symmetric bf16 buffer of the same geometry.
+//   phase 0  cast own gradients fp32 -> bf16 into the local stage
+//   phase 1  rank r reduces slice r:  multimem.ld_reduce.acc::f32 (bf16x2) -> * scale -> multimem.st (bf16x2)
+//   phase 2  stage (now the reduced values, identical on every rank) -> fp32 gradients
+// Work is laid out so that a block only ever touches, in every phase, sub-part `blockIdx.x` of every rank's
+// slice: the per-block cross-GPU barriers between the phases are then sufficient (no grid-wide barrier).
+__device__ __forceinline__ uint4 mc_ld_reduce_bf16x8(const void* mc_addr) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc_addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st_bf16x8(void* mc_addr, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};"
+               ::"l"(mc_addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+__global__ void __launch_bounds__(512)
+allreduce_bf16_kernel(const CommCtx c, float* __restrict__ grad, int64_t off, int64_t n, float scale) {
+  __shared__ int s_fail;
+  bf16* stage = reinterpret_cast<bf16*>(c.bufs[c.rank]) + off;
+  bf16* stage_mc = reinterpret_cast<bf16*>(c.mc) + off;
+  float* g = grad + off;
+  const int64_t nvec = n >> 3;                       // 8 elements = 16 bytes of bf16
+  const int64_t per_rank = (nvec + c.world - 1) / c.world;
+  const int64_t per_blk = (per_rank + gridDim.x - 1) / gridDim.x;
+  // this block's sub-part of rank r's slice: [lo(r), hi(r))
+  auto span = [&](int r, int64_t& lo, int64_t& hi) {
+    const int64_t s0 = per_rank * r, s1 = s0 + per_rank < nvec ? s0 + per_rank : nvec;
+    lo = s0 + per_blk * blockIdx.x;
+    hi = lo + per_blk < s1 ? lo + per_blk : s1;
+    if (lo > s1) lo = s1;
+  };
+  for (int r = 0; r < c.world; ++r) {                 // phase 0
+    int64_t lo, hi;
+    span(r, lo, hi);
+    for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+      const float4 a = reinterpret_cast<const float4*>(g)[2 * i], b = reinterpret_cast<const float4*>(g)[2 * i + 1];
+      reinterpret_cast<uint4*>(stage)[i] = make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w),
+                                                      pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+    }
+  }
+  __threadfence_system();
+  if (!block_barrier(c, &s_fail)) return;
+  {                                                   // phase 1
+    int64_t lo, hi;
+    span(c.rank, lo, hi);
+    constexpr int U = 8;
+    for (int64_t i0 = lo + threadIdx.x; i0 < hi; i0 += static_cast<int64_t>(blockDim.x) * U) {
+      uint4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t i = i0 + static_cast<int64_t>(u) * blockDim.x;
+        if (i < hi) v[u] = mc_ld_reduce_bf16x8(stage_mc + 8 * i);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t i = i0 + static_cast<int64_t>(u) * blockDim.x;
+        if (i < hi) {
+          uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const float2 f = unpack_bf16x2(w[t]);
+            w[t] = pack_bf16x2(f.x * scale, f.y * scale);
+          }
+          mc_st_bf16x8(stage_mc + 8 * i, make_uint4(w[0], w[1], w[2], w[3]));
+        }
+      }
+    }
+  }
+  __threadfence_system();
+  if (!block_barrier(c, &s_fail)) return;
+  for (int r = 0; r < c.world; ++r) {                 // phase 2
+    int64_t lo, hi;
+    span(r, lo, hi);
+    for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+      const uint4 u = reinterpret_cast<const uint4*>(stage)[i];
+      const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+      reinterpret_cast<float4*>(g)[2 * i] = make_float4(a.x, a.y, b.x, b.y);
+      reinterpret_cast<float4*>(g)[2 * i + 1] = make_float4(cc.x, cc.y, d.x, d.y);
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -329,6 +420,16 @@ allgather_kernel(const CommCtx c, int64_t src_off_bytes, int64_t shard_bytes, ui
   }
 }
 
+// busy-wait of a given length on the stream (race-stress tests skew the ranks with it)
+__global__ void spin_kernel(long long ns) {
+  long long t0, t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  do {
+    __nanosleep(200);
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  } while (t - t0 < ns);
+}
+
 __global__ void barrier_kernel(const CommCtx c) {
   __shared__ int s_fail;
   __threadfence_system();
@@ -364,6 +465,26 @@ int b200_allreduce(const void* bufs_dev, void* mc_ptr, const void* flags_dev, in
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (mc_ptr != nullptr) allreduce_kernel<true><<<nblocks, 512, 0, st>>>(c, offset_elems, n_elems, scale);
   else allreduce_kernel<false><<<nblocks, 512, 0, st>>>(c, offset_elems, n_elems, scale);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// Bucket all-reduce with bf16 on the wire (the "bf16/fp32 cast" variant of the DDP reducer, main-ddp.py:55,124):
+// grad (local fp32 arena) elements [offset, offset + n) are summed over the ranks, scaled, and written back; the
+// values travel as bf16 through `stage` (symmetric bf16 buffer with a multicast mapping, same element offsets),
+// accumulated in fp32 inside the switch.  The result carries one bf16 rounding of every rank's addend and one of
+// the sum.  Needs NVLS (stage_mc_ptr != NULL); callers fall back to b200_allreduce otherwise.
+int b200_allreduce_bf16(float* grad, const void* stage_bufs_dev, void* stage_mc_ptr, const void* flags_dev, int rank,
+                        int world, int64_t offset_elems, int64_t n_elems, float scale, int nblocks, int channel_base,
+                        void* stream) {
+  B200_REQUIRE(n_elems % 8 == 0 && offset_elems % 8 == 0, "allreduce_bf16: offset/count must be multiples of 8");
+  B200_REQUIRE(stage_mc_ptr != nullptr, "allreduce_bf16: needs a multicast mapping of the staging buffer");
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(grad) & 15) == 0, "allreduce_bf16: gradient arena must be 16-byte aligned");
+  if (n_elems == 0) return 0;
+  CommCtx c;
+  int rc = make_ctx(&c, stage_bufs_dev, stage_mc_ptr, flags_dev, rank, world, channel_base, nblocks);
+  if (rc != 0) return rc;
+  allreduce_bf16_kernel<<<nblocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(c, grad, offset_elems, n_elems, scale);
   B200_LAUNCH_CHECK();
   return 0;
 }
@@ -419,6 +540,25 @@ int b200_allgather(const void* src_bufs_dev, const void* flags_dev, int rank, in
   allgather_kernel<<<nblocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(
       c, src_off_bytes, shard_bytes, reinterpret_cast<uint8_t*>(dst), start_barrier);
   B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// Test aids.  b200_spin: keep the stream busy for `ns` nanoseconds (skews ranks against each other).
+// b200_set_comm_timeout_ms: bound of every cross-GPU wait on the current device (default ~20 s); b200_reset_flags
+// clears a flag buffer after a deliberately provoked timeout left its words half-signalled.
+int b200_spin(int64_t ns, void* stream) {
+  spin_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<long long>(ns));
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+int b200_set_comm_timeout_ms(int ms) {
+  B200_REQUIRE(ms > 0, "comm timeout must be positive");
+  int dev = 0, khz = 0;
+  B200_CHECK_CUDA(cudaGetDevice(&dev));
+  B200_CHECK_CUDA(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev));
+  const long long cycles = static_cast<long long>(ms) * (khz > 0 ? khz : 1965000);
+  B200_CHECK_CUDA(cudaMemcpyToSymbol(g_comm_timeout_cycles, &cycles, sizeof(cycles)));
   return 0;
 }
 

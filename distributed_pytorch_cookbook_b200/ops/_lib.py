@@ -51,10 +51,13 @@ _SIGS = {
     "b200_attn_fwd": [P, P, P, I, I, I, I, Fl, P, P],
     "b200_attn_bwd": [P, P, P, P, P, P, P, I, I, I, I, Fl, P, P],
     "b200_allreduce": [P, P, P, I, I, L, L, Fl, I, I, P],
+    "b200_allreduce_bf16": [P, P, P, P, I, I, L, L, Fl, I, I, P],
     "b200_rs_adamw": [P, P, P, I, I, L, L, Fl, P, P, P, P, P, Fl, Fl, Fl, Fl, I, I, I, P],
     "b200_reduce_scatter": [P, P, P, I, I, L, L, Fl, P, I, I, I, P],
     "b200_allgather": [P, P, I, I, L, L, P, I, I, I, P],
     "b200_ag_gemm_bf16": [P, P, P, I, I, I, I, I, I, P, P, I, I, I, P, P, P, L, L, L, P, I, P],
+    "b200_spin": [L, P],
+    "b200_set_comm_timeout_ms": [I],
     "b200_barrier": [P, I, I, I, P],
     "b200_smoke": [P],
     "b200_gemm_set_debug_buffer": [P],

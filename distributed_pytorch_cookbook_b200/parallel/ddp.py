@@ -55,12 +55,21 @@ def plan_buckets(params: List[torch.nn.Parameter], offsets: List[int], total: in
 
 class GradReducer:
     def __init__(self, arena: ParamArena, group=None, bucket_mb: float = 4.0, transport: str = "nccl",
-                 symm: Optional[SymmContext] = None, grad_buf=None, nblocks: int = 16):
+                 symm: Optional[SymmContext] = None, grad_buf=None, nblocks: int = 16, comm_dtype: str = "fp32"):
         self.arena, self.group, self.transport = arena, group, transport
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.symm, self.grad_buf, self.nblocks = symm, grad_buf, nblocks
         cap = max(int(bucket_mb * (1 << 20) / 4), 1)
+        self.cap = cap
+        # --comm_dtype bf16: gradients cross NVLink as bf16 (fp32 accumulation in the switch) through a symmetric
+        # bf16 staging buffer; needs the NVLS multicast mapping, otherwise the fp32 kernel is used
+        self.stage_buf = None
+        if comm_dtype == "bf16" and transport == "symm" and self.world > 1:
+            buf = symm.alloc(arena.total, torch.bfloat16)
+            if buf.mc_ptr:
+                self.stage_buf = buf
+        self.comm_dtype = "bf16" if self.stage_buf is not None else "fp32"
         self.buckets = plan_buckets(arena.params, arena.offsets, arena.total, cap)
         self.bucket_of = {}
         for b, (_, _, idxs) in enumerate(self.buckets):
@@ -86,6 +95,7 @@ class GradReducer:
         self.remaining = [len(idxs) for _, _, idxs in self.buckets]
         self.launched = [False] * len(self.buckets)
         self.events = [None] * len(self.buckets)
+        self.sub_events = {}
         self.order = []
         self.works = []
         self.active = True
@@ -100,7 +110,10 @@ class GradReducer:
         if self.remaining[b] == 0 and not self.launched[b]:
             self._launch(b)
 
-    def _launch(self, b: int):
+    def _launch(self, b: int, tail: bool = False):
+        """Reduce bucket b.  ``tail``: the bucket is reduced after backward has ended (nothing left to overlap
+        with, nothing to disturb), so it goes out in sub-ranges of at most the bucket cap - each with its own
+        event, so AdamW of sub-range i runs under the all-reduce of sub-range i+1 - on a wider grid."""
         self.launched[b] = True
         self.order.append(b)
         lo, hi, _ = self.buckets[b]
@@ -110,13 +123,26 @@ class GradReducer:
             ev = torch.cuda.Event()
             ev.record()
             self.comm_stream.wait_event(ev)
+            spans = [(lo, hi)]
+            if tail and (hi - lo) > self.cap:
+                step = (self.cap + 7) // 8 * 8
+                spans = [(a, min(a + step, hi)) for a in range(lo, hi, step)]
+            max_blocks = 2 * self.nblocks if tail else self.nblocks       # tail: the rs_adamw channel range is idle too
             with torch.cuda.stream(self.comm_stream):
-                nblocks = max(4, min(self.nblocks, ((hi - lo) * 4) >> 18))      # ~256 KiB of bucket per block
-                _lib.call("b200_allreduce", self.grad_buf.ptrs_dev, self.grad_buf.mc_ptr or None,
-                          self.symm.flags.ptrs_dev, self.rank, self.world, lo, hi - lo, 1.0 / self.world,
-                          nblocks, CH_ALLREDUCE, self.comm_stream.cuda_stream)
-                self.events[b] = torch.cuda.Event()
-                self.events[b].record(self.comm_stream)
+                for a, z in spans:
+                    nblocks = max(4, min(max_blocks, 128, ((z - a) * 4) >> 18))      # ~256 KiB of bucket per block
+                    if self.stage_buf is not None and a % 8 == 0 and (z - a) % 8 == 0:
+                        _lib.call("b200_allreduce_bf16", self.arena.grad.data_ptr(), self.stage_buf.ptrs_dev,
+                                  self.stage_buf.mc_ptr, self.symm.flags.ptrs_dev, self.rank, self.world, a, z - a,
+                                  1.0 / self.world, nblocks, CH_ALLREDUCE, self.comm_stream.cuda_stream)
+                    else:
+                        _lib.call("b200_allreduce", self.grad_buf.ptrs_dev, self.grad_buf.mc_ptr or None,
+                                  self.symm.flags.ptrs_dev, self.rank, self.world, a, z - a, 1.0 / self.world,
+                                  nblocks, CH_ALLREDUCE, self.comm_stream.cuda_stream)
+                    e = torch.cuda.Event()
+                    e.record(self.comm_stream)
+                    self.sub_events.setdefault(b, []).append((a, z, e))
+                self.events[b] = self.sub_events[b][-1][2]
         elif self.cuda:
             ev = torch.cuda.Event()
             ev.record()
@@ -139,7 +165,7 @@ class GradReducer:
         embedding, whose gradient only completes at the very end of backward)."""
         for b in range(len(self.buckets)):
             if not self.launched[b]:
-                self._launch(b)
+                self._launch(b, tail=True)
         for w in self.works:
             w.wait()
         self.works = []
@@ -168,8 +194,9 @@ class GradReducer:
         for lo, hi in merged:
             optimizer.step(lo, hi, tick=first)
             first = False
-        cur.wait_event(self.events[tail])
-        optimizer.step(self.buckets[tail][0], self.buckets[tail][1], tick=False)
+        for a, z, e in self.sub_events.get(tail) or [(self.buckets[tail][0], self.buckets[tail][1], self.events[tail])]:
+            cur.wait_event(e)
+            optimizer.step(a, z, tick=False)
 
 
 class DDPStrategy:
@@ -215,7 +242,9 @@ class DDPStrategy:
         self.comm_kind = transport
         self._verify_replicas()
         self.reducer = GradReducer(self.arena, self.group, getattr(args, "bucket_mb", 4.0), transport,
-                                   self.symm, grad_buf, nblocks=64)
+                                   self.symm, grad_buf, nblocks=64, comm_dtype=getattr(args, "comm_dtype", "fp32"))
+        if transport == "symm":
+            self.comm_kind = f"symm:{self.reducer.comm_dtype}"
         self.use_graph = (transport == "symm" and not getattr(args, "disable_cuda_graph", False)) or \
                          (self.world == 1 and native_ok and not getattr(args, "disable_cuda_graph", False))
 

@@ -262,7 +262,7 @@ class PipeStrategy:
         if dp > 1:
             from .ddp import GradReducer
             self.reducer = GradReducer(self.arena, self.dp_group, getattr(args, "bucket_mb", 4.0), transport,
-                                       symm, holder.get("buf"))
+                                       symm, holder.get("buf"), comm_dtype=getattr(args, "comm_dtype", "fp32"))
         self.mb = args.batch_size // self.M
         assert self.mb * self.M == args.batch_size, "batch_size must be divisible by the number of micro-batches"
         self.T = args.sequence_length - 1

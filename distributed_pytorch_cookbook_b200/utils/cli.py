@@ -51,6 +51,9 @@ def build_parser(recipe: str = "single") -> argparse.ArgumentParser:
         x.add_argument("--bucket_mb", type=float, default=4.0)
         x.add_argument("--comm", choices=["auto", "symm", "nccl"], default="auto",
                        help="gradient all-reduce transport: own NVLink kernels or NCCL")
+        x.add_argument("--comm_dtype", choices=["fp32", "bf16"], default="fp32",
+                       help="own NVLink all-reduce: what crosses the wire (bf16 = half the bytes, fp32 accumulation "
+                            "in the switch, one extra bf16 rounding of every addend and of the sum)")
     if recipe == "fsdp":
         x.add_argument("--comm", choices=["auto", "symm", "nccl"], default="auto")
     if recipe in ("pipe", "pipe-ddp"):

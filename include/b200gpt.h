@@ -151,6 +151,11 @@ int b200_attn_bwd(const void* qkv_bf16, const void* out_bf16, const void* dout_b
 int b200_allreduce(const void* bufs_dev, void* mc_ptr, const void* flags_dev, int rank, int world,
                    int64_t offset_elems, int64_t n_elems, float scale, int nblocks, int channel_base,
                    void* stream);
+/* same reduction with bf16 on the wire and fp32 accumulation in the switch: grad is the LOCAL fp32 arena, stage a
+ * symmetric bf16 buffer of the same element geometry (needs its multicast mapping)  (main-ddp.py:55,124) */
+int b200_allreduce_bf16(float* grad, const void* stage_bufs_dev, void* stage_mc_ptr, const void* flags_dev, int rank,
+                        int world, int64_t offset_elems, int64_t n_elems, float scale, int nblocks, int channel_base,
+                        void* stream);
 /* reduce-scatter of this rank's shard fused with the sharded AdamW update and the bf16 shard
  * write  (FSDP post-backward reduce-scatter + optimizer step, main-fsdp.py:138-140) */
 int b200_rs_adamw(const void* grad_bufs_dev, void* grad_mc_ptr, const void* flags_dev, int rank, int world,
@@ -168,6 +173,9 @@ int b200_allgather(const void* src_bufs_dev, const void* flags_dev, int rank, in
                    int64_t src_off_bytes, int64_t shard_bytes, void* dst, int start_barrier, int nblocks,
                    int channel_base, void* stream);
 int b200_barrier(const void* flags_dev, int rank, int world, int channel, void* stream);
+/* test aids: busy-wait on the stream; bound of every cross-GPU wait on the current device (default ~20 s) */
+int b200_spin(int64_t ns, void* stream);
+int b200_set_comm_timeout_ms(int ms);
 
 #ifdef __cplusplus
 }

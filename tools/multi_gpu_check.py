@@ -182,8 +182,14 @@ if "ddp" in which:
     l_nccl, sd_nccl, _ = run_strategy(DDPStrategy, "nccl", graph=False)
     l_symm, sd_symm, st = run_strategy(DDPStrategy, "symm", graph=True)
     d = max(abs(a - b) for a, b in zip(l_nccl, l_symm))
-    report("ddp_symm_vs_nccl", st.comm_kind == "symm" and d < 2e-2 and l_symm[-1] < l_symm[0] and dev_err() == 0,
+    report("ddp_symm_vs_nccl", st.comm_kind.startswith("symm") and d < 2e-2 and l_symm[-1] < l_symm[0] and dev_err() == 0,
            losses_symm=l_symm, losses_nccl=l_nccl, graph=bool(st._graphed and st._graphed.graph))
+
+if "ddp" in which:
+    l_bf, _, st = run_strategy(DDPStrategy, "symm", graph=True, extra={"comm_dtype": "bf16"})
+    d = max(abs(a - b) for a, b in zip(l_nccl, l_bf))
+    report("ddp_bf16_wire_vs_nccl", d < 3e-2 and l_bf[-1] < l_bf[0] and dev_err() == 0, losses=l_bf, comm=st.comm_kind,
+           max_loss_diff=d)
 
 if "fsdp" in which:
     from distributed_pytorch_cookbook_b200.parallel.fsdp import FSDPStrategy
@@ -193,37 +199,46 @@ if "fsdp" in which:
     d = max(abs(a - b) for a, b in zip(l_nccl, l_symm))
     d2 = max(abs(a - b) for a, b in zip(l_gr, l_symm))
     worst = max((sd_nccl[k] - sd_symm[k]).abs().max().item() for k in sd_nccl) if rank == 0 else 0.0
-    report("fsdp_symm_vs_nccl", st.comm_kind == "symm" and d < 2e-2 and d2 < 2e-2 and l_symm[-1] < l_symm[0]
+    report("fsdp_symm_vs_nccl", st.comm_kind.startswith("symm") and d < 2e-2 and d2 < 2e-2 and l_symm[-1] < l_symm[0]
            and dev_err() == 0, losses_symm=l_symm, losses_nccl=l_nccl, losses_graph=l_gr, max_param_diff=worst)
 
 if "pipe" in which and world >= 2:
     from distributed_pytorch_cookbook_b200.parallel.pipe import PipeStrategy
     # every rank feeds the same (rank-0) data slice in pipeline mode: emulate by forcing rank 0's slice
-    def run_pipe(schedule, dp):
+    def run_pipe(schedule, dp, graph=False, ckpt="never", steps=6):
         from distributed_pytorch_cookbook_b200.trainer import build_model
         torch.manual_seed(0)
-        ns = SimpleNamespace(**CFG, disable_amp=False, disable_cuda_graph=True, bucket_mb=1.0, comm="auto")
+        ns = SimpleNamespace(**CFG, disable_amp=False, disable_cuda_graph=not graph, bucket_mb=1.0, comm="auto")
         model = build_model(ns, CFG["vocab_size"])
-        st = PipeStrategy(num_stages=world // dp, num_microbatches=4, schedule=schedule, dp_size=dp)
+        st = PipeStrategy(num_stages=world // dp, num_microbatches=4, schedule=schedule, dp_size=dp, checkpoint=ckpt)
         st.setup(model, ns, dev)
         g = torch.Generator().manual_seed(3)
-        ids_all = torch.randint(0, CFG["vocab_size"], (4, CFG["batch_size"] * dp, CFG["sequence_length"] - 1), generator=g)
+        ids_all = torch.randint(0, CFG["vocab_size"], (steps, CFG["batch_size"] * dp, CFG["sequence_length"] - 1), generator=g)
         pos = torch.arange(CFG["sequence_length"] - 1).unsqueeze(0).repeat(CFG["batch_size"], 1).to(dev)
         out = []
         r = rank % dp
-        for s in range(4):
+        for s in range(steps):
             ids = ids_all[s, r * CFG["batch_size"]:(r + 1) * CFG["batch_size"]].to(dev)
-            out.append(float(st.train_step({"input_ids": ids, "position_ids": pos}, ids, amp=True)))
+            l = st.train_step({"input_ids": ids, "position_ids": pos}, ids, amp=True).detach().float().reshape(1).clone()
+            dist.all_reduce(l, op=dist.ReduceOp.MAX)          # the loss lives on the first / last stage
+            out.append(float(l))
         sd = st.state_dict()
         torch.cuda.synchronize(); dist.barrier()
+        st.close()
         return out, sd, st
-    for schedule in ("gpipe", "1f1b"):
-        out, sd, st = run_pipe(schedule, 1)
-        report(f"pipe_{schedule}", out[-1] < out[0] and all(x == x for x in out) and dev_err() == 0, losses=out,
-               comm=st.comm_kind, keys=len(sd) if sd else None)
+    base = None
+    for schedule, graph, ckpt in (("gpipe", False, "never"), ("1f1b", False, "never"), ("1f1b", True, "never"),
+                                  ("gpipe", True, "except_last")):
+        out, sd, st = run_pipe(schedule, 1, graph, ckpt)
+        base = base or out
+        d = max(abs(a - b) for a, b in zip(out, base))
+        graphs = sum(1 for sl in st.slots if sl.fgraph is not None) if graph else 0
+        report(f"pipe_{schedule}_{'graph' if graph else 'eager'}_{ckpt}",
+               out[-1] < out[0] and all(x == x for x in out) and d < 2e-2 and dev_err() == 0, losses=out,
+               max_diff_vs_first=d, comm=st.comm_kind, keys=len(sd) if sd else None)
     if world >= 4 and world % 2 == 0:
-        out, sd, st = run_pipe("1f1b", world // 2)
-        report("pipe_ddp", out[-1] < out[0] and dev_err() == 0, losses=out, comm=st.comm_kind)
+        out, sd, st = run_pipe("1f1b", world // 2, True)
+        report("pipe_ddp", out[-1] < out[0] and all(x == x for x in out) and dev_err() == 0, losses=out, comm=st.comm_kind)
 
 dist.barrier()
 dist.destroy_process_group()
