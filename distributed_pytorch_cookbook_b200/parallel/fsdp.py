@@ -21,6 +21,14 @@ groups per unit - ``big`` (matrices, consumed by the tensor-core kernels as bf16
   available), applies 1/world, runs AdamW on its master shard and writes the bf16 shard the peers
   will gather next step.  Reduce-scatter, cast and optimizer are one kernel; no NCCL on the path.
 
+Two memory modes.  *Resident* (default): the gathered bf16 weights and the full-size gradient buffer stay
+allocated for the whole step, so backward needs no second all-gather - the fastest choice while the model fits
+(10 B/param un-sharded + 18 B/param / world).  *Sharded* (``--reshard_after_forward``, the reference's
+FULL_SHARD, main-fsdp.py:60-69): units are gathered into two rotating unit-sized buffers, freed for reuse as
+soon as the next-but-one unit needs the slot, gathered again right before their backward (prefetched one unit
+ahead), and their gradients live in a two-unit ring that is reduce-scattered into the shard-sized buffer - per
+GPU that is 18 (+4) B/param / world plus two units, so the model size scales with the number of GPUs.
+
 Fallback transports (``--comm nccl`` or CPU/gloo) run the same schedule with
 ``all_gather_into_tensor`` / ``all_reduce`` + the same AdamW maths in PyTorch.
 ``--cpu_offload`` keeps master shards and moments in pinned host memory and steps them on the CPU.
@@ -152,9 +160,31 @@ class FSDPStrategy:
                 return buf.tensor, buf
             return torch.zeros(n, dtype=dtype, device=dev), None
 
-        self.full_fp32 = torch.zeros(self.G, dtype=f32, device=dev)
-        self.full_bf16 = torch.zeros(self.G, dtype=bf16, device=dev) if self.native else None
-        self.grads, self.grads_buf = alloc(self.G, f32, True)
+        import os
+        self.reshard = bool(getattr(args, "reshard_after_forward", False)) or os.environ.get("B200GPT_FSDP_RESHARD") == "1"
+        assert not (self.reshard and self.cpu_offload), "--reshard_after_forward and --cpu_offload are not combined"
+        # "full space": where gathered weights and un-reduced gradients live.  Resident mode: the whole model
+        # (offset = g.base).  Sharded mode: two unit-sized slots, unit u uses slot u % 2.
+        for ui, unit in enumerate(self.units):
+            off = 0
+            for g in unit:
+                g.unit, g.local = ui, off
+                off += g.n
+        if self.reshard:
+            self.Umax = _round_up(max(sum(g.n for g in u) for u in self.units), ALIGN * self.world)
+            for g in self.groups:
+                g.fbase = (g.unit % 2) * self.Umax + g.local
+            self.F = 2 * self.Umax
+        else:
+            for g in self.groups:
+                g.fbase = g.base
+            self.F = self.G
+        self.slot_unit = [None, None]                # sharded mode: which unit's weights each slot holds
+        self.slot_events = [[], []]                  # ... and the reduce-scatters still reading its gradient slot
+        init_fp32 = torch.zeros(self.G, dtype=f32, device=dev) if self.reshard else None
+        self.full_fp32 = torch.zeros(self.F, dtype=f32, device=dev)
+        self.full_bf16 = torch.zeros(self.F, dtype=bf16, device=dev) if self.native else None
+        self.grads, self.grads_buf = alloc(self.F, f32, True)
         state_dev = torch.device("cpu") if self.cpu_offload else dev
         if self.cpu_offload:
             pin = cuda
@@ -170,22 +200,27 @@ class FSDPStrategy:
         self.shard_bf16, self.shard_bf16_buf = alloc(Gs, bf16, True) if self.native else (None, None)
         self.hyper = torch.tensor([self.lr, 0.0, 0.0, 0.0], dtype=f32, device=dev)
         self.host_step = 0
-        import os
         # B200GPT_FSDP_RS=fused: the one-kernel reduce-scatter + AdamW (b200_rs_adamw, up to 64 resident blocks);
         # default: small-grid b200_reduce_scatter into a shard-sized buffer + b200_adamw behind it
         self.rs_split = transport == "symm" and os.environ.get("B200GPT_FSDP_RS", "split") != "fused"
         self.rs_blocks = int(os.environ.get("B200GPT_FSDP_RS_BLOCKS", "8"))
-        self.shard_grad = torch.zeros(Gs, dtype=f32, device=dev) if self.rs_split else None
+        self.shard_grad = torch.zeros(Gs, dtype=f32, device=dev) if (self.rs_split or transport == "nccl") else None
 
         # re-point parameters / gradients at the flat buffers and cut the shards
         self.group_of = {}
+        self.param_names = {id(p): n for n, p in self.model.named_parameters()}
         with torch.no_grad():
             for g in self.groups:
+                src = init_fp32 if self.reshard else self.full_fp32      # where the initial values are collected
                 for p, o in zip(g.params, g.offsets):
                     n = p.numel()
-                    lo = g.base + o
-                    self.full_fp32[lo:lo + n].copy_(p.data.reshape(-1))
-                    p.data = self.full_fp32[lo:lo + n].view(p.shape)
+                    lo = g.fbase + o
+                    src[g.base + o:g.base + o + n].copy_(p.data.reshape(-1))
+                    if self.reshard and self.native and g.kind == "big":
+                        # consumed as bf16 only: the fp32 tensor keeps its shape but owns one element
+                        p.data = torch.zeros(1, dtype=f32, device=dev).expand(p.shape)
+                    else:
+                        p.data = self.full_fp32[lo:lo + n].view(p.shape)
                     p.grad = self.grads[lo:lo + n].view(p.shape)
                     if self.native and g.kind == "big":
                         p._b200_bf16 = self.full_bf16[lo:lo + n].view(p.shape)
@@ -193,10 +228,10 @@ class FSDPStrategy:
                     self.group_of[id(p)] = g
                     p.register_post_accumulate_grad_hook(self._on_grad_ready)
                 s_lo = g.base + self.rank * g.shard_n
-                self.master[g.shard_base:g.shard_base + g.shard_n].copy_(self.full_fp32[s_lo:s_lo + g.shard_n])
+                self.master[g.shard_base:g.shard_base + g.shard_n].copy_(src[s_lo:s_lo + g.shard_n])
                 if self.native:
-                    self.shard_bf16[g.shard_base:g.shard_base + g.shard_n].copy_(
-                        self.full_fp32[s_lo:s_lo + g.shard_n])
+                    self.shard_bf16[g.shard_base:g.shard_base + g.shard_n].copy_(src[s_lo:s_lo + g.shard_n])
+            del init_fp32
             if self.cpu_offload:
                 self.master_dev.copy_(self.master, non_blocking=True)
         # fused all-gather: big (bf16) groups are not gathered by a separate kernel - the first GEMM that
@@ -207,7 +242,8 @@ class FSDPStrategy:
         # 91.5 ms.  B200GPT_FUSED_AG=1 / 0 forces it; unset, it is used for model widths >= 1024.
         fa = os.environ.get("B200GPT_FUSED_AG", "")
         wide = int(getattr(model, "dim", 0) or 0) >= 1024
-        self.fused_ag = transport == "symm" and (fa == "1" or (fa != "0" and wide))
+        # (sharded mode re-gathers every unit for its backward on the side stream anyway: no fused gather there)
+        self.fused_ag = transport == "symm" and (fa == "1" or (fa != "0" and wide)) and not self.reshard
         for g in self.groups:
             g.fused = False
         if self.fused_ag:
@@ -233,8 +269,21 @@ class FSDPStrategy:
         self.active = False
         self.skip_comm = False
         # forward pre-hooks: make the unit's weights resident (and prefetch the next unit)
-        for ui, mods in enumerate(plan_units(self.model)):
+        unit_mods = plan_units(self.model)
+        for ui, mods in enumerate(unit_mods):
             mods[0].register_forward_pre_hook(lambda m, inp, ui=ui: self._pre_forward(ui))
+            if self.reshard and ui < len(unit_mods) - 1:
+                # sharded mode: the gradient of a unit's output arriving is the cue to bring its weights back
+                mods[-1].register_forward_hook(lambda m, inp, out, ui=ui: self._arm_backward(ui, out))
+        # the native path reads norm_out / lm_head weights without calling those modules (models/gpt.py head_input,
+        # loss), so their forward pre-hook never fires there: hook the head unit on head_input itself
+        head_ui = len(unit_mods) - 1
+        orig_head_input = self.model.head_input
+
+        def head_input(x, _orig=orig_head_input, _ui=head_ui):
+            self._pre_forward(_ui)
+            return _orig(x)
+        self.model.head_input = head_input
         if cuda:
             torch.cuda.synchronize(dev)
         if dist.is_initialized():
@@ -245,13 +294,13 @@ class FSDPStrategy:
     def _gather_dtype(self, g: ShardGroup):
         return torch.bfloat16 if (self.native and g.kind == "big") else torch.float32
 
-    def _gather(self, g: ShardGroup, dtype=None):
-        """All-gather one shard group into the local full buffer (on the side stream on CUDA)."""
+    def _gather(self, g: ShardGroup, dtype=None, dest=None):
+        """All-gather one shard group into the local full buffer (on the side stream on CUDA), or into ``dest``."""
         dtype = dtype or self._gather_dtype(g)
         esz = 2 if dtype == torch.bfloat16 else 4
         full = self.full_bf16 if dtype == torch.bfloat16 else self.full_fp32
         shard = self.shard_bf16 if dtype == torch.bfloat16 else self.master_dev
-        full_view = full[g.base:g.base + g.n]
+        full_view = dest if dest is not None else full[g.fbase:g.fbase + g.n]
         shard_view = shard[g.shard_base:g.shard_base + g.shard_n]
         if self.world == 1:
             full_view.copy_(shard_view)
@@ -284,9 +333,22 @@ class FSDPStrategy:
     def _ensure(self, g: ShardGroup):
         if g.fused:
             return                                        # gathered inside the consuming GEMMs
+        if self.reshard:
+            slot = g.unit % 2
+            if self.slot_unit[slot] != g.unit:            # the slot held the unit two places away: evict it
+                if self.slot_unit[slot] is not None:
+                    for h in self.units[self.slot_unit[slot]]:
+                        h.gathered_version = 0
+                self.slot_unit[slot] = g.unit
         if g.gathered_version != self.version:
             self._gather(g)
             g.gathered_version = self.version
+
+    def _wait_unit(self, ui: int):
+        if self.device.type == "cuda":
+            for g in self.units[ui]:
+                if g.event is not None:
+                    torch.cuda.current_stream().wait_event(g.event)
 
     def _pre_forward(self, ui: int):
         for g in self.units[ui]:
@@ -294,10 +356,34 @@ class FSDPStrategy:
         if ui + 1 < len(self.units):                      # prefetch the next unit under this one's compute
             for g in self.units[ui + 1]:
                 self._ensure(g)
-        if self.device.type == "cuda":
-            for g in self.units[ui]:
-                if g.event is not None:
-                    torch.cuda.current_stream().wait_event(g.event)
+        self._wait_unit(ui)
+
+    # -- sharded mode: weights come back, and the gradient slot is recycled, right before a unit's backward --------
+    def _arm_backward(self, ui: int, out):
+        t = out[0] if isinstance(out, (tuple, list)) else out
+        if self.active and torch.is_tensor(t) and t.requires_grad:
+            t.register_hook(lambda grad, ui=ui: self._pre_backward(ui))
+
+    def _pre_backward(self, ui: int):
+        if not self.active or self.bwd_seen.get(ui):
+            return None
+        self.bwd_seen[ui] = True
+        cuda = self.device.type == "cuda"
+        # this unit's gradient slot last held unit ui + 2: its reduce-scatters must be done reading, then clear it
+        slot = ui % 2
+        if ui + 2 < len(self.units):
+            if cuda:
+                for e in self.slot_events[slot]:
+                    torch.cuda.current_stream().wait_event(e)
+            self.slot_events[slot] = []
+            self.grads[slot * self.Umax:(slot + 1) * self.Umax].zero_()
+        for g in self.units[ui]:
+            self._ensure(g)
+        if ui > 0:                                        # prefetch the unit whose backward comes next
+            for g in self.units[ui - 1]:
+                self._ensure(g)
+        self._wait_unit(ui)
+        return None
 
     # ------------------------------------------------------------------------------
     def _on_grad_ready(self, p):
@@ -315,7 +401,7 @@ class FSDPStrategy:
         b1, b2 = self.betas
         cuda = self.device.type == "cuda"
         sb, sn = g.shard_base, g.shard_n
-        lo = g.base + self.rank * sn
+        lo = g.fbase + self.rank * sn
         ctx = nullcontext()
         if cuda:
             ev = torch.cuda.Event()
@@ -323,6 +409,14 @@ class FSDPStrategy:
             self.comm_stream.wait_event(ev)
             ctx = torch.cuda.stream(self.comm_stream)
         with ctx:
+            self._reduce_and_step_on_stream(g, sb, sn, lo, b1, b2, cuda)
+            if cuda and self.reshard:
+                e = torch.cuda.Event()
+                e.record(self.comm_stream)
+                self.slot_events[g.unit % 2].append(e)
+
+    def _reduce_and_step_on_stream(self, g, sb, sn, lo, b1, b2, cuda):
+        if True:
             if self.skip_comm:                            # measurement only: AdamW on the shard's local gradients
                 pb = self.shard_bf16.data_ptr() + 2 * sb if g.kind == "big" else None
                 _lib.call("b200_adamw", self.master.data_ptr() + 4 * sb, self.grads.data_ptr() + 4 * lo,
@@ -351,11 +445,15 @@ class FSDPStrategy:
                           self.exp_avg_sq.data_ptr() + 4 * sb, pb, self.hyper.data_ptr(), b1, b2, self.eps,
                           self.wd, 1, nblocks, CH_RS_ADAMW, self.comm_stream.cuda_stream)
                 return
-            gview = self.grads[g.base:g.base + g.n]
+            gview = self.grads[g.fbase:g.fbase + g.n]
+            gs = self.grads[lo:lo + sn]
             if self.world > 1:
                 gview.mul_(1.0 / self.world)
-                dist.all_reduce(gview, group=self.group)   # gloo has no reduce_scatter; NCCL path keeps parity
-            gs = self.grads[lo:lo + sn]
+                if self.comm_kind == "nccl" and self.shard_grad is not None:
+                    gs = self.shard_grad[sb:sb + sn]       # the reference's collective: reduce-scatter into the shard
+                    dist.reduce_scatter_tensor(gs, gview, group=self.group)
+                else:
+                    dist.all_reduce(gview, group=self.group)   # gloo has no reduce_scatter
             if self.cpu_offload:
                 self.shard_grad_host[sb:sb + sn].copy_(gs, non_blocking=False)
                 adamw_torch_(self.master[sb:sb + sn], self.shard_grad_host[sb:sb + sn], self.exp_avg[sb:sb + sn],
@@ -389,6 +487,8 @@ class FSDPStrategy:
             self.hyper[1] += 1
         for g in self.groups:
             g.ready = 0
+        self.bwd_seen = {}
+        self.slot_events = [[], []]
         self.active = True
         from ..utils import nvtx
         with self._autocast(amp), nvtx.phase("forward (+ all-gather)"):
@@ -483,13 +583,54 @@ class FSDPStrategy:
         if self.device.type == "cuda":
             torch.cuda.current_stream().wait_stream(self.comm_stream)
 
+    def _full_state(self):
+        """Sharded mode, collective: the canonical fp32 state_dict assembled from a temporary full-size buffer
+        (the only moment a whole model's worth of fp32 exists on a GPU in this mode)."""
+        from collections import OrderedDict
+        if self.device.type == "cuda":
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        flat = torch.empty(self.G, dtype=torch.float32, device=self.device)
+        for g in self.groups:
+            self._gather(g, torch.float32, dest=flat[g.base:g.base + g.n])
+        if self.device.type == "cuda":
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        by_name = {}
+        for g in self.groups:
+            for p, o in zip(g.params, g.offsets):
+                by_name[self.param_names[id(p)]] = flat[g.base + o:g.base + o + p.numel()].view(p.shape).cpu().clone()
+        return OrderedDict((k, by_name[k]) for k, _ in self.model.named_parameters())
+
     def generation_model(self):
         """All ranks gather (collective) so that rank 0 can run the un-sharded model - avoids the
         reference's rank-0-only forward through FSDP, which deadlocks."""
+        if self.reshard:
+            sd = self._full_state()
+            if self.rank != 0:
+                return None
+            if getattr(self, "_gen_model", None) is None:
+                m = self.model
+                self._gen_model = type(m)(dim=m.dim, head_dim=m.head_dim, heads=m.heads, num_layers=m.num_layers,
+                                          vocab_size=m.vocab_size,
+                                          max_position_embeddings=m.max_position_embeddings).to(self.device)
+            self._gen_model.load_state_dict(sd)
+            for p in self._gen_model.parameters():
+                if hasattr(p, "_b200_bf16_version"):
+                    p._b200_bf16_version = -1
+            return self._gen_model
         self.gather_full_fp32()
         return self.model
 
     def state_dict(self):
         from ..utils import canonical_state_dict
+        if self.reshard:
+            return self._full_state()
         self.gather_full_fp32()
         return canonical_state_dict(self.model)
+
+    def memory_bytes(self):
+        """Bytes this rank holds for parameters / gradients / optimizer state (what --reshard_after_forward shrinks)."""
+        def nbytes(*ts):
+            return sum(t.numel() * t.element_size() for t in ts if t is not None)
+        return {"gathered_params": nbytes(self.full_fp32, self.full_bf16), "gradients": nbytes(self.grads, self.shard_grad),
+                "shards_and_optimizer": nbytes(self.master, self.shard_bf16, self.exp_avg, self.exp_avg_sq),
+                "mode": "sharded" if self.reshard else "resident", "world": self.world, "params": self.G}

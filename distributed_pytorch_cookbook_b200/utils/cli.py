@@ -56,6 +56,9 @@ def build_parser(recipe: str = "single") -> argparse.ArgumentParser:
                             "in the switch, one extra bf16 rounding of every addend and of the sum)")
     if recipe == "fsdp":
         x.add_argument("--comm", choices=["auto", "symm", "nccl"], default="auto")
+        x.add_argument("--reshard_after_forward", action="store_true",
+                       help="memory-sharded mode (the reference's FULL_SHARD): gathered weights and gradients live in "
+                            "two rotating unit-sized buffers, units are re-gathered for their backward")
     if recipe in ("pipe", "pipe-ddp"):
         x.add_argument("--num_stages", type=int, default=0, help="0 = world size (pipe) / 2 (pipe-ddp)")
         x.add_argument("--num_microbatches", type=int, default=0, help="0 = num_stages (reference chunks=num_stages)")

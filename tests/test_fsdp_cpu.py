@@ -35,14 +35,14 @@ def test_shard_plan_index_math():
         assert [g.kind for g in units[-1]] == ["small", "big"]
 
 
-def _fsdp_worker(rank, world, cpu_offload):
+def _fsdp_worker(rank, world, cpu_offload, reshard=False):
     from distributed_pytorch_cookbook_b200 import TransformerDecoderLM
     from distributed_pytorch_cookbook_b200.parallel.fsdp import FSDPStrategy
     torch.manual_seed(0)
     model = TransformerDecoderLM(**CFG)
     strat = FSDPStrategy(cpu_offload=cpu_offload)
     args = SimpleNamespace(learning_rate=1e-2, disable_amp=True, comm="auto", disable_cuda_graph=True,
-                           cpu_offload=cpu_offload)
+                           cpu_offload=cpu_offload, reshard_after_forward=reshard)
     strat.setup(model, args, "cpu")
     g = torch.Generator().manual_seed(1)
     ids_all = torch.randint(0, CFG["vocab_size"], (3, 4 * world, 12), generator=g)
@@ -54,13 +54,26 @@ def _fsdp_worker(rank, world, cpu_offload):
     ev = strat.eval_step({"input_ids": ids_all[0, :4], "position_ids": pos}, ids_all[0, :4], amp=False)
     sd = strat.state_dict()
     shard_elems = strat.master.numel()
+    gen = strat.generation_model()                 # collective; sharded mode hands rank 0 a fresh un-sharded model
+    if rank == 0:
+        with torch.no_grad():
+            assert gen(ids_all[0, :2], pos[:2]).shape == (2, 12, CFG["vocab_size"])
+    mem = strat.memory_bytes()
+    if reshard:
+        # nothing of full-model size is left: two unit-sized slots for weights and for gradients
+        unit = max(sum(g.n for g in u) for u in strat.units)
+        assert strat.full_fp32.numel() == strat.grads.numel() and strat.grads.numel() <= 2 * unit + 2 * 128 * world
+        assert strat.grads.numel() < strat.G
+        assert mem["mode"] == "sharded"
     return {k: v.numpy().copy() for k, v in sd.items()}, losses, float(ev[0]), shard_elems, strat.G
 
 
-@pytest.mark.parametrize("cpu_offload", [False, True])
-def test_fsdp_matches_single_process(cpu_offload):
+@pytest.mark.parametrize("cpu_offload,reshard", [(False, False), (True, False), (False, True)])
+def test_fsdp_matches_single_process(cpu_offload, reshard):
+    """Resident mode, cpu_offload, and the memory-sharded mode (units re-gathered for backward, gradients in a
+    two-unit ring) all train exactly like one process with torch.optim.AdamW."""
     world = 2
-    outs = run_distributed(_fsdp_worker, world, cpu_offload)
+    outs = run_distributed(_fsdp_worker, world, cpu_offload, reshard)
     from distributed_pytorch_cookbook_b200 import TransformerDecoderLM
     torch.manual_seed(0)
     ref = TransformerDecoderLM(**CFG)
