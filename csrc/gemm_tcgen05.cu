@@ -39,7 +39,11 @@ constexpr int GEMM_THREADS = 224;  // CG = 1: TMA producer, MMA issuer, 4 epilog
 // CTA pairs run 8 epilogue warps (two per TMEM lane quarter, each taking half of the tile's columns): with
 // K = 256 a tile's MMAs last ~2 K cycles, less than 4 warps need for a bias/mask/residual epilogue
 template <int CG> constexpr int epilogue_warps() { return CG == 2 ? 8 : 4; }
-template <int CG> constexpr int gemm_threads() { return CG == 2 ? 32 * (2 + epilogue_warps<2>()) : GEMM_THREADS; }
+// AG: the kernel carries the gather warp of the fused FSDP all-gather.  Single CTAs always do (warp 6); CTA pairs
+// only in their AG instantiation (warp 10), which pays for the bounce buffers with one ring stage.
+template <int CG, bool AG = false> constexpr int gemm_threads() {
+  return CG == 2 ? 32 * (2 + epilogue_warps<2>() + (AG ? 1 : 0)) : GEMM_THREADS;
+}
 constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KB
 
 struct GemmParams {
@@ -90,9 +94,15 @@ template <int CG> constexpr int staging_bytes() { return epilogue_warps<CG>() * 
 // staging buffers per epilogue warp: with two, a warp fills one while the TMA engine still reads the other
 // (CTA pairs hide that wait behind the second warp of the lane quarter instead)
 template <int BN, int CG> constexpr int staging_bufs() { return (CG == 1 && BN == 128) ? 2 : 1; }
-constexpr int AG_SLICE = 16384;           // bounce buffer of the gather warp (fused all-gather)
-// the fused all-gather (single-CTA kernels only) needs the bounce buffer; CTA pairs spend it on a deeper ring
-template <int CG> constexpr int ag_bounce_bytes() { return CG == 2 ? 0 : AG_SLICE; }
+// Gather warp of the fused all-gather: slices of ag_slice() bytes travel peer shard -> smem bounce buffer -> local
+// full buffer with bulk copies.  Single CTAs: one 16 KB buffer.  CTA pairs (AG instantiation): four 8 KB buffers,
+// three loads in flight while the fourth buffer drains.
+template <int CG> constexpr int ag_slice() { return CG == 2 ? 8192 : 16384; }
+template <int CG> constexpr int ag_nbuf() { return CG == 2 ? 4 : 1; }
+template <int CG, bool AG> constexpr int ag_bounce_bytes() { return CG == 2 ? (AG ? ag_slice<2>() * ag_nbuf<2>() : 0) : ag_slice<1>(); }
+template <int N> __device__ __forceinline__ void bulk_wait_group() {
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
 // Wait accounting (tools/gemm_phases.py) costs ~1 % of a training step even when the debug buffer is
 // null, so it is only compiled in with -DB200_GEMM_TRACE (B200_GEMM_TRACE=1 python -m csrc.build).
 #ifdef B200_GEMM_TRACE
@@ -123,8 +133,8 @@ enum : int { EPI_BIAS = 1, EPI_RELU = 2, EPI_AUX = 4, EPI_MASK = 8, EPI_RES = 16
 //         stages its own 128 rows of A and HALF of the B tile, the leader's single thread issues
 //         M = 256 MMAs that read both CTAs' shared memory and write both CTAs' TMEM.  Per FLOP a CTA
 //         pulls 1/3 less operand data out of L2, which is what bounds the short-K GEMMs here.
-template <int BN, int STAGES, int MIN_CTAS, int EPI, int CG>
-__global__ void __launch_bounds__(gemm_threads<CG>(), MIN_CTAS)
+template <int BN, int STAGES, int MIN_CTAS, int EPI, int CG, bool AG = false>
+__global__ void __launch_bounds__(gemm_threads<CG, AG>(), MIN_CTAS)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
   constexpr int B_ROWS = BN / CG;                 // rows of the B tile staged by this CTA
@@ -143,15 +153,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t sB = smem_base + STAGES * A_STAGE_BYTES;
   const uint32_t sStage = smem_base + STAGES * STAGE_BYTES;
   const uint32_t sBounce = sStage + NSTG * STAGING_BYTES;
-  const uint32_t bars = sBounce + ag_bounce_bytes<CG>();  // 8-byte mbarriers
+  const uint32_t bars = sBounce + ag_bounce_bytes<CG, AG>();  // 8-byte mbarriers
   const uint32_t full_bar = bars;
   const uint32_t empty_bar = bars + 8 * STAGES;
   const uint32_t tfull_bar = bars + 16 * STAGES;
   const uint32_t tempty_bar = tfull_bar + 16;
-  const uint32_t gather_bar = tempty_bar + 16;
+  const uint32_t gather_bar = tempty_bar + 16;   // 4 barriers (one per bounce buffer)
   uint32_t* tmem_ptr_smem =
-      reinterpret_cast<uint32_t*>(smem_raw + STAGES * STAGE_BYTES + NSTG * STAGING_BYTES + ag_bounce_bytes<CG>() +
-                                  16 * STAGES + 40);
+      reinterpret_cast<uint32_t*>(smem_raw + STAGES * STAGE_BYTES + NSTG * STAGING_BYTES + ag_bounce_bytes<CG, AG>() +
+                                  16 * STAGES + 64);
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
   if ((smem_base & 1023u) != 0u) {
     if (threadIdx.x == 0) atomicCAS(p.err_word, 0, ERR_GEMM_SMEM_ALIGN);
@@ -176,7 +186,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_init(tfull_bar + 8 * i, 1);
       mbar_init(tempty_bar + 8 * i, EPW * CG);   // the epilogue warps of both CTAs of a pair
     }
-    mbar_init(gather_bar, 1);
+    for (int i = 0; i < 4; ++i) mbar_init(gather_bar + 8 * i, 1);
     fence_barrier_init();
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
@@ -244,8 +254,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j) load(a_dst + j * 8192, &tmA, m0 + 64 * j, k0);
           }
-          if (CG == 1 && p.ag_bytes > 0 && ag_tile_seen != n0) {
+          if ((CG == 1 || AG) && p.ag_bytes > 0 && ag_tile_seen != n0) {
             // the gather warps of all CTAs pull W from the peers tile by tile: wait for this n-tile
+            constexpr int AG_SLICE = ag_slice<CG>();
             const int j = n0 / BN;
             const long long left = p.ag_bytes - static_cast<long long>(j) * p.ag_tile_bytes;
             const int expect = static_cast<int>(((left < p.ag_tile_bytes ? left : p.ag_tile_bytes) + AG_SLICE - 1) / AG_SLICE);
@@ -330,35 +341,67 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       p.dbg[blockIdx.x * 32 + 14] = w_full;
       p.dbg[blockIdx.x * 32 + 15] = w_tempty;
     }
-  } else if (CG == 1 && warp_idx == 6) {
+  } else if ((CG == 1 && warp_idx == 6) || (CG == 2 && AG && warp_idx == 2 + EPW)) {
     // ===================== gather warp (fused all-gather of the B operand) =====================
-    // One lane moves this CTA's share of W with the TMA engine: 16 KB slices, peer shard -> smem bounce
+    // One lane moves this CTA's share of W with the bulk-copy engine: slices travel peer shard -> smem bounce
     // buffer -> local full buffer, round-robin over the CTAs in n-tile order so the first tiles land first.
-    if (CG == 1 && lane == 0 && p.ag_bytes > 0) {
+    // With NBUF > 1 buffers NBUF - 1 loads are in flight while one buffer drains.  (Plain bulk loads: a TMA
+    // multicast load must only ever read this GPU's own memory.)
+    if (lane == 0 && p.ag_bytes > 0) {
+      constexpr int AG_SLICE = ag_slice<CG>();
+      constexpr int NBUF = ag_nbuf<CG>();
+      constexpr int AHEAD = NBUF > 1 ? NBUF - 1 : 1;
       const long long nslices = (p.ag_bytes + AG_SLICE - 1) / AG_SLICE;
-      uint32_t gphase = 0;
-      bool ok = true;
-      for (long long sidx = blockIdx.x; sidx < nslices && ok; sidx += gridDim.x) {
-        long long byte = sidx * AG_SLICE;
-        long long left = p.ag_bytes - byte < AG_SLICE ? p.ag_bytes - byte : AG_SLICE;
-        const int tile_j = static_cast<int>(byte / p.ag_tile_bytes);
-        while (left > 0 && ok) {   // a slice may straddle a shard boundary: one bulk copy per owner
+      const long long n_mine = nslices > blockIdx.x ? (nslices - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+      auto slice_bytes = [&](long long k) {
+        const long long byte = (blockIdx.x + k * gridDim.x) * static_cast<long long>(AG_SLICE);
+        return p.ag_bytes - byte < AG_SLICE ? p.ag_bytes - byte : static_cast<long long>(AG_SLICE);
+      };
+      auto issue_load = [&](long long k) {   // a slice may straddle a shard boundary: one bulk copy per owner
+        long long byte = (blockIdx.x + k * gridDim.x) * static_cast<long long>(AG_SLICE);
+        long long left = slice_bytes(k);
+        const uint32_t buf = sBounce + static_cast<uint32_t>(k % NBUF) * AG_SLICE;
+        const uint32_t bar = gather_bar + 8 * static_cast<uint32_t>(k % NBUF);
+        mbar_arrive_expect_tx(bar, static_cast<uint32_t>(left));
+        uint32_t done = 0;
+        while (left > 0) {
           const long long gbyte = p.ag_off + byte;
           const int peer = static_cast<int>(gbyte / p.ag_shard_bytes);
           const long long in_shard = gbyte - peer * p.ag_shard_bytes;
           long long seg = p.ag_shard_bytes - in_shard;
           if (seg > left) seg = left;
-          mbar_arrive_expect_tx(gather_bar, static_cast<uint32_t>(seg));
-          bulk_load_g2s(sBounce, p.ag_peers[peer] + in_shard, static_cast<uint32_t>(seg), gather_bar);
-          if (!mbar_wait(gather_bar, gphase, abort_flag, p.err_word, ERR_GEMM_AG_WAIT)) { ok = false; break; }
-          gphase ^= 1;
-          bulk_store_s2g(p.ag_full + gbyte, sBounce, static_cast<uint32_t>(seg));
-          tma_store_commit();
-          tma_store_wait_all();     // bytes are in global memory before the tile is announced / the buffer reused
-          byte += seg;
-          left -= seg;
+          bulk_load_g2s(buf + done, p.ag_peers[peer] + in_shard, static_cast<uint32_t>(seg), bar);
+          byte += seg; left -= seg; done += static_cast<uint32_t>(seg);
         }
-        if (ok) asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.ag_sync + 2 + tile_j) : "memory");
+      };
+      auto announce = [&](long long k) {     // slice k is in the full buffer: count it for its n-tile
+        const long long byte = (blockIdx.x + k * gridDim.x) * static_cast<long long>(AG_SLICE);
+        asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(p.ag_sync + 2 + static_cast<int>(byte / p.ag_tile_bytes)) : "memory");
+      };
+      bool ok = true;
+      for (long long k = 0; k < AHEAD && k < n_mine; ++k) issue_load(k);
+      for (long long k = 0; k < n_mine && ok; ++k) {
+        const uint32_t b = static_cast<uint32_t>(k % NBUF);
+        if (!mbar_wait(gather_bar + 8 * b, static_cast<uint32_t>((k / NBUF) & 1), abort_flag, p.err_word, ERR_GEMM_AG_WAIT)) {
+          ok = false;
+          break;
+        }
+        const long long byte = (blockIdx.x + k * gridDim.x) * static_cast<long long>(AG_SLICE);
+        bulk_store_s2g(p.ag_full + p.ag_off + byte, sBounce + b * AG_SLICE, static_cast<uint32_t>(slice_bytes(k)));
+        tma_store_commit();
+        if constexpr (NBUF > 1) {
+          bulk_wait_group<1>();              // everything but the store just issued is in global memory:
+          if (k > 0) announce(k - 1);        // slice k - 1 can be announced and its buffer refilled
+          if (k + AHEAD < n_mine) issue_load(k + AHEAD);
+        } else {
+          bulk_wait_group<0>();
+          announce(k);
+          if (k + 1 < n_mine) issue_load(k + 1);
+        }
+      }
+      if constexpr (NBUF > 1) {
+        bulk_wait_group<0>();
+        if (ok && n_mine > 0) announce(n_mine - 1);
       }
     }
     __syncwarp();
@@ -725,25 +768,25 @@ struct GemmOverrides {
   int no_tma_store;
 };
 
-template <int BN, int STAGES, int MIN_CTAS, int EPI, int CG>
+template <int BN, int STAGES, int MIN_CTAS, int EPI, int CG, bool AG = false>
 int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p,
            int grid, cudaStream_t stream) {
   constexpr int smem = STAGES * (A_STAGE_BYTES + (BN / CG) * BK * 2) + staging_bufs<BN, CG>() * staging_bytes<CG>() +
-                       ag_bounce_bytes<CG>() + 16 * STAGES + 40 + 16;
+                       ag_bounce_bytes<CG, AG>() + 16 * STAGES + 64 + 16;
   static_assert(smem <= 227 * 1024, "gemm: shared memory budget exceeded");
   static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!configured[dev & 63]) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG>,
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG, AG>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG>,
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG, AG>,
                                          cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     configured[dev & 63] = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(gemm_threads<CG>());
+  cfg.blockDim = dim3(gemm_threads<CG, AG>());
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
@@ -762,7 +805,7 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tm
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG>, tmA, tmB, tmC, p));
+  B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG, AG>, tmA, tmB, tmC, p));
   return 0;
 }
 
@@ -799,6 +842,35 @@ int launch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
   }
 }
 
+// CTA pairs with the gather warp (fused FSDP all-gather): the epilogues of the forward GEMMs that consume a weight
+// first - QKV, attention out-projection, MLP up / down (ReLU and GELU)
+int launch_epi_ag_pair(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                       const GemmParams& p, int grid, cudaStream_t st) {
+  switch (epi) {
+#define B200_EPI_CASE(E) case (E): return launch<256, 5, 1, (E), 2, true>(tmA, tmB, tmC, p, grid, st);
+    B200_EPI_CASE(0)
+    B200_EPI_CASE(EPI_BIAS | EPI_RELU)
+    B200_EPI_CASE(EPI_F32 | EPI_BIAS | EPI_RES)
+    B200_EPI_CASE(EPI_F32 | EPI_BIAS | EPI_RELU | EPI_RES)
+    B200_EPI_CASE(EPI_F32 | EPI_BIAS | EPI_RELU | EPI_AUX | EPI_RES)
+    B200_EPI_CASE(EPI_BIAS | EPI_GELU)
+    B200_EPI_CASE(EPI_BIAS | EPI_GELU | EPI_AUX)
+    B200_EPI_CASE(EPI_F32 | EPI_BIAS | EPI_GELU | EPI_RES)
+    B200_EPI_CASE(EPI_F32 | EPI_BIAS | EPI_GELU | EPI_AUX | EPI_RES)
+#undef B200_EPI_CASE
+    default:
+      return -100;   // not instantiated: the caller falls back to single-CTA tiles
+  }
+}
+constexpr bool ag_pair_epilogue(int epi) {
+  return epi == 0 || epi == (EPI_BIAS | EPI_RELU) || epi == (EPI_F32 | EPI_BIAS | EPI_RES) ||
+         epi == (EPI_F32 | EPI_BIAS | EPI_RELU | EPI_RES) || epi == (EPI_F32 | EPI_BIAS | EPI_RELU | EPI_AUX | EPI_RES) ||
+         epi == (EPI_BIAS | EPI_GELU) || epi == (EPI_BIAS | EPI_GELU | EPI_AUX) ||
+         epi == (EPI_F32 | EPI_BIAS | EPI_GELU | EPI_RES) || epi == (EPI_F32 | EPI_BIAS | EPI_GELU | EPI_AUX | EPI_RES);
+}
+// B200GPT_AG_2SM=0: fused all-gather on single-CTA tiles only (the first version of the kernel)
+bool g_ag_2sm = []() { const char* e = getenv("B200GPT_AG_2SM"); return e == nullptr || e[0] != '0'; }();
+
 int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
               int a_mn, int b_mn, const float* bias, const float* residual, int ldr, int act,
               int out_fp32, int accumulate, void* aux_out, const void* mask_src, int cfg,
@@ -815,10 +887,14 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
 
   // CTA pairs (cta_group::2, 256 x 256 tiles): cfg bit 10 forces them on, bit 11 off
   const bool fused_ag = ag != nullptr && ag->bytes > 0;
-  int cg = (bn == 256 && M > BM && !fused_ag && g_gemm_2sm) ? 2 : 1;
+  const int epi_bits = (bias ? EPI_BIAS : 0) | (act == 1 ? EPI_RELU : 0) | (act >= 2 ? EPI_GELU : 0) |
+                       (aux_out ? EPI_AUX : 0) | (mask_src ? EPI_MASK : 0) | (residual ? EPI_RES : 0) |
+                       (out_fp32 ? EPI_F32 : 0) | (accumulate ? EPI_ACC : 0) | (colsum ? EPI_CSUM : 0);
+  int cg = (bn == 256 && M > BM && g_gemm_2sm && (!fused_ag || (g_ag_2sm && ag_pair_epilogue(epi_bits)))) ? 2 : 1;
   if (cfg & 0x400) cg = 2;
   if (cfg & 0x800) cg = 1;
-  B200_REQUIRE(cg == 1 || (bn == 256 && !fused_ag), "gemm: CTA pairs need 256-wide tiles and no fused all-gather");
+  B200_REQUIRE(cg == 1 || (bn == 256 && (!fused_ag || ag_pair_epilogue(epi_bits))),
+               "gemm: CTA pairs need 256-wide tiles (and, with a fused all-gather, one of the forward epilogues)");
 
   GemmParams p{};
   p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.ldr = ldr;
@@ -894,9 +970,10 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
     p.ag_off = ag->off; p.ag_bytes = ag->bytes; p.ag_shard_bytes = ag->shard_bytes;
     p.ag_sync = ag->sync;
     p.ag_tile_bytes = bn * K * 2;
-    B200_REQUIRE(p.ag_tile_bytes % AG_SLICE == 0 && ldb == K && p.num_n_tiles <= ag->max_tiles,
-                 "ag_gemm: needs a contiguous weight with (tile N x K x 2) %% 16 KiB == 0 and <= %d n-tiles (N=%d K=%d)",
-                 ag->max_tiles, N, K);
+    const int slice = cg == 2 ? ag_slice<2>() : ag_slice<1>();
+    B200_REQUIRE(p.ag_tile_bytes % slice == 0 && ldb == K && p.num_n_tiles <= ag->max_tiles,
+                 "ag_gemm: needs a contiguous weight with (tile N x K x 2) %% %d == 0 and <= %d n-tiles (N=%d K=%d)",
+                 slice, ag->max_tiles, N, K);
   }
   B200_REQUIRE(p.err_word != nullptr, "gemm: no CUDA device");
 
@@ -936,6 +1013,7 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
                   (accumulate ? EPI_ACC : 0) | (colsum ? EPI_CSUM : 0) | ((ex && ex->smax) ? EPI_SMAX : 0) |
                   (nostore ? EPI_NOSTORE : 0) | ((ex && ex->rscale) ? EPI_RSCALE : 0);
   if (bn == 128) return launch_epi<128, 2, 2, 1>(epi, tmA, tmB, tmC, p, grid, st);
+  if (cg == 2 && fused_ag) return launch_epi_ag_pair(epi, tmA, tmB, tmC, p, grid, st);
   if (cg == 2) return launch_epi<256, 6, 1, 2>(epi, tmA, tmB, tmC, p, grid, st);
   return launch_epi<256, 4, 1, 1>(epi, tmA, tmB, tmC, p, grid, st);
 }

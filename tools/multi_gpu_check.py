@@ -124,7 +124,7 @@ if "kernels" in which:
     # all-gather fused into the GEMM: W [N, K] bf16 sharded evenly (as a flat byte range) over the ranks
     from distributed_pytorch_cookbook_b200.ops import native
     ctx2 = SymmContext(dev)
-    for (M, N, K) in [(4096, 768, 256), (1000, 2048, 1024)]:
+    for (M, N, K) in [(4096, 768, 256), (1000, 2048, 1024), (128, 512, 256)]:   # CTA pairs, CTA pairs, single CTAs
         n_el = N * K
         shard_el = n_el // world
         shard = ctx2.alloc(shard_el, torch.bfloat16)
