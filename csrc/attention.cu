@@ -26,6 +26,8 @@
 // dV += P^T dO, dK += dS^T Q (TMEM accumulators across the loop) and dQ = dS K, which is
 // reduced across key tiles with fp32 vector atomics into a scratch buffer (converted to bf16
 // by a small second kernel).  delta = rowsum(dO * O) comes from a pre-pass.
+#include <stdlib.h>
+
 #include "../include/b200gpt.h"
 #include "common.cuh"
 
@@ -323,6 +325,238 @@ attn_fwd_kernel(const AttnParams p) {
     tmem_dealloc(tmem, TMEM_COLS);
   }
   ADBG_NS(25);
+}
+
+// ------------------------------------------------------------------------------------------
+// forward, warp-specialised and software-pipelined (long sequences: >= 4 key tiles per head)
+// ------------------------------------------------------------------------------------------
+// One CTA per (batch, head, 128-query tile), 192 threads:
+//   warp 0   loader: one lane issues TMA loads (4-D tensor map over qkv: box {8 elements, 128 rows, D/8 column
+//            groups, 1 batch} lands as the un-swizzled core-matrix layout in one instruction, rows past T are
+//            zero-filled); Q once, K / V tiles through a 2-stage ring
+//   warp 1   MMA issuer (one lane): S(j+1) = Q K(j+1)^T is issued before it waits for P(j), so the tensor pipe
+//            works on the next tile's scores while the softmax warps are busy; then O += P(j) V(j) with P read
+//            from tensor memory
+//   warps 2-5  softmax: one score row per thread, the whole 128-key row in registers (one pass: max, exp2,
+//            row sum), P written back as bf16 over the S columns it came from
+// Tensor memory: S double-buffered [0,128) [128,256), O accumulates in [256, 256 + D) across all key tiles.  The
+// running maximum is only raised when a tile exceeds it by more than 2^8 (then O and the row sum are rescaled
+// in tensor memory, which needs the previous PV to have retired) - rescaling is rare after the first tiles.
+enum : int { ERR_ATTN_WS = 203 };
+constexpr int ATTN_WS_THREADS = 192;
+
+template <int D>
+__global__ void __launch_bounds__(ATTN_WS_THREADS, 1)
+attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p) {
+  constexpr int TILE_BYTES = TQ * D * 2;
+  constexpr uint32_t TMEM_COLS = 512;
+  constexpr uint32_t C_O = 256;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 127u) & ~127u;
+  const uint32_t sQ = base, sK = sQ + TILE_BYTES, sV = sK + 2 * TILE_BYTES;
+  const uint32_t bars = sV + 2 * TILE_BYTES;
+  const uint32_t q_full = bars, kv_full = bars + 8, kv_empty = bars + 24, s_full = bars + 40, p_ready = bars + 56,
+                 o_done = bars + 72;
+  uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + 5 * TILE_BYTES + 80);
+  volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qt = gridDim.z - 1 - blockIdx.z, h = blockIdx.x, b = blockIdx.y;   // long query tiles first
+  const int HD = p.H * D;
+  const int q0 = qt * TQ;
+  const int n_kt = qt + 1;
+
+  if (threadIdx.x == 0) {
+    *abort_flag = 0;
+    mbar_init(q_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(kv_full + 8 * i, 1);
+      mbar_init(kv_empty + 8 * i, 1);
+      mbar_init(s_full + 8 * i, 1);
+      mbar_init(p_ready + 8 * i, 4);
+    }
+    mbar_init(o_done, 1);
+    fence_barrier_init();
+    tma_prefetch_desc(&tmQKV);
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(tmem_ptr_smem), TMEM_COLS);
+    tmem_relinquish();
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ===================== loader =====================
+    if (lane == 0) {
+      mbar_arrive_expect_tx(q_full, TILE_BYTES);
+      tma_load_4d(sQ, &tmQKV, q_full, 0, q0, (h * D) / 8, b);
+      for (int j = 0; j < n_kt; ++j) {
+        const int s = j & 1;
+        if (j >= 2 && !mbar_wait(kv_empty + 8 * s, ((j >> 1) - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) break;
+        mbar_arrive_expect_tx(kv_full + 8 * s, 2 * TILE_BYTES);
+        tma_load_4d(sK + s * TILE_BYTES, &tmQKV, kv_full + 8 * s, 0, j * TK, (HD + h * D) / 8, b);
+        tma_load_4d(sV + s * TILE_BYTES, &tmQKV, kv_full + 8 * s, 0, j * TK, (2 * HD + h * D) / 8, b);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc_s = umma_idesc_bf16(TQ, TK, 0, 0);
+    const uint32_t idesc_pv = umma_idesc_bf16(TQ, D, 0, 1);
+    bool ok = mbar_wait(q_full, 0, abort_flag, p.err_word, ERR_ATTN_WS);
+    auto issue_qk = [&](int j) {   // S[j & 1] = Q K(j)^T
+      const int s = j & 1;
+      if (!mbar_wait(kv_full + 8 * s, (j >> 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) return false;
+      tcgen05_fence_after();
+      if (lane == 0) {
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_f16_ss(tmem + s * 128, desc_kmajor(sQ, kk), desc_kmajor(sK + s * TILE_BYTES, kk), idesc_s, kk > 0 ? 1u : 0u);
+        umma_commit(s_full + 8 * s);
+      }
+      __syncwarp();
+      return true;
+    };
+    if (ok) ok = issue_qk(0);
+    for (int j = 0; j < n_kt && ok; ++j) {
+      const int s = j & 1;
+      if (j + 1 < n_kt) ok = issue_qk(j + 1);
+      if (!ok || !mbar_wait(p_ready + 8 * s, (j >> 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      tcgen05_fence_after();
+      if (lane == 0) {
+#pragma unroll
+        for (int kk = 0; kk < TK / 16; ++kk)   // O (+)= P(j) V(j), P from tensor memory
+          umma_f16_ts(tmem + C_O, tmem + s * 128 + kk * 8, desc_mnmajor(sV + s * TILE_BYTES, kk), idesc_pv,
+                      (j > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(kv_empty + 8 * s);
+        umma_commit(o_done);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ===================== softmax (4 warps, one row per thread) =====================
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const int q = q0 + row;
+    const uint32_t t_lane = tmem + (static_cast<uint32_t>(quarter * 32) << 16);
+    const float sl2 = p.scale * kLog2e;
+    const uint8_t* mask_row = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
+    float m_used = -INFINITY, l_run = 0.f;
+    bool ok = true;
+    for (int j = 0; j < n_kt; ++j) {
+      const int s = j & 1;
+      if (!mbar_wait(s_full + 8 * s, (j >> 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      tcgen05_fence_after();
+      uint32_t r[128];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(t_lane + s * 128 + c * 32, r + c * 32);
+      tmem_ld_wait();
+      const bool diag = (j == qt);
+      const bool masked_tile = diag || mask_row != nullptr;
+      uint32_t kb[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
+      if (masked_tile) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) kb[c] = keep_bits(j * TK + c * 32, q, diag, true, p.T, mask_row);
+      }
+      float m_tile = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float v = __uint_as_float(r[c * 32 + i]);
+          m_tile = fmaxf(m_tile, (!masked_tile || ((kb[c] >> i) & 1u)) ? v : -INFINITY);
+        }
+      }
+      m_tile *= sl2;                                    // log2 domain (scale > 0)
+      // raise the reference maximum only when this tile exceeds it by 2^8 (or there is none yet)
+      const bool raise = m_tile > m_used + 8.0f || (m_used == -INFINITY && m_tile > -INFINITY);
+      // o_done is a parity barrier: a waiter must never fall two phases behind it.  Every iteration j >= 1
+      // therefore observes phase j - 1 (PV(j - 1) retired) exactly once, and does so BEFORE it reports P(j) - PV(j)
+      // cannot be issued earlier, so the barrier is at phase j - 1 or j when it is tested.  By then that MMA has
+      // long finished (it was issued when this tile's softmax began), so the wait costs nothing.
+      bool seen_prev = false;
+      if (__any_sync(0xffffffffu, raise)) {
+        const float m_new = raise ? m_tile : m_used;
+        const float alpha = (m_used == -INFINITY) ? 0.f : fast_exp2(m_used - m_new);   // 1 for rows that keep theirs
+        if (j > 0) {
+          // O of the previous tiles is rescaled in tensor memory: PV(j - 1) must have retired
+          if (!mbar_wait(o_done, (j - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+          seen_prev = true;
+          tcgen05_fence_after();
+#pragma unroll
+          for (int c = 0; c < D / 16; ++c) {
+            uint32_t o[16];
+            tmem_ld_32x32b_x16(t_lane + C_O + c * 16, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st_32x32b_x16(t_lane + C_O + c * 16, o);
+          }
+        }
+        l_run *= alpha;
+        m_used = m_new;
+      }
+      const float m_sub = (m_used == -INFINITY) ? 0.f : m_used;
+      float l_tile = 0.f;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float e0 = fast_exp2(fmaf(__uint_as_float(r[c * 32 + i]), sl2, -m_sub));
+          float e1 = fast_exp2(fmaf(__uint_as_float(r[c * 32 + i + 1]), sl2, -m_sub));
+          if (masked_tile) {
+            e0 = ((kb[c] >> i) & 1u) ? e0 : 0.f;
+            e1 = ((kb[c] >> (i + 1)) & 1u) ? e1 : 0.f;
+          }
+          const uint32_t packed = pack_bf16x2(e0, e1);
+          const float2 back = unpack_bf16x2(packed);     // sum what the tensor core will see
+          l_tile += back.x + back.y;
+          pk[i >> 1] = packed;
+        }
+        tmem_st_32x32b_x16(t_lane + s * 128 + c * 16, pk);   // keys [32c, 32c + 32) -> columns [16c, 16c + 16)
+      }
+      l_run += l_tile;
+      tmem_st_wait();
+      if (j > 0 && !seen_prev && !mbar_wait(o_done, (j - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_ready + 8 * s);
+    }
+    if (ok && mbar_wait(o_done, (n_kt - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) {
+      tcgen05_fence_after();
+      const float inv_l = l_run > 0.f ? 1.0f / l_run : 0.f;
+      bf16* orow = p.out + (static_cast<size_t>(b) * p.T + (q < p.T ? q : 0)) * HD + h * D;
+#pragma unroll
+      for (int c = 0; c < D / 16; ++c) {
+        uint32_t o[16];
+        tmem_ld_32x32b_x16(t_lane + C_O + c * 16, o);
+        tmem_ld_wait();
+        if (q < p.T) {
+#pragma unroll
+          for (int i = 0; i < 16; i += 8)
+            *reinterpret_cast<uint4*>(orow + c * 16 + i) = make_uint4(
+                pack_bf16x2(__uint_as_float(o[i]) * inv_l, __uint_as_float(o[i + 1]) * inv_l),
+                pack_bf16x2(__uint_as_float(o[i + 2]) * inv_l, __uint_as_float(o[i + 3]) * inv_l),
+                pack_bf16x2(__uint_as_float(o[i + 4]) * inv_l, __uint_as_float(o[i + 5]) * inv_l),
+                pack_bf16x2(__uint_as_float(o[i + 6]) * inv_l, __uint_as_float(o[i + 7]) * inv_l));
+        }
+      }
+      if (q < p.T)
+        p.lse[(static_cast<size_t>(b) * p.H + h) * p.T + q] =
+            l_run > 0.f ? m_used * (1.0f / kLog2e) + logf(l_run) : -INFINITY;
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem, TMEM_COLS);
+  }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -660,6 +894,38 @@ int fwd_launch(const AttnParams& p, cudaStream_t st) {
   return 0;
 }
 
+// 4-D view of qkv [B, T, 3*H*D] for the TMA loads of the warp-specialised kernels: (8 elements, T rows, 3*H*D / 8
+// column groups, B); a box {8, 128, D / 8, 1} arrives in shared memory as [column group][row][8] - the un-swizzled
+// core-matrix layout every MMA here reads.
+int make_qkv_tmap(CUtensorMap* out, const bf16* base, int B, int T, int cols, int D) {
+  const uint64_t dims[4] = {8, static_cast<uint64_t>(T), static_cast<uint64_t>(cols / 8), static_cast<uint64_t>(B)};
+  const uint64_t strides[3] = {static_cast<uint64_t>(cols) * 2, 16, static_cast<uint64_t>(T) * cols * 2};
+  const uint32_t box[4] = {8, TQ, static_cast<uint32_t>(D / 8), 1};
+  return b200_make_tmap_nd(out, base, 4, dims, strides, box, 2, 0);
+}
+
+// B200GPT_ATTN_WS=0 / 1 forces the per-tile (v1) / warp-specialised forward; unset: by sequence length
+int g_attn_ws = []() { const char* e = getenv("B200GPT_ATTN_WS"); return e == nullptr ? -1 : (e[0] == '0' ? 0 : 1); }();
+
+template <int D>
+int fwd_ws_launch(const AttnParams& p, cudaStream_t st) {
+  constexpr int smem = 5 * TQ * D * 2 + 80 + 16 + 128;
+  static bool configured[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!configured[dev & 63]) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_ws_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured[dev & 63] = true;
+  }
+  CUtensorMap tm;
+  int rc = make_qkv_tmap(&tm, p.qkv, p.B, p.T, 3 * p.H * D, D);
+  if (rc != 0) return rc;
+  dim3 grid(p.H, p.B, ceil_div(p.T, TQ));
+  attn_fwd_ws_kernel<D><<<grid, ATTN_WS_THREADS, smem, st>>>(tm, p);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
 template <int D>
 int bwd_launch(const AttnParams& p, cudaStream_t st) {
   constexpr int smem = 4 * TQ * D * 2 + 2 * TQ * TK * 2 + 8 + 16 + 128;
@@ -705,8 +971,8 @@ int b200_attn_set_debug_buffer(void* buf) {
   return 0;
 }
 
-int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int D, float scale,
-                  const void* key_mask, void* stream) {
+static int attn_fwd_impl(const void* qkv, void* out, float* lse, int B, int T, int H, int D, float scale,
+                         const void* key_mask, int force_ws, void* stream) {
   B200_REQUIRE(D == 32 || D == 64 || D == 128, "attention: head_dim %d not supported (32, 64, 128)", D);
   B200_REQUIRE(B > 0 && T > 0 && H > 0 && B <= 65535 && H <= 65535, "attention: bad shape");
   AttnParams p{};
@@ -718,9 +984,26 @@ int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, i
   p.err_word = b200_error_word();
   p.dbg = g_attn_dbg;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool ws = force_ws >= 0 ? force_ws == 1 : (g_attn_ws >= 0 ? g_attn_ws == 1 : (T > 3 * TQ && D >= 64));
+  if (ws) {
+    if (D == 32) return fwd_ws_launch<32>(p, st);
+    if (D == 64) return fwd_ws_launch<64>(p, st);
+    return fwd_ws_launch<128>(p, st);
+  }
   if (D == 32) return fwd_launch<32>(p, st);
   if (D == 64) return fwd_launch<64>(p, st);
   return fwd_launch<128>(p, st);
+}
+
+int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int D, float scale,
+                  const void* key_mask, void* stream) {
+  return attn_fwd_impl(qkv, out, lse, B, T, H, D, scale, key_mask, -1, stream);
+}
+
+// same with the kernel chosen by the caller: ws = 0 per-tile kernel, 1 warp-specialised kernel, -1 automatic
+int b200_attn_fwd_select(const void* qkv, void* out, float* lse, int B, int T, int H, int D, float scale,
+                         const void* key_mask, int ws, void* stream) {
+  return attn_fwd_impl(qkv, out, lse, B, T, H, D, scale, key_mask, ws, stream);
 }
 
 int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,

@@ -185,6 +185,14 @@ __device__ __forceinline__ void tma_load_3d(uint32_t smem_dst, const void* tmap,
       : "memory");
 }
 
+__device__ __forceinline__ void tma_load_4d(uint32_t smem_dst, const void* tmap, uint32_t bar,
+                                            int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
 // plain (non-tensor) bulk copies: global -> smem completing on an mbarrier, smem -> global in a bulk group
 __device__ __forceinline__ void bulk_load_g2s(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint32_t bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -399,6 +407,9 @@ __host__ __device__ inline uint32_t umma_idesc_bf16(int M, int N, int a_mn_major
 // 2D bf16 tensor [outer][inner] with row stride ld_elems; box = box_inner x box_outer; 128B swizzle.
 int b200_make_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
                       uint64_t ld_elems, uint32_t box_inner, uint32_t box_outer, int elem_bytes = 2);
+// general form: rank <= 5, strides_bytes[i] = byte stride of dimension i + 1, swizzle 0 = none / 1 = 128B
+int b200_make_tmap_nd(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box, int elem_bytes, int swizzle128);
 int b200_make_tmap_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t d1, uint64_t d2,
                       uint64_t stride1_elems, uint64_t stride2_elems, uint32_t b0, uint32_t b1,
                       uint32_t b2);

@@ -108,6 +108,28 @@ int b200_make_tmap_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t 
   return 0;
 }
 
+int b200_make_tmap_nd(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box, int elem_bytes, int swizzle128) {
+  PFN_encodeTiled enc = get_encode();
+  B200_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point not found");
+  B200_REQUIRE(rank >= 1 && rank <= 5, "TMA rank %d not supported", rank);
+  B200_REQUIRE(elem_bytes == 2 || elem_bytes == 4, "TMA element size %d not supported", elem_bytes);
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base %p not 16B aligned", base);
+  cuuint64_t d[5], st[4];
+  cuuint32_t bx[5], estr[5];
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; bx[i] = box[i]; estr[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) {
+    B200_REQUIRE(strides_bytes[i] % 16 == 0, "TMA stride %d (%llu B) not a multiple of 16 B", i, (unsigned long long)strides_bytes[i]);
+    st[i] = strides_bytes[i];
+  }
+  CUresult r = enc(out, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, rank,
+                   const_cast<void*>(base), d, st, bx, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(rank %d) failed: %d", rank, (int)r);
+  return 0;
+}
+
 __global__ void smoke_kernel(int* out) {
   if (threadIdx.x == 0) atomicAdd(out, 0);
 }

@@ -49,6 +49,7 @@ _SIGS = {
     "b200_gemm_debug": [P, P, P] + [I] * 16 + [P],
     "b200_gemm_mask_colsum_bf16": [P, P, P, I, I, I, I, I, I, I, P, P, I, P],
     "b200_attn_fwd": [P, P, P, I, I, I, I, Fl, P, P],
+    "b200_attn_fwd_select": [P, P, P, I, I, I, I, Fl, P, I, P],
     "b200_attn_bwd": [P, P, P, P, P, P, P, I, I, I, I, Fl, P, P],
     "b200_allreduce": [P, P, P, I, I, L, L, Fl, I, I, P],
     "b200_allreduce_bf16": [P, P, P, P, I, I, L, L, Fl, I, I, P],

@@ -135,6 +135,10 @@ int b200_gemm_debug(const void* A, const void* B, void* C, int M, int N, int K, 
  * key_mask: optional uint8 [B,T], 1 = padding key.  lse = log-sum-exp of the scaled scores. */
 int b200_attn_fwd(const void* qkv_bf16, void* out_bf16, float* lse, int B, int T, int H, int D, float scale,
                   const void* key_mask, void* stream);
+/* same, forward kernel chosen by the caller: ws = 0 per-tile kernel (short sequences), 1 warp-specialised TMA-fed
+ * pipelined kernel (long sequences), -1 automatic (what b200_attn_fwd does) */
+int b200_attn_fwd_select(const void* qkv_bf16, void* out_bf16, float* lse, int B, int T, int H, int D, float scale,
+                         const void* key_mask, int ws, void* stream);
 /* scratch (caller-provided, overwritten): delta fp32 [B,H,T], dq_acc fp32 [B,T,H*D] */
 int b200_attn_bwd(const void* qkv_bf16, const void* out_bf16, const void* dout_bf16, const float* lse,
                   void* dqkv_bf16, float* delta, float* dq_acc, int B, int T, int H, int D, float scale,

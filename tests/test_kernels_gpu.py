@@ -543,7 +543,9 @@ def test_model_forward_returns_logits_at_odd_vocab():
 
 
 @pytest.mark.parametrize("B,T,H,D,masked", [(2, 255, 8, 32, False), (2, 100, 2, 64, True), (1, 300, 2, 128, False),
-                                            (64, 255, 8, 32, False), (1, 1023, 2, 128, True)])
+                                            (64, 255, 8, 32, False), (1, 1023, 2, 128, True), (2, 1024, 3, 128, False),
+                                            (1, 641, 2, 64, True), (1, 1, 2, 32, False), (2, 127, 2, 64, False),
+                                            (2, 129, 2, 128, False), (1, 2000, 1, 128, False)])
 def test_flash_attention_fwd_bwd(B, T, H, D, masked):
     from distributed_pytorch_cookbook_b200 import ops
     torch.manual_seed(0)
@@ -565,3 +567,28 @@ def test_flash_attention_fwd_bwd(B, T, H, D, masked):
     assert torch.allclose(out.float()[valid], ref[valid], atol=3e-2, rtol=3e-2)
     gd = (got_dqkv.float() - q32.grad)[valid]
     assert gd.abs().max().item() <= 0.05 * q32.grad.abs().max().item() + 2e-2, gd.abs().max().item()
+
+
+@pytest.mark.parametrize("B,T,H,D", [(2, 1023, 4, 128), (1, 513, 2, 64), (3, 255, 2, 32)])
+def test_attention_forward_kernels_agree(B, T, H, D):
+    """The per-tile forward and the warp-specialised, TMA-fed forward (the default for long sequences) compute the
+    same O and log-sum-exp; both are checked against fp32."""
+    import ctypes
+    from distributed_pytorch_cookbook_b200 import ops
+    torch.manual_seed(5)
+    qkv = (torch.randn(B, T, 3 * H * D, device="cuda") * 0.8).to(BF16)
+    scale = D ** -0.5
+    q, k, v = (t.float().reshape(B, T, H, D).transpose(1, 2) for t in qkv.chunk(3, dim=-1))
+    ref = ops.attention_reference(q, k, v, scale, None).transpose(1, 2).reshape(B, T, H * D)
+    outs = []
+    for ws in (0, 1):
+        out = torch.empty((B, T, H * D), dtype=BF16, device="cuda")
+        lse = torch.empty((B, H, T), dtype=torch.float32, device="cuda")
+        _lib.call("b200_attn_fwd_select", qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), B, T, H, D, float(scale), None,
+                  ws, _lib.stream())
+        torch.cuda.synchronize()
+        assert torch.allclose(out.float(), ref, atol=3e-2, rtol=3e-2), ws
+        outs.append((out, lse))
+    assert torch.allclose(outs[0][0].float(), outs[1][0].float(), atol=2e-2, rtol=2e-2)
+    assert torch.allclose(outs[0][1], outs[1][1], atol=2e-3, rtol=1e-3)
+    assert _dev_err() == 0
