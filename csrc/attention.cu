@@ -342,8 +342,27 @@ attn_fwd_kernel(const AttnParams p) {
 // Tensor memory: S double-buffered [0,128) [128,256), O accumulates in [256, 256 + D) across all key tiles.  The
 // running maximum is only raised when a tile exceeds it by more than 2^8 (then O and the row sum are rescaled
 // in tensor memory, which needs the previous PV to have retired) - rescaling is rare after the first tiles.
-enum : int { ERR_ATTN_WS = 203 };
+enum : int { ERR_ATTN_WS = 203, ERR_ATTN_SMEM_ALIGN = 204 };
 constexpr int ATTN_WS_THREADS = 192;
+
+// Tile layout of the warp-specialised kernels: a [128 x D] bf16 tile is D / 64 blocks of [128 rows x 64 columns]
+// (16 KB: rows of 128 bytes whose 16-byte chunks are XOR-swizzled with row % 8) - exactly what ONE TMA box
+// {64 columns, 128 rows} with SWIZZLE_128B writes, so a tile costs D / 64 bulk tensor loads of full 128-byte rows
+// (the un-swizzled core-matrix layout of the per-tile kernels would cost 16 x as many 16-byte rows).  The same block
+// serves as a K-major operand (MN = rows, K = columns) and as an MN-major operand (K = rows, MN = columns).
+constexpr uint32_t SW_BLK = 16384;
+__device__ __forceinline__ uint64_t desc_sw_k(uint32_t tile, int kk) {    // 16 K-columns per MMA, 4 MMAs per block
+  return umma_desc_at(umma_smem_desc_base(16, 1024), tile + (kk >> 2) * SW_BLK + (kk & 3) * 32);
+}
+__device__ __forceinline__ uint64_t desc_sw_mn(uint32_t tile, int kk) {   // 16 K-rows per MMA; 64-wide MN groups one block apart
+  return umma_desc_at(umma_smem_desc_base(SW_BLK, 1024), tile + kk * 2048);
+}
+// one tile = D / 64 TMA boxes; coordinates: (column, row in the sequence, batch)
+template <int D>
+__device__ __forceinline__ void tma_load_tile(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int col0, int t0, int b) {
+#pragma unroll
+  for (int i = 0; i < D / 64; ++i) tma_load_3d(dst + i * SW_BLK, tm, bar, col0 + 64 * i, t0, b);
+}
 
 template <int D>
 __global__ void __launch_bounds__(ATTN_WS_THREADS, 1)
@@ -351,15 +370,19 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p
   constexpr int TILE_BYTES = TQ * D * 2;
   constexpr uint32_t TMEM_COLS = 512;
   constexpr uint32_t C_O = 256;
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t base = (smem_u32(smem_raw) + 127u) & ~127u;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t base = smem_u32(smem_raw);      // swizzled blocks need 1024-byte alignment (checked below)
   const uint32_t sQ = base, sK = sQ + TILE_BYTES, sV = sK + 2 * TILE_BYTES;
   const uint32_t bars = sV + 2 * TILE_BYTES;
   const uint32_t q_full = bars, kv_full = bars + 8, kv_empty = bars + 24, s_full = bars + 40, p_ready = bars + 56,
                  o_done = bars + 72;
-  uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
+  uint8_t* gen = smem_raw;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + 5 * TILE_BYTES + 80);
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+  if ((base & 1023u) != 0u) {
+    if (threadIdx.x == 0) atomicCAS(p.err_word, 0, ERR_ATTN_SMEM_ALIGN);
+    return;
+  }
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qt = gridDim.z - 1 - blockIdx.z, h = blockIdx.x, b = blockIdx.y;   // long query tiles first
@@ -393,13 +416,13 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p
     // ===================== loader =====================
     if (lane == 0) {
       mbar_arrive_expect_tx(q_full, TILE_BYTES);
-      tma_load_4d(sQ, &tmQKV, q_full, 0, q0, (h * D) / 8, b);
+      tma_load_tile<D>(sQ, &tmQKV, q_full, h * D, q0, b);
       for (int j = 0; j < n_kt; ++j) {
         const int s = j & 1;
         if (j >= 2 && !mbar_wait(kv_empty + 8 * s, ((j >> 1) - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) break;
         mbar_arrive_expect_tx(kv_full + 8 * s, 2 * TILE_BYTES);
-        tma_load_4d(sK + s * TILE_BYTES, &tmQKV, kv_full + 8 * s, 0, j * TK, (HD + h * D) / 8, b);
-        tma_load_4d(sV + s * TILE_BYTES, &tmQKV, kv_full + 8 * s, 0, j * TK, (2 * HD + h * D) / 8, b);
+        tma_load_tile<D>(sK + s * TILE_BYTES, &tmQKV, kv_full + 8 * s, HD + h * D, j * TK, b);
+        tma_load_tile<D>(sV + s * TILE_BYTES, &tmQKV, kv_full + 8 * s, 2 * HD + h * D, j * TK, b);
       }
     }
     __syncwarp();
@@ -415,7 +438,7 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p
       if (lane == 0) {
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
-          umma_f16_ss(tmem + s * 128, desc_kmajor(sQ, kk), desc_kmajor(sK + s * TILE_BYTES, kk), idesc_s, kk > 0 ? 1u : 0u);
+          umma_f16_ss(tmem + s * 128, desc_sw_k(sQ, kk), desc_sw_k(sK + s * TILE_BYTES, kk), idesc_s, kk > 0 ? 1u : 0u);
         umma_commit(s_full + 8 * s);
       }
       __syncwarp();
@@ -430,7 +453,7 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p
       if (lane == 0) {
 #pragma unroll
         for (int kk = 0; kk < TK / 16; ++kk)   // O (+)= P(j) V(j), P from tensor memory
-          umma_f16_ts(tmem + C_O, tmem + s * 128 + kk * 8, desc_mnmajor(sV + s * TILE_BYTES, kk), idesc_pv,
+          umma_f16_ts(tmem + C_O, tmem + s * 128 + kk * 8, desc_sw_mn(sV + s * TILE_BYTES, kk), idesc_pv,
                       (j > 0 || kk > 0) ? 1u : 0u);
         umma_commit(kv_empty + 8 * s);
         umma_commit(o_done);
@@ -864,6 +887,268 @@ attn_bwd_kernel(const AttnParams p) {
   ADBG_NS(25);
 }
 
+// ------------------------------------------------------------------------------------------
+// backward, warp-specialised and TMA-fed (long sequences)
+// ------------------------------------------------------------------------------------------
+// Same decomposition as attn_bwd_kernel - one CTA per (batch, head, 128-key tile) walking the query tiles at or
+// below the diagonal - but computed TRANSPOSED so that the probabilities never leave tensor memory:
+//   S^T  = K Q^T          dP^T = V dO^T                          (TMEM lanes = keys, columns = queries)
+//   P^T  = exp2(S^T * scale*log2e - lse[q]),  dS^T = P^T (dP^T - delta[q]) * scale     -> bf16, back into TMEM
+//   dV  += P^T dO         dK  += dS^T Q                          (A operand from tensor memory)
+//   dQ   = dS K                                                  (dS^T also goes to smem once: MN-major A operand)
+// 320 threads: warp 0 loader (TMA; K / V once, Q / dO double-buffered so the next query tile arrives under the
+// current one), warp 1 MMA issuer, warps 2-9 compute (two threads per key row, half of the query columns each) -
+// they also drain dQ into the fp32 accumulator with vector reductions.
+// Tensor memory (512 columns): A [0,128) S^T -> P^T -> dQ;  B [128,256) dP^T -> dS^T;  dV [256,256+D);  dK after it.
+// Each half-row thread writes its packed bf16 results over the first half of the columns it read itself
+// (queries [64h, 64h+64) -> columns 64h + [0,32)), so the two threads of a row never touch each other's inputs.
+constexpr int ATTN_BWD_WS_THREADS = 320;
+
+template <int D>
+__global__ void __launch_bounds__(ATTN_BWD_WS_THREADS, 1)
+attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
+                   const AttnParams p) {
+  constexpr int TILE_BYTES = TQ * D * 2;
+  constexpr int SS_BYTES = TQ * TK * 2;
+  constexpr uint32_t TMEM_COLS = 512;
+  constexpr uint32_t C_A = 0, C_B = 128, C_DV = 256, C_DK = 256 + D;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t base = smem_u32(smem_raw);      // swizzled blocks need 1024-byte alignment (checked below)
+  const uint32_t sK = base, sV = sK + TILE_BYTES, sQ = sV + TILE_BYTES, sdO = sQ + 2 * TILE_BYTES;
+  const uint32_t sdS = sdO + 2 * TILE_BYTES, sStat = sdS + SS_BYTES;       // sStat: [lse2 128 | delta 128] floats
+  const uint32_t bars = sStat + 1024;
+  const uint32_t kv_full = bars, qdo_full = bars + 8, qdo_empty = bars + 24, sdp_full = bars + 40, ps_ready = bars + 48,
+                 dq_full = bars + 56, a_free = bars + 64, stat_bar = bars + 72;
+  uint8_t* gen = smem_raw;
+  float* stat = reinterpret_cast<float*>(gen + 6 * TILE_BYTES + SS_BYTES);
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + 6 * TILE_BYTES + SS_BYTES + 1024 + 80);
+  volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+  if ((base & 1023u) != 0u) {
+    if (threadIdx.x == 0) atomicCAS(p.err_word, 0, ERR_ATTN_SMEM_ALIGN);
+    return;
+  }
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;     // early key tiles (most query tiles) first
+  const int HD = p.H * D;
+  const int k0 = kt * TK;
+  const int nq_tiles = (p.T + TQ - 1) / TQ;
+  const int n_it = nq_tiles - kt;
+
+  if (threadIdx.x == 0) {
+    *abort_flag = 0;
+    mbar_init(kv_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(qdo_full + 8 * i, 1);
+      mbar_init(qdo_empty + 8 * i, 1);
+    }
+    mbar_init(sdp_full, 1);
+    mbar_init(ps_ready, 8);
+    mbar_init(dq_full, 1);
+    mbar_init(a_free, 8);
+    mbar_init(stat_bar, 256);
+    fence_barrier_init();
+    tma_prefetch_desc(&tmQKV);
+    tma_prefetch_desc(&tmDO);
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(tmem_ptr_smem), TMEM_COLS);
+    tmem_relinquish();
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ===================== loader =====================
+    if (lane == 0) {
+      mbar_arrive_expect_tx(kv_full, 2 * TILE_BYTES);
+      tma_load_tile<D>(sK, &tmQKV, kv_full, HD + h * D, k0, b);
+      tma_load_tile<D>(sV, &tmQKV, kv_full, 2 * HD + h * D, k0, b);
+      for (int it = 0; it < n_it; ++it) {
+        const int s = it & 1;
+        if (it >= 2 && !mbar_wait(qdo_empty + 8 * s, ((it >> 1) - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) break;
+        mbar_arrive_expect_tx(qdo_full + 8 * s, 2 * TILE_BYTES);
+        tma_load_tile<D>(sQ + s * TILE_BYTES, &tmQKV, qdo_full + 8 * s, h * D, (kt + it) * TQ, b);
+        tma_load_tile<D>(sdO + s * TILE_BYTES, &tmDO, qdo_full + 8 * s, h * D, (kt + it) * TQ, b);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc_st = umma_idesc_bf16(TK, TQ, 0, 0);     // S^T, dP^T: K-major x K-major, N = 128 queries
+    const uint32_t idesc_tv = umma_idesc_bf16(TK, D, 0, 1);      // dV, dK: A from TMEM, B MN-major
+    const uint32_t idesc_dq = umma_idesc_bf16(TQ, D, 1, 1);      // dQ: both operands MN-major
+    bool ok = mbar_wait(kv_full, 0, abort_flag, p.err_word, ERR_ATTN_WS);
+    for (int it = 0; it < n_it && ok; ++it) {
+      const int s = it & 1;
+      const uint32_t q_s = sQ + s * TILE_BYTES, do_s = sdO + s * TILE_BYTES;
+      if (!mbar_wait(qdo_full + 8 * s, (it >> 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      if (it > 0 && !mbar_wait(a_free, (it - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      tcgen05_fence_after();
+      if (lane == 0) {
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_f16_ss(tmem + C_A, desc_sw_k(sK, kk), desc_sw_k(q_s, kk), idesc_st, kk > 0 ? 1u : 0u);
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_f16_ss(tmem + C_B, desc_sw_k(sV, kk), desc_sw_k(do_s, kk), idesc_st, kk > 0 ? 1u : 0u);
+        umma_commit(sdp_full);
+      }
+      __syncwarp();
+      if (!mbar_wait(ps_ready, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      tcgen05_fence_after();
+      if (lane == 0) {
+        const uint32_t acc0 = it > 0 ? 1u : 0u;
+#pragma unroll
+        for (int kk = 0; kk < TQ / 16; ++kk) {   // reduction over the 128 queries; query 16 kk -> column 8 (kk % 4) + 64 (kk / 4)
+          const uint32_t col = static_cast<uint32_t>((kk & 3) * 8 + (kk >> 2) * 64);
+          umma_f16_ts(tmem + C_DV, tmem + C_A + col, desc_sw_mn(do_s, kk), idesc_tv, kk > 0 ? 1u : acc0);
+        }
+#pragma unroll
+        for (int kk = 0; kk < TQ / 16; ++kk) {
+          const uint32_t col = static_cast<uint32_t>((kk & 3) * 8 + (kk >> 2) * 64);
+          umma_f16_ts(tmem + C_DK, tmem + C_B + col, desc_sw_mn(q_s, kk), idesc_tv, kk > 0 ? 1u : acc0);
+        }
+#pragma unroll
+        for (int kk = 0; kk < TK / 16; ++kk)     // dQ[q, d] = sum over keys dS[q, key] K[key, d]
+          umma_f16_ss(tmem + C_A, desc_sw_mn(sdS, kk), desc_sw_mn(sK, kk), idesc_dq, kk > 0 ? 1u : 0u);
+        umma_commit(qdo_empty + 8 * s);
+        umma_commit(dq_full);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ===================== compute (8 warps) =====================
+    const int quarter = warp & 3, half = (warp - 2) >> 2;
+    const int krow = quarter * 32 + lane;              // key row of the tile = TMEM lane
+    const int key = k0 + krow;
+    const int ctid = threadIdx.x - 64;                 // 0 .. 255
+    const uint32_t t_lane = tmem + (static_cast<uint32_t>(quarter * 32) << 16);
+    const float sl2 = p.scale * kLog2e;
+    const bool key_ok = key < p.T && !(p.key_mask != nullptr && p.key_mask[static_cast<size_t>(b) * p.T + key] != 0);
+    const size_t stat_base = (static_cast<size_t>(b) * p.H + h) * p.T;
+    bool ok = true;
+    for (int it = 0; it < n_it; ++it) {
+      const int s = it & 1;
+      const int q0 = (kt + it) * TQ;
+      // stage lse (log2 units, +inf for rows past T: their probabilities vanish) and delta of this query tile (one
+      // buffer is enough: everybody has read the previous tile's values before dq_full of that tile could fire)
+      {
+        const int qq = q0 + (ctid & 127);
+        float v;
+        if (ctid < 128) v = qq < p.T ? p.lse[stat_base + qq] * kLog2e : INFINITY;
+        else v = qq < p.T ? p.delta[stat_base + qq] : 0.f;
+        stat[ctid] = v;
+      }
+      mbar_arrive(stat_bar);     // (a bounded mbarrier rather than bar.sync: a failed wait elsewhere must not strand anyone)
+      if (!mbar_wait(stat_bar, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      if (!mbar_wait(sdp_full, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      tcgen05_fence_after();
+      uint32_t rs[64], rd[64];
+      tmem_ld_32x32b_x32(t_lane + C_A + half * 64, rs);
+      tmem_ld_32x32b_x32(t_lane + C_A + half * 64 + 32, rs + 32);
+      tmem_ld_32x32b_x32(t_lane + C_B + half * 64, rd);
+      tmem_ld_32x32b_x32(t_lane + C_B + half * 64 + 32, rd + 32);
+      tmem_ld_wait();
+      const bool diag = it == 0;
+      const float4* lse4 = reinterpret_cast<const float4*>(stat + half * 64);
+      const float4* del4 = reinterpret_cast<const float4*>(stat + 128 + half * 64);
+      uint32_t pk[32], dk[32];
+#pragma unroll
+      for (int g = 0; g < 16; ++g) {
+        const float4 l4 = lse4[g], d4 = del4[g];
+        const float lv[4] = {l4.x, l4.y, l4.z, l4.w}, dv[4] = {d4.x, d4.y, d4.z, d4.w};
+        float pv[4], dsv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int i = 4 * g + u;
+          const int q = q0 + half * 64 + i;
+          const bool keep = key_ok && (!diag || q >= key);
+          const float e = fast_exp2(fmaf(__uint_as_float(rs[i]), sl2, -lv[u]));
+          pv[u] = keep ? e : 0.f;
+          dsv[u] = pv[u] * (__uint_as_float(rd[i]) - dv[u]) * p.scale;
+        }
+        pk[2 * g] = pack_bf16x2(pv[0], pv[1]);
+        pk[2 * g + 1] = pack_bf16x2(pv[2], pv[3]);
+        dk[2 * g] = pack_bf16x2(dsv[0], dsv[1]);
+        dk[2 * g + 1] = pack_bf16x2(dsv[2], dsv[3]);
+      }
+      tmem_st_32x32b_x16(t_lane + C_A + half * 64, pk);
+      tmem_st_32x32b_x16(t_lane + C_A + half * 64 + 16, pk + 16);
+      tmem_st_32x32b_x16(t_lane + C_B + half * 64, dk);
+      tmem_st_32x32b_x16(t_lane + C_B + half * 64 + 16, dk + 16);
+      // dS^T row of this key into smem: queries [64 half, 64 half + 64) = block `half`, eight swizzled 16-byte chunks
+#pragma unroll
+      for (int g = 0; g < 8; ++g)
+        st_shared_v4(sdS + half * SW_BLK + krow * 128 + ((g ^ (krow & 7)) << 4), dk[4 * g], dk[4 * g + 1], dk[4 * g + 2],
+                     dk[4 * g + 3]);
+      tmem_st_wait();
+      fence_proxy_async_smem();
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(ps_ready);
+      // dQ of this (query tile, key tile) pair: lanes are query rows now
+      if (!mbar_wait(dq_full, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      tcgen05_fence_after();
+      const int q = q0 + krow;
+      float* dq_row = p.dq_acc + (static_cast<size_t>(b) * p.T + (q < p.T ? q : 0)) * HD + h * D;
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        const int col = half * (D / 2) + c * 16;
+        uint32_t r[16];
+        tmem_ld_32x32b_x16(t_lane + C_A + col, r);
+        tmem_ld_wait();
+        if (q < p.T) {
+#pragma unroll
+          for (int j = 0; j < 16; j += 4)
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dq_row + col + j),
+                         "f"(__uint_as_float(r[j])), "f"(__uint_as_float(r[j + 1])),
+                         "f"(__uint_as_float(r[j + 2])), "f"(__uint_as_float(r[j + 3]))
+                         : "memory");
+        }
+      }
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(a_free);
+    }
+    if (ok) {   // dK / dV of this key tile (complete since the last dq_full)
+      bf16* dk_row = p.dqkv + (static_cast<size_t>(b) * p.T + (key < p.T ? key : 0)) * (3 * static_cast<size_t>(HD)) + HD + h * D;
+      bf16* dv_row = dk_row + HD;
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        const int col = half * (D / 2) + c * 16;
+        uint32_t rk[16], rv[16];
+        tmem_ld_32x32b_x16(t_lane + C_DK + col, rk);
+        tmem_ld_32x32b_x16(t_lane + C_DV + col, rv);
+        tmem_ld_wait();
+        if (key < p.T) {
+#pragma unroll
+          for (int j = 0; j < 16; j += 8) {
+            *reinterpret_cast<uint4*>(dk_row + col + j) = make_uint4(
+                pack_bf16x2(__uint_as_float(rk[j]), __uint_as_float(rk[j + 1])),
+                pack_bf16x2(__uint_as_float(rk[j + 2]), __uint_as_float(rk[j + 3])),
+                pack_bf16x2(__uint_as_float(rk[j + 4]), __uint_as_float(rk[j + 5])),
+                pack_bf16x2(__uint_as_float(rk[j + 6]), __uint_as_float(rk[j + 7])));
+            *reinterpret_cast<uint4*>(dv_row + col + j) = make_uint4(
+                pack_bf16x2(__uint_as_float(rv[j]), __uint_as_float(rv[j + 1])),
+                pack_bf16x2(__uint_as_float(rv[j + 2]), __uint_as_float(rv[j + 3])),
+                pack_bf16x2(__uint_as_float(rv[j + 4]), __uint_as_float(rv[j + 5])),
+                pack_bf16x2(__uint_as_float(rv[j + 6]), __uint_as_float(rv[j + 7])));
+          }
+        }
+      }
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem, TMEM_COLS);
+  }
+}
+
 // dq fp32 scratch [B*T, H*D] -> bf16 q section of dqkv [B*T, 3*H*D]
 __global__ void __launch_bounds__(256)
 attn_dq_convert_kernel(const float* __restrict__ dq_acc, bf16* __restrict__ dqkv, int64_t rows, int HD) {
@@ -894,22 +1179,24 @@ int fwd_launch(const AttnParams& p, cudaStream_t st) {
   return 0;
 }
 
-// 4-D view of qkv [B, T, 3*H*D] for the TMA loads of the warp-specialised kernels: (8 elements, T rows, 3*H*D / 8
-// column groups, B); a box {8, 128, D / 8, 1} arrives in shared memory as [column group][row][8] - the un-swizzled
-// core-matrix layout every MMA here reads.
+// 3-D view (columns, T, B) of qkv [B, T, 3*H*D] / dO [B, T, H*D] for the TMA loads of the warp-specialised kernels:
+// a box {64 columns, 128 rows, 1} with the 128-byte swizzle is one block of a tile (rows past T are zero-filled).
 int make_qkv_tmap(CUtensorMap* out, const bf16* base, int B, int T, int cols, int D) {
-  const uint64_t dims[4] = {8, static_cast<uint64_t>(T), static_cast<uint64_t>(cols / 8), static_cast<uint64_t>(B)};
-  const uint64_t strides[3] = {static_cast<uint64_t>(cols) * 2, 16, static_cast<uint64_t>(T) * cols * 2};
-  const uint32_t box[4] = {8, TQ, static_cast<uint32_t>(D / 8), 1};
-  return b200_make_tmap_nd(out, base, 4, dims, strides, box, 2, 0);
+  (void)D;
+  const uint64_t dims[3] = {static_cast<uint64_t>(cols), static_cast<uint64_t>(T), static_cast<uint64_t>(B)};
+  const uint64_t strides[2] = {static_cast<uint64_t>(cols) * 2, static_cast<uint64_t>(T) * cols * 2};
+  const uint32_t box[3] = {64, TQ, 1};
+  return b200_make_tmap_nd(out, base, 3, dims, strides, box, 2, 1);
 }
 
 // B200GPT_ATTN_WS=0 / 1 forces the per-tile (v1) / warp-specialised forward; unset: by sequence length
 int g_attn_ws = []() { const char* e = getenv("B200GPT_ATTN_WS"); return e == nullptr ? -1 : (e[0] == '0' ? 0 : 1); }();
 
+int g_attn_bwd_ws = []() { const char* e = getenv("B200GPT_ATTN_BWD_WS"); return e == nullptr ? -1 : (e[0] == '0' ? 0 : 1); }();
+
 template <int D>
 int fwd_ws_launch(const AttnParams& p, cudaStream_t st) {
-  constexpr int smem = 5 * TQ * D * 2 + 80 + 16 + 128;
+  constexpr int smem = 5 * TQ * D * 2 + 80 + 16;
   static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -947,11 +1234,32 @@ int bwd_launch(const AttnParams& p, cudaStream_t st) {
     B200_LAUNCH_CHECK();
   }
   const int nkt = ceil_div(p.T, TK);
-  AttnParams pb = p;
-  pb.tile_in_z = nkt <= 2 ? 1 : 0;
-  dim3 grid = pb.tile_in_z ? dim3(p.H, p.B, nkt) : dim3(nkt, p.H, p.B);
-  attn_bwd_kernel<D><<<grid, ATTN_BWD_THREADS, smem, st>>>(pb);
-  B200_LAUNCH_CHECK();
+  const bool ws = D >= 64 && (g_attn_bwd_ws >= 0 ? g_attn_bwd_ws == 1 : nkt >= 4);
+  bool launched = false;
+  if constexpr (D >= 64) if (ws) {
+    launched = true;
+    constexpr int smem_ws = 6 * TQ * D * 2 + TQ * TK * 2 + 1024 + 80 + 16;
+    static_assert(smem_ws <= 227 * 1024, "attention backward (warp-specialised): shared memory budget exceeded");
+    static bool configured_ws[64] = {false};
+    if (!configured_ws[dev & 63]) {
+      B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_ws_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_ws));
+      configured_ws[dev & 63] = true;
+    }
+    CUtensorMap tq, tdo;
+    int rc = make_qkv_tmap(&tq, p.qkv, p.B, p.T, 3 * HD, D);
+    if (rc != 0) return rc;
+    rc = make_qkv_tmap(&tdo, p.dout, p.B, p.T, HD, D);
+    if (rc != 0) return rc;
+    attn_bwd_ws_kernel<D><<<dim3(nkt, p.H, p.B), ATTN_BWD_WS_THREADS, smem_ws, st>>>(tq, tdo, p);
+    B200_LAUNCH_CHECK();
+  }
+  if (!launched) {
+    AttnParams pb = p;
+    pb.tile_in_z = nkt <= 2 ? 1 : 0;
+    dim3 grid = pb.tile_in_z ? dim3(p.H, p.B, nkt) : dim3(nkt, p.H, p.B);
+    attn_bwd_kernel<D><<<grid, ATTN_BWD_THREADS, smem, st>>>(pb);
+    B200_LAUNCH_CHECK();
+  }
   {
     const int64_t total = rows * (HD / 4);
     int grid2 = static_cast<int>((total + 255) / 256);
@@ -985,8 +1293,7 @@ static int attn_fwd_impl(const void* qkv, void* out, float* lse, int B, int T, i
   p.dbg = g_attn_dbg;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool ws = force_ws >= 0 ? force_ws == 1 : (g_attn_ws >= 0 ? g_attn_ws == 1 : (T > 3 * TQ && D >= 64));
-  if (ws) {
-    if (D == 32) return fwd_ws_launch<32>(p, st);
+  if (ws && D >= 64) {
     if (D == 64) return fwd_ws_launch<64>(p, st);
     return fwd_ws_launch<128>(p, st);
   }
