@@ -372,12 +372,16 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p
   constexpr uint32_t C_O = 256;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = smem_u32(smem_raw);      // swizzled blocks need 1024-byte alignment (checked below)
-  const uint32_t sQ = base, sK = sQ + TILE_BYTES, sV = sK + 2 * TILE_BYTES;
-  const uint32_t bars = sV + 2 * TILE_BYTES;
-  const uint32_t q_full = bars, kv_full = bars + 8, kv_empty = bars + 24, s_full = bars + 40, p_ready = bars + 56,
-                 o_done = bars + 72;
+  // K and V travel through separate NST-deep rings: a K slot is free again as soon as the S MMAs that read it have
+  // retired, a V slot only after its PV - with one shared 2-deep ring the load of tile j + 2 could not start before
+  // PV(j) and its whole latency sat in front of QK(j + 2)
+  constexpr int NST = 3;
+  const uint32_t sQ = base, sK = sQ + TILE_BYTES, sV = sK + NST * TILE_BYTES;
+  const uint32_t bars = sV + NST * TILE_BYTES;
+  const uint32_t q_full = bars, k_full = bars + 8, k_empty = bars + 32, v_full = bars + 56, v_empty = bars + 80,
+                 s_full = bars + 104, p_ready = bars + 120, o_done = bars + 136;
   uint8_t* gen = smem_raw;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + 5 * TILE_BYTES + 80);
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + (1 + 2 * NST) * TILE_BYTES + 144);
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
   if ((base & 1023u) != 0u) {
     if (threadIdx.x == 0) atomicCAS(p.err_word, 0, ERR_ATTN_SMEM_ALIGN);
@@ -393,9 +397,13 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p
   if (threadIdx.x == 0) {
     *abort_flag = 0;
     mbar_init(q_full, 1);
+    for (int i = 0; i < NST; ++i) {
+      mbar_init(k_full + 8 * i, 1);
+      mbar_init(k_empty + 8 * i, 1);
+      mbar_init(v_full + 8 * i, 1);
+      mbar_init(v_empty + 8 * i, 1);
+    }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(kv_full + 8 * i, 1);
-      mbar_init(kv_empty + 8 * i, 1);
       mbar_init(s_full + 8 * i, 1);
       mbar_init(p_ready + 8 * i, 4);
     }
@@ -418,11 +426,21 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p
       mbar_arrive_expect_tx(q_full, TILE_BYTES);
       tma_load_tile<D>(sQ, &tmQKV, q_full, h * D, q0, b);
       for (int j = 0; j < n_kt; ++j) {
-        const int s = j & 1;
-        if (j >= 2 && !mbar_wait(kv_empty + 8 * s, ((j >> 1) - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) break;
-        mbar_arrive_expect_tx(kv_full + 8 * s, 2 * TILE_BYTES);
-        tma_load_tile<D>(sK + s * TILE_BYTES, &tmQKV, kv_full + 8 * s, HD + h * D, j * TK, b);
-        tma_load_tile<D>(sV + s * TILE_BYTES, &tmQKV, kv_full + 8 * s, 2 * HD + h * D, j * TK, b);
+        const int st = j % NST;
+        const uint32_t use = static_cast<uint32_t>(j / NST);
+        if (j >= NST && !mbar_wait(k_empty + 8 * st, (use - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) break;
+        const bool skip = p.tile_in_z == 3 && j >= NST;    // timing experiment: no K / V traffic after the first tiles
+        if (skip) mbar_arrive(k_full + 8 * st);
+        else {
+          mbar_arrive_expect_tx(k_full + 8 * st, TILE_BYTES);
+          tma_load_tile<D>(sK + st * TILE_BYTES, &tmQKV, k_full + 8 * st, HD + h * D, j * TK, b);
+        }
+        if (j >= NST && !mbar_wait(v_empty + 8 * st, (use - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) break;
+        if (skip) mbar_arrive(v_full + 8 * st);
+        else {
+          mbar_arrive_expect_tx(v_full + 8 * st, TILE_BYTES);
+          tma_load_tile<D>(sV + st * TILE_BYTES, &tmQKV, v_full + 8 * st, 2 * HD + h * D, j * TK, b);
+        }
       }
     }
     __syncwarp();
@@ -432,13 +450,14 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p
     const uint32_t idesc_pv = umma_idesc_bf16(TQ, D, 0, 1);
     bool ok = mbar_wait(q_full, 0, abort_flag, p.err_word, ERR_ATTN_WS);
     auto issue_qk = [&](int j) {   // S[j & 1] = Q K(j)^T
-      const int s = j & 1;
-      if (!mbar_wait(kv_full + 8 * s, (j >> 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) return false;
+      const int s = j & 1, st = j % NST;
+      if (!mbar_wait(k_full + 8 * st, (j / NST) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) return false;
       tcgen05_fence_after();
       if (lane == 0) {
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
-          umma_f16_ss(tmem + s * 128, desc_sw_k(sQ, kk), desc_sw_k(sK + s * TILE_BYTES, kk), idesc_s, kk > 0 ? 1u : 0u);
+          umma_f16_ss(tmem + s * 128, desc_sw_k(sQ, kk), desc_sw_k(sK + st * TILE_BYTES, kk), idesc_s, kk > 0 ? 1u : 0u);
+        umma_commit(k_empty + 8 * st);
         umma_commit(s_full + 8 * s);
       }
       __syncwarp();
@@ -446,16 +465,17 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p
     };
     if (ok) ok = issue_qk(0);
     for (int j = 0; j < n_kt && ok; ++j) {
-      const int s = j & 1;
+      const int s = j & 1, st = j % NST;
       if (j + 1 < n_kt) ok = issue_qk(j + 1);
       if (!ok || !mbar_wait(p_ready + 8 * s, (j >> 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      if (!mbar_wait(v_full + 8 * st, (j / NST) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
       tcgen05_fence_after();
       if (lane == 0) {
 #pragma unroll
         for (int kk = 0; kk < TK / 16; ++kk)   // O (+)= P(j) V(j), P from tensor memory
-          umma_f16_ts(tmem + C_O, tmem + s * 128 + kk * 8, desc_sw_mn(sV + s * TILE_BYTES, kk), idesc_pv,
+          umma_f16_ts(tmem + C_O, tmem + s * 128 + kk * 8, desc_sw_mn(sV + st * TILE_BYTES, kk), idesc_pv,
                       (j > 0 || kk > 0) ? 1u : 0u);
-        umma_commit(kv_empty + 8 * s);
+        umma_commit(v_empty + 8 * st);
         umma_commit(o_done);
       }
       __syncwarp();
@@ -485,15 +505,22 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p
 #pragma unroll
         for (int c = 0; c < 4; ++c) kb[c] = keep_bits(j * TK + c * 32, q, diag, true, p.T, mask_row);
       }
-      float m_tile = -INFINITY;
+      // (masked and unmasked tiles run separate straight-line loops: a per-element branch or select on a run-time
+      // flag would cut the unrolled code into two-element pieces and leave the single warp of each scheduler
+      // waiting out every MUFU latency)
+      float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+      if (!masked_tile) {
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+        for (int i = 0; i < 128; ++i) mx[i & 3] = fmaxf(mx[i & 3], __uint_as_float(r[i]));
+      } else {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const float v = __uint_as_float(r[c * 32 + i]);
-          m_tile = fmaxf(m_tile, (!masked_tile || ((kb[c] >> i) & 1u)) ? v : -INFINITY);
+        for (int c = 0; c < 4; ++c) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            mx[i & 3] = fmaxf(mx[i & 3], ((kb[c] >> i) & 1u) ? __uint_as_float(r[c * 32 + i]) : -INFINITY);
         }
       }
+      float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
       m_tile *= sl2;                                    // log2 domain (scale > 0)
       // raise the reference maximum only when this tile exceeds it by 2^8 (or there is none yet)
       const bool raise = m_tile > m_used + 8.0f || (m_used == -INFINITY && m_tile > -INFINITY);
@@ -524,25 +551,40 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p
         m_used = m_new;
       }
       const float m_sub = (m_used == -INFINITY) ? 0.f : m_used;
-      float l_tile = 0.f;
+      float ls[4] = {0.f, 0.f, 0.f, 0.f};
+      if (!masked_tile) {
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        uint32_t pk[16];
+        for (int c = 0; c < 4; ++c) {
+          uint32_t pk[16];
+          float e[32];
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float e0 = fast_exp2(fmaf(__uint_as_float(r[c * 32 + i]), sl2, -m_sub));
-          float e1 = fast_exp2(fmaf(__uint_as_float(r[c * 32 + i + 1]), sl2, -m_sub));
-          if (masked_tile) {
-            e0 = ((kb[c] >> i) & 1u) ? e0 : 0.f;
-            e1 = ((kb[c] >> (i + 1)) & 1u) ? e1 : 0.f;
+          for (int i = 0; i < 32; ++i) e[i] = fast_exp2(fmaf(__uint_as_float(r[c * 32 + i]), sl2, -m_sub));
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            pk[i >> 1] = pack_bf16x2(e[i], e[i + 1]);
+            ls[(i >> 1) & 3] += e[i] + e[i + 1];
           }
-          const uint32_t packed = pack_bf16x2(e0, e1);
-          const float2 back = unpack_bf16x2(packed);     // sum what the tensor core will see
-          l_tile += back.x + back.y;
-          pk[i >> 1] = packed;
+          tmem_st_32x32b_x16(t_lane + s * 128 + c * 16, pk);   // keys [32c, 32c + 32) -> columns [16c, 16c + 16)
         }
-        tmem_st_32x32b_x16(t_lane + s * 128 + c * 16, pk);   // keys [32c, 32c + 32) -> columns [16c, 16c + 16)
+      } else {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t pk[16];
+          float e[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const float x = fast_exp2(fmaf(__uint_as_float(r[c * 32 + i]), sl2, -m_sub));
+            e[i] = ((kb[c] >> i) & 1u) ? x : 0.f;
+          }
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            pk[i >> 1] = pack_bf16x2(e[i], e[i + 1]);
+            ls[(i >> 1) & 3] += e[i] + e[i + 1];
+          }
+          tmem_st_32x32b_x16(t_lane + s * 128 + c * 16, pk);
+        }
       }
+      const float l_tile = (ls[0] + ls[1]) + (ls[2] + ls[3]);
       l_run += l_tile;
       tmem_st_wait();
       if (j > 0 && !seen_prev && !mbar_wait(o_done, (j - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
@@ -1100,7 +1142,7 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         uint32_t r[16];
         tmem_ld_32x32b_x16(t_lane + C_A + col, r);
         tmem_ld_wait();
-        if (q < p.T) {
+        if (q < p.T && p.tile_in_z != 2) {   // (tile_in_z == 2: timing experiment without the reductions)
 #pragma unroll
           for (int j = 0; j < 16; j += 4)
             asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dq_row + col + j),
@@ -1196,7 +1238,8 @@ int g_attn_bwd_ws = []() { const char* e = getenv("B200GPT_ATTN_BWD_WS"); return
 
 template <int D>
 int fwd_ws_launch(const AttnParams& p, cudaStream_t st) {
-  constexpr int smem = 5 * TQ * D * 2 + 80 + 16;
+  constexpr int smem = 7 * TQ * D * 2 + 144 + 16;
+  static_assert(smem <= 227 * 1024, "attention forward (warp-specialised): shared memory budget exceeded");
   static bool configured[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -1208,7 +1251,9 @@ int fwd_ws_launch(const AttnParams& p, cudaStream_t st) {
   int rc = make_qkv_tmap(&tm, p.qkv, p.B, p.T, 3 * p.H * D, D);
   if (rc != 0) return rc;
   dim3 grid(p.H, p.B, ceil_div(p.T, TQ));
-  attn_fwd_ws_kernel<D><<<grid, ATTN_WS_THREADS, smem, st>>>(tm, p);
+  AttnParams pw = p;
+  pw.tile_in_z = getenv("B200GPT_ATTN_NO_KV") != nullptr ? 3 : (getenv("B200GPT_ATTN_NO_EXP") != nullptr ? 4 : 0);
+  attn_fwd_ws_kernel<D><<<grid, ATTN_WS_THREADS, smem, st>>>(tm, pw);
   B200_LAUNCH_CHECK();
   return 0;
 }
@@ -1250,7 +1295,9 @@ int bwd_launch(const AttnParams& p, cudaStream_t st) {
     if (rc != 0) return rc;
     rc = make_qkv_tmap(&tdo, p.dout, p.B, p.T, HD, D);
     if (rc != 0) return rc;
-    attn_bwd_ws_kernel<D><<<dim3(nkt, p.H, p.B), ATTN_BWD_WS_THREADS, smem_ws, st>>>(tq, tdo, p);
+    AttnParams pw = p;
+    pw.tile_in_z = getenv("B200GPT_ATTN_NO_DQ") != nullptr ? 2 : 0;
+    attn_bwd_ws_kernel<D><<<dim3(nkt, p.H, p.B), ATTN_BWD_WS_THREADS, smem_ws, st>>>(tq, tdo, pw);
     B200_LAUNCH_CHECK();
   }
   if (!launched) {
