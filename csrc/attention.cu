@@ -429,18 +429,11 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p
         const int st = j % NST;
         const uint32_t use = static_cast<uint32_t>(j / NST);
         if (j >= NST && !mbar_wait(k_empty + 8 * st, (use - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) break;
-        const bool skip = p.tile_in_z == 3 && j >= NST;    // timing experiment: no K / V traffic after the first tiles
-        if (skip) mbar_arrive(k_full + 8 * st);
-        else {
-          mbar_arrive_expect_tx(k_full + 8 * st, TILE_BYTES);
-          tma_load_tile<D>(sK + st * TILE_BYTES, &tmQKV, k_full + 8 * st, HD + h * D, j * TK, b);
-        }
+        mbar_arrive_expect_tx(k_full + 8 * st, TILE_BYTES);
+        tma_load_tile<D>(sK + st * TILE_BYTES, &tmQKV, k_full + 8 * st, HD + h * D, j * TK, b);
         if (j >= NST && !mbar_wait(v_empty + 8 * st, (use - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) break;
-        if (skip) mbar_arrive(v_full + 8 * st);
-        else {
-          mbar_arrive_expect_tx(v_full + 8 * st, TILE_BYTES);
-          tma_load_tile<D>(sV + st * TILE_BYTES, &tmQKV, v_full + 8 * st, 2 * HD + h * D, j * TK, b);
-        }
+        mbar_arrive_expect_tx(v_full + 8 * st, TILE_BYTES);
+        tma_load_tile<D>(sV + st * TILE_BYTES, &tmQKV, v_full + 8 * st, 2 * HD + h * D, j * TK, b);
       }
     }
     __syncwarp();
@@ -941,7 +934,8 @@ attn_bwd_kernel(const AttnParams p) {
 // 320 threads: warp 0 loader (TMA; K / V once, Q / dO double-buffered so the next query tile arrives under the
 // current one), warp 1 MMA issuer, warps 2-9 compute (two threads per key row, half of the query columns each) -
 // they also drain dQ into the fp32 accumulator with vector reductions.
-// Tensor memory (512 columns): A [0,128) S^T -> P^T -> dQ;  B [128,256) dP^T -> dS^T;  dV [256,256+D);  dK after it.
+// Tensor memory (512 columns): A [0,128) S^T -> P^T;  B [128,256) dP^T -> dS^T -> dQ (so the next S^T MMA can run
+// while dQ is still being drained);  dV [256,256+D);  dK after it.
 // Each half-row thread writes its packed bf16 results over the first half of the columns it read itself
 // (queries [64h, 64h+64) -> columns 64h + [0,32)), so the two threads of a row never touch each other's inputs.
 constexpr int ATTN_BWD_WS_THREADS = 320;
@@ -1027,12 +1021,17 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       const int s = it & 1;
       const uint32_t q_s = sQ + s * TILE_BYTES, do_s = sdO + s * TILE_BYTES;
       if (!mbar_wait(qdo_full + 8 * s, (it >> 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
-      if (it > 0 && !mbar_wait(a_free, (it - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
       tcgen05_fence_after();
-      if (lane == 0) {
+      if (lane == 0) {    // S^T goes to region A, which the previous iteration's dV MMA has finished reading (in order)
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
           umma_f16_ss(tmem + C_A, desc_sw_k(sK, kk), desc_sw_k(q_s, kk), idesc_st, kk > 0 ? 1u : 0u);
+      }
+      __syncwarp();
+      // dP^T goes to region B, where the previous dQ sits until the compute warps have drained it
+      if (it > 0 && !mbar_wait(a_free, (it - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      tcgen05_fence_after();
+      if (lane == 0) {
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk)
           umma_f16_ss(tmem + C_B, desc_sw_k(sV, kk), desc_sw_k(do_s, kk), idesc_st, kk > 0 ? 1u : 0u);
@@ -1055,7 +1054,7 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         }
 #pragma unroll
         for (int kk = 0; kk < TK / 16; ++kk)     // dQ[q, d] = sum over keys dS[q, key] K[key, d]
-          umma_f16_ss(tmem + C_A, desc_sw_mn(sdS, kk), desc_sw_mn(sK, kk), idesc_dq, kk > 0 ? 1u : 0u);
+          umma_f16_ss(tmem + C_B, desc_sw_mn(sdS, kk), desc_sw_mn(sK, kk), idesc_dq, kk > 0 ? 1u : 0u);
         umma_commit(qdo_empty + 8 * s);
         umma_commit(dq_full);
       }
@@ -1088,44 +1087,54 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       if (!mbar_wait(stat_bar, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
       if (!mbar_wait(sdp_full, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
       tcgen05_fence_after();
-      uint32_t rs[64], rd[64];
-      tmem_ld_32x32b_x32(t_lane + C_A + half * 64, rs);
-      tmem_ld_32x32b_x32(t_lane + C_A + half * 64 + 32, rs + 32);
-      tmem_ld_32x32b_x32(t_lane + C_B + half * 64, rd);
-      tmem_ld_32x32b_x32(t_lane + C_B + half * 64 + 32, rd + 32);
-      tmem_ld_wait();
       const bool diag = it == 0;
-      const float4* lse4 = reinterpret_cast<const float4*>(stat + half * 64);
-      const float4* del4 = reinterpret_cast<const float4*>(stat + 128 + half * 64);
-      uint32_t pk[32], dk[32];
+      // two passes of 32 query columns each; inside a pass everything is straight-line code over independent elements
+      // (two warps per scheduler cannot hide a MUFU / LDS latency behind a branchy loop)
 #pragma unroll
-      for (int g = 0; g < 16; ++g) {
-        const float4 l4 = lse4[g], d4 = del4[g];
-        const float lv[4] = {l4.x, l4.y, l4.z, l4.w}, dv[4] = {d4.x, d4.y, d4.z, d4.w};
-        float pv[4], dsv[4];
+      for (int sub = 0; sub < 2; ++sub) {
+        const int cbase = half * 64 + sub * 32;          // first query column of this pass
+        uint32_t rs[32], rd[32];
+        tmem_ld_32x32b_x32(t_lane + C_A + cbase, rs);
+        tmem_ld_32x32b_x32(t_lane + C_B + cbase, rd);
+        float lv[32], dv[32];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int i = 4 * g + u;
-          const int q = q0 + half * 64 + i;
-          const bool keep = key_ok && (!diag || q >= key);
-          const float e = fast_exp2(fmaf(__uint_as_float(rs[i]), sl2, -lv[u]));
-          pv[u] = keep ? e : 0.f;
-          dsv[u] = pv[u] * (__uint_as_float(rd[i]) - dv[u]) * p.scale;
+        for (int g = 0; g < 8; ++g) {
+          const float4 l4 = reinterpret_cast<const float4*>(stat + cbase)[g];
+          const float4 d4 = reinterpret_cast<const float4*>(stat + 128 + cbase)[g];
+          lv[4 * g] = l4.x; lv[4 * g + 1] = l4.y; lv[4 * g + 2] = l4.z; lv[4 * g + 3] = l4.w;
+          dv[4 * g] = d4.x; dv[4 * g + 1] = d4.y; dv[4 * g + 2] = d4.z; dv[4 * g + 3] = d4.w;
         }
-        pk[2 * g] = pack_bf16x2(pv[0], pv[1]);
-        pk[2 * g + 1] = pack_bf16x2(pv[2], pv[3]);
-        dk[2 * g] = pack_bf16x2(dsv[0], dsv[1]);
-        dk[2 * g + 1] = pack_bf16x2(dsv[2], dsv[3]);
-      }
-      tmem_st_32x32b_x16(t_lane + C_A + half * 64, pk);
-      tmem_st_32x32b_x16(t_lane + C_A + half * 64 + 16, pk + 16);
-      tmem_st_32x32b_x16(t_lane + C_B + half * 64, dk);
-      tmem_st_32x32b_x16(t_lane + C_B + half * 64 + 16, dk + 16);
-      // dS^T row of this key into smem: queries [64 half, 64 half + 64) = block `half`, eight swizzled 16-byte chunks
+        // keys this row may attend from: all 32 queries, except above the diagonal (first iteration) / padded keys
+        uint32_t kb = 0xffffffffu;
+        if (diag) {
+          const int first = key - (q0 + cbase);          // queries q0 + cbase + i with i >= first see this key
+          kb = first <= 0 ? 0xffffffffu : (first >= 32 ? 0u : (0xffffffffu << first));
+        }
+        if (!key_ok) kb = 0u;
+        tmem_ld_wait();
+        float e[32];
 #pragma unroll
-      for (int g = 0; g < 8; ++g)
-        st_shared_v4(sdS + half * SW_BLK + krow * 128 + ((g ^ (krow & 7)) << 4), dk[4 * g], dk[4 * g + 1], dk[4 * g + 2],
-                     dk[4 * g + 3]);
+        for (int i = 0; i < 32; ++i) e[i] = fast_exp2(fmaf(__uint_as_float(rs[i]), sl2, -lv[i]));
+        if (__any_sync(0xffffffffu, kb != 0xffffffffu)) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) e[i] = ((kb >> i) & 1u) ? e[i] : 0.f;
+        }
+        uint32_t pk[16], dk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          const float d0 = e[i] * ((__uint_as_float(rd[i]) - dv[i]) * p.scale);
+          const float d1 = e[i + 1] * ((__uint_as_float(rd[i + 1]) - dv[i + 1]) * p.scale);
+          pk[i >> 1] = pack_bf16x2(e[i], e[i + 1]);
+          dk[i >> 1] = pack_bf16x2(d0, d1);
+        }
+        tmem_st_32x32b_x16(t_lane + C_A + half * 64 + sub * 16, pk);
+        tmem_st_32x32b_x16(t_lane + C_B + half * 64 + sub * 16, dk);
+        // dS^T row of this key into smem: queries [cbase, cbase + 32) = block `half`, four swizzled 16-byte chunks
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          st_shared_v4(sdS + half * SW_BLK + krow * 128 + (((sub * 4 + g) ^ (krow & 7)) << 4), dk[4 * g], dk[4 * g + 1],
+                       dk[4 * g + 2], dk[4 * g + 3]);
+      }
       tmem_st_wait();
       fence_proxy_async_smem();
       tcgen05_fence_before();
@@ -1140,9 +1149,9 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       for (int c = 0; c < D / 32; ++c) {
         const int col = half * (D / 2) + c * 16;
         uint32_t r[16];
-        tmem_ld_32x32b_x16(t_lane + C_A + col, r);
+        tmem_ld_32x32b_x16(t_lane + C_B + col, r);
         tmem_ld_wait();
-        if (q < p.T && p.tile_in_z != 2) {   // (tile_in_z == 2: timing experiment without the reductions)
+        if (q < p.T && p.tile_in_z != 2) {   // (B200GPT_ATTN_NO_DQ: timing experiment without the reductions)
 #pragma unroll
           for (int j = 0; j < 16; j += 4)
             asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dq_row + col + j),
@@ -1251,9 +1260,7 @@ int fwd_ws_launch(const AttnParams& p, cudaStream_t st) {
   int rc = make_qkv_tmap(&tm, p.qkv, p.B, p.T, 3 * p.H * D, D);
   if (rc != 0) return rc;
   dim3 grid(p.H, p.B, ceil_div(p.T, TQ));
-  AttnParams pw = p;
-  pw.tile_in_z = getenv("B200GPT_ATTN_NO_KV") != nullptr ? 3 : (getenv("B200GPT_ATTN_NO_EXP") != nullptr ? 4 : 0);
-  attn_fwd_ws_kernel<D><<<grid, ATTN_WS_THREADS, smem, st>>>(tm, pw);
+  attn_fwd_ws_kernel<D><<<grid, ATTN_WS_THREADS, smem, st>>>(tm, p);
   B200_LAUNCH_CHECK();
   return 0;
 }
