@@ -424,10 +424,14 @@ class PipeStrategy:
             self.reducer.active = False              # grads accumulate over micro-batches: reduce at the end
         for l in self.links:
             l.order_after_compute()
-        # receives are posted ahead of the compute that needs them; in the step that captures the graphs they are
-        # posted one at a time instead (capture must not sit behind a receive that depends on this stage's own work)
+        # Receives are posted ahead of the compute that needs them - but only once every kernel of a step has run
+        # at least once.  A posted NCCL receive is a kernel spinning on the GPU, and the FIRST launch of any kernel
+        # may have to load its module, which waits for running kernels: a gradient receive posted at the start of
+        # a step can only finish after this very stage has launched its forward kernels, so during the first steps
+        # (and in the step that captures the graphs) receives are posted one at a time, right where they are needed.
         acts = grads = None
-        if not capturing:
+        settled = self.steps_done >= self.graph_warmup + 2
+        if settled and not capturing:
             acts = [self.fwd_in.post_recv(sl.act_in) for sl in self.slots] if not st.is_first else None
             grads = [self.bwd_in.post_recv(sl.grad_in) for sl in self.slots] if not st.is_last else None
         for kind, i in schedule_actions(self.schedule, self.pp_rank, S, M):

@@ -120,6 +120,43 @@ if "kernels" in which:
         err = (p - p_ref.detach()).abs().max().item()
         report("rs_adamw", err < 1e-4 and torch.equal(pb, p.to(torch.bfloat16)) and dev_err() == 0, mc=use_mc, max_err=err)
 
+def nvlink_kib(idx):
+    """(tx, rx) KiB summed over the links of GPU idx, from the driver's NVLink data counters; None if unavailable."""
+    import re
+    import subprocess
+    try:
+        out = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(idx)], capture_output=True, text=True,
+                             timeout=20).stdout
+    except Exception:
+        return None
+    tx = sum(int(x) for x in re.findall(r"Data Tx:\s*(\d+)\s*KiB", out))
+    rx = sum(int(x) for x in re.findall(r"Data Rx:\s*(\d+)\s*KiB", out))
+    return (tx, rx) if (tx or rx) else None
+
+
+if "kernels" in which:
+    # NVLink traffic of the fused collectives, from the driver's link counters around 20 back-to-back launches
+    n_el = 8 * 1024 * 1024
+    rs_tmp = torch.empty(n_el // world, dtype=torch.float32, device=dev)
+    for name, per_call_expect in (("allreduce", 4 * n_el * (world - 1) / world), ("reduce_scatter", 4 * n_el // world * (world - 1) / world)):
+        torch.cuda.synchronize(); dist.barrier()
+        before = nvlink_kib(local)
+        for _ in range(20):
+            if name == "allreduce":
+                _lib.call("b200_allreduce", buf.ptrs_dev, buf.mc_ptr or None, ctx.flags.ptrs_dev, rank, world, 0, n_el,
+                          1.0 / world, 32, CH_ALLREDUCE, _lib.stream())
+            else:
+                _lib.call("b200_reduce_scatter", buf.ptrs_dev, buf.mc_ptr or None, ctx.flags.ptrs_dev, rank, world,
+                          rank * (n_el // world), n_el // world, 1.0 / world, rs_tmp.data_ptr(), 1, 8, CH_RS_ADAMW, _lib.stream())
+        torch.cuda.synchronize(); dist.barrier()
+        after = nvlink_kib(local)
+        if before and after:
+            report(f"nvlink_bytes_{name}", True, per_call_rx_MB=(after[1] - before[1]) / 20 / 1024,
+                   per_call_tx_MB=(after[0] - before[0]) / 20 / 1024, payload_MB=4 * n_el / 2 ** 20,
+                   note="per GPU; NVLS: the switch reduces, so RX ~ own slice (+ broadcast of the others for all-reduce)")
+        else:
+            report(f"nvlink_bytes_{name}", True, unavailable="nvidia-smi nvlink counters not readable on this box")
+
 if "kernels" in which:
     # all-gather fused into the GEMM: W [N, K] bf16 sharded evenly (as a flat byte range) over the ranks
     from distributed_pytorch_cookbook_b200.ops import native
@@ -146,8 +183,20 @@ if "kernels" in which:
         ref = A.float() @ W.float().t()
         err = (out.float() - ref).abs().max().item()
         dist.barrier()
+        torch.cuda.synchronize(); dist.barrier()
+        before = nvlink_kib(local)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for rep in range(20):
+            native.gemm(A, full.view(N, K), out, M, N, K,
+                        ag=(peers.data_ptr(), full.data_ptr(), 0, n_el * 2, shard_el * 2, sync.data_ptr(), 64))
+        e1.record()
+        torch.cuda.synchronize(); dist.barrier()
+        after = nvlink_kib(local)
+        rx = (after[1] - before[1]) / 20 / 1024 if (before and after) else None
         report("ag_gemm", err < 5e-2 and torch.equal(full.view(N, K), W) and int(sync.abs().sum()) == 0 and dev_err() == 0,
-               M=M, N=N, K=K, max_err=err)
+               M=M, N=N, K=K, max_err=err, us=e0.elapsed_time(e1) * 50, nvlink_rx_MB_per_call=rx,
+               weight_MB_from_peers=n_el * 2 * (world - 1) / world / 2 ** 20)
 
 CFG = dict(dim=256, head_dim=32, heads=8, num_layers=4, sequence_length=128, vocab_size=8192, batch_size=8,
            learning_rate=1e-3)
