@@ -464,9 +464,10 @@ class PipeStrategy:
                 self._loss_out = loss.reshape(1).clone()
                 self.loss_link.send(self._loss_out)
         elif st.is_first and self.loss_link is not None:
-            buf = torch.zeros(1, dtype=torch.float32, device=self.device)
-            self.loss_link.post_recv(buf).wait()
-            loss = buf[0]
+            if getattr(self, "_loss_in", None) is None:
+                self._loss_in = torch.zeros(1, dtype=torch.float32, device=self.device)   # (a fresh zeros() each step would
+            self.loss_link.post_recv(self._loss_in).wait()                                # race its fill kernel with the receive)
+            loss = self._loss_in[0].clone()
         for l in self.links:
             l.join()
         if st.is_first and self.dp_size > 1:
