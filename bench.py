@@ -307,7 +307,7 @@ def selfcheck(device):
         for name, make, comm in (("ddp_symm", DDPStrategy, "symm"), ("ddp_nccl", DDPStrategy, "nccl"),
                                  ("fsdp_symm", FSDPStrategy, "symm")):
             seed_everything(0)
-            ns = SimpleNamespace(**CFG, disable_amp=False, disable_cuda_graph=False, bucket_mb=4.0, comm=comm,
+            ns = SimpleNamespace(**CFG, disable_amp=False, disable_cuda_graph=False, bucket_mb=16.0, comm=comm,
                                  epochs=1, cpu_offload=False)
             st = make()
             st.setup(build_model(ns, CFG["vocab_size"]), ns, device)
@@ -478,7 +478,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--ref-compile", dest="ref_compile", choices=["both", "on", "off"], default="both")
-    ap.add_argument("--bucket_mb", type=float, default=4.0)
+    ap.add_argument("--bucket_mb", type=float, default=16.0)
     ap.add_argument("--comm", choices=["auto", "symm", "nccl"], default="auto")
     ap.add_argument("--comm_dtype", choices=["fp32", "bf16"], default="fp32")
     ap.add_argument("--min-seconds", dest="min_seconds", type=float, default=1.0,

@@ -17,6 +17,7 @@ and gloo on CPU - same bucket plan, ``dist.all_reduce`` per bucket.
 """
 from __future__ import annotations
 
+import os
 from contextlib import nullcontext
 from typing import List, Optional
 
@@ -60,6 +61,7 @@ class GradReducer:
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.symm, self.grad_buf, self.nblocks = symm, grad_buf, nblocks
+        self.tail_blocks = int(os.environ.get("B200GPT_DDP_TAIL_BLOCKS", "64"))
         cap = max(int(bucket_mb * (1 << 20) / 4), 1)
         self.cap = cap
         # --comm_dtype bf16: gradients cross NVLink as bf16 (fp32 accumulation in the switch) through a symmetric
@@ -127,7 +129,8 @@ class GradReducer:
             if tail and (hi - lo) > self.cap:
                 step = (self.cap + 7) // 8 * 8
                 spans = [(a, min(a + step, hi)) for a in range(lo, hi, step)]
-            max_blocks = 2 * self.nblocks if tail else self.nblocks       # tail: the rs_adamw channel range is idle too
+            # tail: compute has ended, so a wider grid costs nothing (channels [0, 128): the rs_adamw range is idle in DDP)
+            max_blocks = self.tail_blocks if tail else self.nblocks
             with torch.cuda.stream(self.comm_stream):
                 for a, z in spans:
                     nblocks = max(4, min(max_blocks, 128, ((z - a) * 4) >> 18))      # ~256 KiB of bucket per block
@@ -241,8 +244,9 @@ class DDPStrategy:
         self.optim = FusedAdamW(params, lr=args.learning_rate, device=self.device, arena=self.arena)
         self.comm_kind = transport
         self._verify_replicas()
-        self.reducer = GradReducer(self.arena, self.group, getattr(args, "bucket_mb", 4.0), transport,
-                                   self.symm, grad_buf, nblocks=64, comm_dtype=getattr(args, "comm_dtype", "fp32"))
+        self.reducer = GradReducer(self.arena, self.group, getattr(args, "bucket_mb", 16.0), transport,
+                                   self.symm, grad_buf, nblocks=int(os.environ.get("B200GPT_DDP_BLOCKS", "16")),
+                                   comm_dtype=getattr(args, "comm_dtype", "fp32"))
         if transport == "symm":
             self.comm_kind = f"symm:{self.reducer.comm_dtype}"
         self.use_graph = (transport == "symm" and not getattr(args, "disable_cuda_graph", False)) or \

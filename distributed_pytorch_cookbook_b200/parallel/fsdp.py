@@ -540,6 +540,7 @@ class FSDPStrategy:
         assert self.comm_kind == "symm", "skip_comm is a measurement aid of the symmetric-memory transport"
         self.skip_comm = on
         for g in self.groups:
+            g.event = None                                # events recorded inside the dropped graph capture are dead
             if hasattr(g, "peers_dev"):
                 g.fused = self.fused_ag and not on
         self._graphed = None

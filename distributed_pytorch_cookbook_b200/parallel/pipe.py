@@ -261,7 +261,7 @@ class PipeStrategy:
         self.optim = FusedAdamW(params, lr=args.learning_rate, device=self.device, arena=self.arena)
         if dp > 1:
             from .ddp import GradReducer
-            self.reducer = GradReducer(self.arena, self.dp_group, getattr(args, "bucket_mb", 4.0), transport,
+            self.reducer = GradReducer(self.arena, self.dp_group, getattr(args, "bucket_mb", 16.0), transport,
                                        symm, holder.get("buf"), comm_dtype=getattr(args, "comm_dtype", "fp32"))
         self.mb = args.batch_size // self.M
         assert self.mb * self.M == args.batch_size, "batch_size must be divisible by the number of micro-batches"

@@ -48,7 +48,8 @@ def build_parser(recipe: str = "single") -> argparse.ArgumentParser:
                    help="NVTX ranges around train_step / forward / backward / grad-sync / optimizer "
                         "(runs the step eagerly instead of as one CUDA graph so the ranges bracket kernels)")
     if recipe in ("ddp", "pipe-ddp"):
-        x.add_argument("--bucket_mb", type=float, default=4.0)
+        x.add_argument("--bucket_mb", type=float, default=16.0,
+                       help="gradient bucket size of the DDP reducer (16 MiB: five decoder layers of the default GPT per all-reduce)")
         x.add_argument("--comm", choices=["auto", "symm", "nccl"], default="auto",
                        help="gradient all-reduce transport: own NVLink kernels or NCCL")
         x.add_argument("--comm_dtype", choices=["fp32", "bf16"], default="fp32",

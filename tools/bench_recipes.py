@@ -61,7 +61,7 @@ def run_recipe(recipe, impl="ours", model="default", steps=10, warmup=4, schedul
     torch.manual_seed(0)
     if a.impl == "ours":
         from distributed_pytorch_cookbook_b200.trainer import build_model
-        ns = SimpleNamespace(**cfg, learning_rate=1e-4, disable_amp=False, disable_cuda_graph=a.no_graph, bucket_mb=4.0,
+        ns = SimpleNamespace(**cfg, learning_rate=1e-4, disable_amp=False, disable_cuda_graph=a.no_graph, bucket_mb=16.0,
                              comm=a.comm, cpu_offload=False)
         model = build_model(ns, V)
         if a.recipe == "fsdp":
