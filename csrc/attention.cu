@@ -940,7 +940,9 @@ attn_bwd_kernel(const AttnParams p) {
 // (queries [64h, 64h+64) -> columns 64h + [0,32)), so the two threads of a row never touch each other's inputs.
 constexpr int ATTN_BWD_WS_THREADS = 320;
 
-template <int D>
+// WITH_DQ = false: dK / dV only (dQ comes from attn_bwd_dq_kernel): no dS^T copy in shared memory, no dQ MMA, no
+// drain - the next tile's MMAs follow the dK MMA directly.
+template <int D, bool WITH_DQ>
 __global__ void __launch_bounds__(ATTN_BWD_WS_THREADS, 1)
 attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                    const AttnParams p) {
@@ -956,7 +958,8 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
   const uint32_t kv_full = bars, qdo_full = bars + 8, qdo_empty = bars + 24, sdp_full = bars + 40, ps_ready = bars + 48,
                  dq_full = bars + 56, a_free = bars + 64, stat_bar = bars + 72;
   uint8_t* gen = smem_raw;
-  float* stat = reinterpret_cast<float*>(gen + 6 * TILE_BYTES + SS_BYTES);
+  // lse / delta staging: one 1 KB buffer behind sdS; the dK / dV-only kernel double-buffers it inside the unused sdS region
+  float* stat = reinterpret_cast<float*>(gen + 6 * TILE_BYTES + (WITH_DQ ? SS_BYTES : 0));
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + 6 * TILE_BYTES + SS_BYTES + 1024 + 80);
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
   if ((base & 1023u) != 0u) {
@@ -1029,7 +1032,7 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       }
       __syncwarp();
       // dP^T goes to region B, where the previous dQ sits until the compute warps have drained it
-      if (it > 0 && !mbar_wait(a_free, (it - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      if (WITH_DQ && it > 0 && !mbar_wait(a_free, (it - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
       tcgen05_fence_after();
       if (lane == 0) {
 #pragma unroll
@@ -1052,11 +1055,13 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
           const uint32_t col = static_cast<uint32_t>((kk & 3) * 8 + (kk >> 2) * 64);
           umma_f16_ts(tmem + C_DK, tmem + C_B + col, desc_sw_mn(q_s, kk), idesc_tv, kk > 0 ? 1u : acc0);
         }
+        if constexpr (WITH_DQ) {
 #pragma unroll
-        for (int kk = 0; kk < TK / 16; ++kk)     // dQ[q, d] = sum over keys dS[q, key] K[key, d]
-          umma_f16_ss(tmem + C_B, desc_sw_mn(sdS, kk), desc_sw_mn(sK, kk), idesc_dq, kk > 0 ? 1u : 0u);
+          for (int kk = 0; kk < TK / 16; ++kk)     // dQ[q, d] = sum over keys dS[q, key] K[key, d]
+            umma_f16_ss(tmem + C_B, desc_sw_mn(sdS, kk), desc_sw_mn(sK, kk), idesc_dq, kk > 0 ? 1u : 0u);
+        }
         umma_commit(qdo_empty + 8 * s);
-        umma_commit(dq_full);
+        if (WITH_DQ || it == n_it - 1) umma_commit(dq_full);
       }
       __syncwarp();
     }
@@ -1081,7 +1086,7 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         float v;
         if (ctid < 128) v = qq < p.T ? p.lse[stat_base + qq] * kLog2e : INFINITY;
         else v = qq < p.T ? p.delta[stat_base + qq] : 0.f;
-        stat[ctid] = v;
+        stat[(WITH_DQ ? 0 : s * 256) + ctid] = v;
       }
       mbar_arrive(stat_bar);     // (a bounded mbarrier rather than bar.sync: a failed wait elsewhere must not strand anyone)
       if (!mbar_wait(stat_bar, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
@@ -1099,8 +1104,8 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         float lv[32], dv[32];
 #pragma unroll
         for (int g = 0; g < 8; ++g) {
-          const float4 l4 = reinterpret_cast<const float4*>(stat + cbase)[g];
-          const float4 d4 = reinterpret_cast<const float4*>(stat + 128 + cbase)[g];
+          const float4 l4 = reinterpret_cast<const float4*>(stat + (WITH_DQ ? 0 : s * 256) + cbase)[g];
+          const float4 d4 = reinterpret_cast<const float4*>(stat + (WITH_DQ ? 0 : s * 256) + 128 + cbase)[g];
           lv[4 * g] = l4.x; lv[4 * g + 1] = l4.y; lv[4 * g + 2] = l4.z; lv[4 * g + 3] = l4.w;
           dv[4 * g] = d4.x; dv[4 * g + 1] = d4.y; dv[4 * g + 2] = d4.z; dv[4 * g + 3] = d4.w;
         }
@@ -1130,16 +1135,19 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         tmem_st_32x32b_x16(t_lane + C_A + half * 64 + sub * 16, pk);
         tmem_st_32x32b_x16(t_lane + C_B + half * 64 + sub * 16, dk);
         // dS^T row of this key into smem: queries [cbase, cbase + 32) = block `half`, four swizzled 16-byte chunks
+        if constexpr (WITH_DQ) {
 #pragma unroll
-        for (int g = 0; g < 4; ++g)
-          st_shared_v4(sdS + half * SW_BLK + krow * 128 + (((sub * 4 + g) ^ (krow & 7)) << 4), dk[4 * g], dk[4 * g + 1],
-                       dk[4 * g + 2], dk[4 * g + 3]);
+          for (int g = 0; g < 4; ++g)
+            st_shared_v4(sdS + half * SW_BLK + krow * 128 + (((sub * 4 + g) ^ (krow & 7)) << 4), dk[4 * g], dk[4 * g + 1],
+                         dk[4 * g + 2], dk[4 * g + 3]);
+        }
       }
       tmem_st_wait();
       fence_proxy_async_smem();
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(ps_ready);
+      if constexpr (!WITH_DQ) continue;
       // dQ of this (query tile, key tile) pair: lanes are query rows now
       if (!mbar_wait(dq_full, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
       tcgen05_fence_after();
@@ -1164,7 +1172,9 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       __syncwarp();
       if (lane == 0) mbar_arrive(a_free);
     }
+    if (!WITH_DQ && ok) ok = mbar_wait(dq_full, 0, abort_flag, p.err_word, ERR_ATTN_WS);   // the one commit after the last MMAs
     if (ok) {   // dK / dV of this key tile (complete since the last dq_full)
+      tcgen05_fence_after();
       bf16* dk_row = p.dqkv + (static_cast<size_t>(b) * p.T + (key < p.T ? key : 0)) * (3 * static_cast<size_t>(HD)) + HD + h * D;
       bf16* dv_row = dk_row + HD;
 #pragma unroll
@@ -1188,6 +1198,184 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
                 pack_bf16x2(__uint_as_float(rv[j + 4]), __uint_as_float(rv[j + 5])),
                 pack_bf16x2(__uint_as_float(rv[j + 6]), __uint_as_float(rv[j + 7])));
           }
+        }
+      }
+    }
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// backward, dQ by the query tile's own CTA (no atomics): one CTA per (batch, head, 128-query tile) walks the key
+// tiles up to the diagonal like the forward does -  S = Q K^T, dP = dO V^T, dS = P (dP - delta) * scale written back
+// as bf16 over the S columns, dQ += dS K with the A operand from tensor memory - and writes its dQ rows once, as
+// bf16, straight into dqkv.  Costs two extra MMAs and a second exp per tile pair compared with reducing dQ out of
+// the dK / dV kernel, but removes 64 KB of fp32 read-modify-write per pair (a third of that kernel's time), the
+// accumulator memset and the fp32 -> bf16 conversion pass.
+// 192 threads: loader (Q, dO once; K, V through a 2-deep ring), MMA issuer, four compute warps (one query row per
+// thread: lse and delta are per-thread scalars here).  TMEM: S / dS [0,128), dP [128,256), dQ [256, 256 + D).
+template <int D>
+__global__ void __launch_bounds__(ATTN_WS_THREADS, 1)
+attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
+                   const AttnParams p) {
+  constexpr int TILE_BYTES = TQ * D * 2;
+  constexpr uint32_t TMEM_COLS = 512;
+  constexpr uint32_t C_S = 0, C_DP = 128, C_DQ = 256;
+  constexpr int NST = 2;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t base = smem_u32(smem_raw);
+  const uint32_t sQ = base, sdO = sQ + TILE_BYTES, sK = sdO + TILE_BYTES, sV = sK + NST * TILE_BYTES;
+  const uint32_t bars = sV + NST * TILE_BYTES;
+  const uint32_t q_full = bars, kv_full = bars + 8, kv_empty = bars + 24, sdp_full = bars + 40, ds_ready = bars + 48,
+                 dq_done = bars + 56;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem_raw + (2 + 2 * NST) * TILE_BYTES + 64);
+  volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
+  if ((base & 1023u) != 0u) {
+    if (threadIdx.x == 0) atomicCAS(p.err_word, 0, ERR_ATTN_SMEM_ALIGN);
+    return;
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qt = gridDim.z - 1 - blockIdx.z, h = blockIdx.x, b = blockIdx.y;   // long query tiles first
+  const int HD = p.H * D;
+  const int q0 = qt * TQ;
+  const int n_kt = qt + 1;
+
+  if (threadIdx.x == 0) {
+    *abort_flag = 0;
+    mbar_init(q_full, 1);
+    for (int i = 0; i < NST; ++i) {
+      mbar_init(kv_full + 8 * i, 1);
+      mbar_init(kv_empty + 8 * i, 1);
+    }
+    mbar_init(sdp_full, 1);
+    mbar_init(ds_ready, 4);
+    mbar_init(dq_done, 1);
+    fence_barrier_init();
+    tma_prefetch_desc(&tmQKV);
+    tma_prefetch_desc(&tmDO);
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(tmem_ptr_smem), TMEM_COLS);
+    tmem_relinquish();
+  }
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ===================== loader =====================
+    if (lane == 0) {
+      mbar_arrive_expect_tx(q_full, 2 * TILE_BYTES);
+      tma_load_tile<D>(sQ, &tmQKV, q_full, h * D, q0, b);
+      tma_load_tile<D>(sdO, &tmDO, q_full, h * D, q0, b);
+      for (int j = 0; j < n_kt; ++j) {
+        const int st = j % NST;
+        if (j >= NST && !mbar_wait(kv_empty + 8 * st, (j / NST - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) break;
+        mbar_arrive_expect_tx(kv_full + 8 * st, 2 * TILE_BYTES);
+        tma_load_tile<D>(sK + st * TILE_BYTES, &tmQKV, kv_full + 8 * st, HD + h * D, j * TK, b);
+        tma_load_tile<D>(sV + st * TILE_BYTES, &tmQKV, kv_full + 8 * st, 2 * HD + h * D, j * TK, b);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc_s = umma_idesc_bf16(TQ, TK, 0, 0);      // S, dP: K-major x K-major, N = 128 keys
+    const uint32_t idesc_dq = umma_idesc_bf16(TQ, D, 0, 1);      // dQ: A from TMEM, B = K tile MN-major
+    bool ok = mbar_wait(q_full, 0, abort_flag, p.err_word, ERR_ATTN_WS);
+    for (int j = 0; j < n_kt && ok; ++j) {
+      const int st = j % NST;
+      if (!mbar_wait(kv_full + 8 * st, (j / NST) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      tcgen05_fence_after();
+      if (lane == 0) {     // (S / dP of tile j overwrite dS of tile j - 1: its dQ MMA was issued before, in order)
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_f16_ss(tmem + C_S, desc_sw_k(sQ, kk), desc_sw_k(sK + st * TILE_BYTES, kk), idesc_s, kk > 0 ? 1u : 0u);
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk)
+          umma_f16_ss(tmem + C_DP, desc_sw_k(sdO, kk), desc_sw_k(sV + st * TILE_BYTES, kk), idesc_s, kk > 0 ? 1u : 0u);
+        umma_commit(sdp_full);
+      }
+      __syncwarp();
+      if (!mbar_wait(ds_ready, j & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      tcgen05_fence_after();
+      if (lane == 0) {
+#pragma unroll
+        for (int kk = 0; kk < TK / 16; ++kk)   // dQ (+)= dS K, reduction over the 128 keys
+          umma_f16_ts(tmem + C_DQ, tmem + C_S + kk * 8, desc_sw_mn(sK + st * TILE_BYTES, kk), idesc_dq,
+                      (j > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(kv_empty + 8 * st);
+        if (j == n_kt - 1) umma_commit(dq_done);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ===================== compute (4 warps, one query row per thread) =====================
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const int q = q0 + row;
+    const bool q_ok = q < p.T;
+    const uint32_t t_lane = tmem + (static_cast<uint32_t>(quarter * 32) << 16);
+    const float sl2 = p.scale * kLog2e;
+    const uint8_t* mask_row = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
+    const size_t stat_idx = (static_cast<size_t>(b) * p.H + h) * p.T + (q_ok ? q : 0);
+    const float lse2 = q_ok ? p.lse[stat_idx] * kLog2e : INFINITY;      // +inf: rows past T contribute nothing
+    const float delta = q_ok ? p.delta[stat_idx] : 0.f;
+    bool ok = true;
+    for (int j = 0; j < n_kt; ++j) {
+      if (!mbar_wait(sdp_full, j & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      tcgen05_fence_after();
+      const bool diag = (j == qt);
+      const bool masked_tile = diag || mask_row != nullptr;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {      // 32 keys per pass, straight-line code inside
+        uint32_t rs[32], rd[32];
+        tmem_ld_32x32b_x32(t_lane + C_S + c * 32, rs);
+        tmem_ld_32x32b_x32(t_lane + C_DP + c * 32, rd);
+        uint32_t kb = 0xffffffffu;
+        if (masked_tile) kb = keep_bits(j * TK + c * 32, q, diag, q_ok, p.T, mask_row);
+        tmem_ld_wait();
+        float e[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) e[i] = fast_exp2(fmaf(__uint_as_float(rs[i]), sl2, -lse2));
+        if (masked_tile) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) e[i] = ((kb >> i) & 1u) ? e[i] : 0.f;
+        }
+        uint32_t dk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2)
+          dk[i >> 1] = pack_bf16x2(e[i] * ((__uint_as_float(rd[i]) - delta) * p.scale),
+                                   e[i + 1] * ((__uint_as_float(rd[i + 1]) - delta) * p.scale));
+        // keys [32c, 32c + 32) -> columns [16c, 16c + 16) of the S region: already read by this thread
+        tmem_st_32x32b_x16(t_lane + C_S + c * 16, dk);
+      }
+      tmem_st_wait();
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(ds_ready);
+    }
+    if (ok && mbar_wait(dq_done, 0, abort_flag, p.err_word, ERR_ATTN_WS)) {
+      tcgen05_fence_after();
+      bf16* dq_row = p.dqkv + (static_cast<size_t>(b) * p.T + (q_ok ? q : 0)) * (3 * static_cast<size_t>(HD)) + h * D;
+#pragma unroll
+      for (int c = 0; c < D / 16; ++c) {
+        uint32_t o[16];
+        tmem_ld_32x32b_x16(t_lane + C_DQ + c * 16, o);
+        tmem_ld_wait();
+        if (q_ok) {
+#pragma unroll
+          for (int i = 0; i < 16; i += 8)
+            *reinterpret_cast<uint4*>(dq_row + c * 16 + i) = make_uint4(
+                pack_bf16x2(__uint_as_float(o[i]), __uint_as_float(o[i + 1])),
+                pack_bf16x2(__uint_as_float(o[i + 2]), __uint_as_float(o[i + 3])),
+                pack_bf16x2(__uint_as_float(o[i + 4]), __uint_as_float(o[i + 5])),
+                pack_bf16x2(__uint_as_float(o[i + 6]), __uint_as_float(o[i + 7])));
         }
       }
     }
@@ -1243,6 +1431,9 @@ int make_qkv_tmap(CUtensorMap* out, const bf16* base, int B, int T, int cols, in
 // B200GPT_ATTN_WS=0 / 1 forces the per-tile (v1) / warp-specialised forward; unset: by sequence length
 int g_attn_ws = []() { const char* e = getenv("B200GPT_ATTN_WS"); return e == nullptr ? -1 : (e[0] == '0' ? 0 : 1); }();
 
+// B200GPT_ATTN_DQ=atomic: dQ reduced out of the dK / dV kernel with fp32 vector reductions (+ memset + conversion
+// pass) instead of the query-owned dQ kernel
+bool g_attn_dq_kernel = []() { const char* e = getenv("B200GPT_ATTN_DQ"); return e != nullptr && e[0] == 'k'; }();
 int g_attn_bwd_ws = []() { const char* e = getenv("B200GPT_ATTN_BWD_WS"); return e == nullptr ? -1 : (e[0] == '0' ? 0 : 1); }();
 
 template <int D>
@@ -1266,7 +1457,7 @@ int fwd_ws_launch(const AttnParams& p, cudaStream_t st) {
 }
 
 template <int D>
-int bwd_launch(const AttnParams& p, cudaStream_t st) {
+int bwd_launch(const AttnParams& p, cudaStream_t st, int mode) {
   constexpr int smem = 4 * TQ * D * 2 + 2 * TQ * TK * 2 + 8 + 16 + 128;
   static bool configured[64] = {false};
   int dev = 0;
@@ -1277,6 +1468,40 @@ int bwd_launch(const AttnParams& p, cudaStream_t st) {
   }
   const int64_t rows = static_cast<int64_t>(p.B) * p.T;
   const int HD = p.H * D;
+  const int nkt = ceil_div(p.T, TK);
+  // mode: -1 automatic, 0 per-tile kernel, 1 warp-specialised + dQ by fp32 reductions, 2 warp-specialised dK / dV + dQ kernel
+  const bool ws = D >= 64 && (mode >= 0 ? mode >= 1 : (g_attn_bwd_ws >= 0 ? g_attn_bwd_ws == 1 : nkt >= 4));
+  const bool dq_kernel = mode >= 0 ? mode == 2 : g_attn_dq_kernel;
+  bool launched = false;
+  if constexpr (D >= 64) if (ws && dq_kernel) {
+    // dK / dV by key-tile CTAs, dQ by query-tile CTAs: no atomics, no accumulator memset, no conversion pass
+    constexpr int smem_kv = 6 * TQ * D * 2 + TQ * TK * 2 + 1024 + 80 + 16;
+    constexpr int smem_dq = 6 * TQ * D * 2 + 64 + 16;
+    static bool configured_kv[64] = {false};
+    if (!configured_kv[dev & 63]) {
+      B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_ws_kernel<D, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_kv));
+      B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dq));
+      configured_kv[dev & 63] = true;
+    }
+    {
+      const int64_t total = rows * p.H;
+      int grid = static_cast<int>((total + 255) / 256);
+      if (grid > b200_num_sms() * 16) grid = b200_num_sms() * 16;
+      attn_delta_kernel<D><<<grid, 256, 0, st>>>(p.out, p.dout, p.delta, p.B, p.T, p.H);
+      B200_LAUNCH_CHECK();
+    }
+    CUtensorMap tq, tdo;
+    int rc = make_qkv_tmap(&tq, p.qkv, p.B, p.T, 3 * HD, D);
+    if (rc != 0) return rc;
+    rc = make_qkv_tmap(&tdo, p.dout, p.B, p.T, HD, D);
+    if (rc != 0) return rc;
+    const int nkt2 = ceil_div(p.T, TK);
+    attn_bwd_ws_kernel<D, false><<<dim3(nkt2, p.H, p.B), ATTN_BWD_WS_THREADS, smem_kv, st>>>(tq, tdo, p);
+    B200_LAUNCH_CHECK();
+    attn_bwd_dq_kernel<D><<<dim3(p.H, p.B, ceil_div(p.T, TQ)), ATTN_WS_THREADS, smem_dq, st>>>(tq, tdo, p);
+    B200_LAUNCH_CHECK();
+    return 0;
+  }
   B200_CHECK_CUDA(cudaMemsetAsync(p.dq_acc, 0, rows * HD * sizeof(float), st));
   {
     const int64_t total = rows * p.H;
@@ -1285,16 +1510,13 @@ int bwd_launch(const AttnParams& p, cudaStream_t st) {
     attn_delta_kernel<D><<<grid, 256, 0, st>>>(p.out, p.dout, p.delta, p.B, p.T, p.H);
     B200_LAUNCH_CHECK();
   }
-  const int nkt = ceil_div(p.T, TK);
-  const bool ws = D >= 64 && (g_attn_bwd_ws >= 0 ? g_attn_bwd_ws == 1 : nkt >= 4);
-  bool launched = false;
   if constexpr (D >= 64) if (ws) {
     launched = true;
     constexpr int smem_ws = 6 * TQ * D * 2 + TQ * TK * 2 + 1024 + 80 + 16;
     static_assert(smem_ws <= 227 * 1024, "attention backward (warp-specialised): shared memory budget exceeded");
     static bool configured_ws[64] = {false};
     if (!configured_ws[dev & 63]) {
-      B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_ws_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_ws));
+      B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_ws_kernel<D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_ws));
       configured_ws[dev & 63] = true;
     }
     CUtensorMap tq, tdo;
@@ -1304,7 +1526,7 @@ int bwd_launch(const AttnParams& p, cudaStream_t st) {
     if (rc != 0) return rc;
     AttnParams pw = p;
     pw.tile_in_z = getenv("B200GPT_ATTN_NO_DQ") != nullptr ? 2 : 0;
-    attn_bwd_ws_kernel<D><<<dim3(nkt, p.H, p.B), ATTN_BWD_WS_THREADS, smem_ws, st>>>(tq, tdo, pw);
+    attn_bwd_ws_kernel<D, true><<<dim3(nkt, p.H, p.B), ATTN_BWD_WS_THREADS, smem_ws, st>>>(tq, tdo, pw);
     B200_LAUNCH_CHECK();
   }
   if (!launched) {
@@ -1367,9 +1589,9 @@ int b200_attn_fwd_select(const void* qkv, void* out, float* lse, int B, int T, i
   return attn_fwd_impl(qkv, out, lse, B, T, H, D, scale, key_mask, ws, stream);
 }
 
-int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
-                  float* delta, float* dq_acc, int B, int T, int H, int D, float scale,
-                  const void* key_mask, void* stream) {
+static int attn_bwd_impl(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                         float* delta, float* dq_acc, int B, int T, int H, int D, float scale,
+                         const void* key_mask, int mode, void* stream) {
   B200_REQUIRE(D == 32 || D == 64 || D == 128, "attention: head_dim %d not supported (32, 64, 128)", D);
   B200_REQUIRE(B > 0 && T > 0 && H > 0 && B <= 65535 && H <= 65535, "attention: bad shape");
   AttnParams p{};
@@ -1385,9 +1607,23 @@ int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const floa
   p.err_word = b200_error_word();
   p.dbg = g_attn_dbg;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (D == 32) return bwd_launch<32>(p, st);
-  if (D == 64) return bwd_launch<64>(p, st);
-  return bwd_launch<128>(p, st);
+  if (D == 32) return bwd_launch<32>(p, st, mode);
+  if (D == 64) return bwd_launch<64>(p, st, mode);
+  return bwd_launch<128>(p, st, mode);
+}
+
+int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                  float* delta, float* dq_acc, int B, int T, int H, int D, float scale,
+                  const void* key_mask, void* stream) {
+  return attn_bwd_impl(qkv, out, dout, lse, dqkv, delta, dq_acc, B, T, H, D, scale, key_mask, -1, stream);
+}
+
+// same with the kernels chosen by the caller: mode 0 per-tile kernel, 1 warp-specialised with dQ reduced by fp32 vector
+// reductions, 2 warp-specialised dK / dV kernel + query-owned dQ kernel (no atomics; dq_acc unused), -1 automatic
+int b200_attn_bwd_select(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                         float* delta, float* dq_acc, int B, int T, int H, int D, float scale,
+                         const void* key_mask, int mode, void* stream) {
+  return attn_bwd_impl(qkv, out, dout, lse, dqkv, delta, dq_acc, B, T, H, D, scale, key_mask, mode, stream);
 }
 
 }  // extern "C"

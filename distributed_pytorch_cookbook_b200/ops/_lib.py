@@ -51,6 +51,7 @@ _SIGS = {
     "b200_attn_fwd": [P, P, P, I, I, I, I, Fl, P, P],
     "b200_attn_fwd_select": [P, P, P, I, I, I, I, Fl, P, I, P],
     "b200_attn_bwd": [P, P, P, P, P, P, P, I, I, I, I, Fl, P, P],
+    "b200_attn_bwd_select": [P, P, P, P, P, P, P, I, I, I, I, Fl, P, I, P],
     "b200_allreduce": [P, P, P, I, I, L, L, Fl, I, I, P],
     "b200_allreduce_bf16": [P, P, P, P, I, I, L, L, Fl, I, I, P],
     "b200_rs_adamw": [P, P, P, I, I, L, L, Fl, P, P, P, P, P, Fl, Fl, Fl, Fl, I, I, I, P],

@@ -144,6 +144,12 @@ int b200_attn_bwd(const void* qkv_bf16, const void* out_bf16, const void* dout_b
                   void* dqkv_bf16, float* delta, float* dq_acc, int B, int T, int H, int D, float scale,
                   const void* key_mask, void* stream);
 
+/* same, kernels chosen by the caller: mode 0 per-tile kernel, 1 warp-specialised (dQ by fp32 vector reductions into
+ * dq_acc), 2 warp-specialised dK / dV kernel + query-owned dQ kernel (no atomics, dq_acc unused), -1 automatic */
+int b200_attn_bwd_select(const void* qkv_bf16, const void* out_bf16, const void* dout_bf16, const float* lse,
+                         void* dqkv_bf16, float* delta, float* dq_acc, int B, int T, int H, int D, float scale,
+                         const void* key_mask, int mode, void* stream);
+
 /* ---- NVLink / NVSwitch collectives over symmetric memory (no NCCL) --------------------------
  * bufs_dev : device array [world] of every rank's base pointer of the symmetric data buffer
  * mc_ptr   : NVLS multicast mapping of that buffer (NULL -> peer load/store fallback)

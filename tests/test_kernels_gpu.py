@@ -592,3 +592,41 @@ def test_attention_forward_kernels_agree(B, T, H, D):
     assert torch.allclose(outs[0][0].float(), outs[1][0].float(), atol=2e-2, rtol=2e-2)
     assert torch.allclose(outs[0][1], outs[1][1], atol=2e-3, rtol=1e-3)
     assert _dev_err() == 0
+
+
+@pytest.mark.parametrize("B,T,H,D,masked", [(2, 1023, 3, 128, False), (1, 641, 2, 64, True), (1, 2000, 1, 128, False)])
+def test_attention_backward_kernels_agree(B, T, H, D, masked):
+    """Three backward implementations - per-tile kernel, warp-specialised kernel reducing dQ with fp32 vector reductions,
+    warp-specialised dK / dV kernel + query-owned dQ kernel (no atomics) - against fp32 autograd and each other."""
+    from distributed_pytorch_cookbook_b200 import ops
+    torch.manual_seed(6)
+    qkv = (torch.randn(B, T, 3 * H * D, device="cuda") * 0.7).to(BF16)
+    scale = D ** -0.5
+    mask = None
+    km = None
+    if masked:
+        mask = torch.zeros(B, T, dtype=torch.bool, device="cuda")
+        mask[0, T - 29:] = True
+        km = mask.to(torch.uint8).contiguous()
+    out = torch.empty((B, T, H * D), dtype=BF16, device="cuda")
+    lse = torch.empty((B, H, T), dtype=torch.float32, device="cuda")
+    _lib.call("b200_attn_fwd", qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), B, T, H, D, float(scale),
+              _lib.ptr(km), _lib.stream())
+    dout = torch.randn_like(out)
+    q32 = qkv.float().requires_grad_(True)
+    q, k, v = (t.reshape(B, T, H, D).transpose(1, 2) for t in q32.chunk(3, dim=-1))
+    ops.attention_reference(q, k, v, scale, mask).transpose(1, 2).reshape(B, T, H * D).backward(dout.float())
+    valid = torch.ones(B, T, dtype=torch.bool, device="cuda") if mask is None else ~mask
+    got = []
+    for mode in (0, 1, 2):
+        dqkv = torch.full_like(qkv, float("nan"))
+        delta = torch.empty((B, H, T), dtype=torch.float32, device="cuda")
+        dq_acc = torch.empty((B, T, H * D), dtype=torch.float32, device="cuda")
+        _lib.call("b200_attn_bwd_select", qkv.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(), dqkv.data_ptr(),
+                  delta.data_ptr(), dq_acc.data_ptr(), B, T, H, D, float(scale), _lib.ptr(km), mode, _lib.stream())
+        torch.cuda.synchronize()
+        gd = (dqkv.float() - q32.grad)[valid]
+        assert gd.abs().max().item() <= 0.05 * q32.grad.abs().max().item() + 2e-2, (mode, gd.abs().max().item())
+        got.append(dqkv.float()[valid])
+    assert torch.allclose(got[0], got[1], atol=3e-2, rtol=3e-2) and torch.allclose(got[1], got[2], atol=3e-2, rtol=3e-2)
+    assert _dev_err() == 0

@@ -40,8 +40,12 @@ for (B, T, H, D) in [(8, 1023, 16, 128), (64, 255, 8, 32), (4, 4096, 16, 128), (
     for ws in (0, 1):
         res[ws] = timeit(lambda: _lib.call("b200_attn_fwd_select", qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), B, T, H,
                                            D, scale, None, ws, _lib.stream()))
-    bwd = timeit(lambda: _lib.call("b200_attn_bwd", qkv.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(),
-                                   dqkv.data_ptr(), delta.data_ptr(), dq_acc.data_ptr(), B, T, H, D, scale, None,
-                                   _lib.stream()))
-    print(f"B{B} T{T} H{H} D{D}: fwd per-tile {res[0]:8.1f} us ({flops/res[0]/1e6:6.1f} TFLOP/s)  fwd warp-spec {res[1]:8.1f} us "
-          f"({flops/res[1]/1e6:6.1f} TFLOP/s)  bwd {bwd:8.1f} us ({2.5*flops/bwd/1e6:6.1f} TFLOP/s)", flush=True)
+    bw = {}
+    for mode in (0, 1, 2):
+        bw[mode] = timeit(lambda: _lib.call("b200_attn_bwd_select", qkv.data_ptr(), out.data_ptr(), dout.data_ptr(),
+                                            lse.data_ptr(), dqkv.data_ptr(), delta.data_ptr(), dq_acc.data_ptr(), B, T, H,
+                                            D, scale, None, mode, _lib.stream()))
+    print(f"B{B} T{T} H{H} D{D}: fwd per-tile {res[0]:7.1f} us ({flops/res[0]/1e6:5.0f} TF)  warp-spec {res[1]:7.1f} us "
+          f"({flops/res[1]/1e6:5.0f} TF) | bwd per-tile {bw[0]:7.1f} us ({2.5*flops/bw[0]/1e6:5.0f} TF)  warp-spec+red "
+          f"{bw[1]:7.1f} us ({2.5*flops/bw[1]/1e6:5.0f} TF)  warp-spec+dQ kernel {bw[2]:7.1f} us ({2.5*flops/bw[2]/1e6:5.0f} TF)",
+          flush=True)

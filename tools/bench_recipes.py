@@ -182,7 +182,7 @@ def run_recipe(recipe, impl="ours", model="default", steps=10, warmup=4, schedul
         # what is left of the difference is communication that compute did not hide
         try:
             st.set_skip_comm(True)
-            for i in range(3):
+            for i in range(6):                       # eager warm-up steps + the (re-)capture of the step graph
                 step(i)
             ms_nc = timed(step, a.steps, dev)
             out["compute_only_ms_per_step"] = ms_nc / a.steps
