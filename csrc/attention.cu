@@ -343,6 +343,24 @@ attn_fwd_kernel(const AttnParams p) {
 // running maximum is only raised when a tile exceeds it by more than 2^8 (then O and the row sum are rescaled
 // in tensor memory, which needs the previous PV to have retired) - rescaling is rare after the first tiles.
 enum : int { ERR_ATTN_WS = 203, ERR_ATTN_SMEM_ALIGN = 204 };
+
+// wait / phase accounting of the warp-specialised kernels (trace build only: B200_GEMM_TRACE=1 python -m csrc.build;
+// tools/attn_ws_phases.py): cycles a role spent in each wait and in its own work, dumped per CTA into p.dbg
+#ifdef B200_GEMM_TRACE
+#define WS_NOW() clock64()
+#define WS_T0() _ws_t0 = clock64()
+#define WS_ACC(v) (v) += clock64() - _ws_t0
+#define WS_DUMP(slot, v)                                                                                         \
+  do {                                                                                                           \
+    if (p.dbg != nullptr && lane == 0)                                                                           \
+      p.dbg[((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 32 + (slot)] = (long long)(v);   \
+  } while (0)
+#else
+#define WS_NOW() 0LL
+#define WS_T0() do { } while (0)
+#define WS_ACC(v) do { } while (0)
+#define WS_DUMP(slot, v) do { } while (0)
+#endif
 constexpr int ATTN_WS_THREADS = 192;
 
 // Tile layout of the warp-specialised kernels: a [128 x D] bf16 tile is D / 64 blocks of [128 rows x 64 columns]
@@ -1020,10 +1038,13 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     const uint32_t idesc_tv = umma_idesc_bf16(TK, D, 0, 1);      // dV, dK: A from TMEM, B MN-major
     const uint32_t idesc_dq = umma_idesc_bf16(TQ, D, 1, 1);      // dQ: both operands MN-major
     bool ok = mbar_wait(kv_full, 0, abort_flag, p.err_word, ERR_ATTN_WS);
+    [[maybe_unused]] long long w_qdo = 0, w_afree = 0, w_ps = 0, t_begin = WS_NOW(), _ws_t0 = 0;
     for (int it = 0; it < n_it && ok; ++it) {
       const int s = it & 1;
       const uint32_t q_s = sQ + s * TILE_BYTES, do_s = sdO + s * TILE_BYTES;
+      WS_T0();
       if (!mbar_wait(qdo_full + 8 * s, (it >> 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      WS_ACC(w_qdo);
       tcgen05_fence_after();
       if (lane == 0) {    // S^T goes to region A, which the previous iteration's dV MMA has finished reading (in order)
 #pragma unroll
@@ -1032,7 +1053,9 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       }
       __syncwarp();
       // dP^T goes to region B, where the previous dQ sits until the compute warps have drained it
+      WS_T0();
       if (WITH_DQ && it > 0 && !mbar_wait(a_free, (it - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      WS_ACC(w_afree);
       tcgen05_fence_after();
       if (lane == 0) {
 #pragma unroll
@@ -1041,7 +1064,9 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         umma_commit(sdp_full);
       }
       __syncwarp();
+      WS_T0();
       if (!mbar_wait(ps_ready, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      WS_ACC(w_ps);
       tcgen05_fence_after();
       if (lane == 0) {
         const uint32_t acc0 = it > 0 ? 1u : 0u;
@@ -1065,6 +1090,7 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       }
       __syncwarp();
     }
+    WS_DUMP(0, w_qdo); WS_DUMP(1, w_afree); WS_DUMP(2, w_ps); WS_DUMP(3, WS_NOW() - t_begin); WS_DUMP(4, n_it);
   } else {
     // ===================== compute (8 warps) =====================
     const int quarter = warp & 3, half = (warp - 2) >> 2;
@@ -1076,9 +1102,11 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     const bool key_ok = key < p.T && !(p.key_mask != nullptr && p.key_mask[static_cast<size_t>(b) * p.T + key] != 0);
     const size_t stat_base = (static_cast<size_t>(b) * p.H + h) * p.T;
     bool ok = true;
+    [[maybe_unused]] long long w_stat = 0, w_sdp = 0, w_dq = 0, t_comp = 0, t_drain = 0, _ws_t0 = 0;
     for (int it = 0; it < n_it; ++it) {
       const int s = it & 1;
       const int q0 = (kt + it) * TQ;
+      WS_T0();
       // stage lse (log2 units, +inf for rows past T: their probabilities vanish) and delta of this query tile (one
       // buffer is enough: everybody has read the previous tile's values before dq_full of that tile could fire)
       {
@@ -1090,7 +1118,11 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       }
       mbar_arrive(stat_bar);     // (a bounded mbarrier rather than bar.sync: a failed wait elsewhere must not strand anyone)
       if (!mbar_wait(stat_bar, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      WS_ACC(w_stat);
+      WS_T0();
       if (!mbar_wait(sdp_full, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      WS_ACC(w_sdp);
+      WS_T0();
       tcgen05_fence_after();
       const bool diag = it == 0;
       // two passes of 32 query columns each; inside a pass everything is straight-line code over independent elements
@@ -1147,9 +1179,13 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(ps_ready);
+      WS_ACC(t_comp);
       if constexpr (!WITH_DQ) continue;
       // dQ of this (query tile, key tile) pair: lanes are query rows now
+      WS_T0();
       if (!mbar_wait(dq_full, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
+      WS_ACC(w_dq);
+      WS_T0();
       tcgen05_fence_after();
       const int q = q0 + krow;
       float* dq_row = p.dq_acc + (static_cast<size_t>(b) * p.T + (q < p.T ? q : 0)) * HD + h * D;
@@ -1171,7 +1207,9 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(a_free);
+      WS_ACC(t_drain);
     }
+    if (warp == 2) { WS_DUMP(8, w_stat); WS_DUMP(9, w_sdp); WS_DUMP(10, w_dq); WS_DUMP(11, t_comp); WS_DUMP(12, t_drain); }
     if (!WITH_DQ && ok) ok = mbar_wait(dq_full, 0, abort_flag, p.err_word, ERR_ATTN_WS);   // the one commit after the last MMAs
     if (ok) {   // dK / dV of this key tile (complete since the last dq_full)
       tcgen05_fence_after();
