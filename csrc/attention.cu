@@ -963,7 +963,7 @@ constexpr int ATTN_BWD_WS_THREADS = 320;
 template <int D, bool WITH_DQ>
 __global__ void __launch_bounds__(ATTN_BWD_WS_THREADS, 1)
 attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
-                   const AttnParams p) {
+                   const __grid_constant__ CUtensorMap tmDQ, const AttnParams p) {
   constexpr int TILE_BYTES = TQ * D * 2;
   constexpr int SS_BYTES = TQ * TK * 2;
   constexpr uint32_t TMEM_COLS = 512;
@@ -971,14 +971,13 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = smem_u32(smem_raw);      // swizzled blocks need 1024-byte alignment (checked below)
   const uint32_t sK = base, sV = sK + TILE_BYTES, sQ = sV + TILE_BYTES, sdO = sQ + 2 * TILE_BYTES;
-  const uint32_t sdS = sdO + 2 * TILE_BYTES, sStat = sdS + SS_BYTES;       // sStat: [lse2 128 | delta 128] floats
-  const uint32_t bars = sStat + 1024;
+  const uint32_t sdS = sdO + 2 * TILE_BYTES, sStat = sdS + SS_BYTES;       // sStat: [2][lse2 128 | delta 128] floats
+  const uint32_t bars = sStat + 2048;
   const uint32_t kv_full = bars, qdo_full = bars + 8, qdo_empty = bars + 24, sdp_full = bars + 40, ps_ready = bars + 48,
-                 dq_full = bars + 56, a_free = bars + 64, stat_bar = bars + 72;
+                 dq_full = bars + 56, a_free = bars + 64, stat_bar = bars + 72, drain_bar = bars + 80;
   uint8_t* gen = smem_raw;
-  // lse / delta staging: one 1 KB buffer behind sdS; the dK / dV-only kernel double-buffers it inside the unused sdS region
-  float* stat = reinterpret_cast<float*>(gen + 6 * TILE_BYTES + (WITH_DQ ? SS_BYTES : 0));
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + 6 * TILE_BYTES + SS_BYTES + 1024 + 80);
+  float* stat = reinterpret_cast<float*>(gen + 6 * TILE_BYTES + SS_BYTES);
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(gen + 6 * TILE_BYTES + SS_BYTES + 2048 + 88);
   volatile int* abort_flag = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
   if ((base & 1023u) != 0u) {
     if (threadIdx.x == 0) atomicCAS(p.err_word, 0, ERR_ATTN_SMEM_ALIGN);
@@ -1004,9 +1003,11 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     mbar_init(dq_full, 1);
     mbar_init(a_free, 8);
     mbar_init(stat_bar, 256);
+    mbar_init(drain_bar, 8);
     fence_barrier_init();
     tma_prefetch_desc(&tmQKV);
     tma_prefetch_desc(&tmDO);
+    if (WITH_DQ) tma_prefetch_desc(&tmDQ);
   }
   if (warp == 1) {
     tmem_alloc(smem_u32(tmem_ptr_smem), TMEM_COLS);
@@ -1085,7 +1086,7 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
           for (int kk = 0; kk < TK / 16; ++kk)     // dQ[q, d] = sum over keys dS[q, key] K[key, d]
             umma_f16_ss(tmem + C_B, desc_sw_mn(sdS, kk), desc_sw_mn(sK, kk), idesc_dq, kk > 0 ? 1u : 0u);
         }
-        umma_commit(qdo_empty + 8 * s);
+        if constexpr (!WITH_DQ) umma_commit(qdo_empty + 8 * s);   // (with dQ: the drain stages dQ in this Q / dO slot first)
         if (WITH_DQ || it == n_it - 1) umma_commit(dq_full);
       }
       __syncwarp();
@@ -1103,20 +1104,21 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
     const size_t stat_base = (static_cast<size_t>(b) * p.H + h) * p.T;
     bool ok = true;
     [[maybe_unused]] long long w_stat = 0, w_sdp = 0, w_dq = 0, t_comp = 0, t_drain = 0, _ws_t0 = 0;
+    // lse (log2 units, +inf for rows past T: their probabilities vanish) and delta of a query tile are staged one
+    // iteration ahead (two buffers), off the critical path
+    auto stage_stats = [&](int it_) {
+      const int qq = (kt + it_) * TQ + (ctid & 127);
+      float v;
+      if (ctid < 128) v = qq < p.T ? p.lse[stat_base + qq] * kLog2e : INFINITY;
+      else v = qq < p.T ? p.delta[stat_base + qq] : 0.f;
+      stat[(it_ & 1) * 256 + ctid] = v;
+      mbar_arrive(stat_bar);
+    };
+    stage_stats(0);
     for (int it = 0; it < n_it; ++it) {
       const int s = it & 1;
       const int q0 = (kt + it) * TQ;
       WS_T0();
-      // stage lse (log2 units, +inf for rows past T: their probabilities vanish) and delta of this query tile (one
-      // buffer is enough: everybody has read the previous tile's values before dq_full of that tile could fire)
-      {
-        const int qq = q0 + (ctid & 127);
-        float v;
-        if (ctid < 128) v = qq < p.T ? p.lse[stat_base + qq] * kLog2e : INFINITY;
-        else v = qq < p.T ? p.delta[stat_base + qq] : 0.f;
-        stat[(WITH_DQ ? 0 : s * 256) + ctid] = v;
-      }
-      mbar_arrive(stat_bar);     // (a bounded mbarrier rather than bar.sync: a failed wait elsewhere must not strand anyone)
       if (!mbar_wait(stat_bar, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; break; }
       WS_ACC(w_stat);
       WS_T0();
@@ -1136,8 +1138,8 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
         float lv[32], dv[32];
 #pragma unroll
         for (int g = 0; g < 8; ++g) {
-          const float4 l4 = reinterpret_cast<const float4*>(stat + (WITH_DQ ? 0 : s * 256) + cbase)[g];
-          const float4 d4 = reinterpret_cast<const float4*>(stat + (WITH_DQ ? 0 : s * 256) + 128 + cbase)[g];
+          const float4 l4 = reinterpret_cast<const float4*>(stat + s * 256 + cbase)[g];
+          const float4 d4 = reinterpret_cast<const float4*>(stat + s * 256 + 128 + cbase)[g];
           lv[4 * g] = l4.x; lv[4 * g + 1] = l4.y; lv[4 * g + 2] = l4.z; lv[4 * g + 3] = l4.w;
           dv[4 * g] = d4.x; dv[4 * g + 1] = d4.y; dv[4 * g + 2] = d4.z; dv[4 * g + 3] = d4.w;
         }
@@ -1179,6 +1181,7 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(ps_ready);
+      if (it + 1 < n_it) stage_stats(it + 1);
       WS_ACC(t_comp);
       if constexpr (!WITH_DQ) continue;
       // dQ of this (query tile, key tile) pair: lanes are query rows now
@@ -1187,28 +1190,50 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       WS_ACC(w_dq);
       WS_T0();
       tcgen05_fence_after();
-      const int q = q0 + krow;
-      float* dq_row = p.dq_acc + (static_cast<size_t>(b) * p.T + (q < p.T ? q : 0)) * HD + h * D;
+      // dQ tile -> fp32 in the Q / dO slot of this iteration (its MMAs have retired), laid out as 128B-swizzled
+      // [128 rows x 32 columns] boxes, then ONE thread hands it to the TMA engine as reduce-adds into the fp32
+      // accumulator: full 128-byte lines instead of 32 row-divergent 16-byte reductions per warp instruction
+      // (which kept the LSU busy for ~4400 cycles per tile pair), and asynchronous
+      {
+        const uint32_t stage = (half ? sdO : sQ) + s * TILE_BYTES;
 #pragma unroll
-      for (int c = 0; c < D / 32; ++c) {
-        const int col = half * (D / 2) + c * 16;
-        uint32_t r[16];
-        tmem_ld_32x32b_x16(t_lane + C_B + col, r);
-        tmem_ld_wait();
-        if (q < p.T && p.tile_in_z != 2) {   // (B200GPT_ATTN_NO_DQ: timing experiment without the reductions)
+        for (int c = 0; c < D / 32; ++c) {       // this thread's D / 2 columns, 16 at a time
+          const int col = c * 16;                // within the half
+          uint32_t r[16];
+          tmem_ld_32x32b_x16(t_lane + C_B + half * (D / 2) + col, r);
+          tmem_ld_wait();
+          const uint32_t box = stage + (col >> 5) * SW_BLK + krow * 128;
 #pragma unroll
-          for (int j = 0; j < 16; j += 4)
-            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dq_row + col + j),
-                         "f"(__uint_as_float(r[j])), "f"(__uint_as_float(r[j + 1])),
-                         "f"(__uint_as_float(r[j + 2])), "f"(__uint_as_float(r[j + 3]))
-                         : "memory");
+          for (int j = 0; j < 4; ++j) {
+            const int chunk = ((col & 31) >> 2) + j;          // 16-byte chunk (4 floats) within the 128-byte row
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(box + ((chunk ^ (krow & 7)) << 4)),
+                         "r"(r[4 * j]), "r"(r[4 * j + 1]), "r"(r[4 * j + 2]), "r"(r[4 * j + 3]) : "memory");
+          }
+        }
+        tcgen05_fence_before();
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(a_free);                   // region B has been read: the next dP^T MMA may overwrite it
+          mbar_arrive(drain_bar);
+        }
+        if (ctid == 0) {
+          if (!mbar_wait(drain_bar, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; }
+          if (ok && p.tile_in_z != 2) {
+#pragma unroll
+            for (int bx = 0; bx < D / 32; ++bx) {
+              const uint32_t src = ((bx * 32 >= D / 2) ? sdO : sQ) + s * TILE_BYTES + ((bx * 32) % (D / 2) >> 5) * SW_BLK;
+              tma_reduce_add_3d(&tmDQ, src, h * D + bx * 32, q0, b);
+            }
+            tma_store_commit();
+            tma_store_wait_read0();
+          }
+          mbar_arrive(qdo_empty + 8 * s);        // the slot may be refilled with the query tile two iterations ahead
         }
       }
-      tcgen05_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(a_free);
       WS_ACC(t_drain);
     }
+    if (WITH_DQ && ctid == 0) tma_store_wait_all();     // the reduce-adds have landed before the kernel ends
     if (warp == 2) { WS_DUMP(8, w_stat); WS_DUMP(9, w_sdp); WS_DUMP(10, w_dq); WS_DUMP(11, t_comp); WS_DUMP(12, t_drain); }
     if (!WITH_DQ && ok) ok = mbar_wait(dq_full, 0, abort_flag, p.err_word, ERR_ATTN_WS);   // the one commit after the last MMAs
     if (ok) {   // dK / dV of this key tile (complete since the last dq_full)
@@ -1513,7 +1538,7 @@ int bwd_launch(const AttnParams& p, cudaStream_t st, int mode) {
   bool launched = false;
   if constexpr (D >= 64) if (ws && dq_kernel) {
     // dK / dV by key-tile CTAs, dQ by query-tile CTAs: no atomics, no accumulator memset, no conversion pass
-    constexpr int smem_kv = 6 * TQ * D * 2 + TQ * TK * 2 + 1024 + 80 + 16;
+    constexpr int smem_kv = 6 * TQ * D * 2 + TQ * TK * 2 + 2048 + 88 + 16;
     constexpr int smem_dq = 6 * TQ * D * 2 + 64 + 16;
     static bool configured_kv[64] = {false};
     if (!configured_kv[dev & 63]) {
@@ -1534,7 +1559,7 @@ int bwd_launch(const AttnParams& p, cudaStream_t st, int mode) {
     rc = make_qkv_tmap(&tdo, p.dout, p.B, p.T, HD, D);
     if (rc != 0) return rc;
     const int nkt2 = ceil_div(p.T, TK);
-    attn_bwd_ws_kernel<D, false><<<dim3(nkt2, p.H, p.B), ATTN_BWD_WS_THREADS, smem_kv, st>>>(tq, tdo, p);
+    attn_bwd_ws_kernel<D, false><<<dim3(nkt2, p.H, p.B), ATTN_BWD_WS_THREADS, smem_kv, st>>>(tq, tdo, tq, p);
     B200_LAUNCH_CHECK();
     attn_bwd_dq_kernel<D><<<dim3(p.H, p.B, ceil_div(p.T, TQ)), ATTN_WS_THREADS, smem_dq, st>>>(tq, tdo, p);
     B200_LAUNCH_CHECK();
@@ -1550,7 +1575,7 @@ int bwd_launch(const AttnParams& p, cudaStream_t st, int mode) {
   }
   if constexpr (D >= 64) if (ws) {
     launched = true;
-    constexpr int smem_ws = 6 * TQ * D * 2 + TQ * TK * 2 + 1024 + 80 + 16;
+    constexpr int smem_ws = 6 * TQ * D * 2 + TQ * TK * 2 + 2048 + 88 + 16;
     static_assert(smem_ws <= 227 * 1024, "attention backward (warp-specialised): shared memory budget exceeded");
     static bool configured_ws[64] = {false};
     if (!configured_ws[dev & 63]) {
@@ -1564,7 +1589,15 @@ int bwd_launch(const AttnParams& p, cudaStream_t st, int mode) {
     if (rc != 0) return rc;
     AttnParams pw = p;
     pw.tile_in_z = getenv("B200GPT_ATTN_NO_DQ") != nullptr ? 2 : 0;
-    attn_bwd_ws_kernel<D, true><<<dim3(nkt, p.H, p.B), ATTN_BWD_WS_THREADS, smem_ws, st>>>(tq, tdo, pw);
+    CUtensorMap tdq;   // fp32 dQ accumulator [B, T, H*D] as (columns, T, B): box {32 columns = 128 bytes, 128 rows}
+    {
+      const uint64_t dims[3] = {static_cast<uint64_t>(HD), static_cast<uint64_t>(p.T), static_cast<uint64_t>(p.B)};
+      const uint64_t strides[2] = {static_cast<uint64_t>(HD) * 4, static_cast<uint64_t>(p.T) * HD * 4};
+      const uint32_t box[3] = {32, TQ, 1};
+      rc = b200_make_tmap_nd(&tdq, p.dq_acc, 3, dims, strides, box, 4, 1);
+      if (rc != 0) return rc;
+    }
+    attn_bwd_ws_kernel<D, true><<<dim3(nkt, p.H, p.B), ATTN_BWD_WS_THREADS, smem_ws, st>>>(tq, tdo, tdq, pw);
     B200_LAUNCH_CHECK();
   }
   if (!launched) {
