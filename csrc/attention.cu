@@ -1024,12 +1024,38 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
       mbar_arrive_expect_tx(kv_full, 2 * TILE_BYTES);
       tma_load_tile<D>(sK, &tmQKV, kv_full, HD + h * D, k0, b);
       tma_load_tile<D>(sV, &tmQKV, kv_full, 2 * HD + h * D, k0, b);
-      for (int it = 0; it < n_it; ++it) {
+      auto load_qdo = [&](int it) {
         const int s = it & 1;
-        if (it >= 2 && !mbar_wait(qdo_empty + 8 * s, ((it >> 1) - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) break;
         mbar_arrive_expect_tx(qdo_full + 8 * s, 2 * TILE_BYTES);
         tma_load_tile<D>(sQ + s * TILE_BYTES, &tmQKV, qdo_full + 8 * s, h * D, (kt + it) * TQ, b);
         tma_load_tile<D>(sdO + s * TILE_BYTES, &tmDO, qdo_full + 8 * s, h * D, (kt + it) * TQ, b);
+      };
+      if constexpr (!WITH_DQ) {
+        for (int it = 0; it < n_it; ++it) {
+          if (it >= 2 && !mbar_wait(qdo_empty + 8 * (it & 1), ((it >> 1) - 1) & 1, abort_flag, p.err_word, ERR_ATTN_WS)) break;
+          load_qdo(it);
+        }
+      } else {
+        // with dQ this thread also hands every drained dQ tile (staged by the compute warps in the Q / dO slot of
+        // its iteration) to the TMA engine as reduce-adds, and refills the slot once the engine has read it - the
+        // wait for that read would otherwise sit in a compute warp and hold up the next tile's math
+        load_qdo(0);
+        if (n_it > 1) load_qdo(1);
+        for (int it = 0; it < n_it; ++it) {
+          const int s = it & 1;
+          if (!mbar_wait(drain_bar, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) break;
+          if (p.tile_in_z != 2) {
+#pragma unroll
+            for (int bx = 0; bx < D / 32; ++bx) {
+              const uint32_t src = ((bx * 32 >= D / 2) ? sdO : sQ) + s * TILE_BYTES + ((bx * 32) % (D / 2) >> 5) * SW_BLK;
+              tma_reduce_add_3d(&tmDQ, src, h * D + bx * 32, (kt + it) * TQ, b);
+            }
+            tma_store_commit();
+            tma_store_wait_read0();
+          }
+          if (it + 2 < n_it) load_qdo(it + 2);
+        }
+        tma_store_wait_all();     // the reduce-adds have landed before the kernel ends
       }
     }
     __syncwarp();
@@ -1217,23 +1243,9 @@ attn_bwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_const
           mbar_arrive(a_free);                   // region B has been read: the next dP^T MMA may overwrite it
           mbar_arrive(drain_bar);
         }
-        if (ctid == 0) {
-          if (!mbar_wait(drain_bar, it & 1, abort_flag, p.err_word, ERR_ATTN_WS)) { ok = false; }
-          if (ok && p.tile_in_z != 2) {
-#pragma unroll
-            for (int bx = 0; bx < D / 32; ++bx) {
-              const uint32_t src = ((bx * 32 >= D / 2) ? sdO : sQ) + s * TILE_BYTES + ((bx * 32) % (D / 2) >> 5) * SW_BLK;
-              tma_reduce_add_3d(&tmDQ, src, h * D + bx * 32, q0, b);
-            }
-            tma_store_commit();
-            tma_store_wait_read0();
-          }
-          mbar_arrive(qdo_empty + 8 * s);        // the slot may be refilled with the query tile two iterations ahead
-        }
       }
       WS_ACC(t_drain);
     }
-    if (WITH_DQ && ctid == 0) tma_store_wait_all();     // the reduce-adds have landed before the kernel ends
     if (warp == 2) { WS_DUMP(8, w_stat); WS_DUMP(9, w_sdp); WS_DUMP(10, w_dq); WS_DUMP(11, t_comp); WS_DUMP(12, t_drain); }
     if (!WITH_DQ && ok) ok = mbar_wait(dq_full, 0, abort_flag, p.err_word, ERR_ATTN_WS);   // the one commit after the last MMAs
     if (ok) {   // dK / dV of this key tile (complete since the last dq_full)
