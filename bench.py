@@ -350,8 +350,16 @@ def run_recipes(impl, n, args):
     if n >= 4:
         plan.append((f"pipe_ddp_2x{n // 2}", dict(recipe="pipe-ddp", steps=20, warmup=6, schedule="1f1b", microbatches=4)))
     out = {}
+    t_start = time.time()
     for name, kw in plan:
         if args.recipes != "all" and name.split("_")[0] not in args.recipes.split(","):
+            continue
+        # the recipes must never cost the headline line: stop adding them once the time budget is used up (every rank
+        # takes the same decision: rank 0's clock is broadcast)
+        spent = torch.tensor([time.time() - t_start], device=f"cuda:{torch.cuda.current_device()}")
+        dist.broadcast(spent, src=0)
+        if float(spent) > args.recipe_budget_s:
+            out[name] = {"skipped": f"recipe time budget of {args.recipe_budget_s:.0f} s used up"}
             continue
         try:
             r = run_recipe(impl=impl, **kw)
@@ -487,6 +495,8 @@ def main():
                     help="N > 1: skip the FSDP-1.3B / pipeline / pipeline x DDP recipes after the headline run")
     ap.add_argument("--recipes", default="all", help="comma list out of fsdp,pipe (pipe covers pipe and pipe_ddp)")
     ap.add_argument("--no-selfcheck", dest="no_selfcheck", action="store_true")
+    ap.add_argument("--recipe-budget-s", dest="recipe_budget_s", type=float, default=240.0,
+                    help="wall-clock budget for the recipes of one arm; recipes that would start later are skipped")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank, _, n = world()
