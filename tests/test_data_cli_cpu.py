@@ -141,3 +141,20 @@ def test_resume_restores_adamw_moments_and_step():
     assert float(la) == float(lb)
     for (k, x), (_, y) in zip(a.model.state_dict().items(), b.model.state_dict().items()):
         assert torch.equal(x, y), k
+
+
+def test_additive_flags_parse_and_cpu_guards():
+    """Round-2 flags exist on the right recipes; the device-error check and the NVTX phases are no-ops without a GPU."""
+    from distributed_pytorch_cookbook_b200.trainer import check_device_error
+    from distributed_pytorch_cookbook_b200.utils import build_parser, nvtx
+    a = build_parser("fsdp").parse_args(["--reshard_after_forward", "--resume", "x.pt", "--resume_epochs", "--profile"])
+    assert a.reshard_after_forward and a.resume_epochs and a.profile
+    a = build_parser("pipe").parse_args(["--checkpoint", "except_last", "--num_microbatches", "8", "--schedule", "1f1b"])
+    assert a.checkpoint == "except_last" and a.num_microbatches == 8
+    a = build_parser("ddp").parse_args(["--comm_dtype", "bf16"])
+    assert a.comm_dtype == "bf16" and a.bucket_mb == 16.0
+    check_device_error("in a CPU test")          # nothing to poll: must not raise
+    nvtx.enable(True)
+    with nvtx.phase("x"):
+        pass
+    nvtx.enable(False)
