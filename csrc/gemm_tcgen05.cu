@@ -444,7 +444,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       [[maybe_unused]] float rowa = 0.f;
       [[maybe_unused]] int tgt = -1;
       [[maybe_unused]] float s_sum[4] = {0.f, 0.f, 0.f, 0.f};
-      [[maybe_unused]] float s_max = -INFINITY;
+      [[maybe_unused]] float s_max4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // independent chains
       if constexpr (E_RSCALE) rowa = row_ok ? __ldg(p.row_a + row) : 0.f;
       if constexpr (E_SMAX) {
         rowa = lm_row_shift(row_ok ? __ldg(p.row_a + row) : 0.f, __ldg(p.wmax), __ldg(p.wmax + 1)) * kLog2e;
@@ -582,7 +582,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             p.tgt_val[row] = tv;
           }
 #pragma unroll
-          for (int j = 0; j < 32; ++j) s_max = fmaxf(s_max, v[j]);
+          for (int j = 0; j < 32; ++j) s_max4[j & 3] = fmaxf(s_max4[j & 3], v[j]);
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             v[j] = fast_exp2(fmaf(v[j], kLog2e, -rowa));
@@ -656,7 +656,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if constexpr (E_SMAX) {   // one (sum, max) partial per row and per NCH * 32-column span, coalesced over the warp
         if (row_ok)
           p.part[static_cast<size_t>(n0 / (NCH * 32)) * p.M + row] =
-              make_float2((s_sum[0] + s_sum[1]) + (s_sum[2] + s_sum[3]), s_max);
+              make_float2((s_sum[0] + s_sum[1]) + (s_sum[2] + s_sum[3]),
+                          fmaxf(fmaxf(s_max4[0], s_max4[1]), fmaxf(s_max4[2], s_max4[3])));
       }
     }
     if (warp_idx == 2 && lane == 0) DBG_STAMP(6);
