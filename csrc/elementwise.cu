@@ -79,7 +79,8 @@ constexpr int REPLICAS = 16;
 
 __device__ __forceinline__ void finish_column_sums(float* __restrict__ scratch, int* __restrict__ counter,
                                                    int ncols, int total_blocks, float* __restrict__ out_a,
-                                                   float* __restrict__ out_b, int split) {
+                                                   float* __restrict__ out_b, int split,
+                                                   float* __restrict__ out_c = nullptr, bool three = false) {
   __shared__ int s_last;
   __threadfence();
   __syncthreads();
@@ -97,7 +98,8 @@ __device__ __forceinline__ void finish_column_sums(float* __restrict__ scratch, 
       scratch[r * ncols + c] = 0.f;
     }
     if (c < split) out_a[c] += s;
-    else out_b[c - split] += s;
+    else if (!three || c < 2 * split) out_b[c - split] += s;
+    else if (out_c != nullptr) out_c[c - 2 * split] += s;   // three equally wide outputs, the third optional
   }
   if (tid == 0) *counter = 0;
 }
@@ -160,31 +162,38 @@ layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
 // Narrow rows (dim <= 256): one warp handles R rows per iteration with every load of the R rows
 // issued before the first use (the kernel is latency bound: a row is only 1.5 KB), values stay in
 // registers for the single pass, and the dres (residual-branch gradient) add is folded in.
-template <int NV, int R>
+// FUSE: the kernel also does the first step of the backward of the layer that PRODUCED x (a Linear or MLP whose
+// epilogue added the residual, reference models/gpt.py:33-41,105-123): dz = dx * act'(mask_src) as bf16 (the operand
+// of that layer's dgrad / wgrad GEMMs) and dbias_z += column sums of dz, so no separate pass re-reads dx.
+template <int NV, int R, bool FUSE = false>
 __global__ void __launch_bounds__(256, 2)   // <= 128 registers: two blocks (16 warps) per SM keep twice the rows in flight
 layernorm_bwd_small_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
                            const float* __restrict__ gamma, const float* __restrict__ mean_in,
                            const float* __restrict__ rstd_in, const float* __restrict__ dres,
                            float* __restrict__ dx, bf16* __restrict__ dx_bf16, float* __restrict__ dgamma,
                            float* __restrict__ dbeta, int rows, int dim, float* __restrict__ scratch,
-                           int* __restrict__ counter) {
+                           int* __restrict__ counter, const bf16* __restrict__ mask_src = nullptr, int act = 0,
+                           float* __restrict__ dbias_z = nullptr) {
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int warps_per_block = blockDim.x >> 5;
   const int nvec = dim >> 2;
   const float inv_dim = 1.0f / static_cast<float>(dim);
   float4 g4[NV], dg[NV], db[NV];
+  [[maybe_unused]] float4 dbz[NV];
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     const int c = lane + 32 * i;
     g4[i] = c < nvec ? __ldg(reinterpret_cast<const float4*>(gamma) + c) : make_float4(0.f, 0.f, 0.f, 0.f);
     dg[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     db[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if constexpr (FUSE) dbz[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   const int row_stride = gridDim.x * warps_per_block * R;
   for (int row0 = (blockIdx.x * warps_per_block + warp) * R; row0 < rows; row0 += row_stride) {
     float4 xv[R][NV], rv[R][NV];
     uint2 dv[R][NV];
+    [[maybe_unused]] uint2 mv[R][NV];   // FUSE: the producer's activation mask, fetched with everything else
     float mean[R], rstd[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
@@ -201,6 +210,9 @@ layernorm_bwd_small_kernel(const bf16* __restrict__ dy, const float* __restrict_
         dv[r][i] = okc ? reinterpret_cast<const uint2*>(dy + off)[c] : make_uint2(0u, 0u);
         rv[r][i] = (okc && dres != nullptr) ? reinterpret_cast<const float4*>(dres + off)[c]
                                             : make_float4(0.f, 0.f, 0.f, 0.f);
+        if constexpr (FUSE)
+          mv[r][i] = (okc && mask_src != nullptr) ? reinterpret_cast<const uint2*>(mask_src + off)[c]
+                                                  : make_uint2(0x3f803f80u, 0x3f803f80u);   // 1.0: keeps everything
       }
     }
     float c1[R], c2[R];
@@ -244,6 +256,21 @@ layernorm_bwd_small_kernel(const bf16* __restrict__ dy, const float* __restrict_
           o.z = (d23.x * g4[i].z - m1 - xv[r][i].z * m2) * rstd[r] + rv[r][i].z;
           o.w = (d23.y * g4[i].w - m1 - xv[r][i].w * m2) * rstd[r] + rv[r][i].w;
           reinterpret_cast<float4*>(dx + static_cast<size_t>(row) * dim)[c] = o;
+          if constexpr (FUSE) {
+            if (mask_src != nullptr) {
+              const float2 m01 = unpack_bf16x2(mv[r][i].x), m23 = unpack_bf16x2(mv[r][i].y);
+              if (act >= 2) {   // GELU: mask_src is the pre-activation
+                o.x *= gelu_grad(m01.x, act); o.y *= gelu_grad(m01.y, act);
+                o.z *= gelu_grad(m23.x, act); o.w *= gelu_grad(m23.y, act);
+              } else {          // ReLU: mask_src is the activated output
+                if (!(m01.x > 0.f)) o.x = 0.f;
+                if (!(m01.y > 0.f)) o.y = 0.f;
+                if (!(m23.x > 0.f)) o.z = 0.f;
+                if (!(m23.y > 0.f)) o.w = 0.f;
+              }
+            }
+            dbz[i].x += o.x; dbz[i].y += o.y; dbz[i].z += o.z; dbz[i].w += o.w;
+          }
           if (dx_bf16 != nullptr)
             reinterpret_cast<uint2*>(dx_bf16 + static_cast<size_t>(row) * dim)[c] =
                 make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
@@ -251,24 +278,26 @@ layernorm_bwd_small_kernel(const bf16* __restrict__ dy, const float* __restrict_
       }
     }
   }
-  extern __shared__ float red[];  // [warps][2][dim]
-  float* my = red + static_cast<size_t>(warp) * 2 * dim;
+  constexpr int NOUT = FUSE ? 3 : 2;
+  extern __shared__ float red[];  // [warps][NOUT][dim]
+  float* my = red + static_cast<size_t>(warp) * NOUT * dim;
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     const int c = lane + 32 * i;
     if (c < nvec) {
       reinterpret_cast<float4*>(my)[c] = dg[i];
       reinterpret_cast<float4*>(my + dim)[c] = db[i];
+      if constexpr (FUSE) reinterpret_cast<float4*>(my + 2 * dim)[c] = dbz[i];
     }
   }
   __syncthreads();
-  float* rep = scratch + static_cast<size_t>(blockIdx.x % REPLICAS) * 2 * dim;
-  for (int j = threadIdx.x; j < 2 * dim; j += blockDim.x) {
+  float* rep = scratch + static_cast<size_t>(blockIdx.x % REPLICAS) * NOUT * dim;
+  for (int j = threadIdx.x; j < NOUT * dim; j += blockDim.x) {
     float sacc = 0.f;
-    for (int w = 0; w < warps_per_block; ++w) sacc += red[static_cast<size_t>(w) * 2 * dim + j];
+    for (int w = 0; w < warps_per_block; ++w) sacc += red[static_cast<size_t>(w) * NOUT * dim + j];
     atomicAdd(rep + j, sacc);
   }
-  finish_column_sums(scratch, counter, 2 * dim, gridDim.x, dgamma, dbeta, dim);
+  finish_column_sums(scratch, counter, NOUT * dim, gridDim.x, dgamma, dbeta, dim, dbias_z, FUSE);
 }
 
 template <int NV, bool DX_ONLY = false>
@@ -278,7 +307,7 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
                      const float* __restrict__ rstd_in, const float* __restrict__ dres,
                      float* __restrict__ dx, bf16* __restrict__ dx_bf16, float* __restrict__ dgamma,
                      float* __restrict__ dbeta, int rows, int dim, float* __restrict__ scratch,
-                     int* __restrict__ counter) {
+                     int* __restrict__ counter, const bf16* __restrict__ mask_src = nullptr, int act = 0) {
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int warps_per_block = blockDim.x >> 5;
@@ -338,6 +367,19 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
           o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
         }
         dxr[c] = o;
+        if (mask_src != nullptr) {   // dx_bf16 becomes dz = dx * act'(mask_src) of the layer that produced x
+          const uint2 m = reinterpret_cast<const uint2*>(mask_src + static_cast<int64_t>(row) * dim)[c];
+          const float2 m01 = unpack_bf16x2(m.x), m23 = unpack_bf16x2(m.y);
+          if (act >= 2) {
+            o.x *= gelu_grad(m01.x, act); o.y *= gelu_grad(m01.y, act);
+            o.z *= gelu_grad(m23.x, act); o.w *= gelu_grad(m23.y, act);
+          } else {
+            if (!(m01.x > 0.f)) o.x = 0.f;
+            if (!(m01.y > 0.f)) o.y = 0.f;
+            if (!(m23.x > 0.f)) o.z = 0.f;
+            if (!(m23.y > 0.f)) o.w = 0.f;
+          }
+        }
         if (dx_bf16 != nullptr)
           reinterpret_cast<uint2*>(dx_bf16 + static_cast<int64_t>(row) * dim)[c] =
               make_uint2(pack_bf16x2(o.x, o.y), pack_bf16x2(o.z, o.w));
@@ -373,11 +415,15 @@ __global__ void __launch_bounds__(256)
 layernorm_bwd_dgdb_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
                           const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
                           float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int dim,
-                          float* __restrict__ scratch, int* __restrict__ counter) {
+                          float* __restrict__ scratch, int* __restrict__ counter,
+                          const bf16* __restrict__ dz = nullptr, float* __restrict__ dbias_z = nullptr) {
+  // dz / dbias_z (optional): third column sum, over the bf16 dz the dx kernel wrote (fused backward hand-off)
   const int cg = blockIdx.x * 32 + threadIdx.x;
   const int col = cg * 4;
   const bool col_ok = col < dim;
-  float4 g = make_float4(0.f, 0.f, 0.f, 0.f), b = make_float4(0.f, 0.f, 0.f, 0.f);
+  const bool three = dz != nullptr;
+  const int nout = three ? 3 : 2;
+  float4 g = make_float4(0.f, 0.f, 0.f, 0.f), b = make_float4(0.f, 0.f, 0.f, 0.f), z = make_float4(0.f, 0.f, 0.f, 0.f);
   const int r0 = blockIdx.y * LN_DG_ROWS;
   if (col_ok) {
 #pragma unroll 4
@@ -389,25 +435,33 @@ layernorm_bwd_dgdb_kernel(const bf16* __restrict__ dy, const float* __restrict__
       g.x += d01.x * (xv.x - mean) * rstd; g.y += d01.y * (xv.y - mean) * rstd;
       g.z += d23.x * (xv.z - mean) * rstd; g.w += d23.y * (xv.w - mean) * rstd;
       b.x += d01.x; b.y += d01.y; b.z += d23.x; b.w += d23.y;
+      if (three) {
+        const uint2 w = *reinterpret_cast<const uint2*>(dz + static_cast<size_t>(r) * dim + col);
+        const float2 z01 = unpack_bf16x2(w.x), z23 = unpack_bf16x2(w.y);
+        z.x += z01.x; z.y += z01.y; z.z += z23.x; z.w += z23.y;
+      }
     }
   }
-  __shared__ float red[8][32][9];
+  __shared__ float red[8][32][13];
   red[threadIdx.y][threadIdx.x][0] = g.x; red[threadIdx.y][threadIdx.x][1] = g.y;
   red[threadIdx.y][threadIdx.x][2] = g.z; red[threadIdx.y][threadIdx.x][3] = g.w;
   red[threadIdx.y][threadIdx.x][4] = b.x; red[threadIdx.y][threadIdx.x][5] = b.y;
   red[threadIdx.y][threadIdx.x][6] = b.z; red[threadIdx.y][threadIdx.x][7] = b.w;
+  red[threadIdx.y][threadIdx.x][8] = z.x; red[threadIdx.y][threadIdx.x][9] = z.y;
+  red[threadIdx.y][threadIdx.x][10] = z.z; red[threadIdx.y][threadIdx.x][11] = z.w;
   __syncthreads();
   if (threadIdx.y == 0 && col_ok) {
-    float* rep = scratch + static_cast<size_t>(blockIdx.y % REPLICAS) * 2 * dim;
+    float* rep = scratch + static_cast<size_t>(blockIdx.y % REPLICAS) * nout * dim;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
+    for (int j = 0; j < 12; ++j) {
+      if (j >= 4 * nout) break;
       float s = 0.f;
 #pragma unroll
       for (int w = 0; w < 8; ++w) s += red[w][threadIdx.x][j];
-      atomicAdd(rep + (j < 4 ? col + j : dim + col + (j - 4)), s);
+      atomicAdd(rep + (j >> 2) * dim + col + (j & 3), s);
     }
   }
-  finish_column_sums(scratch, counter, 2 * dim, gridDim.x * gridDim.y, dgamma, dbeta, dim);
+  finish_column_sums(scratch, counter, nout * dim, gridDim.x * gridDim.y, dgamma, dbeta, dim, dbias_z, three);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -966,16 +1020,29 @@ int b200_layernorm_fwd(const float* x, const float* gamma, const float* beta, vo
 int b200_layernorm_bwd(const void* dy, const float* x, const float* gamma, const float* mean,
                        const float* rstd, const float* dres, float* dx, void* dx_bf16, float* dgamma,
                        float* dbeta, int rows, int dim, float* scratch, int* counter, void* stream) {
+  return b200_layernorm_bwd_fused(dy, x, gamma, mean, rstd, dres, dx, dx_bf16, dgamma, dbeta, rows, dim, scratch,
+                                  counter, nullptr, 0, nullptr, 0, stream);
+}
+
+// fuse != 0: dz_out (the dx_bf16 slot) = bf16(dx * act'(mask_src)) and dbias_z += column sums of dz - the first step of
+// the backward of the Linear / MLP whose residual epilogue produced x (mask_src NULL: no activation; dbias_z NULL:
+// no bias).  scratch: 16 x 3*dim floats.
+int b200_layernorm_bwd_fused(const void* dy, const float* x, const float* gamma, const float* mean,
+                             const float* rstd, const float* dres, float* dx, void* dx_bf16, float* dgamma,
+                             float* dbeta, int rows, int dim, float* scratch, int* counter, const void* mask_src,
+                             int act, float* dbias_z, int fuse, void* stream) {
   B200_REQUIRE(dim % 4 == 0 && dim <= 4096, "layernorm: dim %d must be a multiple of 4 and <= 4096", dim);
-  B200_REQUIRE(scratch != nullptr && counter != nullptr, "layernorm_bwd: scratch (16 x 2*dim floats) and counter required");
+  B200_REQUIRE(scratch != nullptr && counter != nullptr, "layernorm_bwd: scratch (16 x 3*dim floats) and counter required");
+  B200_REQUIRE(!fuse || dx_bf16 != nullptr, "layernorm_bwd: the fused hand-off needs the bf16 output buffer");
   if (rows == 0) return 0;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int grid = b200_num_sms() * 4;
   const int max_grid = ceil_div(rows, 8);
   if (grid > max_grid) grid = max_grid;
-  const size_t smem = static_cast<size_t>(8) * 2 * dim * sizeof(float);
+  const size_t smem = static_cast<size_t>(8) * (fuse ? 3 : 2) * dim * sizeof(float);
   const bf16* dyb = reinterpret_cast<const bf16*>(dy);
   bf16* dxb = reinterpret_cast<bf16*>(dx_bf16);
+  const bf16* msk = reinterpret_cast<const bf16*>(mask_src);
 #define LN_BWD(NV)                                                                                  \
   do {                                                                                              \
     if (smem > 48 * 1024)                                                                           \
@@ -989,26 +1056,42 @@ int b200_layernorm_bwd(const void* dy, const float* x, const float* gamma, const
     const int mg = ceil_div(rows, 8 * 4);
     if (g > mg) g = mg;
     if (g < 1) g = 1;
-    if (dim <= 128)
-      layernorm_bwd_small_kernel<1, 4><<<g, 256, smem, st>>>(dyb, x, gamma, mean, rstd, dres, dx, dxb, dgamma, dbeta,
-                                                             rows, dim, scratch, counter);
-    else
-      layernorm_bwd_small_kernel<2, 4><<<g, 256, smem, st>>>(dyb, x, gamma, mean, rstd, dres, dx, dxb, dgamma, dbeta,
-                                                             rows, dim, scratch, counter);
-  } else if (dim <= 1024) LN_BWD(8);
+    // rows a warp keeps in flight per iteration for 129..256 columns (B200GPT_LN_ROWS = 2 / 3 / 4)
+    // (measured in the default training step: 2 rows 4.24 ms, 3 rows 4.27 ms, 4 rows - which spills - 4.36 ms)
+    static const int rows_per_iter = []() { const char* e = getenv("B200GPT_LN_ROWS"); return e ? atoi(e) : 2; }();
+#define LN_SMALL(NV, R, F)                                                                                          \
+  layernorm_bwd_small_kernel<NV, R, F><<<g, 256, smem, st>>>(dyb, x, gamma, mean, rstd, dres, dx, dxb, dgamma, dbeta, \
+                                                             rows, dim, scratch, counter, msk, act, dbias_z)
+    if (fuse) {
+      if (dim <= 128) LN_SMALL(1, 4, true);
+      else if (rows_per_iter == 2) LN_SMALL(2, 2, true);
+      else if (rows_per_iter == 3) LN_SMALL(2, 3, true);
+      else LN_SMALL(2, 4, true);
+    } else {
+      if (dim <= 128) LN_SMALL(1, 4, false);
+      else if (rows_per_iter == 2) LN_SMALL(2, 2, false);
+      else if (rows_per_iter == 3) LN_SMALL(2, 3, false);
+      else LN_SMALL(2, 4, false);
+    }
+#undef LN_SMALL
+  } else if (dim <= 1024 && !fuse) LN_BWD(8);
   else {
-    // wide rows: dx by the warp-per-row kernel without the column accumulators (they would need
-    // 128+ registers per lane), dgamma/dbeta by a column-parallel pass
+    // wide rows (and the fused hand-off above 256 columns): dx by the warp-per-row kernel without the column
+    // accumulators (they would need 128+ registers per lane), dgamma / dbeta (/ dbias_z) by a column-parallel pass
     const int gdx = (rows + 7) / 8 < b200_num_sms() * 8 ? (rows + 7) / 8 : b200_num_sms() * 8;
-    if (dim <= 2048)
+    if (dim <= 1024)
+      layernorm_bwd_kernel<8, true><<<gdx, 256, 0, st>>>(dyb, x, gamma, mean, rstd, dres, dx, dxb, dgamma, dbeta,
+                                                         rows, dim, scratch, counter, msk, act);
+    else if (dim <= 2048)
       layernorm_bwd_kernel<16, true><<<gdx, 256, 0, st>>>(dyb, x, gamma, mean, rstd, dres, dx, dxb, dgamma, dbeta,
-                                                          rows, dim, scratch, counter);
+                                                          rows, dim, scratch, counter, msk, act);
     else
       layernorm_bwd_kernel<32, true><<<gdx, 256, 0, st>>>(dyb, x, gamma, mean, rstd, dres, dx, dxb, dgamma, dbeta,
-                                                          rows, dim, scratch, counter);
+                                                          rows, dim, scratch, counter, msk, act);
     B200_LAUNCH_CHECK();
     dim3 g2(ceil_div(dim / 4, 32), ceil_div(rows, LN_DG_ROWS)), b2(32, 8);
-    layernorm_bwd_dgdb_kernel<<<g2, b2, 0, st>>>(dyb, x, mean, rstd, dgamma, dbeta, rows, dim, scratch, counter);
+    layernorm_bwd_dgdb_kernel<<<g2, b2, 0, st>>>(dyb, x, mean, rstd, dgamma, dbeta, rows, dim, scratch, counter,
+                                                 (fuse && dbias_z != nullptr) ? dxb : nullptr, dbias_z);
   }
 #undef LN_BWD
   B200_LAUNCH_CHECK();

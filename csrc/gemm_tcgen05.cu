@@ -92,8 +92,12 @@ enum : int { ERR_GEMM_PRODUCER = 101, ERR_GEMM_MMA = 102, ERR_GEMM_EPILOGUE = 10
 // one 32-row x 128-byte swizzled staging tile per epilogue warp (x NSTG buffers)
 template <int CG> constexpr int staging_bytes() { return epilogue_warps<CG>() * 4096; }
 // staging buffers per epilogue warp: with two, a warp fills one while the TMA engine still reads the other
-// (CTA pairs hide that wait behind the second warp of the lane quarter instead)
-template <int BN, int CG> constexpr int staging_bufs() { return (CG == 1 && BN == 128) ? 2 : 1; }
+// (CTA pairs hide that wait behind the second warp of the lane quarter; a pair kernel with 5 operand stages and
+// no gather buffers has room for a second 32 KB set, which the write-bound LM-head GEMM uses: its exp2 work
+// then runs while the stores of the previous tile drain)
+template <int BN, int CG, int STAGES = 6, bool AG = false> constexpr int staging_bufs() {
+  return (CG == 1 && BN == 128) ? 2 : (CG == 2 && STAGES <= 5 && !AG) ? 2 : 1;
+}
 // Gather warp of the fused all-gather: slices of ag_slice() bytes travel peer shard -> smem bounce buffer -> local
 // full buffer with bulk copies.  Single CTAs: one 16 KB buffer.  CTA pairs (AG instantiation): four 8 KB buffers,
 // three loads in flight while the fourth buffer drains.
@@ -141,7 +145,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   constexpr int B_STAGE_BYTES = B_ROWS * BK * 2;
   constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   constexpr uint32_t TMEM_COLS = 2 * BN;
-  constexpr int NSTG = staging_bufs<BN, CG>();
+  constexpr int NSTG = staging_bufs<BN, CG, STAGES, AG>();
   constexpr int STAGING_BYTES = staging_bytes<CG>();
   constexpr int EPW = epilogue_warps<CG>();
 
@@ -473,6 +477,95 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + cbase * 32;
       uint32_t rr[2][32];  // TMEM loads are software-pipelined: chunk c+1 is in flight under chunk c
       tmem_ld_32x32b_x32(taddr, rr[0]);
+      if constexpr (E_SMAX) {
+        // LM head.  exp2 runs on the 16-lane/clk SFU pipe (8 cycles per warp instruction) and everything that
+        // consumes its results queues up behind it.  The loop is skewed by one chunk: iteration c holds exp2 of
+        // chunk c AND the sums / bf16 packing / staging stores of chunk c-1 in one branch-free block, independent
+        // of each other, so ptxas interleaves SFU and ALU work (582 -> 561 us for the 16320 x 50257 x 256 head;
+        // starting the second warp of a lane quarter 150-900 cycles late on top of that changed nothing).  Rare
+        // cases (vocabulary tail, target column) are handled on the raw values before the block; waits and the
+        // TMA store sit between blocks.
+        float ex[2][32];
+#pragma unroll
+        for (int c = 0; c <= NCH; ++c) {
+          const int col0 = n0 + c * 32;
+          uint32_t* r = rr[c & 1];
+          if (c < NCH) {
+            tmem_ld_wait_dep(r);
+            if (c + 1 < NCH) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, rr[(c + 1) & 1]);
+            if (c == NCH - 1) {  // accumulator fully in registers: hand the TMEM buffer back early
+              tcgen05_fence_before();
+              __syncwarp();
+              if (lane == 0) {
+                if constexpr (CG == 2) mbar_arrive_leader(tempty_bar + 8 * as);
+                else mbar_arrive(tempty_bar + 8 * as);
+              }
+            }
+            if (col0 + 32 > p.N) {   // columns past N (zero-filled B rows) must not count
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (col0 + j >= p.N) r[j] = 0xff800000u;   // -inf
+            }
+            if (tgt >= col0 && tgt < col0 + 32) {   // rare: this thread holds its row's target column
+              uint32_t tv = 0u;
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (col0 + j == tgt) tv = r[j];
+              p.tgt_val[row] = __uint_as_float(tv);
+            }
+          }
+          [[maybe_unused]] const uint32_t stage_buf = stage_base + (nstore % NSTG) * STAGING_BYTES;
+          if constexpr (!E_NOSTORE) {
+            if (c >= 1 && ((c - 1) & 1) == 0) {   // the store issued NSTG stores ago must be done reading this buffer
+              const long long ts0 = TRACE_ON(p) ? clock64() : 0;
+              if (lane == 0) {
+                if constexpr (NSTG == 2) tma_store_wait_read1();
+                else tma_store_wait_read0();
+              }
+              __syncwarp();
+              if (TRACE_ON(p)) w_stage += clock64() - ts0;
+            }
+          }
+          // ---- the block: exp2 of chunk c, sums and staging of chunk c-1 ----
+          if (c < NCH) {
+            float* e = ex[c & 1];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float v = __uint_as_float(r[j]);
+              s_max4[j & 3] = fmaxf(s_max4[j & 3], v);
+              e[j] = fast_exp2(fmaf(v, kLog2e, -rowa));
+            }
+          }
+          if (c >= 1) {
+            const float* e = ex[(c - 1) & 1];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) s_sum[j & 3] += e[j];
+            if constexpr (!E_NOSTORE) {
+              const uint32_t my_row = stage_buf + lane * 128;
+              const int half = ((c - 1) & 1) * 4;
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_row + (((half + j) ^ swz) << 4)),
+                             "r"(pack_bf16x2(e[8 * j], e[8 * j + 1])), "r"(pack_bf16x2(e[8 * j + 2], e[8 * j + 3])),
+                             "r"(pack_bf16x2(e[8 * j + 4], e[8 * j + 5])), "r"(pack_bf16x2(e[8 * j + 6], e[8 * j + 7]))
+                             : "memory");
+            }
+          }
+          // ---- between blocks: two chunks fill one 32 x 64 bf16 staging tile ----
+          if constexpr (!E_NOSTORE) {
+            if (c >= 1 && ((c - 1) & 1) == 1) {
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
+                const int sc0 = col0 - 64;   // first column of chunk c-2
+                if (sc0 < p.N && m0 + q * 32 < p.M) tma_store_2d(&tmC, stage_buf, sc0, m0 + q * 32);
+                tma_store_commit();
+              }
+              ++nstore;
+            }
+          }
+        }
+      } else {
 #pragma unroll
       for (int c = 0; c < NCH; ++c) {
         uint32_t* r = rr[c & 1];
@@ -568,27 +661,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] *= rowa;
         }
-        if constexpr (E_SMAX) {
-          if (col0 + 32 > p.N) {   // columns past N (zero-filled B rows) must not count
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + j >= p.N) v[j] = -INFINITY;
-          }
-          if (tgt >= col0 && tgt < col0 + 32) {   // rare: this thread holds its row's target column
-            float tv = 0.f;
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + j == tgt) tv = v[j];
-            p.tgt_val[row] = tv;
-          }
-#pragma unroll
-          for (int j = 0; j < 32; ++j) s_max4[j & 3] = fmaxf(s_max4[j & 3], v[j]);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            v[j] = fast_exp2(fmaf(v[j], kLog2e, -rowa));
-            s_sum[j & 3] += v[j];
-          }
-        }
         if constexpr (!E_NOSTORE) {
         // stage: fp32 -> one 32x32 tile per chunk; bf16 -> two chunks fill one 32x64 tile
         constexpr bool kStoreEvery = E_F32;
@@ -653,6 +725,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (col0 + lane < p.N) atomicAdd(p.colsum + col0 + lane, v[0]);
         }
       }
+      }  // generic epilogue loop
       if constexpr (E_SMAX) {   // one (sum, max) partial per row and per NCH * 32-column span, coalesced over the warp
         if (row_ok)
           p.part[static_cast<size_t>(n0 / (NCH * 32)) * p.M + row] =
@@ -772,7 +845,7 @@ struct GemmOverrides {
 template <int BN, int STAGES, int MIN_CTAS, int EPI, int CG, bool AG = false>
 int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p,
            int grid, cudaStream_t stream) {
-  constexpr int smem = STAGES * (A_STAGE_BYTES + (BN / CG) * BK * 2) + staging_bufs<BN, CG>() * staging_bytes<CG>() +
+  constexpr int smem = STAGES * (A_STAGE_BYTES + (BN / CG) * BK * 2) + staging_bufs<BN, CG, STAGES, AG>() * staging_bytes<CG>() +
                        ag_bounce_bytes<CG, AG>() + 16 * STAGES + 64 + 16;
   static_assert(smem <= 227 * 1024, "gemm: shared memory budget exceeded");
   static bool configured[64] = {false};
@@ -871,6 +944,9 @@ constexpr bool ag_pair_epilogue(int epi) {
 }
 // B200GPT_AG_2SM=0: fused all-gather on single-CTA tiles only (the first version of the kernel)
 bool g_ag_2sm = []() { const char* e = getenv("B200GPT_AG_2SM"); return e == nullptr || e[0] != '0'; }();
+
+// B200GPT_GEMM_STAGING2=0: keep the 6-stage / one-staging-set pair kernel for every epilogue
+bool g_two_staging = []() { const char* e = getenv("B200GPT_GEMM_STAGING2"); return e == nullptr || e[0] != '0'; }();
 
 int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
               int a_mn, int b_mn, const float* bias, const float* residual, int ldr, int act,
@@ -1015,6 +1091,11 @@ int gemm_impl(const void* A, const void* B, void* C, int M, int N, int K, int ld
                   (nostore ? EPI_NOSTORE : 0) | ((ex && ex->rscale) ? EPI_RSCALE : 0);
   if (bn == 128) return launch_epi<128, 2, 2, 1>(epi, tmA, tmB, tmC, p, grid, st);
   if (cg == 2 && fused_ag) return launch_epi_ag_pair(epi, tmA, tmB, tmC, p, grid, st);
+  if (cg == 2 && g_two_staging) {
+    // LM head: 5 operand stages leave room for a second staging set per epilogue warp (the plain logits GEMM
+    // measured 4 % slower that way and keeps 6 stages)
+    if (epi == EPI_SMAX) return launch<256, 5, 1, EPI_SMAX, 2>(tmA, tmB, tmC, p, grid, st);
+  }
   if (cg == 2) return launch_epi<256, 6, 1, 2>(epi, tmA, tmB, tmC, p, grid, st);
   return launch_epi<256, 4, 1, 1>(epi, tmA, tmB, tmC, p, grid, st);
 }

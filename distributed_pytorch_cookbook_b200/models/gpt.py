@@ -114,7 +114,7 @@ class SelfAttention(nn.Module):
             qkv = ops.linear_qkv(x, self.to_q.weight, self.to_k.weight, self.to_v.weight)
             o = ops.attention(qkv, self.heads, self.head_dim, self.attn_scale, key_mask=mask)
             return ops.linear(o, self.to_out.weight, self.to_out.bias, residual=residual,
-                              out_fp32=residual is not None)
+                              out_fp32=residual is not None, handoff="block")
         N, S, _ = x.shape
         h, d = self.heads, self.head_dim
         q = self.to_q(x).view(N, S, h, d).transpose(1, 2)

@@ -102,9 +102,9 @@ def lmhead_cross_entropy(x, weight, targets, ignore_index: int = -100, grad_scal
 
 
 def linear(x, weight, bias=None, activation: Optional[str] = None, residual=None,
-           out_fp32: bool = False):
+           out_fp32: bool = False, handoff: str = "stream"):
     from . import native
-    return native.linear(x, weight, bias, activation, residual, out_fp32)
+    return native.linear(x, weight, bias, activation, residual, out_fp32, handoff)
 
 
 def mlp(x, w1, b1, w2, b2, residual=None, activation: str = "relu"):

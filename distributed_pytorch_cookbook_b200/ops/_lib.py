@@ -29,6 +29,7 @@ _SIGS = {
     "b200_embedding_bwd": [P, P, P, P, P, I, I, I, I, P],
     "b200_layernorm_fwd": [P, P, P, P, P, P, I, I, Fl, P],
     "b200_layernorm_bwd": [P, P, P, P, P, P, P, P, P, P, I, I, P, P, P],
+    "b200_layernorm_bwd_fused": [P, P, P, P, P, P, P, P, P, P, I, I, P, P, P, I, P, I, P],
     "b200_adamw": [P, P, P, P, P, L, P, Fl, Fl, Fl, Fl, P],
     "b200_adamw_tick": [P, P],
     "b200_cast_bf16": [P, P, L, P],

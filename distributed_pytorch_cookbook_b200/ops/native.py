@@ -32,7 +32,7 @@ _LM_SUB_ROWS = int(_os.environ.get("B200GPT_LM_SUB", "0"))     # rows per logits
 
 
 _SCRATCH = {}
-SCRATCH_COLS = 8192
+SCRATCH_COLS = 12288   # 3 x the widest LayerNorm row (dgamma, dbeta and the handed-off bias gradient)
 
 
 def colsum_scratch(device):
@@ -147,9 +147,52 @@ def fused_gather_args(weights):
 
 
 # ----------------------------------------------------------------------------------------
+# ----------------------------------------------------------------------------------------
+# LayerNorm-backward hand-off.  In a pre-LN block the residual stream x is written by the epilogue of
+# a Linear / MLP (reference models/gpt.py:119-123: ``x = x + attn(...)``, ``x = x + ff(...)``) and read by exactly one
+# node, the next LayerNorm.  That LayerNorm's backward produces dx - which is the producer's incoming gradient - so
+# it also writes what the producer's backward would compute first: dz = bf16(dx * act'(.)) and the bias gradient's
+# column sums (``b200_layernorm_bwd_fused``).  The producer then skips its own pass over dx.  The producer's autograd
+# node carries ``fuse_info``; the LayerNorm leaves ``fused = (dz, dx.data_ptr())`` on it.
+_LN_FUSE = _os.environ.get("B200GPT_LN_FUSE", "1") != "0"
+_FUSE_SCOPE = "all"
+
+
+def set_fuse_scope(scope: str) -> None:
+    """"all": any producer; "block": only a producer inside the same transformer block as the LayerNorm (the
+    attention out-projection -> ln2).  FSDP needs "block": a unit's gradient buffer is only valid during that unit's
+    backward, and the MLP -> next block's ln1 hand-off would write the bias gradient of the previous unit early."""
+    global _FUSE_SCOPE
+    assert scope in ("all", "block", "off")
+    _FUSE_SCOPE = scope
+
+
+def _producer_of(x: torch.Tensor):
+    if not _LN_FUSE or _FUSE_SCOPE == "off" or not torch.is_grad_enabled() or x.dtype != torch.float32:
+        return None
+    node = x.grad_fn
+    info = getattr(node, "fuse_info", None)
+    if info is None or (_FUSE_SCOPE == "block" and info[0] != "block"):
+        return None
+    if x.shape[-1] % 4 != 0 or not x.is_contiguous():
+        return None
+    return node
+
+
+def _take_handoff(ctx, dy2: torch.Tensor):
+    h = ctx.__dict__.pop("fused", None)
+    if h is None:
+        return None
+    dz, ptr_dx = h
+    if ptr_dx != dy2.data_ptr() or dz.shape != dy2.shape:
+        raise RuntimeError("fused LayerNorm backward: the residual stream has a second consumer, so the gradient this "
+                           "layer received is not the one the LayerNorm handed over (set B200GPT_LN_FUSE=0)")
+    return dz
+
+
 class _Linear(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, residual, act, out_fp32, params, grad_on):
+    def forward(ctx, x, weight, bias, residual, act, out_fp32, params, grad_on, kind="stream"):
         lead = x.shape[:-1]
         x2 = _as_bf16_2d(x)
         M, K = x2.shape
@@ -170,6 +213,7 @@ class _Linear(torch.autograd.Function):
         if act != 0:
             y_act = aux if need_aux else out
         ctx.save_for_backward(x2, wb, y_act)
+        ctx.fuse_info = (kind, y_act, act, bias) if (residual is not None and out_fp32 and grad_on) else None
         return out.view(*lead, N)
 
     @staticmethod
@@ -181,7 +225,10 @@ class _Linear(torch.autograd.Function):
         dy2 = dy.reshape(M, N)
         dres = dy if ctx.has_res else None
         need_dz = ctx.act != 0 or dy2.dtype != BF16 or bias is not None
-        if need_dz:
+        dz = _take_handoff(ctx, dy2)
+        if dz is not None:
+            pass                                  # the LayerNorm that consumed our output already wrote dz and db
+        elif need_dz:
             if not dy2.is_contiguous():
                 dy2 = dy2.contiguous()
             dz = torch.empty((M, N), dtype=BF16, device=dy.device)
@@ -203,12 +250,15 @@ class _Linear(torch.autograd.Function):
             gw = grad_of(weight)
             gemm(dz, x2, gw, N, K, M, a_mn_major=True, b_mn_major=True, accumulate=True)  # dW += dZ^T . X
         _notify(weight, bias)
-        return dx, None, None, dres, None, None, None, None
+        return dx, None, None, dres, None, None, None, None, None
 
 
-def linear(x, weight, bias=None, activation: Optional[str] = None, residual=None, out_fp32=False):
+def linear(x, weight, bias=None, activation: Optional[str] = None, residual=None, out_fp32=False,
+           handoff: str = "stream"):
+    """``handoff``: where the LayerNorm that reads the residual output lives - "block" (same transformer block, e.g.
+    attention out-projection -> ln2) or "stream" (the next block / the final norm); see set_fuse_scope."""
     act = {None: 0, "relu": 1}[activation]
-    return _Linear.apply(x, weight, bias, residual, act, out_fp32, (weight, bias), torch.is_grad_enabled())
+    return _Linear.apply(x, weight, bias, residual, act, out_fp32, (weight, bias), torch.is_grad_enabled(), handoff)
 
 
 # ----------------------------------------------------------------------------------------
@@ -247,6 +297,7 @@ class _MLP(torch.autograd.Function):
         gemm(u, w2b, out, M, N, F1, bias=b2, residual=res2, act=act, aux_out=aux, ag=fused_gather_args([w2]))
         ctx.params, ctx.has_res, ctx.in_dtype, ctx.act = params, residual is not None, x.dtype, act
         ctx.save_for_backward(x2, w1b, w2b, u, aux if aux is not None else out, z1)
+        ctx.fuse_info = ("stream", aux, act, b2) if (residual is not None and grad_on and aux is not None) else None
         return out.view(*lead, N)
 
     @staticmethod
@@ -260,9 +311,11 @@ class _MLP(torch.autograd.Function):
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
         sc, cnt = colsum_scratch(dy.device)
-        dz2 = torch.empty((M, N), dtype=BF16, device=dy.device)
-        call("b200_act_bwd", dy2.data_ptr(), y_act.data_ptr(), dz2.data_ptr(), grad_of(b2).data_ptr(), M, N,
-             int(dy2.dtype == torch.float32), act, sc.data_ptr(), cnt.data_ptr(), stream())
+        dz2 = _take_handoff(ctx, dy2)
+        if dz2 is None:
+            dz2 = torch.empty((M, N), dtype=BF16, device=dy.device)
+            call("b200_act_bwd", dy2.data_ptr(), y_act.data_ptr(), dz2.data_ptr(), grad_of(b2).data_ptr(), M, N,
+                 int(dy2.dtype == torch.float32), act, sc.data_ptr(), cnt.data_ptr(), stream())
         gemm(dz2, u, grad_of(w2), N, F1, M, a_mn_major=True, b_mn_major=True, accumulate=True)     # dW2 += dZ2^T u
         dz1 = torch.empty((M, F1), dtype=BF16, device=dy.device)
         # dZ1 = (dZ2 W2) * act'(.), with db1 += column sums of dZ1 folded into the same epilogue
@@ -364,14 +417,39 @@ def linear_qkv(x, wq, wk, wv):
 
 
 # ----------------------------------------------------------------------------------------
+def _ln_backward(ctx, dy2, x2, mean, rstd, dr):
+    """dx = LN'(dy) [+ dres]; with a producer hand-off also that layer's dz / bias gradient (see _producer_of)."""
+    weight, bias = ctx.params
+    rows, D = x2.shape
+    dx = torch.empty((rows, D), dtype=torch.float32, device=dy2.device)
+    sc, cnt = colsum_scratch(dy2.device)
+    prod = getattr(ctx, "producer", None)
+    if prod is not None and getattr(prod, "fuse_info", None) is not None:
+        _, mask, act, pbias = prod.fuse_info
+        dz = torch.empty((rows, D), dtype=BF16, device=dy2.device)
+        dbz = grad_of(pbias) if (pbias is not None and pbias.requires_grad) else None
+        call("b200_layernorm_bwd_fused", dy2.data_ptr(), x2.data_ptr(), weight.data_ptr(), mean.data_ptr(),
+             rstd.data_ptr(), ptr(dr), dx.data_ptr(), dz.data_ptr(), grad_of(weight).data_ptr(),
+             grad_of(bias).data_ptr(), rows, D, sc.data_ptr(), cnt.data_ptr(), ptr(mask) if act != 0 else None, act,
+             ptr(dbz), 1, stream())
+        prod.fused = (dz, dx.data_ptr())
+    else:
+        call("b200_layernorm_bwd", dy2.data_ptr(), x2.data_ptr(), weight.data_ptr(), mean.data_ptr(),
+             rstd.data_ptr(), ptr(dr), dx.data_ptr(), None, grad_of(weight).data_ptr(),
+             grad_of(bias).data_ptr(), rows, D, sc.data_ptr(), cnt.data_ptr(), stream())
+    _notify(weight, bias)
+    return dx
+
+
 class _LayerNorm(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, eps, params):
+    def forward(ctx, x, weight, bias, eps, params, producer=None):
         D = x.shape[-1]
         x2 = x.reshape(-1, D)
         if x2.dtype != torch.float32:
             x2 = x2.float()
         x2 = x2.contiguous()
+        ctx.producer = producer
         rows = x2.shape[0]
         y = torch.empty((rows, D), dtype=BF16, device=x.device)
         mean = torch.empty(rows, dtype=torch.float32, device=x.device)
@@ -392,19 +470,15 @@ class _LayerNorm(torch.autograd.Function):
         if dy2.dtype != BF16:
             dy2 = dy2.to(BF16)
         dy2 = dy2.contiguous()
-        dx = torch.empty((rows, D), dtype=torch.float32, device=dy.device)
-        call("b200_layernorm_bwd", dy2.data_ptr(), x2.data_ptr(), weight.data_ptr(), mean.data_ptr(),
-             rstd.data_ptr(), None, dx.data_ptr(), None, grad_of(weight).data_ptr(),
-             grad_of(bias).data_ptr(), rows, D, *[t.data_ptr() for t in colsum_scratch(dy.device)], stream())
-        _notify(weight, bias)
+        dx = _ln_backward(ctx, dy2, x2, mean, rstd, None)
         dx = dx.view(dy.shape)
         if ctx.in_dtype != torch.float32:
             dx = dx.to(ctx.in_dtype)
-        return dx, None, None, None, None
+        return dx, None, None, None, None, None
 
 
 def layernorm(x, weight, bias, eps):
-    return _LayerNorm.apply(x, weight, bias, eps, (weight, bias))
+    return _LayerNorm.apply(x, weight, bias, eps, (weight, bias), _producer_of(x))
 
 
 class _LayerNormResidual(torch.autograd.Function):
@@ -415,11 +489,12 @@ class _LayerNormResidual(torch.autograd.Function):
     launching a separate fp32 add over the whole residual stream."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, eps, params):
+    def forward(ctx, x, weight, bias, eps, params, producer=None):
         D = x.shape[-1]
         x2 = x.reshape(-1, D)
         if x2.dtype != torch.float32 or not x2.is_contiguous():
             x2 = x2.float().contiguous()
+        ctx.producer = producer
         rows = x2.shape[0]
         y = torch.empty((rows, D), dtype=BF16, device=x.device)
         mean = torch.empty(rows, dtype=torch.float32, device=x.device)
@@ -437,7 +512,7 @@ class _LayerNormResidual(torch.autograd.Function):
         weight, bias = ctx.params
         rows, D = x2.shape
         if dy is None:
-            return dres, None, None, None, None
+            return dres, None, None, None, None, None
         dy2 = dy.reshape(rows, D)
         if dy2.dtype != BF16:
             dy2 = dy2.to(BF16)
@@ -447,20 +522,16 @@ class _LayerNormResidual(torch.autograd.Function):
             dr = dres.reshape(rows, D)
             if dr.dtype != torch.float32 or not dr.is_contiguous():
                 dr = dr.float().contiguous()
-        dx = torch.empty((rows, D), dtype=torch.float32, device=dy.device)
-        call("b200_layernorm_bwd", dy2.data_ptr(), x2.data_ptr(), weight.data_ptr(), mean.data_ptr(),
-             rstd.data_ptr(), ptr(dr), dx.data_ptr(), None, grad_of(weight).data_ptr(),
-             grad_of(bias).data_ptr(), rows, D, *[t.data_ptr() for t in colsum_scratch(dy.device)], stream())
-        _notify(weight, bias)
+        dx = _ln_backward(ctx, dy2, x2, mean, rstd, dr)
         dx = dx.view(dy.shape)
         if ctx.in_dtype != torch.float32:
             dx = dx.to(ctx.in_dtype)
-        return dx, None, None, None, None
+        return dx, None, None, None, None, None
 
 
 def layernorm_residual(x, weight, bias, eps):
     """-> (x for the residual branch, LayerNorm(x) as bf16)"""
-    return _LayerNormResidual.apply(x, weight, bias, eps, (weight, bias))
+    return _LayerNormResidual.apply(x, weight, bias, eps, (weight, bias), _producer_of(x))
 
 
 # ----------------------------------------------------------------------------------------

@@ -261,6 +261,8 @@ class FSDPStrategy:
                     p._b200_ag = (self, g, 2 * o, 2 * p.numel())
                     p._b200_ag_version = 0
         native.grad_ready_hooks.append(self._on_grad_ready)
+        # a unit's gradient buffer is only valid during that unit's backward: LayerNorm hand-offs stay inside a block
+        native.set_fuse_scope("block")
         self.comm_stream = torch.cuda.Stream(dev) if cuda else None
         self.version = 1
         for g in self.groups:
@@ -564,6 +566,7 @@ class FSDPStrategy:
         """Detach from the process-wide gradient-ready hook list (benchmarks run several strategies in one process)."""
         if self._on_grad_ready in native.grad_ready_hooks:
             native.grad_ready_hooks.remove(self._on_grad_ready)
+            native.set_fuse_scope("all")
         self._graphed = None
 
     # ------------------------------------------------------------------------------

@@ -36,6 +36,14 @@ int b200_layernorm_fwd(const float* x, const float* gamma, const float* beta, vo
 int b200_layernorm_bwd(const void* dy_bf16, const float* x, const float* gamma, const float* mean,
                        const float* rstd, const float* dres, float* dx, void* dx_bf16, float* dgamma,
                        float* dbeta, int rows, int dim, float* scratch, int* counter, void* stream);
+/* ... and, with fuse != 0, the first step of the backward of the Linear / MLP whose residual epilogue produced x
+ * (models/gpt.py:33-41,105-123): the bf16 output becomes dz = dx * act'(mask_src) (mask_src NULL: plain copy; act 1:
+ * mask_src is the ReLU output, 2 / 3: the GELU pre-activation) and dbias_z += column sums of dz (NULL: no bias).
+ * scratch: [16][3*dim] floats. */
+int b200_layernorm_bwd_fused(const void* dy_bf16, const float* x, const float* gamma, const float* mean,
+                             const float* rstd, const float* dres, float* dx, void* dz_bf16, float* dgamma,
+                             float* dbeta, int rows, int dim, float* scratch, int* counter, const void* mask_src,
+                             int act, float* dbias_z, int fuse, void* stream);
 
 /* fused AdamW over a flat arena; hyper = {lr, step, skipped, -} in device memory  (main-single.py:42,99-101).
  * Non-finite gradient elements are skipped one by one (parameter and moments keep their values) and counted in

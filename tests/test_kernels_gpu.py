@@ -630,3 +630,59 @@ def test_attention_backward_kernels_agree(B, T, H, D, masked):
         got.append(dqkv.float()[valid])
     assert torch.allclose(got[0], got[1], atol=3e-2, rtol=3e-2) and torch.allclose(got[1], got[2], atol=3e-2, rtol=3e-2)
     assert _dev_err() == 0
+
+
+@pytest.mark.parametrize("dim,heads,act", [(256, 8, "relu"), (512, 8, "gelu"), (192, 6, "relu")])
+def test_layernorm_backward_handoff_matches_separate_passes(monkeypatch, dim, heads, act):
+    """The LayerNorm backward that also writes the producer layer's dz / bias gradient (b200_layernorm_bwd_fused)
+    gives the same gradients as the separate relu_bwd / act_bwd passes, and launches fewer kernels."""
+    from distributed_pytorch_cookbook_b200 import TransformerDecoderLM
+    from distributed_pytorch_cookbook_b200.ops import native
+    dev = torch.device("cuda")
+    vocab, B, T = 1000, 3, 127
+    torch.manual_seed(0)
+    model = TransformerDecoderLM(dim=dim, head_dim=32, heads=heads, num_layers=2, vocab_size=vocab,
+                                 max_position_embeddings=T).to(dev)
+    if act == "gelu":
+        for layer in model.decoder.layers:
+            layer.fc.activation = F.gelu
+    ids = torch.randint(0, vocab, (B, T), device=dev)
+    pos = torch.arange(T, device=dev).unsqueeze(0).repeat(B, 1)
+    tgt = torch.randint(0, vocab, (B, T), device=dev)
+
+    def run(fuse):
+        monkeypatch.setattr(native, "_LN_FUSE", fuse)
+        model.zero_grad(set_to_none=True)
+        n0 = _lib.launch_count()
+        with torch.autocast("cuda", dtype=BF16):
+            loss, _, _ = model.loss(ids, pos, tgt)
+        loss.backward()
+        torch.cuda.synchronize()
+        return float(loss), {n: p.grad.clone() for n, p in model.named_parameters()}, _lib.launch_count() - n0
+
+    run(True)                                # one-time launches (LM-head state, first-call checks) stay out of the count
+    l1, g1, k1 = run(True)
+    l0, g0, k0 = run(False)
+    assert abs(l1 - l0) < 1e-5               # same forward (its atomics make the last digit vary)
+    assert k1 == k0 - 4, (k1, k0)            # 2 layers x (out-projection cast + MLP activation backward)
+    for n in g0:
+        assert _rel(g1[n], g0[n]) < 2e-3, (n, _rel(g1[n], g0[n]))
+
+
+def test_layernorm_backward_handoff_detects_a_second_consumer():
+    """If the residual stream feeds something besides the LayerNorm, the producer's incoming gradient is a sum the
+    LayerNorm never saw: the hand-off must fail loudly instead of using the stale dz."""
+    from distributed_pytorch_cookbook_b200 import ops
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    D = 256
+    lin = torch.nn.Linear(D, D).to(dev)
+    ln = torch.nn.LayerNorm(D).to(dev)
+    x = torch.randn(64, D, device=dev, requires_grad=True)
+    res = torch.randn(64, D, device=dev)
+    with torch.autocast("cuda", dtype=BF16):
+        y = ops.linear(x.to(BF16), lin.weight, lin.bias, residual=res, out_fp32=True)
+        _, h = ops.layernorm_residual(y, ln.weight, ln.bias, ln.eps)
+        loss = h.float().sum() + y.sum()                 # second consumer of y
+    with pytest.raises(RuntimeError, match="second consumer"):
+        loss.backward()
