@@ -641,7 +641,9 @@ attn_fwd_ws_kernel(const __grid_constant__ CUtensorMap tmQKV, const AttnParams p
 template <int D>
 __global__ void __launch_bounds__(256)
 attn_delta_kernel(const bf16* __restrict__ out, const bf16* __restrict__ dout, float* __restrict__ delta,
-                  int B, int T, int H) {
+                  int B, int T, int H, float* __restrict__ dq_zero = nullptr) {
+  // dq_zero (optional): the fp32 dQ accumulator [B, T, H*D] the backward kernel reduces into - cleared here instead
+  // of by a separate memset launch
   const int64_t total = static_cast<int64_t>(B) * T * H;
   for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
@@ -663,6 +665,13 @@ attn_delta_kernel(const bf16* __restrict__ out, const bf16* __restrict__ dout, f
       }
     }
     delta[(static_cast<int64_t>(b) * H + h) * T + t] = s;
+  }
+  if (dq_zero != nullptr) {   // flat, fully coalesced 16-byte stores
+    float4* z = reinterpret_cast<float4*>(dq_zero);
+    const int64_t nz = total * (D / 4);
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < nz;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x)
+      z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
 }
 
@@ -1577,12 +1586,11 @@ int bwd_launch(const AttnParams& p, cudaStream_t st, int mode) {
     B200_LAUNCH_CHECK();
     return 0;
   }
-  B200_CHECK_CUDA(cudaMemsetAsync(p.dq_acc, 0, rows * HD * sizeof(float), st));
-  {
+  {   // delta = rowsum(dO * O), and the dQ accumulator cleared in the same pass
     const int64_t total = rows * p.H;
     int grid = static_cast<int>((total + 255) / 256);
     if (grid > b200_num_sms() * 16) grid = b200_num_sms() * 16;
-    attn_delta_kernel<D><<<grid, 256, 0, st>>>(p.out, p.dout, p.delta, p.B, p.T, p.H);
+    attn_delta_kernel<D><<<grid, 256, 0, st>>>(p.out, p.dout, p.delta, p.B, p.T, p.H, p.dq_acc);
     B200_LAUNCH_CHECK();
   }
   if constexpr (D >= 64) if (ws) {

@@ -166,7 +166,7 @@ layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
 // epilogue added the residual, reference models/gpt.py:33-41,105-123): dz = dx * act'(mask_src) as bf16 (the operand
 // of that layer's dgrad / wgrad GEMMs) and dbias_z += column sums of dz, so no separate pass re-reads dx.
 template <int NV, int R, bool FUSE = false>
-__global__ void __launch_bounds__(256, 2)   // <= 128 registers: two blocks (16 warps) per SM keep twice the rows in flight
+__global__ void __launch_bounds__(256, R == 1 ? 3 : 2)   // <= 128 (R = 1: 80) registers: 16 (24) warps per SM
 layernorm_bwd_small_kernel(const bf16* __restrict__ dy, const float* __restrict__ x,
                            const float* __restrict__ gamma, const float* __restrict__ mean_in,
                            const float* __restrict__ rstd_in, const float* __restrict__ dres,
@@ -1052,23 +1052,27 @@ int b200_layernorm_bwd_fused(const void* dy, const float* x, const float* gamma,
                                                       dgamma, dbeta, rows, dim, scratch, counter);  \
   } while (0)
   if (dim <= 256) {
-    int g = b200_num_sms() * 2;
+    static const int rows_per_iter0 = []() { const char* e = getenv("B200GPT_LN_ROWS"); return e ? atoi(e) : 1; }();
+    int g = b200_num_sms() * (rows_per_iter0 == 1 && dim > 128 ? 3 : 2);
     const int mg = ceil_div(rows, 8 * 4);
     if (g > mg) g = mg;
     if (g < 1) g = 1;
-    // rows a warp keeps in flight per iteration for 129..256 columns (B200GPT_LN_ROWS = 2 / 3 / 4)
-    // (measured in the default training step: 2 rows 4.24 ms, 3 rows 4.27 ms, 4 rows - which spills - 4.36 ms)
-    static const int rows_per_iter = []() { const char* e = getenv("B200GPT_LN_ROWS"); return e ? atoi(e) : 2; }();
+    // rows a warp keeps in flight per iteration for 129..256 columns (B200GPT_LN_ROWS = 1 / 2 / 3 / 4)
+    // (measured in the default training step: 1 row - 80 registers, 24 warps per SM - 4.19 ms, 2 rows 4.22 ms,
+    // 3 rows 4.27 ms, 4 rows - which spills - 4.36 ms)
+    static const int rows_per_iter = []() { const char* e = getenv("B200GPT_LN_ROWS"); return e ? atoi(e) : 1; }();
 #define LN_SMALL(NV, R, F)                                                                                          \
   layernorm_bwd_small_kernel<NV, R, F><<<g, 256, smem, st>>>(dyb, x, gamma, mean, rstd, dres, dx, dxb, dgamma, dbeta, \
                                                              rows, dim, scratch, counter, msk, act, dbias_z)
     if (fuse) {
       if (dim <= 128) LN_SMALL(1, 4, true);
+      else if (rows_per_iter == 1) LN_SMALL(2, 1, true);
       else if (rows_per_iter == 2) LN_SMALL(2, 2, true);
       else if (rows_per_iter == 3) LN_SMALL(2, 3, true);
       else LN_SMALL(2, 4, true);
     } else {
       if (dim <= 128) LN_SMALL(1, 4, false);
+      else if (rows_per_iter == 1) LN_SMALL(2, 1, false);
       else if (rows_per_iter == 2) LN_SMALL(2, 2, false);
       else if (rows_per_iter == 3) LN_SMALL(2, 3, false);
       else LN_SMALL(2, 4, false);

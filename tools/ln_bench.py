@@ -1,7 +1,7 @@
 """Time the LayerNorm backward kernels (CUDA events, 1 GPU): plain, and with the producer hand-off
 (dz = dx * relu'(mask) as bf16 + bias-gradient column sums, b200_layernorm_bwd_fused).
 
-    python tools/ln_bench.py [--rows 16320] [--dim 256]        # B200GPT_LN_ROWS=2|3|4 picks the rows per warp iteration
+    python tools/ln_bench.py [--rows 16320] [--dim 256]        # B200GPT_LN_ROWS=1|2|3|4 picks the rows per warp iteration
 
 Four rotating buffer sets (x, dy, dres, dx, dz, mask: ~75 MB each at the default shape) keep the working set
 larger than L2.  For comparison the separate pass the hand-off removes (b200_act_bwd on the fp32 dx) is timed too.
@@ -60,7 +60,7 @@ def main():
         ts = sorted(ev[i].elapsed_time(ev[i + 1]) * 1e3 for i in range(a.iters))
         return round(ts[len(ts) // 2], 2)
 
-    res = {"rows": R, "dim": D, "rows_per_iter": os.environ.get("B200GPT_LN_ROWS", "2"),
+    res = {"rows": R, "dim": D, "rows_per_iter": os.environ.get("B200GPT_LN_ROWS", "1"),
            "ln_bwd_us": timed(lambda s: ln(s, False, False)),
            "ln_bwd_handoff_cast_us": timed(lambda s: ln(s, True, False)),
            "ln_bwd_handoff_relu_mask_us": timed(lambda s: ln(s, True, True)),
