@@ -85,6 +85,27 @@ struct GemmParams {
   float* tgt_val;
 };
 
+// Grouped launch (small weight-gradient GEMMs of one transformer block): up to MAX_GROUP independent problems with
+// the same operand majors, epilogue and K split share one persistent grid; a tile index selects its problem.
+constexpr int MAX_GROUP = 4;
+struct GroupDesc {
+  int tile_end;                    // exclusive prefix sum of tiles (m tiles x n tiles x k splits)
+  int M, N;
+  int num_m_tiles, num_n_tiles;
+  int k_splits, kb_total, kb_per_split;
+};
+struct alignas(64) GroupParams {
+  CUtensorMap a[MAX_GROUP], b[MAX_GROUP], c[MAX_GROUP];
+  GroupDesc g[MAX_GROUP];
+  int n, total_tiles;
+};
+struct NoGroup { int unused; };
+template <bool GRP> using GroupArg = std::conditional_t<GRP, GroupParams, NoGroup>;
+struct TileMap {
+  int m0, n0, kb0, kb1, M, N;      // m0 / n0: first row / column of the (CTA pair's) tile
+  const CUtensorMap *a, *b, *c;
+};
+
 enum : int { ERR_GEMM_PRODUCER = 101, ERR_GEMM_MMA = 102, ERR_GEMM_EPILOGUE = 103, ERR_GEMM_SMEM_ALIGN = 104,
              ERR_GEMM_AG_WAIT = 105 };
 
@@ -137,10 +158,11 @@ enum : int { EPI_BIAS = 1, EPI_RELU = 2, EPI_AUX = 4, EPI_MASK = 8, EPI_RES = 16
 //         stages its own 128 rows of A and HALF of the B tile, the leader's single thread issues
 //         M = 256 MMAs that read both CTAs' shared memory and write both CTAs' TMEM.  Per FLOP a CTA
 //         pulls 1/3 less operand data out of L2, which is what bounds the short-K GEMMs here.
-template <int BN, int STAGES, int MIN_CTAS, int EPI, int CG, bool AG = false>
+template <int BN, int STAGES, int MIN_CTAS, int EPI, int CG, bool AG = false, bool GRP = false>
 __global__ void __launch_bounds__(gemm_threads<CG, AG>(), MIN_CTAS)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
+                    const __grid_constant__ CUtensorMap tmC, const GemmParams p,
+                    const __grid_constant__ GroupArg<GRP> gp) {
   constexpr int B_ROWS = BN / CG;                 // rows of the B tile staged by this CTA
   constexpr int B_STAGE_BYTES = B_ROWS * BK * 2;
   constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
@@ -218,7 +240,36 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   asm volatile("griddepcontrol.wait;" ::: "memory");
 
-  const int total_tiles = p.num_m_tiles * p.num_n_tiles * p.k_splits;
+  int total_tiles = p.num_m_tiles * p.num_n_tiles * p.k_splits;
+  if constexpr (GRP) total_tiles = gp.total_tiles;
+  // tile index -> problem, tile origin (of the CTA pair), k-block range
+  auto map_tile = [&](int tile) -> TileMap {
+    TileMap t;
+    if constexpr (GRP) {
+      int g = 0;
+      while (g + 1 < gp.n && tile >= gp.g[g].tile_end) ++g;
+      const GroupDesc& d = gp.g[g];
+      const int local = tile - (g > 0 ? gp.g[g - 1].tile_end : 0);
+      const int split = local % d.k_splits;
+      const int t2 = local / d.k_splits;
+      t.m0 = (t2 % d.num_m_tiles) * (BM * CG);
+      t.n0 = (t2 / d.num_m_tiles) * BN;
+      t.kb0 = split * d.kb_per_split;
+      t.kb1 = min(t.kb0 + d.kb_per_split, d.kb_total);
+      t.M = d.M; t.N = d.N;
+      t.a = &gp.a[g]; t.b = &gp.b[g]; t.c = &gp.c[g];
+    } else {
+      const int split = tile % p.k_splits;
+      const int t2 = tile / p.k_splits;
+      t.m0 = (p.n_fastest ? t2 / p.num_n_tiles : t2 % p.num_m_tiles) * (BM * CG);
+      t.n0 = (p.n_fastest ? t2 % p.num_n_tiles : t2 / p.num_m_tiles) * BN;
+      t.kb0 = split * p.kb_per_split;
+      t.kb1 = min(t.kb0 + p.kb_per_split, p.kb_total);
+      t.M = p.M; t.N = p.N;
+      t.a = &tmA; t.b = &tmB; t.c = &tmC;
+    }
+    return t;
+  };
 
   if (warp_idx == 0) {
     // ===================== TMA producer =====================
@@ -228,13 +279,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       int ag_tile_seen = -1;
       long long w_empty = 0;   // bring-up: cycles this producer spent waiting for a free smem slot
       for (int tile = unit; tile < total_tiles && ok; tile += num_units) {
-        const int split = tile % p.k_splits;
-        const int t2 = tile / p.k_splits;
-        const int m0 = (p.n_fastest ? t2 / p.num_n_tiles : t2 % p.num_m_tiles) * (BM * CG) + cta_rank * BM;
-        const int n0 = (p.n_fastest ? t2 % p.num_n_tiles : t2 / p.num_m_tiles) * BN;
+        const TileMap tm = map_tile(tile);
+        const int m0 = tm.m0 + cta_rank * BM;
+        const int n0 = tm.n0;
         const int nb0 = n0 + cta_rank * B_ROWS;   // first B row staged by this CTA
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+        const int kb0 = tm.kb0, kb1 = tm.kb1;
         for (int kb = kb0; kb < kb1; ++kb) {
           const long long tw0 = TRACE_ON(p) ? clock64() : 0;
           if (!mbar_wait(empty_bar + 8 * stage, phase ^ 1, abort_flag, p.err_word, ERR_GEMM_PRODUCER)) {
@@ -253,10 +302,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             else tma_load_2d(dst, tm, fb, c0, c1);
           };
           if (!p.a_mn) {
-            load(a_dst, &tmA, k0, m0);
+            load(a_dst, tm.a, k0, m0);
           } else {
 #pragma unroll
-            for (int j = 0; j < BM / 64; ++j) load(a_dst + j * 8192, &tmA, m0 + 64 * j, k0);
+            for (int j = 0; j < BM / 64; ++j) load(a_dst + j * 8192, tm.a, m0 + 64 * j, k0);
           }
           if ((CG == 1 || AG) && p.ag_bytes > 0 && ag_tile_seen != n0) {
             // the gather warps of all CTAs pull W from the peers tile by tile: wait for this n-tile
@@ -279,10 +328,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             ag_tile_seen = n0;
           }
           if (!p.b_mn) {
-            load(b_dst, &tmB, k0, nb0);
+            load(b_dst, tm.b, k0, nb0);
           } else {
 #pragma unroll
-            for (int j = 0; j < B_ROWS / 64; ++j) load(b_dst + j * 8192, &tmB, nb0 + 64 * j, k0);
+            for (int j = 0; j < B_ROWS / 64; ++j) load(b_dst + j * 8192, tm.b, nb0 + 64 * j, k0);
           }
           if (kb == kb0 && tile == unit) DBG_STAMP(2);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -299,9 +348,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     bool ok = true;
     long long w_full = 0, w_tempty = 0;   // bring-up: cycles waiting for operands / for a drained accumulator
     for (int tile = unit; tile < total_tiles && ok && (CG == 1 || cta_rank == 0); tile += num_units, ++lt) {
-      const int split = tile % p.k_splits;
-      const int kb0 = split * p.kb_per_split;
-      const int kb1 = min(kb0 + p.kb_per_split, p.kb_total);
+      const TileMap tm = map_tile(tile);
+      const int kb0 = tm.kb0, kb1 = tm.kb1;
       const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
       long long tw0 = TRACE_ON(p) ? clock64() : 0;
       if (!mbar_wait(tempty_bar + 8 * as, aph ^ 1, abort_flag, p.err_word, ERR_GEMM_MMA)) break;
@@ -431,12 +479,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     int lt = 0;
     long long w_tfull = 0, w_stage = 0;   // bring-up: cycles waiting for the MMAs / for a free staging buffer
     for (int tile = unit; tile < total_tiles; tile += num_units, ++lt) {
-      const int t2 = tile / p.k_splits;
-      const int m0 = (p.n_fastest ? t2 / p.num_n_tiles : t2 % p.num_m_tiles) * (BM * CG) + cta_rank * BM;
-      const int n0 = (p.n_fastest ? t2 % p.num_n_tiles : t2 / p.num_m_tiles) * BN + cbase * 32;  // this warp's first column
+      const TileMap tm = map_tile(tile);
+      const int m0 = tm.m0 + cta_rank * BM;
+      const int n0 = tm.n0 + cbase * 32;  // this warp's first column
       const uint32_t as = lt & 1, aph = (lt >> 1) & 1;
       const int row = m0 + q * 32 + lane;
-      const bool row_ok = row < p.M;
+      const bool row_ok = row < tm.M;
       const size_t row_c = static_cast<size_t>(row_ok ? row : 0);
       [[maybe_unused]] const float* res_row = E_RES ? p.residual + row_c * p.ldr : nullptr;
       [[maybe_unused]] const bf16* msk_row = E_MASK ? p.mask_src + row_c * p.ldc : nullptr;
@@ -695,9 +743,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           __syncwarp();
           if (lane == 0) {
             const int sc0 = E_F32 ? col0 : col0 - 32;
-            if (sc0 < p.N && m0 + q * 32 < p.M) {
-              if constexpr (E_ACC) tma_reduce_add_2d(&tmC, stage_buf, sc0, m0 + q * 32);
-              else tma_store_2d(&tmC, stage_buf, sc0, m0 + q * 32);
+            if (sc0 < tm.N && m0 + q * 32 < tm.M) {
+              if constexpr (E_ACC) tma_reduce_add_2d(tm.c, stage_buf, sc0, m0 + q * 32);
+              else tma_store_2d(tm.c, stage_buf, sc0, m0 + q * 32);
             }
             tma_store_commit();
           }
@@ -842,9 +890,9 @@ struct GemmOverrides {
   int no_tma_store;
 };
 
-template <int BN, int STAGES, int MIN_CTAS, int EPI, int CG, bool AG = false>
+template <int BN, int STAGES, int MIN_CTAS, int EPI, int CG, bool AG = false, bool GRP = false>
 int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p,
-           int grid, cudaStream_t stream) {
+           int grid, cudaStream_t stream, const GroupArg<GRP>& gp = GroupArg<GRP>{}) {
   constexpr int smem = STAGES * (A_STAGE_BYTES + (BN / CG) * BK * 2) + staging_bufs<BN, CG, STAGES, AG>() * staging_bytes<CG>() +
                        ag_bounce_bytes<CG, AG>() + 16 * STAGES + 64 + 16;
   static_assert(smem <= 227 * 1024, "gemm: shared memory budget exceeded");
@@ -852,9 +900,9 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tm
   int dev = 0;
   cudaGetDevice(&dev);
   if (!configured[dev & 63]) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG, AG>,
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG, AG, GRP>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG, AG>,
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG, AG, GRP>,
                                          cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     configured[dev & 63] = true;
   }
@@ -879,7 +927,7 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tm
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG, AG>, tmA, tmB, tmC, p));
+  B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<BN, STAGES, MIN_CTAS, EPI, CG, AG, GRP>, tmA, tmB, tmC, p, gp));
   return 0;
 }
 
@@ -1177,6 +1225,69 @@ int b200_gemm_dact_colsum_bf16(const void* A, const void* B, void* C, int M, int
 int b200_gemm_set_debug_buffer(void* buf) {
   g_gemm_dbg = reinterpret_cast<long long*>(buf);
   return 0;
+}
+
+// Grouped weight gradients: C_i[M_i, N_i] (fp32) += A_i^T . B_i for up to 4 problems in ONE launch, A_i stored
+// [K, M_i] and B_i stored [K, N_i] (both MN-major: dZ and X of a Linear layer as they sit in memory, K = tokens).
+// The problems share one persistent grid of CTA pairs and one K split, so the fixed cost of a launch (cluster
+// scheduling, tensor-memory allocation, pipeline fill, the reduce-add tail) is paid once per transformer block
+// instead of once per weight.  Returns -100 when CTA pairs are switched off (the caller launches one by one).
+int b200_gemm_wgrad_group(int n, const void* const* A, const void* const* B, void* const* C, const int* M,
+                          const int* N, int K, const int* lda, const int* ldb, const int* ldc, void* stream) {
+  B200_REQUIRE(n >= 1 && n <= MAX_GROUP && K > 0, "gemm_wgrad_group: 1..%d problems (got %d)", MAX_GROUP, n);
+  if (!g_gemm_2sm) return -100;
+  constexpr int CG = 2, BN = 256;
+  GroupParams gp{};
+  GemmParams p{};
+  const int kb_total = ceil_div(K, BK);
+  int base_tiles = 0;
+  for (int i = 0; i < n; ++i) {
+    B200_REQUIRE(M[i] > 0 && N[i] > 0, "gemm_wgrad_group: empty problem %d", i);
+    base_tiles += ceil_div(M[i], BM * CG) * ceil_div(N[i], BN);
+  }
+  const int slots = b200_num_sms() / CG;
+  int splits = slots / base_tiles;
+  const int max_splits = kb_total / 4 > 0 ? kb_total / 4 : 1;
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  const int kb_per_split = ceil_div(kb_total, splits);
+  const int k_splits = ceil_div(kb_total, kb_per_split);
+  int end = 0;
+  for (int i = 0; i < n; ++i) {
+    B200_REQUIRE((reinterpret_cast<uintptr_t>(C[i]) & 15) == 0 && (static_cast<int64_t>(ldc[i]) * 4) % 16 == 0,
+                 "gemm_wgrad_group: output %d must be 16-byte aligned with a 16-byte multiple row stride", i);
+    GroupDesc& d = gp.g[i];
+    d.M = M[i]; d.N = N[i];
+    d.num_m_tiles = ceil_div(M[i], BM * CG);
+    d.num_n_tiles = ceil_div(N[i], BN);
+    d.k_splits = k_splits; d.kb_total = kb_total; d.kb_per_split = kb_per_split;
+    end += d.num_m_tiles * d.num_n_tiles * k_splits;
+    d.tile_end = end;
+    int rc = get_tmap(&gp.a[i], A[i], M[i], K, lda[i], 64, BK);
+    if (rc != 0) return rc;
+    rc = get_tmap(&gp.b[i], B[i], N[i], K, ldb[i], 64, BK);
+    if (rc != 0) return rc;
+    rc = get_tmap(&gp.c[i], C[i], N[i], M[i], ldc[i], 32, 32, 4);
+    if (rc != 0) return rc;
+  }
+  gp.n = n; gp.total_tiles = end;
+  p.M = M[0]; p.N = N[0]; p.K = K; p.ldc = ldc[0];
+  p.num_m_tiles = gp.g[0].num_m_tiles; p.num_n_tiles = gp.g[0].num_n_tiles;
+  p.kb_total = kb_total; p.kb_per_split = kb_per_split; p.k_splits = k_splits;
+  p.idesc = umma_idesc_bf16(BM * CG, BN, 1, 1);
+  p.a_desc_base = umma_smem_desc_base(8192, 1024);
+  p.b_desc_base = umma_smem_desc_base(8192, 1024);
+  p.a_kstep = 2048; p.b_kstep = 2048;
+  p.a_mn = 1; p.b_mn = 1;
+  p.C = C[0];
+  p.out_fp32 = 1; p.accumulate = 1;
+  p.err_word = b200_error_word();
+  p.dbg = g_gemm_dbg;
+  p.tma_store = 1;
+  B200_REQUIRE(p.err_word != nullptr, "gemm: no CUDA device");
+  const int grid = (end < slots ? end : slots) * CG;
+  return launch<256, 6, 1, EPI_F32 | EPI_ACC, 2, false, true>(gp.a[0], gp.b[0], gp.c[0], p, grid,
+                                                              static_cast<cudaStream_t>(stream), gp);
 }
 
 // Bring-up / regression entry: same GEMM with the UMMA descriptor fields overridable, so one GPU

@@ -48,6 +48,7 @@ _SIGS = {
     "b200_gemm_rowscale_bf16": [P, P, P, I, I, I, I, I, I, I, P, I, P],
     "b200_gemm_bf16": [P, P, P, I, I, I, I, I, I, I, I, P, P, I, I, I, I, P, P, I, P],
     "b200_gemm_debug": [P, P, P] + [I] * 16 + [P],
+    "b200_gemm_wgrad_group": [I, P, P, P, P, P, I, P, P, P, P],
     "b200_gemm_mask_colsum_bf16": [P, P, P, I, I, I, I, I, I, I, P, P, I, P],
     "b200_attn_fwd": [P, P, P, I, I, I, I, Fl, P, P],
     "b200_attn_fwd_select": [P, P, P, I, I, I, I, Fl, P, I, P],

@@ -148,6 +148,66 @@ def fused_gather_args(weights):
 
 # ----------------------------------------------------------------------------------------
 # ----------------------------------------------------------------------------------------
+# Grouped weight gradients.  A small dW GEMM (a few output tiles, K = tokens) costs ~13 us however little it computes:
+# launch, tensor-memory allocation, pipeline fill and the split-K reduce-add tail dominate.  The dW GEMMs of one
+# transformer block are therefore queued and launched together (``b200_gemm_wgrad_group``: one persistent grid, one
+# K split).  The queue is flushed when it holds 4 problems, when the LayerNorm at a block's entry runs its backward
+# (so under FSDP a unit's gradients are complete inside that unit's backward), and by an autograd-engine callback at
+# the end of every backward pass; the gradient-ready notifications of the queued weights are issued at the flush.
+_WGRAD_GROUP = (_os.environ.get("B200GPT_WGRAD_GROUP", "1") != "0" and _os.environ.get("B200GPT_GEMM_2SM", "1") != "0")
+_WGRAD_MAX_TILES = 16          # defer only GEMMs that leave most of the GPU idle on their own
+_wgrad_queue: list = []        # (dz, x, gw, n_out, k_in, tokens, lda, params)
+_wgrad_cb_armed = [False]
+
+
+def flush_wgrads() -> None:
+    q = list(_wgrad_queue)
+    _wgrad_queue.clear()
+    if not q:
+        return
+    if len(q) == 1:
+        dz, x, gw, n_out, k_in, tok, lda, params = q[0]
+        gemm(dz, x, gw, n_out, k_in, tok, a_mn_major=True, b_mn_major=True, accumulate=True, lda=lda)
+    else:
+        n = len(q)
+        vp, ci = _ctypes.c_void_p, _ctypes.c_int
+        arr = lambda t, vals: _ctypes.cast((t * n)(*vals), vp)   # noqa: E731
+        call("b200_gemm_wgrad_group", n, arr(vp, [e[0].data_ptr() for e in q]), arr(vp, [e[1].data_ptr() for e in q]),
+             arr(vp, [e[2].data_ptr() for e in q]), arr(ci, [e[3] for e in q]), arr(ci, [e[4] for e in q]), q[0][5],
+             arr(ci, [e[6] for e in q]), arr(ci, [e[1].stride(0) for e in q]), arr(ci, [e[2].stride(0) for e in q]),
+             stream())
+    for e in q:
+        _notify(*e[7])
+
+
+def _flush_wgrads_at_end() -> None:
+    _wgrad_cb_armed[0] = False
+    flush_wgrads()
+
+
+def wgrad(dz: torch.Tensor, x: torch.Tensor, gw: torch.Tensor, n_out: int, k_in: int, tokens: int, params, lda=None):
+    """gw[n_out, k_in] (fp32) += dz^T x, then ``_notify(*params)`` - deferred and grouped when the GEMM is small."""
+    lda = lda if lda is not None else dz.stride(0)
+    tiles = ((n_out + 255) // 256) * ((k_in + 255) // 256)
+    if not _WGRAD_GROUP or tiles > _WGRAD_MAX_TILES or n_out <= 128 or gw.stride(0) % 4 != 0 or gw.data_ptr() % 16 != 0:
+        gemm(dz, x, gw, n_out, k_in, tokens, a_mn_major=True, b_mn_major=True, accumulate=True, lda=lda)
+        _notify(*params)
+        return
+    if _wgrad_queue and _wgrad_queue[0][5] != tokens:
+        flush_wgrads()
+    _wgrad_queue.append((dz, x, gw, n_out, k_in, tokens, lda, tuple(params)))
+    if not _wgrad_cb_armed[0]:
+        try:   # runs when the current backward pass is over, whoever started it
+            torch.autograd.Variable._execution_engine.queue_callback(_flush_wgrads_at_end)
+            _wgrad_cb_armed[0] = True
+        except RuntimeError:      # not inside a backward pass: nothing would flush later
+            flush_wgrads()
+            return
+    if len(_wgrad_queue) >= 4:
+        flush_wgrads()
+
+
+# ----------------------------------------------------------------------------------------
 # LayerNorm-backward hand-off (VERDICT r1 #8).  In a pre-LN block the residual stream x is written by the epilogue of
 # a Linear / MLP (reference models/gpt.py:119-123: ``x = x + attn(...)``, ``x = x + ff(...)``) and read by exactly one
 # node, the next LayerNorm.  That LayerNorm's backward produces dx - which is the producer's incoming gradient - so
@@ -168,15 +228,18 @@ def set_fuse_scope(scope: str) -> None:
 
 
 def _producer_of(x: torch.Tensor):
-    if not _LN_FUSE or _FUSE_SCOPE == "off" or not torch.is_grad_enabled() or x.dtype != torch.float32:
-        return None
-    node = x.grad_fn
+    """-> (autograd node of the layer that wrote x if the hand-off applies, else None;
+           True if that layer sits in the same transformer block as the LayerNorm reading x)"""
+    node = x.grad_fn if torch.is_grad_enabled() else None
     info = getattr(node, "fuse_info", None)
-    if info is None or (_FUSE_SCOPE == "block" and info[0] != "block"):
-        return None
+    mid_block = info is not None and info[0] == "block"
+    if not _LN_FUSE or _FUSE_SCOPE == "off" or info is None or x.dtype != torch.float32:
+        return None, mid_block
+    if _FUSE_SCOPE == "block" and not mid_block:
+        return None, mid_block
     if x.shape[-1] % 4 != 0 or not x.is_contiguous():
-        return None
-    return node
+        return None, mid_block
+    return node, mid_block
 
 
 def _take_handoff(ctx, dy2: torch.Tensor):
@@ -247,9 +310,9 @@ class _Linear(torch.autograd.Function):
             if ctx.in_dtype != BF16:
                 dx = dx.to(ctx.in_dtype)
         if weight.requires_grad:
-            gw = grad_of(weight)
-            gemm(dz, x2, gw, N, K, M, a_mn_major=True, b_mn_major=True, accumulate=True)  # dW += dZ^T . X
-        _notify(weight, bias)
+            wgrad(dz, x2, grad_of(weight), N, K, M, (weight, bias))                        # dW += dZ^T . X
+        else:
+            _notify(weight, bias)
         return dx, None, None, dres, None, None, None, None, None
 
 
@@ -316,12 +379,12 @@ class _MLP(torch.autograd.Function):
             dz2 = torch.empty((M, N), dtype=BF16, device=dy.device)
             call("b200_act_bwd", dy2.data_ptr(), y_act.data_ptr(), dz2.data_ptr(), grad_of(b2).data_ptr(), M, N,
                  int(dy2.dtype == torch.float32), act, sc.data_ptr(), cnt.data_ptr(), stream())
-        gemm(dz2, u, grad_of(w2), N, F1, M, a_mn_major=True, b_mn_major=True, accumulate=True)     # dW2 += dZ2^T u
+        wgrad(dz2, u, grad_of(w2), N, F1, M, (w2, b2))                                             # dW2 += dZ2^T u
         dz1 = torch.empty((M, F1), dtype=BF16, device=dy.device)
         # dZ1 = (dZ2 W2) * act'(.), with db1 += column sums of dZ1 folded into the same epilogue
         call("b200_gemm_dact_colsum_bf16", dz2.data_ptr(), w2b.data_ptr(), dz1.data_ptr(), M, F1, N, dz2.stride(0),
              w2b.stride(0), dz1.stride(0), 1, (z1 if act >= 2 else u).data_ptr(), grad_of(b1).data_ptr(), act, 0, stream())
-        gemm(dz1, x2, grad_of(w1), F1, K, M, a_mn_major=True, b_mn_major=True, accumulate=True)    # dW1 += dZ1^T x
+        wgrad(dz1, x2, grad_of(w1), F1, K, M, (w1, b1))                                            # dW1 += dZ1^T x
         dx = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty((M, K), dtype=BF16, device=dy.device)
@@ -329,7 +392,6 @@ class _MLP(torch.autograd.Function):
             dx = dx.view(*dy.shape[:-1], K)
             if ctx.in_dtype != BF16:
                 dx = dx.to(ctx.in_dtype)
-        _notify(w2, b2, w1, b1)
         return dx, None, None, None, None, (dy if ctx.has_res else None), None, None, None
 
 
@@ -400,7 +462,8 @@ class _LinearQKV(torch.autograd.Function):
         grads = [grad_of(p) for p in params]
         gp = _packed(grads)
         if gp is not None:
-            gemm(dz, x2, gp, N, K, M, a_mn_major=True, b_mn_major=True, accumulate=True)
+            wgrad(dz, x2, gp, N, K, M, params)
+            return dx, None, None, None, None
         else:
             r = 0
             for g in grads:
@@ -421,6 +484,8 @@ def _ln_backward(ctx, dy2, x2, mean, rstd, dr):
     """dx = LN'(dy) [+ dres]; with a producer hand-off also that layer's dz / bias gradient (see _producer_of)."""
     weight, bias = ctx.params
     rows, D = x2.shape
+    if not getattr(ctx, "mid_block", False):
+        flush_wgrads()            # a block's entry LayerNorm is the last node of that block's backward
     dx = torch.empty((rows, D), dtype=torch.float32, device=dy2.device)
     sc, cnt = colsum_scratch(dy2.device)
     prod = getattr(ctx, "producer", None)
@@ -443,13 +508,13 @@ def _ln_backward(ctx, dy2, x2, mean, rstd, dr):
 
 class _LayerNorm(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, eps, params, producer=None):
+    def forward(ctx, x, weight, bias, eps, params, producer=(None, False)):
         D = x.shape[-1]
         x2 = x.reshape(-1, D)
         if x2.dtype != torch.float32:
             x2 = x2.float()
         x2 = x2.contiguous()
-        ctx.producer = producer
+        ctx.producer, ctx.mid_block = producer
         rows = x2.shape[0]
         y = torch.empty((rows, D), dtype=BF16, device=x.device)
         mean = torch.empty(rows, dtype=torch.float32, device=x.device)
@@ -489,12 +554,12 @@ class _LayerNormResidual(torch.autograd.Function):
     launching a separate fp32 add over the whole residual stream."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, eps, params, producer=None):
+    def forward(ctx, x, weight, bias, eps, params, producer=(None, False)):
         D = x.shape[-1]
         x2 = x.reshape(-1, D)
         if x2.dtype != torch.float32 or not x2.is_contiguous():
             x2 = x2.float().contiguous()
-        ctx.producer = producer
+        ctx.producer, ctx.mid_block = producer
         rows = x2.shape[0]
         y = torch.empty((rows, D), dtype=BF16, device=x.device)
         mean = torch.empty(rows, dtype=torch.float32, device=x.device)

@@ -126,6 +126,11 @@ int b200_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, i
                    int ldc, int a_mn_major, int b_mn_major, const float* bias, const float* residual,
                    int ldr, int act, int out_fp32, int accumulate, void* aux_out_bf16,
                    const void* mask_src_bf16, int cfg, void* stream);
+/* Weight gradients of up to 4 Linear layers in ONE launch: C_i[M_i,N_i] (fp32) += A_i^T . B_i with A_i stored [K][M_i]
+ * and B_i stored [K][N_i] (dZ and X as they sit in memory, K = tokens; main-single.py:97 loss.backward()).  The
+ * problems share one persistent grid of CTA pairs and one split of K.  -100: CTA pairs are off, launch one by one. */
+int b200_gemm_wgrad_group(int n, const void* const* A, const void* const* B, void* const* C, const int* M,
+                          const int* N, int K, const int* lda, const int* ldb, const int* ldc, void* stream);
 /* GEMM with the FSDP all-gather of its weight fused in (pre-forward unshard of main-fsdp.py:131, folded
  * into the first consuming GEMM): the kernel pulls bytes [ag_off, ag_off+ag_bytes) of a flat, evenly
  * sharded parameter group from the owning peers' shard buffers over NVLink into full_base, then

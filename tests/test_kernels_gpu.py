@@ -686,3 +686,58 @@ def test_layernorm_backward_handoff_detects_a_second_consumer():
         loss = h.float().sum() + y.sum()                 # second consumer of y
     with pytest.raises(RuntimeError, match="second consumer"):
         loss.backward()
+
+
+@pytest.mark.parametrize("tok,shapes", [(16320, [(768, 256), (256, 256), (1024, 256), (256, 1024)]),
+                                        (1000, [(768, 256), (264, 520)]), (4096, [(296, 256), (512, 512), (256, 768)])])
+def test_grouped_weight_gradient_gemm(tok, shapes):
+    """b200_gemm_wgrad_group: several dW += dZ^T X problems in one launch vs fp32 matmuls (accumulating into a
+    non-zero gradient)."""
+    import ctypes
+    from distributed_pytorch_cookbook_b200.ops.native import call, stream
+    dev = torch.device("cuda")
+    torch.manual_seed(0)
+    dz = [torch.randn(tok, n, device=dev).to(BF16) for n, _ in shapes]
+    xs = [torch.randn(tok, k, device=dev).to(BF16) for _, k in shapes]
+    init = [torch.randn(n, k, device=dev) for n, k in shapes]
+    out = [t.clone() for t in init]
+    n = len(shapes)
+    vp, ci = ctypes.c_void_p, ctypes.c_int
+    arr = lambda t, vals: ctypes.cast((t * n)(*vals), vp)   # noqa: E731
+    call("b200_gemm_wgrad_group", n, arr(vp, [t.data_ptr() for t in dz]), arr(vp, [t.data_ptr() for t in xs]),
+         arr(vp, [t.data_ptr() for t in out]), arr(ci, [s[0] for s in shapes]), arr(ci, [s[1] for s in shapes]), tok,
+         arr(ci, [t.stride(0) for t in dz]), arr(ci, [t.stride(0) for t in xs]), arr(ci, [t.stride(0) for t in out]),
+         stream())
+    torch.cuda.synchronize()
+    for i in range(n):
+        ref = init[i] + dz[i].float().t() @ xs[i].float()
+        assert _rel(out[i], ref) < 2e-3, (i, shapes[i], _rel(out[i], ref))
+
+
+def test_grouped_weight_gradients_in_the_model_match_separate_launches(monkeypatch):
+    """Deferring and grouping the dW GEMMs of a block changes the launch count, not the gradients."""
+    from distributed_pytorch_cookbook_b200.ops import native
+    dev = torch.device("cuda")
+    model = _tiny_model(dev, vocab=1000, seq=128)
+    B, T = 8, 127
+    ids = torch.randint(0, 1000, (B, T), device=dev)
+    pos = torch.arange(T, device=dev).unsqueeze(0).repeat(B, 1)
+    tgt = torch.randint(0, 1000, (B, T), device=dev)
+
+    def run(group):
+        monkeypatch.setattr(native, "_WGRAD_GROUP", group)
+        model.zero_grad(set_to_none=True)
+        n0 = _lib.launch_count()
+        with torch.autocast("cuda", dtype=BF16):
+            loss, _, _ = model.loss(ids, pos, tgt)
+        loss.backward()
+        torch.cuda.synchronize()
+        assert not native._wgrad_queue
+        return {n: p.grad.clone() for n, p in model.named_parameters()}, _lib.launch_count() - n0
+
+    run(True)
+    g1, k1 = run(True)
+    g0, k0 = run(False)
+    assert k1 == k0 - 2 * 3, (k1, k0)            # 2 layers: four dW launches become one
+    for n in g0:
+        assert _rel(g1[n], g0[n]) < 2e-3, (n, _rel(g1[n], g0[n]))
