@@ -466,12 +466,10 @@ class _LinearQKV(torch.autograd.Function):
             return dx, None, None, None, None
         else:
             r = 0
-            for g in grads:
+            for prm, g in zip(params, grads):
                 n = g.shape[0]
-                gemm(dz[:, r:r + n], x2, g, n, K, M, a_mn_major=True, b_mn_major=True,
-                     accumulate=True, lda=dz.stride(0))
+                wgrad(dz[:, r:r + n], x2, g, n, K, M, (prm,), lda=dz.stride(0))
                 r += n
-        _notify(*params)
         return dx, None, None, None, None
 
 

@@ -738,6 +738,6 @@ def test_grouped_weight_gradients_in_the_model_match_separate_launches(monkeypat
     run(True)
     g1, k1 = run(True)
     g0, k0 = run(False)
-    assert k1 == k0 - 2 * 3, (k1, k0)            # 2 layers: four dW launches become one
+    assert k1 <= k0 - 2 * 3, (k1, k0)            # 2 layers: at least four dW launches become one
     for n in g0:
         assert _rel(g1[n], g0[n]) < 2e-3, (n, _rel(g1[n], g0[n]))
