@@ -913,7 +913,7 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tm
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
   int na = 0;
-  if (g_gemm_pdl && CG == 1) {
+  if (g_gemm_pdl) {
     attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[na].val.programmaticStreamSerializationAllowed = 1;
     ++na;

@@ -19,11 +19,13 @@ out_dir.mkdir(parents=True, exist_ok=True)
 
 # (file stem, substring(s) of the demangled name, full listing?)
 WANT = [
-    ("gemm_pair_plain", ["gemm_tcgen05_kernel<256, 6, 1, 0, 2, false>"], False),
-    ("gemm_pair_lmhead_softmax_epilogue", ["gemm_tcgen05_kernel<256, 6, 1, 256, 2, false>"], False),
-    ("gemm_pair_wgrad_reduce_add", ["gemm_tcgen05_kernel<256, 6, 1, 96, 2, false>"], False),
-    ("gemm_pair_fused_allgather", ["gemm_tcgen05_kernel<256, 5, 1, 0, 2, true>"], False),
-    ("gemm_single_fused_allgather", ["gemm_tcgen05_kernel<256, 4, 1, 0, 1, false>"], False),
+    ("gemm_pair_plain", ["gemm_tcgen05_kernel<256, 6, 1, 0, 2, false, false>"], False),
+    ("gemm_pair_lmhead_softmax_epilogue", ["gemm_tcgen05_kernel<256, 5, 1, 256, 2, false, false>"], False),
+    ("gemm_pair_wgrad_reduce_add", ["gemm_tcgen05_kernel<256, 6, 1, 96, 2, false, false>"], False),
+    ("gemm_pair_wgrad_grouped", ["gemm_tcgen05_kernel<256, 6, 1, 96, 2, false, true>"], False),
+    ("gemm_pair_fused_allgather", ["gemm_tcgen05_kernel<256, 5, 1, 0, 2, true, false>"], False),
+    ("gemm_single_fused_allgather", ["gemm_tcgen05_kernel<256, 4, 1, 0, 1, false, false>"], False),
+    ("layernorm_bwd_handoff", ["layernorm_bwd_small_kernel<2, 1, true>"], True),
     ("attn_fwd_warp_specialised_d128", ["attn_fwd_ws_kernel<128>"], False),
     ("attn_bwd_warp_specialised_d128", ["attn_bwd_ws_kernel<128>"], False),
     ("attn_fwd_per_tile_d32", ["attn_fwd_kernel<32>"], False),
