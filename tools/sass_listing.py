@@ -27,7 +27,7 @@ WANT = [
     ("gemm_single_fused_allgather", ["gemm_tcgen05_kernel<256, 4, 1, 0, 1, false, false>"], False),
     ("layernorm_bwd_handoff", ["layernorm_bwd_small_kernel<2, 1, true>"], True),
     ("attn_fwd_warp_specialised_d128", ["attn_fwd_ws_kernel<128>"], False),
-    ("attn_bwd_warp_specialised_d128", ["attn_bwd_ws_kernel<128>"], False),
+    ("attn_bwd_warp_specialised_d128", ["attn_bwd_ws_kernel<128, true>"], False),
     ("attn_fwd_per_tile_d32", ["attn_fwd_kernel<32>"], False),
     ("attn_bwd_per_tile_d32", ["attn_bwd_kernel<32>"], False),
     ("allreduce_nvls", ["allreduce_kernel<true>"], True),
