@@ -249,7 +249,7 @@ attn_fwd_kernel(const AttnParams p) {
     if (kt < 2) ADBG(4 + 6 * kt);
     const float m_new = fmaxf(m_run, m_tile * p.scale);  // scale > 0
     const float m_safe = (m_new == -INFINITY) ? 0.f : m_new;
-    const float alpha = exp2f((m_run - m_safe) * kLog2e);  // m_run = -inf -> 0
+    const float alpha = fast_exp2((m_run - m_safe) * kLog2e);  // m_run = -inf -> 0
     const float m_l2 = m_safe * kLog2e;
     // pass B: p = exp(s - m), row sum, P (bf16) back into tensor memory
     float l_tile = 0.f;
@@ -265,7 +265,7 @@ attn_fwd_kernel(const AttnParams p) {
         float pv[2];
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
-          const float e = exp2f(__uint_as_float(r[j + u]) * sl2 - m_l2);
+          const float e = fast_exp2(fmaf(__uint_as_float(r[j + u]), sl2, -m_l2));
           pv[u] = ((kb >> (j + u)) & 1u) ? e : 0.f;
         }
         // sum what the tensor core will actually see (bf16-rounded), like the reference bf16 path
@@ -795,8 +795,8 @@ attn_bwd_kernel(const AttnParams p) {
         const uint32_t kb = keep_bits(k0 + c * 32, q, diag, q_ok, p.T, mask_row);
 #pragma unroll
         for (int j = 0; j < 32; j += 2) {
-          const float e0 = exp2f(__uint_as_float(rs[j]) * sl2 - lse_l2);
-          const float e1 = exp2f(__uint_as_float(rs[j + 1]) * sl2 - lse_l2);
+          const float e0 = fast_exp2(fmaf(__uint_as_float(rs[j]), sl2, -lse_l2));
+          const float e1 = fast_exp2(fmaf(__uint_as_float(rs[j + 1]), sl2, -lse_l2));
           pkeep[cc * 16 + (j >> 1)] = pack_bf16x2(((kb >> j) & 1u) ? e0 : 0.f, ((kb >> (j + 1)) & 1u) ? e1 : 0.f);
         }
 #pragma unroll
@@ -850,7 +850,7 @@ attn_bwd_kernel(const AttnParams p) {
           float pv[2], dsv[2];
 #pragma unroll
           for (int u = 0; u < 2; ++u) {
-            const float e = exp2f(__uint_as_float(rs[j + u]) * sl2 - lse_l2);
+            const float e = fast_exp2(fmaf(__uint_as_float(rs[j + u]), sl2, -lse_l2));
             const float pr = ((kb >> (j + u)) & 1u) ? e : 0.f;
             pv[u] = pr;
             dsv[u] = pr * (__uint_as_float(rd[j + u]) - delta) * p.scale;
