@@ -112,6 +112,13 @@ def mlp(x, w1, b1, w2, b2, residual=None, activation: str = "relu"):
     return native.mlp(x, w1, b1, w2, b2, residual, activation)
 
 
+def flush_wgrads() -> None:
+    """Launch the weight-gradient GEMMs the native backward has queued (see ``native.wgrad``).  Every backward pass
+    does this by itself when it ends; only code that reads ``.grad`` in the middle of a backward pass needs it."""
+    from . import native
+    native.flush_wgrads()
+
+
 def linear_qkv(x, wq, wk, wv):
     from . import native
     return native.linear_qkv(x, wq, wk, wv)

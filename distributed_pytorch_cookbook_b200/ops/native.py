@@ -601,6 +601,8 @@ def layernorm_residual(x, weight, bias, eps):
 class _Embedding(torch.autograd.Function):
     @staticmethod
     def forward(ctx, input_ids, position_ids, tok_w, pos_w, params):
+        if _wgrad_queue:          # a backward pass that ended without its engine callback (e.g. it raised)
+            flush_wgrads()
         ids = input_ids.reshape(-1).contiguous()
         pos = position_ids.reshape(-1).contiguous()
         n, D = ids.numel(), tok_w.shape[1]
